@@ -1,0 +1,207 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY. Not part of the shipped library; the product
+// (voxel_game_b200/) never includes, links or calls this. PARITY UNPINNED: see glsl_shim.h.
+//
+// Flat C entry points over the shader restatements, for ctypes (tests/, smoke(), bench.py's
+// cpu_baseline and --impl reference legs). Build: `make -C oracle` -> oracle/liboracle.so
+// (g++ -O2 -ffp-contract=off -fopenmp).
+#include <cstring>
+#include <vector>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+#include "common.h"
+#include "compute_voxel.h"
+#include "entities.h"
+#include "raycast.h"
+#include "worldgen.h"
+
+using namespace orc;
+
+// Mirrors orc::SimData field for field (17 x 32-bit words, no padding).
+static_assert(sizeof(SimData) == 68, "SimData must be 17 packed words");
+
+static inline vec3 v3(const float* p) { return vec3(p[0], p[1], p[2]); }
+
+extern "C" {
+
+int orc_num_threads(void) {
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
+
+void orc_set_num_threads(int n) {
+#ifdef _OPENMP
+    omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
+// ---- known-answer helpers (common.glsl) ----
+void orc_pcg2d(const uint32_t* in, uint32_t* out) {
+    uvec2 r = pcg2d(uvec2(in[0], in[1]));
+    out[0] = r.x; out[1] = r.y;
+}
+void orc_pcg3d(const uint32_t* in, uint32_t* out) {
+    uvec3 r = pcg3d(uvec3(in[0], in[1], in[2]));
+    out[0] = r.x; out[1] = r.y; out[2] = r.z;
+}
+void orc_pcg4d(const int32_t* in, int32_t* out) {
+    ivec4 r = pcg4d(ivec4(in[0], in[1], in[2], in[3]));
+    out[0] = r.x; out[1] = r.y; out[2] = r.z; out[3] = r.w;
+}
+void orc_voronoise(const float* p, float u, float v, float* out) {
+    vec4 r = voronoise(v3(p), u, v);
+    out[0] = r.x; out[1] = r.y; out[2] = r.z; out[3] = r.w;
+}
+void orc_grad_noise(const float* x, float* out) {
+    vec4 r = grad_noise(v3(x));
+    out[0] = r.x; out[1] = r.y; out[2] = r.z; out[3] = r.w;
+}
+void orc_quaternion_from_arc(const float* src, const float* dst, float* out) {
+    vec4 r = quaternion_from_arc(v3(src), v3(dst));
+    out[0] = r.x; out[1] = r.y; out[2] = r.z; out[3] = r.w;
+}
+
+// ---- worldgen ----
+uint32_t orc_worldgen_voxel(int map, uint32_t seed, const uint32_t* pos) {
+    uvec3 p(pos[0], pos[1], pos[2]);
+    return map == 0 ? worldgen::open_world::get_worldgen(p) : worldgen::control::get_worldgen(p, seed);
+}
+// n positions [n][3] -> out[n]; OpenMP over positions
+void orc_worldgen_voxels(int map, uint32_t seed, const uint32_t* pos, uint64_t n, uint32_t* out) {
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int64_t i = 0; i < (int64_t)n; i++) {
+        uvec3 p(pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]);
+        out[i] = map == 0 ? worldgen::open_world::get_worldgen(p) : worldgen::control::get_worldgen(p, seed);
+    }
+}
+void orc_worldgen(uint32_t* chunks, uint32_t* voxels, const SimData* sim, const int32_t* chunk_loads, uint32_t wg_count,
+                  uint32_t* load_results, int map) {
+    Images im{chunks, voxels};
+    worldgen::dispatch(im, *sim, reinterpret_cast<const ivec4*>(chunk_loads), wg_count, load_results, map);
+}
+void orc_complete_worldgen(uint32_t* chunks, uint32_t* voxels, const SimData* sim, const int32_t* chunk_loads,
+                           const uint32_t* load_results) {
+    Images im{chunks, voxels};
+    complete_worldgen::dispatch(im, *sim, reinterpret_cast<const ivec4*>(chunk_loads), load_results);
+}
+
+// ---- voxel update / writes / unload ----
+void orc_voxel_update(uint32_t* chunks, uint32_t* voxels, const SimData* sim, int32_t* chunk_updates, uint32_t count) {
+    Images im{chunks, voxels};
+    compute_voxel::dispatch(im, *sim, reinterpret_cast<ivec4*>(chunk_updates), count);
+}
+void orc_write_voxels(uint32_t* chunks, uint32_t* voxels, const SimData* sim, const uint32_t* voxel_writes) {
+    Images im{chunks, voxels};
+    write_voxels::dispatch(im, *sim, reinterpret_cast<const uvec4*>(voxel_writes));
+}
+void orc_unload_chunks(uint32_t* chunks, const SimData* sim) {
+    Images im{chunks, nullptr};
+    unload_chunks::dispatch(im, *sim);
+}
+
+// ---- DDA rays ----
+// Layer outputs are [n][5][...]; only the first layer_count[i] layers of ray i are meaningful.
+static void store_result(const frag::RaycastResult& r, uint64_t i, float* layer_pos, float* layer_normal, uint32_t* layer_voxel,
+                         float* layer_dist, uint32_t* layer_leaving, uint32_t* layer_count, float* dist) {
+    for (uint32_t l = 0; l < 5; l++) {
+        const frag::RaycastResultLayer& L = r.layers[l];
+        for (int c = 0; c < 3; c++) {
+            layer_pos[(i * 5 + l) * 3 + c] = L.pos[c];
+            layer_normal[(i * 5 + l) * 3 + c] = L.normal[c];
+        }
+        layer_voxel[i * 5 + l] = L.voxel_data;
+        layer_dist[i * 5 + l] = L.dist;
+        layer_leaving[i * 5 + l] = L.is_leaving_medium ? 1u : 0u;
+    }
+    layer_count[i] = r.layer_count;
+    dist[i] = r.dist;
+}
+
+// frag.glsl:main ray set-up + raycast() for every pixel of a w x h viewport (row-major, i = py*w + px).
+// raster_depth: null (=> 0 everywhere) or [w*h] max_depth values.
+void orc_raycast_image(uint32_t* chunks, uint32_t* voxels, const SimData* sim, const Player* cam, uint32_t w, uint32_t h,
+                       uint32_t max_iterations, const Projectile* projectiles, const float* raster_depth, float* layer_pos,
+                       float* layer_normal, uint32_t* layer_voxel, float* layer_dist, uint32_t* layer_leaving,
+                       uint32_t* layer_count, float* dist, uint64_t* total_iters) {
+    float aspect_ratio = (float)w / (float)h;  // raytracer.rs:246
+    uint64_t iters_sum = 0;
+#pragma omp parallel for schedule(dynamic, 4) reduction(+ : iters_sum)
+    for (int64_t py = 0; py < (int64_t)h; py++) {
+        uint64_t iters = 0;
+        frag::Env e{Images{chunks, voxels}, *sim, projectiles, &iters};
+        for (uint32_t px = 0; px < w; px++) {
+            uint64_t i = (uint64_t)py * w + px;
+            vec3 ray = frag::primary_ray_dir(*cam, aspect_ratio, px, (uint32_t)py, w, h);
+            vec3 pos = cam->pos.xyz();
+            float max_depth = raster_depth ? raster_depth[i] : 0.0f;
+            frag::RaycastResult r = frag::raycast(e, pos, ray, max_iterations, true, max_depth, vec3(0.0f, 1.0f, 0.0f), 1.0f);
+            store_result(r, i, layer_pos, layer_normal, layer_voxel, layer_dist, layer_leaving, layer_count, dist);
+        }
+        iters_sum += iters;
+    }
+    if (total_iters) *total_iters = iters_sum;
+}
+
+// Arbitrary ray batch through raycast(): pos/ray are [n][3].
+void orc_raycast_batch(uint32_t* chunks, uint32_t* voxels, const SimData* sim, const float* pos, const float* ray, uint64_t n,
+                       uint32_t max_iterations, const Projectile* projectiles, float* layer_pos, float* layer_normal,
+                       uint32_t* layer_voxel, float* layer_dist, uint32_t* layer_leaving, uint32_t* layer_count, float* dist,
+                       uint64_t* total_iters) {
+    uint64_t iters_sum = 0;
+#pragma omp parallel for schedule(dynamic, 256) reduction(+ : iters_sum)
+    for (int64_t i = 0; i < (int64_t)n; i++) {
+        uint64_t iters = 0;
+        frag::Env e{Images{chunks, voxels}, *sim, projectiles, &iters};
+        frag::RaycastResult r = frag::raycast(e, v3(pos + 3 * i), v3(ray + 3 * i), max_iterations, true, 0.0f, vec3(0.0f, 1.0f, 0.0f), 1.0f);
+        store_result(r, (uint64_t)i, layer_pos, layer_normal, layer_voxel, layer_dist, layer_leaving, layer_count, dist);
+        iters_sum += iters;
+    }
+    if (total_iters) *total_iters = iters_sum;
+}
+
+// kind: 0 = single_raycast (frag.glsl:93), 1 = simple_raycast (:275), 2 = simple_raycast_w_projectiles (:161)
+// out_pos [n][3], out_normal [n][3] (kind 0 only), out_voxel [n], out_dist [n], out_light [n] (kinds 1,2)
+void orc_secondary_batch(int kind, uint32_t* chunks, uint32_t* voxels, const SimData* sim, const float* pos, const float* ray,
+                         uint64_t n, uint32_t max_iterations, const Projectile* projectiles, float* out_pos, float* out_normal,
+                         uint32_t* out_voxel, float* out_dist, float* out_light) {
+#pragma omp parallel for schedule(dynamic, 256)
+    for (int64_t i = 0; i < (int64_t)n; i++) {
+        frag::Env e{Images{chunks, voxels}, *sim, projectiles, nullptr};
+        if (kind == 0) {
+            frag::RaycastResultLayer r = frag::single_raycast(e, v3(pos + 3 * i), v3(ray + 3 * i), max_iterations);
+            for (int c = 0; c < 3; c++) { out_pos[3 * i + c] = r.pos[c]; out_normal[3 * i + c] = r.normal[c]; }
+            out_voxel[i] = r.voxel_data; out_dist[i] = r.dist; out_light[i] = 0.0f;
+        } else {
+            frag::SimpleRaycastResult r = kind == 1 ? frag::simple_raycast(e, v3(pos + 3 * i), v3(ray + 3 * i), max_iterations)
+                                                    : frag::simple_raycast_w_projectiles(e, v3(pos + 3 * i), v3(ray + 3 * i), max_iterations);
+            for (int c = 0; c < 3; c++) { out_pos[3 * i + c] = r.pos[c]; out_normal[3 * i + c] = 0.0f; }
+            out_voxel[i] = r.voxel_data; out_dist[i] = r.dist; out_light[i] = r.passthrough_light;
+        }
+    }
+}
+
+// ---- collision queries ----
+// collisions: capacity entries, zero-filled by the caller as the host does (voxel_sim_manager.rs:859-869).
+// counters (nullable): [0] collisions appended, [1] terrain samples visited, [2] LOS iterations
+// (the last two are exact only when parallel == 0).
+void orc_projectiles(uint32_t* chunks, uint32_t* voxels, const SimData* sim, Projectile* projectiles, const Player* players,
+                     Collision* collisions, uint32_t collision_capacity, int parallel, uint64_t* counters) {
+    uint32_t count = 0;
+    uint64_t samples = 0, los = 0;
+    compute_projectile::Env e{Images{chunks, voxels}, *sim, projectiles, players, collisions, &count, collision_capacity,
+                              parallel ? nullptr : &samples, parallel ? nullptr : &los};
+    compute_projectile::dispatch(e, parallel != 0);
+    if (counters) { counters[0] = count; counters[1] = samples; counters[2] = los; }
+}
+void orc_entities(uint32_t* chunks, uint32_t* voxels, const SimData* sim, Player* players) {
+    compute_entity::Env e{Images{chunks, voxels}, *sim, players};
+    compute_entity::dispatch(e);
+}
+
+}  // extern "C"
