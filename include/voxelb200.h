@@ -1,0 +1,270 @@
+/*
+ * voxelb200.h — C ABI of libvoxelb200.so: the B200-native (sm_100a CUDA) voxel hot path of
+ * Devon7925/voxel-game: chunk world generation, the Margolus-block voxel update step and DDA
+ * ray-marching / collision queries over the chunked voxel grid.
+ *
+ * The reference has no FFI; the path sits behind two Rust types. Every entry point below cites
+ * the reference method or shader it replaces (paths relative to the reference root,
+ * `src/X.rs` = client/src/X.rs, `shaders/X.glsl` = client/assets/shaders/X.glsl).
+ *
+ * Conventions
+ *  - Every function returns 0 on success or a negative vxb_status; the message is available
+ *    from vxb_last_error(). Nothing throws or aborts across the boundary (the reference
+ *    `unwrap()`s and panics, src/main.rs:76-105).
+ *  - A ctx is bound to one CUDA device and one CUDA stream. It is not thread-safe.
+ *  - Host pointers are copied before the call returns unless stated otherwise. Device pointers
+ *    returned by vxb_device_ptrs are borrowed and valid until vxb_destroy.
+ *  - There is no CPU fallback: with no CUDA device vxb_create fails with VXB_ERR_CUDA.
+ *  - Plain C types only; no torch / C++ types in any signature.
+ */
+#ifndef VOXELB200_H
+#define VOXELB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VXB_CHUNK_SIZE 16u
+#define VXB_CHUNK_VOLUME 4096u
+#define VXB_MAX_LAYERS 5u
+
+typedef enum vxb_status {
+    VXB_OK = 0,
+    VXB_ERR_INVALID = -1, /* bad argument / size beyond a stated limit */
+    VXB_ERR_CUDA = -2,    /* CUDA runtime error (no device, OOM, launch failure) */
+    VXB_ERR_STATE = -3    /* call order violated */
+} vxb_status;
+
+/* shaders/common.glsl:8-25 == src/voxel_sim_manager.rs:48-67 (112 bytes) */
+typedef struct vxb_projectile {
+    float pos[4];
+    uint32_t chunk_update_pos[4];
+    float dir[4]; /* quaternion xyzw */
+    float size[4]; /* half extents */
+    float vel;
+    float health;
+    float lifetime;
+    uint32_t owner;
+    float damage;
+    uint32_t proj_card_idx;
+    uint32_t wall_bounce;
+    uint32_t is_from_head;
+    uint32_t should_collide_with_terrain;
+    uint32_t _filler0, _filler1, _filler2;
+} vxb_projectile;
+
+/* shaders/common.glsl:27-38 == UploadPlayer, src/rollback_manager.rs:212-225 (128 bytes) */
+typedef struct vxb_player {
+    float pos[4];
+    float rot[4];
+    float vel[4];
+    float dir[4];
+    float up[4];
+    float right[4];
+    int32_t collision_vec[3];
+    float size;
+    float gravity[3];
+    uint32_t has_world_collision;
+} vxb_player;
+
+/* shaders/common.glsl:40-45 == src/voxel_sim_manager.rs:69-76 (16 bytes) */
+typedef struct vxb_collision {
+    uint32_t id1; /* projectile index */
+    uint32_t id2; /* player index */
+    uint32_t properties; /* 1 body, 2 head */
+    float when;
+} vxb_collision;
+
+/* GameSettings fields the path reads (/src/lib.rs:42-55) plus buffer capacities. The reference
+ * hard-codes 1024 for every capacity (src/main.rs:50-52, voxel_sim_manager.rs:95-123); here they
+ * are settings so that the benchmark configurations can lift the caps. 0 selects the reference's
+ * value. */
+typedef struct vxb_settings {
+    uint32_t render_size[3];    /* chunk-table extent, in chunks */
+    uint32_t max_loaded_chunks; /* voxel pool slots, including sentinel slots 0 and 1 */
+    uint32_t max_worldgen_rate; /* 8^3 worldgen workgroups per tick (8 per chunk) */
+    uint32_t max_update_rate;   /* chunk updates per tick */
+    float delta_time;
+    uint32_t world_gen;      /* 0 = WorldGenSettings::Normal (open_world.glsl), 1 = Control (control.glsl) */
+    uint32_t world_gen_seed; /* WorldGenSettings::get_seed(), /src/lib.rs:18-23 */
+    uint32_t max_projectiles;  /* 0 -> 1024 */
+    uint32_t max_players;      /* 0 -> 1024 */
+    uint32_t max_voxel_writes; /* 0 -> 1024 */
+    uint32_t max_collisions;   /* 0 -> 1024 */
+} vxb_settings;
+
+/* GraphicsSettings, src/settings_manager.rs:63-69, + PushConstants of src/raytracer.rs:244-253 */
+typedef struct vxb_ray_caps {
+    uint32_t primary_ray_dist;    /* DDA iteration caps */
+    uint32_t shadow_ray_dist;
+    uint32_t reflection_ray_dist;
+    uint32_t ao_ray_dist;
+    uint32_t projectile_count; /* projectiles of the ctx's device buffer tested per ray (reference uploads <= 128) */
+} vxb_ray_caps;
+
+/* Device-resident result of the primary DDA (frag.glsl RaycastResult, :79-91), structure of
+ * arrays over rays; ray i of view v at pixel (px,py) has index (v*h + py)*w + px.
+ * Per layer l < layer_count[i]:
+ *   pos    [(l*3 + c) * n_rays + i]    normal [(l*3 + c) * n_rays + i]
+ *   voxel  [l * n_rays + i]            ldist  [l * n_rays + i]
+ *   leaving[l * n_rays + i]
+ * Entries of layers >= layer_count[i] are unspecified. */
+typedef struct vxb_ray_buffers {
+    uint64_t n_rays;
+    float* pos;
+    float* normal;
+    uint32_t* voxel;
+    float* ldist;
+    uint32_t* leaving;
+    uint32_t* layer_count;
+    float* dist;
+} vxb_ray_buffers;
+
+/* chunks()/voxels()/projectiles()/players(), src/voxel_sim_manager.rs:537-543,650-656 */
+typedef struct vxb_ptrs {
+    uint32_t* chunk_table; /* render_size x*y*z u32, index (x*ry + y)*rz + z; 0 unloaded, 1 all-air, >=2 slot */
+    uint32_t* voxel_pool;  /* [slot][4096], in-chunk index x*256 + y*16 + z (common.glsl:247) */
+    vxb_projectile* projectiles;
+    vxb_player* players;
+    vxb_collision* collisions;
+    uint64_t pool_slots;
+} vxb_ptrs;
+
+typedef struct vxb_ctx vxb_ctx;
+
+/* ---- life cycle -------------------------------------------------------------------------- */
+
+/* VoxelComputePipeline::new, src/voxel_sim_manager.rs:265-535: allocates the chunk table (zeroed),
+ * the voxel pool with sentinel slot 0 = MAT_OOB<<24 and slot 1 = MAT_AIR_OOB<<24 (:193-207), the
+ * entity/work-list buffers; free list = 2..max_loaded_chunks (:274). */
+int vxb_create(const vxb_settings* settings, int device, vxb_ctx** out);
+void vxb_destroy(vxb_ctx* ctx);
+/* Message of the last failing call on this ctx (or of the last failing vxb_create when ctx is NULL). */
+const char* vxb_last_error(const vxb_ctx* ctx);
+/* Launch all further work of this ctx on `cuda_stream` (a cudaStream_t; NULL = the ctx's own stream). */
+int vxb_set_stream(vxb_ctx* ctx, void* cuda_stream);
+int vxb_synchronize(vxb_ctx* ctx);
+
+/* ---- the compute pass (src/voxel_sim_manager.rs) -------------------------------------------- */
+
+/* VoxelComputePipeline::compute (:830-1008). Uploads projectiles/players, zeroes the collision
+ * list, drains the three host queues into work lists (load_worldgen_updates :1140, load_voxel_writes
+ * :1055, load_chunk_updates :1010) and enqueues, in the reference's order (:944-1000): projectiles,
+ * entities, table-slab unload, worldgen + complete_worldgen, voxel writes, voxel update.
+ * Asynchronous on the ctx stream. start_pos = GameState::start_pos (chunks). */
+int vxb_compute(vxb_ctx* ctx, const uint32_t start_pos[3], const vxb_projectile* projectiles, uint32_t n_projectiles,
+                const vxb_player* players, uint32_t n_players);
+
+/* The read-back half of VoxelComputePipeline::download_projectiles (:545-648): synchronises, copies
+ * out the projectiles and players uploaded by the last vxb_compute, and the collision list (the
+ * reference stops at the first properties == 0 entry, :609-612). Projectiles killed by terrain
+ * (health == 0, chunk_update_pos[3] == 1) queue a chunk update as in :558-578. The card-system
+ * filtering (:618-638) is gameplay and stays with the caller. The collision list is emitted sorted
+ * by (id1, id2): the reference's append order is a GPU race. Any output pointer may be NULL. */
+int vxb_download_projectiles(vxb_ctx* ctx, vxb_projectile* projectiles_out, vxb_collision* collisions_out,
+                             uint32_t* n_collisions, vxb_player* players_out);
+
+/* VoxelComputePipeline::push_updates_from_changed (:741-816): consumes last tick's worldgen_results
+ * and chunk_updates[].w flags; all-air chunks return their slot, changed chunks and their flagged
+ * face neighbours are re-queued with priority-1+sum(6-distance). Synchronises. */
+int vxb_push_updates_from_changed(vxb_ctx* ctx, const float (*player_positions)[3], uint32_t n_players);
+
+/* queue_voxel_write (:658), queue_chunk_update (:662), queue_update_from_world_pos (:673),
+ * ensure_chunk_loaded (:1201) */
+int vxb_queue_voxel_write(vxb_ctx* ctx, const uint32_t write[4]);
+int vxb_queue_chunk_update(vxb_ctx* ctx, const uint32_t chunk[3]);
+int vxb_queue_update_from_world_pos(vxb_ctx* ctx, const float pos[3]);
+int vxb_ensure_chunk_loaded(vxb_ctx* ctx, const uint32_t chunk[3]);
+/* Not in the reference (its only route to forced = true is load_voxel_writes :1122-1131): queue a
+ * chunk for worldgen with the `forced` flag, so that it keeps a pool slot even if all air. */
+int vxb_queue_worldgen(vxb_ctx* ctx, const uint32_t chunk[3], int forced);
+
+/* move_start_pos (:697-737). direction: 0 PosX, 1 NegX, 2 PosY, 3 NegY, 4 PosZ, 5 NegZ
+ * (src/utils.rs:9-17). start_pos is updated in place; the table slab is cleared by the next
+ * vxb_compute (unload_chunks.glsl). */
+int vxb_move_start_pos(vxb_ctx* ctx, uint32_t start_pos[3], int direction);
+
+/* update_count / worldgen_count / worldgen_capacity (:818-828) */
+uint64_t vxb_update_count(const vxb_ctx* ctx);
+uint64_t vxb_worldgen_count(const vxb_ctx* ctx);
+uint64_t vxb_worldgen_capacity(const vxb_ctx* ctx);
+/* VoxelUpdateQueue::queue_set_idx (src/utils.rs:271): the Margolus phase of the last vxb_compute. */
+int vxb_queue_set_idx(const vxb_ctx* ctx, uint32_t phase_out[3]);
+/* Host mirror lookup, get_chunk (:686-689). */
+uint32_t vxb_get_chunk(const vxb_ctx* ctx, const uint32_t chunk[3]);
+/* Counts of the last vxb_compute: [0] worldgen workgroups, [1] voxel writes, [2] chunk updates. */
+int vxb_last_dispatch_counts(const vxb_ctx* ctx, uint32_t counts_out[3]);
+
+int vxb_device_ptrs(vxb_ctx* ctx, vxb_ptrs* out);
+
+/* ---- single dispatches with explicit host work lists (the D8 buffers of the compute pass) ---- */
+/* Each takes the work list the reference's host would have written into the mapped buffer and runs
+ * exactly one of the reference's dispatches on it. They neither touch the host queues nor the host
+ * mirror of the chunk table. Asynchronous unless an output pointer is given. */
+
+/* maps/open_world.glsl | maps/control.glsl main (+ complete_worldgen.glsl when `complete` != 0).
+ * chunk_loads: n_workgroups x ivec4 (8*chunk.xyz + ijk, +-slot), 8 consecutive entries per chunk
+ * (:1155-1166). load_results_out (nullable): n_workgroups/8 u32, pre-set to 1 by the host (:1151). */
+int vxb_dispatch_worldgen(vxb_ctx* ctx, const uint32_t start_pos[3], const int32_t (*chunk_loads)[4], uint32_t n_workgroups,
+                          int complete, uint32_t* load_results_out);
+/* compute_voxel.glsl main. chunk_updates: n x uvec4 (chunk.xyz, 0); offset = voxel_update_offset in
+ * {0,1}^3; flags_out (nullable): n u32 = chunk_updates[i].w after the dispatch. */
+int vxb_dispatch_voxel_update(vxb_ctx* ctx, const uint32_t start_pos[3], const uint32_t (*chunk_updates)[4], uint32_t n,
+                              const uint32_t offset[3], uint32_t* flags_out);
+/* write_voxels.glsl main. writes: n x (x, y, z, voxel word). */
+int vxb_dispatch_write_voxels(vxb_ctx* ctx, const uint32_t start_pos[3], const uint32_t (*writes)[4], uint32_t n);
+/* unload_chunks.glsl main. */
+int vxb_dispatch_unload(vxb_ctx* ctx, int32_t unload_index, uint32_t unload_component);
+/* compute_projectile.glsl + compute_entity.glsl main on host arrays, results copied back in place.
+ * collisions_out: capacity max_collisions; *n_collisions receives the count; sorted by (id1, id2). */
+int vxb_dispatch_entities(vxb_ctx* ctx, const uint32_t start_pos[3], vxb_projectile* projectiles, uint32_t n_projectiles,
+                          vxb_player* players, uint32_t n_players, int run_projectiles, int run_players,
+                          vxb_collision* collisions_out, uint32_t* n_collisions);
+
+/* Resident work list for repeated full sweeps (benchmark configs 3 and 5): upload once, then run
+ * the update dispatch on it any number of times without host traffic. */
+int vxb_update_list_upload(vxb_ctx* ctx, const uint32_t (*chunk_updates)[4], uint32_t n);
+int vxb_update_list_run(vxb_ctx* ctx, const uint32_t start_pos[3], const uint32_t offset[3]);
+int vxb_update_list_flags(vxb_ctx* ctx, uint32_t* flags_out, uint32_t n);
+/* Selects the update kernel: 0 = default (register-tiled, vectorised), 1 = per-voxel gather that
+ * follows the reference's access pattern (kept for profiling comparisons). */
+int vxb_set_update_kernel(vxb_ctx* ctx, int variant);
+
+/* ---- the ray pass (src/raytracer.rs, shaders/frag.glsl) --------------------------------------- */
+
+/* PointLightingSystem::draw (src/raytracer.rs:234-305) without the graphics pipeline: one primary
+ * ray per pixel of each w x h view through frag.glsl raycast() (:348-486) with the ray set-up of
+ * frag.glsl main (:715-733); camera v = cams[v] (the reference uses players[0]). raster_depth is
+ * NULL (no rasterised G-buffer: max_depth = 0) or a HOST array of n_views*w*h max_depth values.
+ * Results stay on the device (vxb_ray_results). Asynchronous. */
+int vxb_raymarch(vxb_ctx* ctx, const uint32_t start_pos[3], const vxb_player* cams, uint32_t n_views, uint32_t w, uint32_t h,
+                 const vxb_ray_caps* caps, const float* raster_depth);
+/* Arbitrary rays (collision / visibility queries): pos, dir are HOST arrays [n][3].
+ * kind 0 = raycast (primary, multi-layer), 1 = single_raycast (frag.glsl:93), 2 = simple_raycast
+ * (:275), 3 = simple_raycast_w_projectiles (:161). For kinds 1-3 the result uses layer 0:
+ * pos, normal (kind 1), voxel, ldist; `dist` holds passthrough_light (kinds 2,3); layer_count = 1. */
+int vxb_raymarch_rays(vxb_ctx* ctx, const uint32_t start_pos[3], const float (*pos)[3], const float (*dir)[3], uint64_t n,
+                      int kind, uint32_t max_iterations, uint32_t projectile_count);
+int vxb_ray_results(vxb_ctx* ctx, vxb_ray_buffers* out);
+/* Synchronises and copies the last ray results to host arrays laid out as documented at
+ * vxb_ray_buffers (any pointer may be NULL). total_iterations: DDA loop iterations executed. */
+int vxb_ray_download(vxb_ctx* ctx, float* pos, float* normal, uint32_t* voxel, float* ldist, uint32_t* leaving,
+                     uint32_t* layer_count, float* dist, uint64_t* total_iterations);
+
+/* ---- bulk test / checkpoint hooks (no reference analogue) --------------------------------------- */
+int vxb_read_pool(vxb_ctx* ctx, uint64_t first_slot, uint64_t n_slots, uint32_t* out);
+int vxb_write_pool(vxb_ctx* ctx, uint64_t first_slot, uint64_t n_slots, const uint32_t* in);
+int vxb_read_table(vxb_ctx* ctx, uint32_t* out);
+/* Overwrites the device table AND the host mirror; slots >= 2 named by the table leave the free list. */
+int vxb_write_table(vxb_ctx* ctx, const uint32_t* in);
+/* 64-bit order-independent checksum of the world as seen through the table: sum over loaded
+ * voxels of hash(global position, voxel word). For size-independent parity checks. */
+int vxb_world_checksum(vxb_ctx* ctx, const uint32_t start_pos[3], uint64_t* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VOXELB200_H */

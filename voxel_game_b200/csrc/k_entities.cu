@@ -1,0 +1,431 @@
+// k_projectiles / k_players — collision queries against the voxel grid.
+// Replaces shaders/compute_projectile.glsl (main :133-243, los_check :69-129) and
+// shaders/compute_entity.glsl (main :236-297, collide_player :102-234, can_step_up :68-100),
+// dispatched by src/voxel_sim_manager.rs:944-957.
+//
+// k_projectiles: one thread per projectile; the player array (128 B each) is staged in shared
+// memory in tiles so the 6-hitsphere test of every projectile against every player runs from
+// on-chip memory; collisions are appended through ONE global zero-initialised counter with a
+// warp-aggregated atomic (the reference's `shared uint collision_count` is uninitialised and
+// per-workgroup, compute_projectile.glsl:131 — see DESIGN.md "Reference quirks").
+#include "vxb_device.cuh"
+#include "vxb_kernels.h"
+
+namespace vxb {
+
+__device__ __forceinline__ f3 ld3(const float* p) { return mk3(p[0], p[1], p[2]); }
+
+// compute_projectile.glsl:69-129
+__device__ bool los_check(const World& w, f3 start, f3 end) {
+    const f3 diff = end - start;
+    const f3 ray = norm3(diff);
+    const float max_dist = len3(diff);
+    uint32_t offset = 0;
+    if (ray.x < 0) offset += 1;
+    if (ray.y < 0) offset += 2;
+    if (ray.z < 0) offset += 4;
+    float depth = 0;
+    f3 pos = start;
+    for (uint32_t i = 0; i < 20; i++) {
+        const f3 floor_pos = floor3(pos);
+        const uint32_t voxel_data = get_data(w, f2u(floor_pos.x), f2u(floor_pos.y), f2u(floor_pos.z));
+        f3 v_min, v_max;
+        const uint32_t voxel_material = voxel_data >> 24;
+        if (voxel_material == MAT_AIR_OOB) {
+            v_min = floor3(pos / 16.0f) * 16.0f;
+            v_max = v_min + mk3(16.0f, 16.0f, 16.0f);
+        } else if (mat_in(MASK_FLUID, voxel_material)) {
+            uint32_t dist = 0;
+            if (mat_in(MASK_DATA_DISTANCE, voxel_material)) dist = (voxel_data >> (offset * 3)) & 7u;
+            const float d = (float)dist, d1 = (float)(dist + 1);
+            v_min = floor_pos - mk3(d, d, d);
+            v_max = floor_pos + mk3(d1, d1, d1);
+        } else {
+            return false;
+        }
+        const f3 delta{ray_box_axis(pos.x, ray.x, v_min.x, v_max.x), ray_box_axis(pos.y, ray.y, v_min.y, v_max.y),
+                       ray_box_axis(pos.z, ray.z, v_min.z, v_max.z)};
+        const float dist_diff = gmin(delta.x, gmin(delta.y, delta.z));
+        depth += dist_diff;
+        if (depth > max_dist) return true;
+        pos = pos + ray * dist_diff;
+        if (delta.x < delta.y && delta.x < delta.z) {
+            if (ray.x > 0 && pos.x < v_max.x) pos.x = v_max.x;
+            else if (ray.x < 0 && pos.x >= v_min.x) pos.x = v_min.x - 0.001f;
+        } else if (delta.y < delta.z) {
+            if (ray.y > 0 && pos.y < v_max.y) pos.y = v_max.y;
+            else if (ray.y < 0 && pos.y >= v_min.y) pos.y = v_min.y - 0.001f;
+        } else {
+            if (ray.z > 0 && pos.z < v_max.z) pos.z = v_max.z;
+            else if (ray.z < 0 && pos.z >= v_min.z) pos.z = v_min.z - 0.001f;
+        }
+    }
+    return false;
+}
+
+// common.glsl:263-278
+__device__ void quaternion_from_arc(f3 src, f3 dst, float out[4]) {
+    const float mag_avg = sqrtf(dot3(src, src) * dot3(dst, dst));
+    const float dotprod = dot3(src, dst);
+    if (dotprod == mag_avg) {
+        out[0] = 0.0f; out[1] = 0.0f; out[2] = 0.0f; out[3] = 1.0f;
+    } else if (dotprod == -mag_avg) {
+        f3 v = cross3(mk3(1.0f, 0.0f, 0.0f), src);
+        if (v.x == 0.0f && v.y == 0.0f && v.z == 0.0f) v = cross3(mk3(0.0f, 1.0f, 0.0f), src);
+        v = norm3(v);
+        out[0] = v.x; out[1] = v.y; out[2] = v.z; out[3] = 3.14159265358979323846f / 2.0f;
+    } else {
+        const f3 c = cross3(src, dst);
+        const float qw = mag_avg + dotprod;
+        const float l = sqrtf(c.x * c.x + c.y * c.y + c.z * c.z + qw * qw);
+        out[0] = c.x / l; out[1] = c.y / l; out[2] = c.z / l; out[3] = qw / l;
+    }
+}
+
+constexpr int PLAYER_TILE = 64;  // 64 x 128 B = 8 KiB of shared memory
+
+__global__ void __launch_bounds__(128) k_projectiles(World w, vxb_projectile* __restrict__ projectiles, uint32_t n_projectiles,
+                                                     const vxb_player* __restrict__ players, uint32_t n_players,
+                                                     vxb_collision* __restrict__ collisions, uint32_t collision_capacity,
+                                                     uint32_t* __restrict__ collision_count, float dt) {
+    __shared__ float4 s_players[PLAYER_TILE];  // (pos.xyz, size) is all the hit test reads
+    const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool active = idx < n_projectiles;
+    vxb_projectile pr;
+    if (active) pr = projectiles[idx];
+    f3 ppos = mk3(0, 0, 0), dir = mk3(0, 0, 1), right = mk3(1, 0, 0), up = mk3(0, 1, 0);
+    f3 adj = mk3(0, 0, 0);
+    if (active) {
+        ppos = ld3(pr.pos);
+        dir = quat_transform(pr.dir, mk3(0.0f, 0.0f, 1.0f));
+        right = quat_transform(pr.dir, mk3(1.0f, 0.0f, 0.0f));
+        up = quat_transform(pr.dir, mk3(0.0f, 1.0f, 0.0f));
+        adj = mk3(pr.size[0], pr.size[1], pr.size[2]);
+        adj.z += dt * pr.vel / 2.0f;
+    }
+    const float hs_off[6] = {0.0f, -1.3f, -1.9f, -2.6f, -3.3f, -3.8f};
+    const float hs_rad[6] = {0.6f, 0.6f, 0.9f, 0.8f, 0.6f, 0.6f};
+
+    for (uint32_t tile = 0; tile < n_players; tile += PLAYER_TILE) {
+        __syncthreads();
+        for (uint32_t t = threadIdx.x; t < PLAYER_TILE && tile + t < n_players; t += blockDim.x) {
+            const vxb_player& pl = players[tile + t];
+            s_players[t] = make_float4(pl.pos[0], pl.pos[1], pl.pos[2], pl.size);
+        }
+        __syncthreads();
+        const uint32_t tile_n = min((uint32_t)PLAYER_TILE, n_players - tile);
+        for (uint32_t t = 0; t < tile_n; t++) {
+            uint32_t collision = 0;
+            f3 prev_collision = mk3(0.0f, 0.0f, 0.0f);
+            if (active) {
+                const float4 pl = s_players[t];
+                const f3 plpos = mk3(pl.x, pl.y, pl.z);
+#pragma unroll
+                for (int h = 0; h < 6; h++) {
+                    // Hitsphere(player.pos + offset * size, radius * size, headshot) (:138)
+                    const f3 centre = plpos + mk3(0.0f, hs_off[h], 0.0f) * pl.w;
+                    const float radius = hs_rad[h] * pl.w;
+                    if (collision > 0) {
+                        if (len3(ppos - centre) > len3(ppos - prev_collision)) continue;
+                    }
+                    bool collide = true;
+                    // projectile_vectors = { right, up, dir } (:140)
+                    if (fabsf(dot3(centre, right) - dot3(ppos, right)) > adj.x + radius) collide = false;
+                    else if (fabsf(dot3(centre, up) - dot3(ppos, up)) > adj.y + radius) collide = false;
+                    else if (fabsf(dot3(centre, dir) - dot3(ppos, dir)) > adj.z + radius) collide = false;
+                    if (!collide) continue;
+                    collision = h == 0 ? 2u : 1u;
+                    prev_collision = centre;
+                }
+            }
+            const bool hit = collision > 0 && los_check(w, ppos, prev_collision);
+            // warp-aggregated append
+            const uint32_t mask = __ballot_sync(0xFFFFFFFFu, hit);
+            if (mask) {
+                const uint32_t lane = threadIdx.x & 31;
+                const uint32_t leader = __ffs(mask) - 1;
+                uint32_t base = 0;
+                if (lane == leader) base = atomicAdd(collision_count, __popc(mask));
+                base = __shfl_sync(0xFFFFFFFFu, base, leader);
+                if (hit) {
+                    const uint32_t slot = base + __popc(mask & ((1u << lane) - 1u));
+                    if (slot < collision_capacity)
+                        collisions[slot] = vxb_collision{idx, tile + t, collision, dot3(dir, prev_collision - ppos)};
+                }
+            }
+        }
+    }
+
+    if (!active) return;
+    if (pr.should_collide_with_terrain != 1) return;
+
+    // terrain part (:181-243)
+    const float SQRT2 = 1.41421356237309504880f;  // sqrt(2.0) folded to the nearest float
+    int gic[3];
+    gic[0] = f2i(ceilf(2.0f * pr.size[0] * SQRT2));
+    gic[1] = f2i(ceilf(2.0f * pr.size[1] * SQRT2));
+    gic[2] = f2i(ceilf((2.0f * pr.size[2] + dt * pr.vel) * SQRT2));
+    f3 grid_dist = mk3(2.0f * pr.size[0] / (float)gic[0], 2.0f * pr.size[1] / (float)gic[1], 0.0f);
+    grid_dist.z = (2.0f * pr.size[2] + dt * pr.vel) / (float)gic[2];
+    const f3 start = ppos - dir * pr.size[2] - right * pr.size[0] - up * pr.size[1];
+    for (int i = 0; i <= gic[0]; i++) {
+        for (int j = 0; j <= gic[1]; j++) {
+            for (int k = 0; k <= gic[2]; k++) {
+                const int mapped_i = gic[0] / 2 + (2 * (i % 2) - 1) * ((i + 1) / 2);
+                const int mapped_j = gic[1] / 2 + (2 * (j % 2) - 1) * ((j + 1) / 2);
+                const int mapped_k = gic[2] / 2 + (2 * (k % 2) - 1) * ((k + 1) / 2);
+                const f3 pos = start + dir * grid_dist.z * (float)mapped_k + right * grid_dist.x * (float)mapped_i +
+                               up * grid_dist.y * (float)mapped_j;
+                const int vx = f2i(pos.x), vy = f2i(pos.y), vz = f2i(pos.z);
+                const uint32_t data = get_data(w, (uint32_t)vx, (uint32_t)vy, (uint32_t)vz);
+                const uint32_t voxel_mat = data >> 24;
+                if (mat_in(MASK_FLUID, voxel_mat)) {
+                    continue;
+                } else if (voxel_mat == MAT_OOB) {
+                    pr.health = 0.0f;
+                    pr.chunk_update_pos[3] = 0;
+                    projectiles[idx] = pr;
+                    return;
+                }
+                const float dist_past_bb = grid_dist.z * (float)mapped_k - 2.0f * pr.size[2];
+                const f3 ndir = -dir;
+                const f3 delta{ray_box_axis(pos.x, ndir.x, (float)vx, (float)(vx + 1)), ray_box_axis(pos.y, ndir.y, (float)vy, (float)(vy + 1)),
+                               ray_box_axis(pos.z, ndir.z, (float)vz, (float)(vz + 1))};
+                const float dist_diff = gmin(delta.x, gmin(delta.y, delta.z));
+                if (dist_past_bb > 0.0f) {
+                    const f3 mv = dir * (dist_past_bb - dist_diff);
+                    pr.pos[0] += mv.x; pr.pos[1] += mv.y; pr.pos[2] += mv.z; pr.pos[3] += 0.0f;
+                }
+                if (pr.wall_bounce == 1) {
+                    f3 new_dir = dir;
+                    if (delta.x == dist_diff) new_dir.x *= -1.0f;
+                    else if (delta.y == dist_diff) new_dir.y *= -1.0f;
+                    else if (delta.z == dist_diff) new_dir.z *= -1.0f;
+                    quaternion_from_arc(mk3(0.0f, 0.0f, 1.0f), new_dir, pr.dir);
+                    projectiles[idx] = pr;
+                    return;
+                }
+                if (pr.damage > 0) {
+                    // imageAtomicAdd(voxels, get_index(voxel_pos), int(projectile.damage)) (:230-233)
+                    atomicAdd(&w.pool[voxel_index(w, (uint32_t)vx, (uint32_t)vy, (uint32_t)vz)], (uint32_t)f2i(pr.damage));
+                }
+                pr.chunk_update_pos[0] = (uint32_t)vx; pr.chunk_update_pos[1] = (uint32_t)vy; pr.chunk_update_pos[2] = (uint32_t)vz;
+                pr.chunk_update_pos[3] = 1;
+                pr.health = 0.0f;
+                projectiles[idx] = pr;
+                return;
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// compute_entity.glsl
+__device__ __forceinline__ f3 hitbox_offset() { return mk3(0.0f, -2.0f, 0.0f); }
+__device__ __forceinline__ f3 hitbox_size() { return mk3(1.8f, 4.8f, 1.8f); }
+
+struct PlayerState {
+    f3 pos, vel;
+    float size;
+    int collision_vec[3];
+};
+
+// compute_entity.glsl:68-100
+__device__ bool can_step_up(const World& w, const PlayerState& player, int component, f3 player_move_pos) {
+    f3 start_pos = player.pos + hitbox_offset() * player.size - 0.5f * player.size * hitbox_size();
+    setcomp(start_pos, component, comp(player_move_pos, component));
+    start_pos.y += 1.0f;
+    const int c1 = (component + 1) % 3, c2 = (component + 2) % 3;
+    const int x_iter_count = f2i(floorf(comp(start_pos, c1) + player.size * comp(hitbox_size(), c1)) - floorf(comp(start_pos, c1)));
+    const int z_iter_count = f2i(floorf(comp(start_pos, c2) + player.size * comp(hitbox_size(), c2)) - floorf(comp(start_pos, c2)));
+    f3 x_vec = mk3(0, 0, 0), z_vec = mk3(0, 0, 0);
+    setcomp(x_vec, c1, 1.0f);
+    setcomp(z_vec, c2, 1.0f);
+    for (int x_iter = 0; x_iter <= x_iter_count; x_iter++) {
+        for (int z_iter = 0; z_iter <= z_iter_count; z_iter++) {
+            const f3 pos = start_pos + (float)x_iter * x_vec + (float)z_iter * z_vec;
+            const uint32_t voxel = get_data(w, f2u(pos.x), f2u(pos.y), f2u(pos.z));
+            if (!mat_in(MASK_FLUID, voxel >> 24)) return false;
+        }
+    }
+    return true;
+}
+
+__device__ __forceinline__ float material_friction(uint32_t m) {
+    // physics_properties[].friction, common.glsl:89-103
+    switch (m) {
+        case MAT_STONE: case MAT_DIRT: case MAT_GRASS: case MAT_WOOD: case MAT_UNBREAKABLE: return 5.0f;
+        case MAT_ICE: return 0.1f;
+        case MAT_WATER: return 1.0f;
+        case MAT_LEAF: return 4.0f;
+        default: return 0.0f;
+    }
+}
+__device__ __forceinline__ float material_density(uint32_t m) {
+    switch (m) {
+        case MAT_PROJECTILE: case MAT_PLAYER: return 0.0f;
+        case MAT_WATER: return 4.4f;
+        default: return 1.0f;
+    }
+}
+
+// compute_entity.glsl:102-234
+__device__ void collide_player(const World& w, PlayerState& player, f3 prev_collision_vec, float dt) {
+    const f3 collision_corner_offset = mk3(gsign(player.vel.x), gsign(player.vel.y), gsign(player.vel.z)) * hitbox_size() * 0.5f * player.size;
+    f3 distance_to_move = player.vel * dt;
+    uint32_t iteration_counter = 0;
+
+    while (dot3(distance_to_move, distance_to_move) > 0.0001f) {
+        iteration_counter += 1;
+        const f3 player_move_pos0 = player.pos + hitbox_offset() * player.size + collision_corner_offset;
+        const f3 vel_dir = norm3(distance_to_move);
+        const f3 lo = floor3(player_move_pos0), hi = mk3(ceilf(player_move_pos0.x), ceilf(player_move_pos0.y), ceilf(player_move_pos0.z));
+        f3 delta{ray_box_axis(player_move_pos0.x, vel_dir.x, lo.x, hi.x), ray_box_axis(player_move_pos0.y, vel_dir.y, lo.y, hi.y),
+                 ray_box_axis(player_move_pos0.z, vel_dir.z, lo.z, hi.z)};
+        if (delta.x != delta.x) delta.x = 2.0f;
+        if (delta.y != delta.y) delta.y = 2.0f;
+        if (delta.z != delta.z) delta.z = 2.0f;
+        float dist_diff = gmin(delta.x, gmin(delta.y, delta.z));
+        if (dist_diff == 0.0f) {
+            dist_diff = len3(distance_to_move);
+            if (delta.x != 0.0f) dist_diff = gmin(dist_diff, delta.x);
+            if (delta.y != 0.0f) dist_diff = gmin(dist_diff, delta.y);
+            if (delta.z != 0.0f) dist_diff = gmin(dist_diff, delta.z);
+        } else if (dist_diff > len3(distance_to_move)) {
+            player.pos = player.pos + distance_to_move;
+            break;
+        }
+        if (iteration_counter > 100) break;
+
+        distance_to_move = distance_to_move - dist_diff * vel_dir;
+        for (int component = 0; component < 3; component++) {
+            const int c1 = (component + 1) % 3, c2 = (component + 2) % 3;
+            f3 fake_pos = player.pos;
+            setcomp(fake_pos, component, comp(fake_pos, component) + dist_diff * comp(vel_dir, component));
+            const f3 player_move_pos = fake_pos + hitbox_offset() * player.size + collision_corner_offset;
+            if (comp(delta, component) <= comp(delta, c1) && comp(delta, component) <= comp(delta, c2)) {
+                f3 start_pos = fake_pos + hitbox_offset() * player.size - 0.5f * player.size * hitbox_size();
+                setcomp(start_pos, component, comp(player_move_pos, component));
+                const int x_iter_count = f2i(floorf(comp(start_pos, c1) + player.size * comp(hitbox_size(), c1)) - floorf(comp(start_pos, c1)));
+                const int z_iter_count = f2i(floorf(comp(start_pos, c2) + player.size * comp(hitbox_size(), c2)) - floorf(comp(start_pos, c2)));
+                f3 x_vec = mk3(0, 0, 0), z_vec = mk3(0, 0, 0);
+                setcomp(x_vec, c1, 1.0f);
+                setcomp(z_vec, c2, 1.0f);
+                bool found_position = false;
+                for (int x_iter = 0; x_iter <= x_iter_count && !found_position; x_iter++) {
+                    for (int z_iter = 0; z_iter <= z_iter_count; z_iter++) {
+                        const f3 pos = start_pos + (float)x_iter * x_vec + (float)z_iter * z_vec;
+                        const uint32_t voxel = get_data(w, f2u(pos.x), f2u(pos.y), f2u(pos.z));
+                        const uint32_t voxel_material = voxel >> 24;
+                        if (!mat_in(MASK_FLUID, voxel_material)) {
+                            if (component != 1 && prev_collision_vec.y == 1 && (pos - start_pos).y < 1.0f &&
+                                can_step_up(w, player, component, player_move_pos)) {
+                                player.pos = fake_pos;
+                                player.pos.y += 1.0f;
+                                found_position = true;
+                                break;
+                            }
+                            setcomp(player.vel, component, 0.0f);
+                            // apply friction
+                            const float pvx = comp(player.vel, c1), pvy = comp(player.vel, c2);
+                            const float plen = sqrtf(pvx * pvx + pvy * pvy);
+                            if (plen > 0.0f) {
+                                const float friction_factor = material_friction(voxel_material);
+                                const float fx = (friction_factor * 0.5f * (pvx / plen) + friction_factor * pvx) * dt;
+                                const float fy = (friction_factor * 0.5f * (pvy / plen) + friction_factor * pvy) * dt;
+                                if (sqrtf(fx * fx + fy * fy) > plen) {
+                                    setcomp(player.vel, c1, 0.0f);
+                                    setcomp(player.vel, c2, 0.0f);
+                                } else {
+                                    setcomp(player.vel, c1, pvx - fx);
+                                    setcomp(player.vel, c2, pvy - fy);
+                                }
+                            }
+                            player.collision_vec[component] = f2i(-gsign(comp(vel_dir, component)));
+                            setcomp(distance_to_move, component, 0.0f);
+                            found_position = true;
+                            break;
+                        }
+                    }
+                }
+                if (found_position) continue;
+            }
+            player.pos = fake_pos;
+        }
+    }
+}
+
+// compute_entity.glsl:236-297
+__global__ void __launch_bounds__(128) k_players(World w, vxb_player* __restrict__ players, uint32_t n_players, float dt) {
+    const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n_players) return;
+    vxb_player pl = players[idx];
+    PlayerState st;
+    st.pos = ld3(pl.pos);
+    st.vel = ld3(pl.vel);
+    st.size = pl.size;
+    const f3 gravity = ld3(pl.gravity);
+
+    const f3 start_pos = st.pos + st.size * hitbox_offset() - st.size * hitbox_size() / 2.0f;
+    const f3 end_pos = st.pos + st.size * hitbox_offset() + st.size * hitbox_size() / 2.0f;
+    const uint32_t svx = f2u(start_pos.x), svy = f2u(start_pos.y), svz = f2u(start_pos.z);
+    const uint32_t icx = f2u(end_pos.x) - svx + 1, icy = f2u(end_pos.y) - svy + 1, icz = f2u(end_pos.z) - svz + 1;
+    float nearby_density = 0.0f;
+    f3 directional_density = mk3(0.0f, 0.0f, 0.0f);
+    const f3 centre = st.pos + st.size * hitbox_offset();
+    for (int x = 0; x < (int)icx; x++) {
+        for (int y = 0; y < (int)icy; y++) {
+            for (int z = 0; z < (int)icz; z++) {
+                const uint32_t vx = svx + (uint32_t)x, vy = svy + (uint32_t)y, vz = svz + (uint32_t)z;
+                const f3 vp = mk3((float)vx, (float)vy, (float)vz);
+                const f3 hi = vp + mk3(1.0f, 1.0f, 1.0f);
+                const f3 od = mk3(gmin(end_pos.x, hi.x), gmin(end_pos.y, hi.y), gmin(end_pos.z, hi.z)) -
+                              mk3(gmax(start_pos.x, vp.x), gmax(start_pos.y, vp.y), gmax(start_pos.z, vp.z));
+                const float overlapping_volume = od.x * od.y * od.z;
+                const uint32_t voxel = get_data(w, vx, vy, vz);
+                const float density = material_density(voxel >> 24);
+                nearby_density += overlapping_volume * density;
+                directional_density = directional_density + overlapping_volume * density * ((vp + mk3(0.5f, 0.5f, 0.5f)) - centre) / st.size;
+            }
+        }
+    }
+    const float denom = st.size * st.size * st.size * 1.8f * 4.8f * 1.8f;
+    nearby_density /= denom;
+    directional_density = directional_density / denom;
+
+    if (pl.has_world_collision == 1) {
+        st.vel = st.vel + (3.8f - nearby_density) * gravity * 11.428571428571429f * dt;
+        if (len3(directional_density) * dt > 0.001f) st.vel = st.vel - 0.5f * directional_density * dt;
+        if (dot3(st.vel, st.vel) > 0.0f)
+            st.vel = st.vel - (nearby_density * 0.0375f * st.vel * len3(st.vel) * dt + 0.2f * norm3(st.vel) * dt);
+        const f3 prev_collision_vec = mk3((float)pl.collision_vec[0], (float)pl.collision_vec[1], (float)pl.collision_vec[2]);
+        st.collision_vec[0] = 0; st.collision_vec[1] = 0; st.collision_vec[2] = 0;
+        collide_player(w, st, prev_collision_vec, dt);
+        pl.pos[0] = st.pos.x; pl.pos[1] = st.pos.y; pl.pos[2] = st.pos.z;
+        pl.vel[0] = st.vel.x; pl.vel[1] = st.vel.y; pl.vel[2] = st.vel.z;
+        pl.collision_vec[0] = st.collision_vec[0]; pl.collision_vec[1] = st.collision_vec[1]; pl.collision_vec[2] = st.collision_vec[2];
+    } else {
+        // player.pos += player.vel; player.vel *= 0.5;  (vec4 ops, :291-292)
+        for (int c = 0; c < 4; c++) {
+            pl.pos[c] += pl.vel[c];
+            pl.vel[c] *= 0.5f;
+        }
+    }
+    players[idx] = pl;
+}
+
+cudaError_t launch_projectiles(const World& w, vxb_projectile* projectiles, uint32_t n_projectiles, const vxb_player* players,
+                               uint32_t n_players, vxb_collision* collisions, uint32_t collision_capacity, uint32_t* collision_count,
+                               float dt, cudaStream_t st) {
+    if (n_projectiles == 0) return cudaSuccess;
+    k_projectiles<<<(n_projectiles + 127) / 128, 128, 0, st>>>(w, projectiles, n_projectiles, players, n_players, collisions,
+                                                               collision_capacity, collision_count, dt);
+    return cudaGetLastError();
+}
+cudaError_t launch_players(const World& w, vxb_player* players, uint32_t n_players, float dt, cudaStream_t st) {
+    if (n_players == 0) return cudaSuccess;
+    k_players<<<(n_players + 127) / 128, 128, 0, st>>>(w, players, n_players, dt);
+    return cudaGetLastError();
+}
+
+}  // namespace vxb

@@ -1,0 +1,504 @@
+// k_worldgen_* — seeded chunk world generation, one CTA per 8^3 worldgen workgroup.
+// Replaces shaders/maps/open_world.glsl (get_worldgen :69-119, main :121-129) and
+// shaders/maps/control.glsl (get_worldgen :187-243, main :245-253), plus complete_worldgen.glsl,
+// write_voxels.glsl and unload_chunks.glsl.
+//
+// Open-world generation is ALU-bound (4 voronoise fields x 125 lattice cells per voxel vs 4 bytes
+// written), so the design removes redundant work while keeping every retained operation and its
+// order bit-identical to the shader:
+//  * per-CTA hash staging: an 8^3 block spans at most 2 lattice cells per axis at every scale used
+//    (<= 0.06), so the 125 pcg4d hashes per voxel per field collapse to 6^3 per CTA per field, held
+//    in shared memory as the ready-made jitter vector o = hash/128 - 1.
+//  * zero-weight skip: a cell with |d|^2 >= 2 has smoothstep == 1 exactly, hence weight w == +0 and
+//    its contributions are +-0; adding +-0 to an accumulator that started at +0 never changes it,
+//    so the sqrt/divide/polynomial are only executed for the ~10-15 % of cells that matter.
+//  * only the y and w lanes of the gradient vec4s feed the material decision tree; x/z lanes of
+//    the reference are dead code and are not computed.
+//  * the density field has y-scale exactly 0, so it only depends on the (x,z) column; it is
+//    evaluated once per column (64 threads) and shared through shared memory.
+#include "vxb_device.cuh"
+#include "vxb_kernels.h"
+
+namespace vxb {
+
+struct yw {
+    float y, w;
+};
+
+// open_world.glsl:45-47 (y and w lanes)
+__device__ __forceinline__ yw y_gradient(float y, float scale, float start_y, float end_y) {
+    return yw{scale * (gstep(start_y, scale * y) - gstep(end_y, scale * y)), gclamp(scale * y, start_y, end_y)};
+}
+
+// One staged voronoise field of an 8^3 block: jitter vectors of the 6^3 lattice cells around it.
+struct FieldStage {
+    float4 o[216];
+};
+
+// Stage field `s` for the block at `origin` with scale (sx,sy,sz). Returns i_min - 2 per axis.
+__device__ __forceinline__ void stage_field(FieldStage& fs, int (&base)[3], const uint32_t origin[3], float sx, float sy, float sz,
+                                            uint32_t tid, uint32_t nthreads) {
+    base[0] = f2i(sx * (float)origin[0]) - 2;
+    base[1] = f2i(sy * (float)origin[1]) - 2;
+    base[2] = f2i(sz * (float)origin[2]) - 2;
+    for (uint32_t c = tid; c < 216; c += nthreads) {
+        const int cx = c % 6, cy = (c / 6) % 6, cz = c / 36;
+        uint32_t hx = (uint32_t)(base[0] + cx), hy = (uint32_t)(base[1] + cy), hz = (uint32_t)(base[2] + cz), hw = 0u;
+        pcg4d(hx, hy, hz, hw);
+        // vec4(pcg4d(..) & 0xFF) / 128.0 - 1.0, times vec4(vec3(u), 1.0) with u == 1.0 (exact)
+        fs.o[c] = make_float4((float)(hx & 0xFF) / 128.0f - 1.0f, (float)(hy & 0xFF) / 128.0f - 1.0f,
+                              (float)(hz & 0xFF) / 128.0f - 1.0f, (float)(hw & 0xFF) / 128.0f - 1.0f);
+    }
+}
+
+// common.glsl:332-355 voronoise(p, 1.0, 1.0) -> (dir.y / a.y, a.x / a.y) from staged jitters.
+__device__ __forceinline__ yw voronoise_staged(const FieldStage& fs, const int (&base)[3], float px, float py, float pz) {
+    const int ix = f2i(px) - base[0], iy = f2i(py) - base[1], iz = f2i(pz) - base[2];  // in [2,3]
+    const float fx = gfract(px), fy = gfract(py), fz = gfract(pz);
+    float ax = 0.0f, ay = 0.0f, diry = 0.0f;
+    float gfx[5], gfy[5], gfz[5];
+#pragma unroll
+    for (int t = 0; t < 5; t++) {
+        gfx[t] = (float)(t - 2) - fx;
+        gfy[t] = (float)(t - 2) - fy;
+        gfz[t] = (float)(t - 2) - fz;
+    }
+    for (int z = 0; z < 5; z++) {
+        for (int y = 0; y < 5; y++) {
+            const float4* row = &fs.o[((iz + z - 2) * 6 + (iy + y - 2)) * 6 + (ix - 2)];
+#pragma unroll
+            for (int x = 0; x < 5; x++) {
+                const float4 o = row[x];
+                const float dx = gfx[x] + o.x, dy = gfy[y] + o.y, dz = gfz[z] + o.z;
+                const float dsq = dx * dx + dy * dy + dz * dz;
+                if (dsq < 2.0f) {
+                    float t = gclamp(sqrtf(dsq) / 1.414f, 0.0f, 1.0f);
+                    const float w = 1.0f - t * t * (3.0f - 2.0f * t);
+                    ax += o.w * w;
+                    ay += w;
+                    diry += dy * (2.0f * o.w - 1.0f) * w;
+                }
+            }
+        }
+    }
+    return yw{diry / ay, ax / ay};
+}
+
+// open_world.glsl:69-119 given the four field samples (V = raw voronoise (y, w) lanes).
+__device__ __forceinline__ uint32_t open_world_decide(uint32_t gx, uint32_t gy, uint32_t gz, yw Vmacro, yw Vdens, yw Vtemp, yw Vcave) {
+    const float SEA_LEVEL = 1796.0f;
+    const uint32_t cpx = gx / 32, cpz = gz / 32;
+    uint32_t hx = cpx, hy = cpx, hz = cpz;
+    pcg3d(hx, hy, hz);
+    const float tree_x = 32.0f * (float)cpx + 3.0f + 26.0f * (float)(hx & 0xFF) / 256.0f;
+    const float tree_y = 32.0f * (float)cpz + 3.0f + 26.0f * (float)(hy & 0xFF) / 256.0f;
+    float tree_z = 32.0f * 0.0f + 3.0f + 26.0f * (float)(hz & 0xFF) / 256.0f;
+    tree_z = tree_z / 100.0f + 0.2f;
+    uint32_t rx = gx, ry = gy, rz = gz;
+    pcg3d(rx, ry, rz);
+    const float random_x = (float)(rx & 0xFF) / 128.0f;
+    const float tx = (float)gx, ty = (float)gy, tz = (float)gz;
+
+    const yw macro_noise{0.00001f * Vmacro.y, 1.0f * Vmacro.w};
+    const yw density{0.0f * Vdens.y, 1.0f * Vdens.w};
+    const yw yg_t = y_gradient(ty - SEA_LEVEL, 1.0f / 80.0f, -0.5f, 2.0f);
+    const yw temperature{0.0f + 0.0005f * Vtemp.y - yg_t.y, 0.2f + 1.0f * Vtemp.w - yg_t.w};
+    // clamp_gradient(vec4(CAVE_SCALE,1) * V, -1.0, 0.5)
+    const float cave_w_raw = 1.0f * Vcave.w;
+    const yw cg{0.035f * Vcave.y * (gstep(-1.0f, cave_w_raw) - gstep(0.5f, cave_w_raw)), gclamp(cave_w_raw, -1.0f, 0.5f)};
+    const yw yg_c = y_gradient(ty - SEA_LEVEL, 1.0f / 80.0f, -1.0f, 0.3f);
+    const yw ncg{-1.0f * yg_c.y, -1.0f * yg_c.w};
+    const yw cave_density{cg.y * ncg.w + cg.w * ncg.y, cg.w * ncg.w};  // mul_gradient
+
+    const yw yg_d = y_gradient(ty - SEA_LEVEL, 1.0f / 62.0f, -0.6f, 10.0f);
+    // max_gradient(vec4(0,0,0,1) - 20 * abs_gradient(temperature - vec4(0,0,0,0.1)), vec4(0))
+    const yw t1{temperature.y - 0.0f, temperature.w - 0.1f};
+    const yw ag{t1.y * gsign(t1.w), fabsf(t1.w)};
+    yw mg{0.0f - 20.0f * ag.y, 1.0f - 20.0f * ag.w};
+    if (!(mg.w > 0.0f)) mg = yw{0.0f, 0.0f};
+    const yw yg_5 = y_gradient(ty - SEA_LEVEL - 5.0f, 0.3f, -2.0f, 0.0f);
+    const yw nyg5{-yg_5.y, -yg_5.w};
+    const yw mul{mg.y * nyg5.w + mg.w * nyg5.y, mg.w * nyg5.w};
+    const yw terrain_density{1.5f * cave_density.y + density.y + 0.7f * macro_noise.y + 0.0f - yg_d.y + mul.y,
+                             1.5f * cave_density.w + density.w + 0.7f * macro_noise.w + 0.1f - yg_d.w + mul.w};
+
+    const float ddx = tx - tree_x, ddz = tz - tree_y;  // true_pos.xz - tree_pos.xy
+    if (terrain_density.w <= 0.0f) {
+        if (temperature.w + tree_z > 0.2f &&
+            sqrtf(ddx * ddx + ddz * ddz) < 0.7f + 0.2f / (temperature.w + tree_z - 0.1f) - 0.25f / (terrain_density.w - 0.2f)) {
+            return MAT_WOOD << 24;
+        } else {
+            const float q = 100.0f * (temperature.w + tree_z - 0.2f);
+            if (sqrtf(ddx * ddx + ddz * ddz + q * q) < 12.0f - 5.0f * random_x) {
+                return MAT_LEAF << 24;
+            } else if (ty > SEA_LEVEL) {
+                if (temperature.w - terrain_density.w < -0.9f) return MAT_ICE << 24;
+                return MAT_AIR << 24;
+            } else if (temperature.w + 0.02f * random_x > 0.1f) {
+                return MAT_WATER << 24;
+            } else if (terrain_density.w + gclamp((ty - SEA_LEVEL) / 30.0f, -2.0f, 0.0f) < -0.27f && temperature.w < 0.1f) {
+                return MAT_AIR << 24;
+            } else {
+                return MAT_ICE << 24;
+            }
+        }
+    } else if (terrain_density.w + gclamp((SEA_LEVEL - ty) / 30.0f, 0.0f, 0.7f) > 0.35f) {
+        return MAT_STONE << 24;
+    } else if (terrain_density.w > 0.2f) {
+        return MAT_DIRT << 24;
+    } else {
+        if (temperature.w + 0.05f * random_x - 1.5f * terrain_density.y > terrain_density.w && ty >= SEA_LEVEL &&
+            terrain_density.y < 0.01f) {
+            return MAT_GRASS << 24;
+        } else {
+            return MAT_DIRT << 24;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(512) k_worldgen_open(uint32_t* __restrict__ pool, const int4* __restrict__ chunk_loads,
+                                                       uint32_t* __restrict__ load_results) {
+    __shared__ FieldStage s_macro, s_dens, s_temp, s_cave;
+    __shared__ int s_base[4][3];
+    __shared__ yw s_density[64];
+
+    const uint32_t tid = threadIdx.x;
+    const int4 load = chunk_loads[blockIdx.x];
+    const uint32_t origin[3] = {8u * (uint32_t)load.x, 8u * (uint32_t)load.y, 8u * (uint32_t)load.z};
+    {
+        int b[3];
+        // MACRO_SCALE, DENSITY_SCALE, TEMP_SCALE, CAVE_SCALE (open_world.glsl:40-43)
+        stage_field(s_macro, b, origin, 0.01f, 0.00001f, 0.01f, tid, 512);
+        if (tid == 0) { s_base[0][0] = b[0]; s_base[0][1] = b[1]; s_base[0][2] = b[2]; }
+        stage_field(s_dens, b, origin, 0.04f, 0.0f, 0.04f, tid, 512);
+        if (tid == 0) { s_base[1][0] = b[0]; s_base[1][1] = b[1]; s_base[1][2] = b[2]; }
+        stage_field(s_temp, b, origin, 0.005f, 0.0005f, 0.005f, tid, 512);
+        if (tid == 0) { s_base[2][0] = b[0]; s_base[2][1] = b[1]; s_base[2][2] = b[2]; }
+        stage_field(s_cave, b, origin, 0.06f, 0.035f, 0.06f, tid, 512);
+        if (tid == 0) { s_base[3][0] = b[0]; s_base[3][1] = b[1]; s_base[3][2] = b[2]; }
+    }
+    __syncthreads();
+
+    const uint32_t lz = tid & 7, ly = (tid >> 3) & 7, lx = tid >> 6;
+    const uint32_t gx = origin[0] + lx, gy = origin[1] + ly, gz = origin[2] + lz;
+    const float tx = (float)gx, ty = (float)gy, tz = (float)gz;
+
+    int base[3];
+    // density depends on (x,z) only: threads of the last two warps (ly == 7... any fixed set of 64)
+    // evaluate it per column. Use the 64 threads with ly == 0 reordered into warps 0-1 by tid < 64.
+    if (tid < 64) {
+        const uint32_t cx = tid >> 3, cz = tid & 7;
+        base[0] = s_base[1][0]; base[1] = s_base[1][1]; base[2] = s_base[1][2];
+        // p.y = 0.0 * y is +0 for every finite y
+        s_density[tid] = voronoise_staged(s_dens, base, 0.04f * (float)(origin[0] + cx), 0.0f * ty, 0.04f * (float)(origin[2] + cz));
+    }
+    base[0] = s_base[0][0]; base[1] = s_base[0][1]; base[2] = s_base[0][2];
+    const yw Vmacro = voronoise_staged(s_macro, base, 0.01f * tx, 0.00001f * ty, 0.01f * tz);
+    base[0] = s_base[2][0]; base[1] = s_base[2][1]; base[2] = s_base[2][2];
+    const yw Vtemp = voronoise_staged(s_temp, base, 0.005f * tx, 0.0005f * ty, 0.005f * tz);
+    base[0] = s_base[3][0]; base[1] = s_base[3][1]; base[2] = s_base[3][2];
+    const yw Vcave = voronoise_staged(s_cave, base, 0.06f * tx, 0.035f * ty, 0.06f * tz);
+    __syncthreads();
+    const yw Vdens = s_density[lx * 8 + lz];
+
+    const uint32_t data = open_world_decide(gx, gy, gz, Vmacro, Vdens, Vtemp, Vcave);
+
+    // set_data_in_chunk(pos, abs(chunk_idx), data) (:28-37) on the linear pool
+    const uint32_t slot = (uint32_t)(load.w < 0 ? -load.w : load.w);
+    pool[(uint64_t)slot * CHUNK_VOLUME + ((gx & 15u) << 8 | (gy & 15u) << 4 | (gz & 15u))] = data;
+    // :126-128
+    const int any = __syncthreads_or((data >> 24) != MAT_AIR || load.w < 0);
+    if (tid == 0 && any) load_results[blockIdx.x / 8] = slot;
+}
+
+// ---------------------------------------------------------------------------------------------
+// control.glsl
+struct f2 {
+    float x, y;
+};
+__device__ __forceinline__ f2 operator+(f2 a, f2 b) { return f2{a.x + b.x, a.y + b.y}; }
+__device__ __forceinline__ f2 operator-(f2 a, f2 b) { return f2{a.x - b.x, a.y - b.y}; }
+__device__ __forceinline__ f2 operator*(float s, f2 a) { return f2{s * a.x, s * a.y}; }
+__device__ __forceinline__ float dot2(f2 a, f2 b) { return a.x * b.x + a.y * b.y; }
+__device__ __forceinline__ float len2(f2 a) { return sqrtf(dot2(a, a)); }
+
+// control.glsl:74-78
+__device__ __forceinline__ f3 hash23(f2 p, uint32_t seed) {
+    uint32_t x = (uint32_t)f2i(p.x), y = (uint32_t)f2i(p.y), z = seed;
+    pcg3d(x, y, z);
+    return f3{(float)(x & 0xFF) / 256.0f, (float)(y & 0xFF) / 256.0f, (float)(z & 0xFF) / 256.0f};
+}
+
+struct VoronoiResult {
+    f2 edge_dir;
+    float height, nearest_height, edge_distance;
+};
+
+// control.glsl:87-147
+__device__ VoronoiResult voronoi_edge_dist(f2 x, uint32_t seed) {
+    const f2 ip{floorf(x.x), floorf(x.y)};
+    const f2 fp{gfract(x.x), gfract(x.y)};
+    f2 mr{0.0f, 0.0f};
+    float h = 0.0f;
+    float md = 8.0f;
+    for (int j = -1; j <= 1; j++)
+        for (int i = -1; i <= 1; i++) {
+            const f2 g{(float)i, (float)j};
+            f2 coords = ip + g;
+            coords.x = fabsf(coords.x);
+            const f3 o = hash23(coords, seed);
+            const f2 r = g + f2{o.x, o.y} - fp;
+            const float d = dot2(r, r);
+            if (d < md) {
+                md = d;
+                mr = r;
+                h = o.z;
+            }
+        }
+    const f2 mg{gstep(.5f, fp.x) - 1.f, gstep(.5f, fp.y) - 1.f};
+    md = 8.0f;
+    float mh = h;
+    f2 max_edge_dir{0.0f, 0.0f};
+    for (int j = -1; j <= 2; j++)
+        for (int i = -1; i <= 2; i++) {
+            const f2 g = mg + f2{(float)i, (float)j};
+            f2 coords = ip + g;
+            coords.x = fabsf(coords.x);
+            const f3 o = hash23(coords, seed);
+            const f2 r = g + f2{o.x, o.y} - fp;
+            const f2 dm = mr - r;
+            if (dot2(dm, dm) > 0.00001f) {
+                const f2 rm = r - mr;
+                const float l = len2(rm);
+                const f2 edge_dir{rm.x / l, rm.y / l};
+                const float d = dot2(0.5f * (mr + r), edge_dir);
+                if (d < md) {
+                    md = d;
+                    mh = o.z;
+                    max_edge_dir = edge_dir;
+                }
+            }
+        }
+    return VoronoiResult{max_edge_dir, h, mh, md};
+}
+
+__device__ __forceinline__ float gsmoothstep(float e0, float e1, float x) {
+    const float t = gclamp((x - e0) / (e1 - e0), 0.0f, 1.0f);
+    return t * t * (3.0f - 2.0f * t);
+}
+
+// control.glsl:149-175
+__device__ f2 blurred_voronoi(f2 x, float w, uint32_t seed) {
+    const f2 n{floorf(x.x), floorf(x.y)};
+    const f2 f{gfract(x.x), gfract(x.y)};
+    f2 m{8.0f, 0.0f};
+    for (int j = -2; j <= 2; j++)
+        for (int i = -2; i <= 2; i++) {
+            const f2 g{(float)i, (float)j};
+            f2 coords = n + g;
+            coords.x = fabsf(coords.x);
+            const f3 o = hash23(coords, seed);
+            const float d = len2(g - f + f2{o.x, o.y});
+            const float height = 30.0f * o.z - 15.0f;
+            if (height < -13.0f) continue;
+            const float h = gsmoothstep(-1.0f, 1.0f, (m.x - d) / w);
+            m.x = gmix(m.x, d, h) - h * (1.0f - h) * w / (1.0f + 3.0f * w);
+            m.y = gmix(m.y, height, h) - h * (1.0f - h) * w / (1.0f + 3.0f * w);
+        }
+    return m;
+}
+
+// common.glsl:357-411, .w lane only (the value; control.glsl:223 reads gap_noise.w)
+__device__ float grad_noise_w(f3 x) {
+    const uint32_t px = f2u(floorf(x.x)), py = f2u(floorf(x.y)), pz = f2u(floorf(x.z));
+    const f3 w{gfract(x.x), gfract(x.y), gfract(x.z)};
+    const f3 u = w * w * w * (w * (w * 6.0f - mk3(15.0f, 15.0f, 15.0f)) + mk3(10.0f, 10.0f, 10.0f));
+    float v[8];
+#pragma unroll
+    for (int c = 0; c < 8; c++) {
+        // corner order a..h = (0,0,0),(1,0,0),(0,1,0),(1,1,0),(0,0,1),(1,0,1),(0,1,1),(1,1,1)
+        const uint32_t ox = c & 1, oy = (c >> 1) & 1, oz = c >> 2;
+        uint32_t hx = px + ox, hy = py + oy, hz = pz + oz;
+        pcg3d(hx, hy, hz);
+        const f3 g{(float)(hx & 0xFF) / 128.0f - 1.0f, (float)(hy & 0xFF) / 128.0f - 1.0f, (float)(hz & 0xFF) / 128.0f - 1.0f};
+        v[c] = dot3(g, w - mk3((float)ox, (float)oy, (float)oz));
+    }
+    const float va = v[0], vb = v[1], vc = v[2], vd = v[3], ve = v[4], vf = v[5], vg = v[6], vh = v[7];
+    return va + u.x * (vb - va) + u.y * (vc - va) + u.z * (ve - va) + u.x * u.y * (va - vb - vc + vd) +
+           u.y * u.z * (va - vc - ve + vg) + u.z * u.x * (va - vb - ve + vf) +
+           u.x * u.y * u.z * (-va + vb + vc - vd + ve - vf - vg + vh);
+}
+
+// control.glsl:177-181
+__device__ __forceinline__ float sdBox(f2 p, f2 b) {
+    const f2 d{fabsf(p.x) - b.x, fabsf(p.y) - b.y};
+    const f2 dm{gmax(d.x, 0.0f), gmax(d.y, 0.0f)};
+    return len2(dm) + gmin(gmax(d.x, d.y), 0.0f);
+}
+
+__device__ __forceinline__ int iabs32(int x) { return x < 0 ? (int)(0u - (uint32_t)x) : x; }
+
+// control.glsl:187-243
+__device__ uint32_t control_worldgen(uint32_t gx, uint32_t gy, uint32_t gz, uint32_t worldgen_seed) {
+    const int SPAWN_ROOM_OFFSET = 150, SPAWN_HEIGHT = 15, SPAWN_DEPTH = 15, SPAWN_WIDTH = 15;
+    const float WALL_SCALE = 0.03f, PATH_SCALE = 0.03f, GAP_SCALE = 0.06f;
+    const uint32_t WALL_SEED = worldgen_seed, PATH_SEED = worldgen_seed + 1;
+    const int sx = iabs32((int)gx - 10000), sy = (int)gy - 1800, sz = (int)gz - 10000;
+    const float tx = (float)sx, ty = (float)sy, tz = (float)sz;
+    if (sx < 12 && iabs32(sz) < 12) {
+        if (sy > 0) return MAT_AIR << 24;
+        return MAT_UNBREAKABLE << 24;
+    }
+    if (sy < -13) return MAT_AIR << 24;
+    if (sx < SPAWN_ROOM_OFFSET + SPAWN_DEPTH - 1 && sx > SPAWN_ROOM_OFFSET && sy < SPAWN_HEIGHT - 1 && sy > 0 &&
+        iabs32(sz) < SPAWN_WIDTH - 1)
+        return MAT_AIR << 24;
+    if (sx < SPAWN_ROOM_OFFSET + SPAWN_DEPTH && sx > SPAWN_ROOM_OFFSET && sy < SPAWN_HEIGHT && iabs32(sz) < SPAWN_WIDTH)
+        return MAT_UNBREAKABLE << 24;
+    if (sx > SPAWN_ROOM_OFFSET) return MAT_AIR << 24;
+    if (fabsf(tz) > 100.0f) return MAT_AIR << 24;
+    VoronoiResult wall_noise = voronoi_edge_dist(f2{WALL_SCALE * tx, WALL_SCALE * tz}, WALL_SEED);
+    wall_noise.height = 30.0f * wall_noise.height - 15.0f;
+    wall_noise.nearest_height = 30.0f * wall_noise.nearest_height - 15.0f;
+    const VoronoiResult path_noise = voronoi_edge_dist(f2{PATH_SCALE * tx, PATH_SCALE * tz}, PATH_SEED);
+    const float ps = path_noise.edge_distance / PATH_SCALE;
+    const f2 path_center{ps * path_noise.edge_dir.x + tx, ps * path_noise.edge_dir.y + tz};
+    const f2 wall_noise_at_path_center = blurred_voronoi(f2{WALL_SCALE * path_center.x, WALL_SCALE * path_center.y}, 0.5f, WALL_SEED);
+    const float gap_noise_w = grad_noise_w(mk3(GAP_SCALE * tx, 0.0f, GAP_SCALE * tz));
+    const float flattening_factor = gmin(0.025f * len2(f2{tx - (float)SPAWN_ROOM_OFFSET, tz - 0.0f}), 1.0f) *
+                                    gmin(0.07f * sdBox(f2{tx, tz}, f2{12.0f, 12.0f}), 1.0f);
+    const float adj_terrain_height = wall_noise.height * flattening_factor;
+    const float adj_path_height = wall_noise_at_path_center.y * flattening_factor;
+    if (path_noise.edge_distance < 0.1f && adj_path_height >= -13.0f) {
+        if (fabsf((float)sy - adj_path_height) < 0.5f) {
+            return MAT_UNBREAKABLE << 24;
+        } else if (ty > adj_path_height && ty < adj_path_height + 15.0f) {
+            return MAT_AIR << 24;
+        } else if (ty < adj_path_height && ty > adj_terrain_height && adj_terrain_height > -13.0f) {
+            return MAT_STONE << 24;
+        }
+    }
+    if (ty < adj_terrain_height) return MAT_STONE << 24;
+    if (wall_noise.edge_distance < 0.05f && ty < 12.0f + adj_terrain_height && wall_noise.height > wall_noise.nearest_height &&
+        gap_noise_w < 0.0f && flattening_factor > 0.2f)
+        return MAT_STONE << 24;
+    return MAT_AIR << 24;
+}
+
+__global__ void __launch_bounds__(512) k_worldgen_control(uint32_t* __restrict__ pool, const int4* __restrict__ chunk_loads,
+                                                          uint32_t* __restrict__ load_results, uint32_t seed) {
+    const uint32_t tid = threadIdx.x;
+    const int4 load = chunk_loads[blockIdx.x];
+    const uint32_t lz = tid & 7, ly = (tid >> 3) & 7, lx = tid >> 6;
+    const uint32_t gx = 8u * (uint32_t)load.x + lx, gy = 8u * (uint32_t)load.y + ly, gz = 8u * (uint32_t)load.z + lz;
+    const uint32_t data = control_worldgen(gx, gy, gz, seed);
+    const uint32_t slot = (uint32_t)(load.w < 0 ? -load.w : load.w);
+    pool[(uint64_t)slot * CHUNK_VOLUME + ((gx & 15u) << 8 | (gy & 15u) << 4 | (gz & 15u))] = data;
+    const int any = __syncthreads_or((data >> 24) != MAT_AIR || load.w < 0);
+    if (tid == 0 && any) load_results[blockIdx.x / 8] = slot;
+}
+
+// complete_worldgen.glsl:29-36
+__global__ void k_complete_worldgen(World w, uint32_t* __restrict__ table, const int4* __restrict__ chunk_loads,
+                                    const uint32_t* __restrict__ load_results, uint32_t worldgen_count) {
+    const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= worldgen_count) return;
+    const int4 l = chunk_loads[8 * gid];
+    const uint32_t px = 8u * (uint32_t)l.x, py = 8u * (uint32_t)l.y, pz = 8u * (uint32_t)l.z;
+    const uint32_t cx = (px >> 4) % w.rs[0], cy = (py >> 4) % w.rs[1], cz = (pz >> 4) % w.rs[2];
+    table[((uint64_t)cx * w.rs[1] + cy) * w.rs[2] + cz] = load_results[gid];
+}
+
+// write_voxels.glsl:40-45
+__global__ void k_write_voxels(World w, const uint4* __restrict__ writes, uint32_t n) {
+    const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= n) return;
+    const uint4 wr = writes[gid];
+    w.pool[voxel_index(w, wr.x, wr.y, wr.z)] = wr.w;
+}
+
+// unload_chunks.glsl:19-26; the reference launches floor(rs/16) 16x16 workgroups per axis.
+__global__ void k_unload_slab(World w, uint32_t* __restrict__ table, int32_t unload_index, uint32_t comp, uint32_t n1, uint32_t n2) {
+    const uint32_t g1 = blockIdx.x * blockDim.x + threadIdx.x, g2 = blockIdx.y * blockDim.y + threadIdx.y;
+    if (g1 >= n1 || g2 >= n2) return;
+    uint32_t c[3];
+    c[comp] = (uint32_t)(unload_index % (int32_t)w.rs[comp]);
+    c[(comp + 1) % 3] = g1;
+    c[(comp + 2) % 3] = g2;
+    table[((uint64_t)c[0] * w.rs[1] + c[1]) * w.rs[2] + c[2]] = 0;
+}
+
+__global__ void k_fill(uint32_t* __restrict__ dst, uint32_t value, uint64_t n) {
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) dst[i] = value;
+}
+
+// Order-independent checksum over every voxel of every in-window chunk with a pool slot >= 2.
+__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
+    z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ULL;
+    z = (z ^ (z >> 27)) * 0x94d049bb133111ebULL;
+    return z ^ (z >> 31);
+}
+__global__ void __launch_bounds__(256) k_checksum(World w, unsigned long long* out) {
+    const uint32_t n_chunks = w.rs[0] * w.rs[1] * w.rs[2];
+    unsigned long long acc = 0;
+    for (uint32_t c = blockIdx.x; c < n_chunks; c += gridDim.x) {
+        const uint32_t rz = c % w.rs[2], ry = (c / w.rs[2]) % w.rs[1], rx = c / (w.rs[2] * w.rs[1]);
+        // global chunk coordinate of table cell (rx,ry,rz) inside the window
+        uint32_t gc[3];
+        const uint32_t r[3] = {rx, ry, rz};
+        for (int a = 0; a < 3; a++) gc[a] = w.sp[a] + ((r[a] + w.rs[a] - (w.sp[a] % w.rs[a])) % w.rs[a]);
+        const uint32_t slot = w.table[c];
+        if (slot < 2) continue;
+        for (uint32_t i = threadIdx.x; i < CHUNK_VOLUME; i += blockDim.x) {
+            const uint32_t v = w.pool[(uint64_t)slot * CHUNK_VOLUME + i];
+            const unsigned long long px = 16ull * gc[0] + (i >> 8), py = 16ull * gc[1] + ((i >> 4) & 15), pz = 16ull * gc[2] + (i & 15);
+            acc += mix64(((px << 42) ^ (py << 21) ^ pz) * 0x9E3779B97F4A7C15ULL + v);
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xFFFFFFFFu, acc, o);
+    if ((threadIdx.x & 31) == 0 && acc) atomicAdd(out, acc);
+}
+
+cudaError_t launch_worldgen(const World& w, const int32_t* chunk_loads, uint32_t n_workgroups, uint32_t* load_results, int map,
+                            uint32_t seed, cudaStream_t st) {
+    if (n_workgroups == 0) return cudaSuccess;
+    if (map == 0)
+        k_worldgen_open<<<n_workgroups, 512, 0, st>>>(w.pool, reinterpret_cast<const int4*>(chunk_loads), load_results);
+    else
+        k_worldgen_control<<<n_workgroups, 512, 0, st>>>(w.pool, reinterpret_cast<const int4*>(chunk_loads), load_results, seed);
+    return cudaGetLastError();
+}
+cudaError_t launch_complete_worldgen(const World& w, uint32_t* table, const int32_t* chunk_loads, const uint32_t* load_results,
+                                     uint32_t worldgen_count, cudaStream_t st) {
+    if (worldgen_count == 0) return cudaSuccess;
+    k_complete_worldgen<<<(worldgen_count + 255) / 256, 256, 0, st>>>(w, table, reinterpret_cast<const int4*>(chunk_loads),
+                                                                      load_results, worldgen_count);
+    return cudaGetLastError();
+}
+cudaError_t launch_write_voxels(const World& w, const uint32_t* writes, uint32_t n, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    k_write_voxels<<<(n + 255) / 256, 256, 0, st>>>(w, reinterpret_cast<const uint4*>(writes), n);
+    return cudaGetLastError();
+}
+cudaError_t launch_unload(const World& w, uint32_t* table, int32_t unload_index, uint32_t comp, cudaStream_t st) {
+    const uint32_t n1 = (w.rs[(comp + 1) % 3] / 16) * 16, n2 = (w.rs[(comp + 2) % 3] / 16) * 16;
+    if (n1 == 0 || n2 == 0) return cudaSuccess;
+    dim3 block(16, 16), grid(n1 / 16, n2 / 16);
+    k_unload_slab<<<grid, block, 0, st>>>(w, table, unload_index, comp, n1, n2);
+    return cudaGetLastError();
+}
+cudaError_t launch_fill(uint32_t* dst, uint32_t value, uint64_t n, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    uint64_t blocks = (n + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    k_fill<<<(uint32_t)blocks, 256, 0, st>>>(dst, value, n);
+    return cudaGetLastError();
+}
+cudaError_t launch_checksum(const World& w, unsigned long long* out, cudaStream_t st) {
+    cudaError_t e = cudaMemsetAsync(out, 0, sizeof(unsigned long long), st);
+    if (e != cudaSuccess) return e;
+    k_checksum<<<148 * 8, 256, 0, st>>>(w, out);
+    return cudaGetLastError();
+}
+
+}  // namespace vxb

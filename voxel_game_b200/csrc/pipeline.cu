@@ -1,0 +1,952 @@
+// Host side of the compute pass and of the ray pass + the C ABI of include/voxelb200.h.
+// Mirrors VoxelComputePipeline (src/voxel_sim_manager.rs) method for method; the Vulkan command
+// buffer / descriptor-set plumbing becomes launches on one CUDA stream. Rust is not available in
+// the build image, so this is C++ (see INTEGRATION.md for the Rust-side binding).
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "host_queues.h"
+#include "vxb_device.cuh"
+#include "vxb_kernels.h"
+
+namespace vxb {
+
+static thread_local std::string g_create_error;
+
+static_assert(sizeof(vxb_projectile) == 112, "Projectile is 112 bytes (common.glsl:8-25)");
+static_assert(sizeof(vxb_player) == 128, "Player is 128 bytes (common.glsl:27-38)");
+static_assert(sizeof(vxb_collision) == 16, "Collision is 16 bytes (common.glsl:40-45)");
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    cudaError_t alloc(size_t count) {
+        n = count;
+        return cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T));
+    }
+    cudaError_t ensure(size_t count) {
+        if (count <= n && p) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        return alloc(count);
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        n = 0;
+    }
+};
+template <typename T>
+struct PinBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    cudaError_t alloc(size_t count) {
+        n = count;
+        return cudaMallocHost(&p, std::max<size_t>(count, 1) * sizeof(T));
+    }
+    cudaError_t ensure(size_t count) {
+        if (count <= n && p) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        return alloc(count);
+    }
+    void release() {
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        n = 0;
+    }
+};
+
+}  // namespace vxb
+
+using namespace vxb;
+
+struct vxb_ctx {
+    vxb_settings s;
+    int device = 0;
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t stream = nullptr;
+    std::string error;
+
+    // device state (D1, D2 of SURVEY §8a)
+    DevBuf<uint32_t> table, pool;
+    DevBuf<vxb_projectile> projectiles;
+    DevBuf<vxb_player> players;
+    DevBuf<vxb_collision> collisions;
+    DevBuf<uint32_t> collision_count;
+    DevBuf<int32_t> worldgen_updates;   // ivec4 per 8^3 workgroup
+    DevBuf<uint32_t> worldgen_results;  // one per chunk
+    DevBuf<uint32_t> chunk_updates;     // uvec4 per chunk
+    DevBuf<uint32_t> update_flags;      // chunk_updates[].w, kept separately (4 B instead of 16 B read-back)
+    DevBuf<uint32_t> voxel_writes;      // uvec4
+    DevBuf<unsigned long long> scalars;  // [0] ray iteration total, [1] checksum
+    // resident update list
+    DevBuf<uint32_t> res_list, res_flags;
+    uint32_t res_n = 0;
+    // rays
+    DevBuf<float> ray_pos, ray_normal, ray_ldist, ray_dist, ray_in_pos, ray_in_dir, raster_depth;
+    DevBuf<uint32_t> ray_voxel, ray_leaving, ray_count;
+    DevBuf<vxb_player> cams;
+    uint64_t n_rays = 0;
+
+    // pinned staging
+    PinBuf<vxb_projectile> h_projectiles;
+    PinBuf<vxb_player> h_players;
+    PinBuf<vxb_collision> h_collisions;
+    PinBuf<uint32_t> h_collision_count;
+    PinBuf<int32_t> h_worldgen_updates;
+    PinBuf<uint32_t> h_worldgen_results;
+    PinBuf<uint32_t> h_chunk_updates;
+    PinBuf<uint32_t> h_update_flags;
+    PinBuf<uint32_t> h_voxel_writes;
+
+    // host bookkeeping (voxel_sim_manager.rs:105-126)
+    std::vector<uint32_t> cpu_chunks_copy;  // (x*ry + y)*rz + z
+    std::vector<uint32_t> available_chunks;
+    int slice_to_unload = -1;  // Direction or -1
+    QueueMapForced worldgen_update_queue;
+    std::unordered_set<Key3, Key3Hash> oob_worldgens;
+    size_t last_worldgen_count = 0;
+    QueueSet4 voxel_write_queue;
+    VoxelUpdateQueue chunk_update_queue;
+    std::vector<int32_t> last_update_priorities;
+    size_t last_update_count = 0;
+    uint32_t upload_projectile_count = 0, upload_player_count = 0;
+    uint32_t last_counts[3] = {0, 0, 0};
+    uint32_t last_start_pos[3] = {0, 0, 0};
+    bool results_pending = false;  // flags / worldgen_results D2H enqueued by the last compute
+    int update_variant = 0;
+
+    World world(const uint32_t start_pos[3]) const {
+        World w;
+        w.table = table.p;
+        w.pool = pool.p;
+        for (int i = 0; i < 3; i++) {
+            w.rs[i] = s.render_size[i];
+            w.sp[i] = start_pos[i];
+        }
+        return w;
+    }
+    size_t table_index(const uint32_t pos[3]) const {
+        return ((size_t)(pos[0] % s.render_size[0]) * s.render_size[1] + (pos[1] % s.render_size[1])) * s.render_size[2] +
+               (pos[2] % s.render_size[2]);
+    }
+    uint32_t get_chunk(const uint32_t pos[3]) const { return cpu_chunks_copy[table_index(pos)]; }  // :686-689
+    void set_chunk(const uint32_t pos[3], uint32_t v) { cpu_chunks_copy[table_index(pos)] = v; }    // :691-695
+    bool is_inbounds(const uint32_t loc[3], const uint32_t start_pos[3]) const {                     // :242-251
+        for (int i = 0; i < 3; i++)
+            if (!(loc[i] >= start_pos[i] && loc[i] < start_pos[i] + s.render_size[i])) return false;
+        return true;
+    }
+};
+
+static int fail(vxb_ctx* ctx, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->error = buf; else g_create_error = buf;
+    return code;
+}
+#define VXB_CUDA(ctx, expr)                                                                        \
+    do {                                                                                           \
+        cudaError_t _e = (expr);                                                                   \
+        if (_e != cudaSuccess) return fail(ctx, VXB_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(_e)); \
+    } while (0)
+#define VXB_REQUIRE(ctx, cond, msg)                                  \
+    do {                                                             \
+        if (!(cond)) return fail(ctx, VXB_ERR_INVALID, "%s", msg);   \
+    } while (0)
+
+static void free_ctx(vxb_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    c->table.release(); c->pool.release(); c->projectiles.release(); c->players.release(); c->collisions.release();
+    c->collision_count.release(); c->worldgen_updates.release(); c->worldgen_results.release(); c->chunk_updates.release();
+    c->update_flags.release(); c->voxel_writes.release(); c->scalars.release(); c->res_list.release(); c->res_flags.release();
+    c->ray_pos.release(); c->ray_normal.release(); c->ray_ldist.release(); c->ray_dist.release(); c->ray_in_pos.release();
+    c->ray_in_dir.release(); c->raster_depth.release(); c->ray_voxel.release(); c->ray_leaving.release(); c->ray_count.release();
+    c->cams.release();
+    c->h_projectiles.release(); c->h_players.release(); c->h_collisions.release(); c->h_collision_count.release();
+    c->h_worldgen_updates.release(); c->h_worldgen_results.release(); c->h_chunk_updates.release(); c->h_update_flags.release();
+    c->h_voxel_writes.release();
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    delete c;
+}
+
+#pragma GCC visibility push(default)
+extern "C" {
+
+const char* vxb_last_error(const vxb_ctx* ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
+
+int vxb_create(const vxb_settings* settings, int device, vxb_ctx** out) {
+    if (!settings || !out) return fail(nullptr, VXB_ERR_INVALID, "vxb_create: null argument");
+    *out = nullptr;
+    vxb_settings s = *settings;
+    if (s.max_projectiles == 0) s.max_projectiles = 1024;
+    if (s.max_players == 0) s.max_players = 1024;
+    if (s.max_voxel_writes == 0) s.max_voxel_writes = 1024;
+    if (s.max_collisions == 0) s.max_collisions = 1024;
+    if (s.max_worldgen_rate == 0) s.max_worldgen_rate = 1024;
+    if (s.max_update_rate == 0) s.max_update_rate = 1024;
+    for (int i = 0; i < 3; i++)
+        if (s.render_size[i] == 0) return fail(nullptr, VXB_ERR_INVALID, "vxb_create: render_size must be > 0 on every axis");
+    if (s.max_loaded_chunks < 2) return fail(nullptr, VXB_ERR_INVALID, "vxb_create: max_loaded_chunks must be >= 2 (sentinel slots)");
+    if (s.world_gen > 1) return fail(nullptr, VXB_ERR_INVALID, "vxb_create: world_gen must be 0 (Normal) or 1 (Control)");
+    if ((uint64_t)s.max_loaded_chunks * CHUNK_VOLUME >= (1ull << 40))
+        return fail(nullptr, VXB_ERR_INVALID, "vxb_create: voxel pool too large");
+
+    int n_dev = 0;
+    cudaError_t e = cudaGetDeviceCount(&n_dev);
+    if (e != cudaSuccess || n_dev == 0)
+        return fail(nullptr, VXB_ERR_CUDA, "vxb_create: no CUDA device (%s); there is no CPU fallback", cudaGetErrorString(e));
+    if (device < 0 || device >= n_dev) return fail(nullptr, VXB_ERR_INVALID, "vxb_create: device %d out of range (%d devices)", device, n_dev);
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return fail(nullptr, VXB_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+
+    vxb_ctx* c = new vxb_ctx();
+    c->s = s;
+    c->device = device;
+    const size_t n_table = (size_t)s.render_size[0] * s.render_size[1] * s.render_size[2];
+    const size_t n_wg_chunks = (s.max_worldgen_rate + 7) / 8 + 1;
+#define TRY(expr)                                                                                   \
+    if ((e = (expr)) != cudaSuccess) {                                                              \
+        int rc = fail(nullptr, VXB_ERR_CUDA, "vxb_create: %s: %s", #expr, cudaGetErrorString(e));   \
+        free_ctx(c);                                                                                \
+        return rc;                                                                                  \
+    }
+    TRY(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+    c->stream = c->own_stream;
+    TRY(c->table.alloc(n_table));
+    TRY(c->pool.alloc((size_t)s.max_loaded_chunks * CHUNK_VOLUME));
+    TRY(c->projectiles.alloc(s.max_projectiles));
+    TRY(c->players.alloc(s.max_players));
+    TRY(c->collisions.alloc(s.max_collisions));
+    TRY(c->collision_count.alloc(1));
+    TRY(c->worldgen_updates.alloc((size_t)(s.max_worldgen_rate + 8) * 4));
+    TRY(c->worldgen_results.alloc(n_wg_chunks));
+    TRY(c->chunk_updates.alloc((size_t)s.max_update_rate * 4));
+    TRY(c->update_flags.alloc(s.max_update_rate));
+    TRY(c->voxel_writes.alloc((size_t)s.max_voxel_writes * 4));
+    TRY(c->scalars.alloc(2));
+    TRY(c->h_projectiles.alloc(s.max_projectiles));
+    TRY(c->h_players.alloc(s.max_players));
+    TRY(c->h_collisions.alloc(s.max_collisions));
+    TRY(c->h_collision_count.alloc(1));
+    TRY(c->h_worldgen_updates.alloc((size_t)(s.max_worldgen_rate + 8) * 4));
+    TRY(c->h_worldgen_results.alloc(n_wg_chunks));
+    TRY(c->h_chunk_updates.alloc((size_t)s.max_update_rate * 4));
+    TRY(c->h_update_flags.alloc(s.max_update_rate));
+    TRY(c->h_voxel_writes.alloc((size_t)s.max_voxel_writes * 4));
+    // empty_chunk_grid (:129-155): host mirror all 0; the device image is zeroed too (the reference
+    // leaves it undefined). empty_voxels (:157-240): slot 0 = Unloaded, slot 1 = UnloadedAir.
+    TRY(cudaMemsetAsync(c->table.p, 0, n_table * sizeof(uint32_t), c->stream));
+    TRY(launch_fill(c->pool.p, VOX_OOB, CHUNK_VOLUME, c->stream));
+    TRY(launch_fill(c->pool.p + CHUNK_VOLUME, VOX_AIR_OOB, CHUNK_VOLUME, c->stream));
+    TRY(cudaMemsetAsync(c->scalars.p, 0, 2 * sizeof(unsigned long long), c->stream));
+    TRY(cudaMemsetAsync(c->collision_count.p, 0, sizeof(uint32_t), c->stream));
+    TRY(cudaStreamSynchronize(c->stream));
+#undef TRY
+    c->cpu_chunks_copy.assign(n_table, 0);
+    c->available_chunks.reserve(s.max_loaded_chunks);
+    for (uint32_t i = 2; i < s.max_loaded_chunks; i++) c->available_chunks.push_back(i);  // :274
+    for (size_t i = 0; i < c->h_worldgen_results.n; i++) c->h_worldgen_results.p[i] = 1;     // :495
+    *out = c;
+    return VXB_OK;
+}
+
+void vxb_destroy(vxb_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    free_ctx(ctx);
+}
+
+int vxb_set_stream(vxb_ctx* ctx, void* cuda_stream) {
+    if (!ctx) return VXB_ERR_INVALID;
+    VXB_CUDA(ctx, cudaSetDevice(ctx->device));
+    VXB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+    return VXB_OK;
+}
+
+int vxb_synchronize(vxb_ctx* ctx) {
+    if (!ctx) return VXB_ERR_INVALID;
+    VXB_CUDA(ctx, cudaSetDevice(ctx->device));
+    VXB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return VXB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// host queue pushes
+
+int vxb_queue_voxel_write(vxb_ctx* ctx, const uint32_t write[4]) {  // :658-660
+    if (!ctx || !write) return VXB_ERR_INVALID;
+    ctx->voxel_write_queue.push(Key4{{write[0], write[1], write[2], write[3]}});
+    return VXB_OK;
+}
+
+static void queue_chunk_update_impl(vxb_ctx* ctx, const uint32_t queued[3]) {  // :662-671 (SUB_CHUNK_COUNT == 1)
+    const uint32_t chunk_idx = ctx->get_chunk(queued);
+    if (chunk_idx == 0) {
+        ctx->worldgen_update_queue.push(Key3{{queued[0], queued[1], queued[2]}}, false);
+    } else if (chunk_idx != 1) {
+        ctx->chunk_update_queue.push_all(Key3{{queued[0], queued[1], queued[2]}});
+    }
+}
+
+int vxb_queue_chunk_update(vxb_ctx* ctx, const uint32_t chunk[3]) {
+    if (!ctx || !chunk) return VXB_ERR_INVALID;
+    queue_chunk_update_impl(ctx, chunk);
+    return VXB_OK;
+}
+
+int vxb_queue_update_from_world_pos(vxb_ctx* ctx, const float pos[3]) {  // :673-684
+    if (!ctx || !pos) return VXB_ERR_INVALID;
+    uint32_t loc[3];
+    for (int i = 0; i < 3; i++) {
+        // `queued[i].floor() as usize * SUB_CHUNK_COUNT / CHUNK_SIZE` — Rust `as` saturates, NaN -> 0
+        float f = std::floor(pos[i]);
+        uint64_t u = (f != f || f <= 0.0f) ? 0ull : (f >= 18446744073709551615.0f ? ~0ull : (uint64_t)f);
+        loc[i] = (uint32_t)(u / CHUNK_SIZE);
+    }
+    queue_chunk_update_impl(ctx, loc);
+    return VXB_OK;
+}
+
+int vxb_ensure_chunk_loaded(vxb_ctx* ctx, const uint32_t chunk[3]) {  // :1201-1206
+    if (!ctx || !chunk) return VXB_ERR_INVALID;
+    if (ctx->get_chunk(chunk) == 0) ctx->worldgen_update_queue.push(Key3{{chunk[0], chunk[1], chunk[2]}}, false);
+    return VXB_OK;
+}
+
+int vxb_queue_worldgen(vxb_ctx* ctx, const uint32_t chunk[3], int forced) {
+    if (!ctx || !chunk) return VXB_ERR_INVALID;
+    ctx->worldgen_update_queue.push(Key3{{chunk[0], chunk[1], chunk[2]}}, forced != 0);
+    return VXB_OK;
+}
+
+int vxb_move_start_pos(vxb_ctx* ctx, uint32_t start_pos[3], int direction) {  // :697-737
+    if (!ctx || !start_pos) return VXB_ERR_INVALID;
+    VXB_REQUIRE(ctx, direction >= 0 && direction < 6, "vxb_move_start_pos: direction must be 0..5");
+    const int comp = direction / 2;
+    const bool positive = (direction % 2) == 0;
+    if (!positive && start_pos[comp] == 0) return fail(ctx, VXB_ERR_INVALID, "vxb_move_start_pos: start_pos underflow");
+    if (positive && start_pos[comp] == 0xFFFFFFFFu) return fail(ctx, VXB_ERR_INVALID, "vxb_move_start_pos: start_pos overflow");
+    start_pos[comp] = positive ? start_pos[comp] + 1 : start_pos[comp] - 1;  // checked_add_signed(..).unwrap()
+    const uint32_t* rs = ctx->s.render_size;
+    const uint32_t load_idx = positive ? rs[comp] - 1 : 0;
+    const int c1 = (comp + 1) % 3, c2 = (comp + 2) % 3;
+    for (uint32_t y_i = 0; y_i < rs[c1]; y_i++) {
+        for (uint32_t z_i = 0; z_i < rs[c2]; z_i++) {
+            uint32_t loc[3] = {start_pos[0], start_pos[1], start_pos[2]};
+            loc[comp] += load_idx;
+            loc[c1] += y_i;
+            loc[c2] += z_i;
+            const uint32_t cur = ctx->get_chunk(loc);
+            if (cur > 1) ctx->available_chunks.push_back(cur);
+            ctx->set_chunk(loc, 0);
+            Key3 k{{loc[0], loc[1], loc[2]}};
+            auto it = ctx->oob_worldgens.find(k);
+            if (it != ctx->oob_worldgens.end()) {
+                ctx->oob_worldgens.erase(it);
+                ctx->worldgen_update_queue.push(k, false);
+            }
+        }
+    }
+    ctx->slice_to_unload = direction;
+    return VXB_OK;
+}
+
+uint64_t vxb_update_count(const vxb_ctx* ctx) { return ctx ? ctx->chunk_update_queue.len() : 0; }       // :818-820
+uint64_t vxb_worldgen_count(const vxb_ctx* ctx) { return ctx ? ctx->worldgen_update_queue.len() : 0; }  // :822-824
+uint64_t vxb_worldgen_capacity(const vxb_ctx* ctx) { return ctx ? ctx->available_chunks.size() : 0; }   // :826-828
+int vxb_queue_set_idx(const vxb_ctx* ctx, uint32_t phase_out[3]) {
+    if (!ctx || !phase_out) return VXB_ERR_INVALID;
+    ctx->chunk_update_queue.queue_set_idx(phase_out);
+    return VXB_OK;
+}
+uint32_t vxb_get_chunk(const vxb_ctx* ctx, const uint32_t chunk[3]) { return (ctx && chunk) ? ctx->get_chunk(chunk) : 0; }
+int vxb_last_dispatch_counts(const vxb_ctx* ctx, uint32_t counts_out[3]) {
+    if (!ctx || !counts_out) return VXB_ERR_INVALID;
+    for (int i = 0; i < 3; i++) counts_out[i] = ctx->last_counts[i];
+    return VXB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// the three list loaders of compute()
+
+static size_t load_worldgen_updates(vxb_ctx* c, const uint32_t start_pos[3]) {  // :1140-1199
+    size_t worldgen_update_count = 0;
+    if (!c->worldgen_update_queue.is_empty() && !c->available_chunks.empty()) {
+        Key3 loc;
+        bool forced;
+        while (c->worldgen_update_queue.pop(loc, forced)) {
+            if (c->is_inbounds(loc.v, start_pos)) {
+                if (c->available_chunks.empty()) {
+                    c->worldgen_update_queue.push(loc, forced);
+                    break;
+                }
+                const uint32_t available_chunk_idx = c->available_chunks.back();
+                c->available_chunks.pop_back();
+                c->h_worldgen_results.p[worldgen_update_count / 8] = 1;
+                for (uint32_t i = 0; i < 2; i++)
+                    for (uint32_t j = 0; j < 2; j++)
+                        for (uint32_t k = 0; k < 2; k++) {
+                            int32_t* e = &c->h_worldgen_updates.p[worldgen_update_count * 4];
+                            e[0] = (int32_t)(2 * loc.v[0] + i);
+                            e[1] = (int32_t)(2 * loc.v[1] + j);
+                            e[2] = (int32_t)(2 * loc.v[2] + k);
+                            e[3] = (int32_t)available_chunk_idx * (forced ? -1 : 1);
+                            worldgen_update_count++;
+                        }
+                c->set_chunk(loc.v, available_chunk_idx);
+                c->chunk_update_queue.push_all(loc);
+                if (worldgen_update_count >= c->s.max_worldgen_rate) break;
+            } else {
+                c->oob_worldgens.insert(loc);
+            }
+        }
+    }
+    c->last_worldgen_count = worldgen_update_count / 8;
+    return worldgen_update_count;
+}
+
+static size_t load_voxel_writes(vxb_ctx* c, const uint32_t start_pos[3]) {  // :1055-1138
+    size_t voxel_write_count = 0;
+    std::vector<Key4> delayed_writes;
+    Key4 vw;
+    while (c->voxel_write_queue.pop(vw)) {
+        const uint32_t chunk[3] = {vw.v[0] / CHUNK_SIZE, vw.v[1] / CHUNK_SIZE, vw.v[2] / CHUNK_SIZE};
+        if (c->is_inbounds(chunk, start_pos)) {
+            const uint32_t voxel_chunk = c->get_chunk(chunk);
+            if (voxel_chunk > 1) {
+                memcpy(&c->h_voxel_writes.p[voxel_write_count * 4], vw.v, 16);
+                voxel_write_count++;
+                int lo[3], hi[3];
+                for (int a = 0; a < 3; a++) {
+                    const uint32_t pic = vw.v[a] % CHUNK_SIZE;
+                    lo[a] = pic == 0 ? -1 : 0;
+                    hi[a] = pic + 1 == CHUNK_SIZE ? 1 : 0;
+                }
+                for (int ox = lo[0]; ox <= hi[0]; ox++)
+                    for (int oy = lo[1]; oy <= hi[1]; oy++)
+                        for (int oz = lo[2]; oz <= hi[2]; oz++)
+                            c->chunk_update_queue.push_with_priority(
+                                Key3{{chunk[0] + (uint32_t)ox, chunk[1] + (uint32_t)oy, chunk[2] + (uint32_t)oz}}, 1);
+                if (voxel_write_count >= c->s.max_voxel_writes) break;
+            } else if (voxel_chunk == 1) {
+                c->worldgen_update_queue.push(Key3{{chunk[0], chunk[1], chunk[2]}}, true);
+                delayed_writes.push_back(vw);
+            }
+        }
+    }
+    c->voxel_write_queue.extend(delayed_writes);
+    return voxel_write_count;
+}
+
+static size_t load_chunk_updates(vxb_ctx* c, const uint32_t start_pos[3]) {  // :1010-1053
+    size_t chunk_update_count = 0;
+    c->last_update_priorities.clear();
+    if (!c->chunk_update_queue.is_empty()) {
+        c->chunk_update_queue.swap_queue_set();
+        Key3 loc;
+        int32_t prio;
+        while (c->chunk_update_queue.pop(loc, prio)) {
+            if (c->is_inbounds(loc.v, start_pos)) {
+                const uint32_t chunk = c->get_chunk(loc.v);
+                if (chunk == 0) {
+                    c->worldgen_update_queue.push(loc, false);
+                } else if (chunk != 1) {
+                    uint32_t* e = &c->h_chunk_updates.p[chunk_update_count * 4];
+                    e[0] = loc.v[0]; e[1] = loc.v[1]; e[2] = loc.v[2]; e[3] = 0;
+                    c->last_update_priorities.push_back(prio);
+                    chunk_update_count++;
+                    if (chunk_update_count >= c->s.max_update_rate) break;
+                }
+            }
+        }
+    }
+    c->last_update_count = chunk_update_count;
+    return chunk_update_count;
+}
+
+int vxb_compute(vxb_ctx* c, const uint32_t start_pos[3], const vxb_projectile* projectiles, uint32_t n_projectiles,
+                const vxb_player* players, uint32_t n_players) {
+    if (!c || !start_pos) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, n_projectiles == 0 || projectiles, "vxb_compute: projectiles is NULL");
+    VXB_REQUIRE(c, n_players == 0 || players, "vxb_compute: players is NULL");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    // the pinned staging lists are reused every tick: the previous tick's copies must have landed
+    VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    cudaStream_t st = c->stream;
+    // :843-869 (the reference clamps to its buffer size of 1024; here to the configured capacity)
+    c->upload_projectile_count = std::min(n_projectiles, c->s.max_projectiles);
+    c->upload_player_count = std::min(n_players, c->s.max_players);
+    if (c->upload_projectile_count) {
+        memcpy(c->h_projectiles.p, projectiles, (size_t)c->upload_projectile_count * sizeof(vxb_projectile));
+        VXB_CUDA(c, cudaMemcpyAsync(c->projectiles.p, c->h_projectiles.p, (size_t)c->upload_projectile_count * sizeof(vxb_projectile),
+                                    cudaMemcpyHostToDevice, st));
+    }
+    if (c->upload_player_count) {
+        memcpy(c->h_players.p, players, (size_t)c->upload_player_count * sizeof(vxb_player));
+        VXB_CUDA(c, cudaMemcpyAsync(c->players.p, c->h_players.p, (size_t)c->upload_player_count * sizeof(vxb_player),
+                                    cudaMemcpyHostToDevice, st));
+    }
+    VXB_CUDA(c, cudaMemsetAsync(c->collisions.p, 0, (size_t)c->s.max_collisions * sizeof(vxb_collision), st));
+    VXB_CUDA(c, cudaMemsetAsync(c->collision_count.p, 0, sizeof(uint32_t), st));
+
+    const size_t worldgen_update_count = load_worldgen_updates(c, start_pos);  // :871
+    const size_t voxel_write_count = load_voxel_writes(c, start_pos);          // :874
+    const size_t chunk_update_count = load_chunk_updates(c, start_pos);        // :877
+    c->last_counts[0] = (uint32_t)worldgen_update_count;
+    c->last_counts[1] = (uint32_t)voxel_write_count;
+    c->last_counts[2] = (uint32_t)chunk_update_count;
+    for (int i = 0; i < 3; i++) c->last_start_pos[i] = start_pos[i];
+
+    const World w = c->world(start_pos);
+    uint32_t offset[3];
+    c->chunk_update_queue.queue_set_idx(offset);  // :911
+
+    // dispatch order of :944-1000
+    if (c->upload_projectile_count > 0)
+        VXB_CUDA(c, launch_projectiles(w, c->projectiles.p, c->upload_projectile_count, c->players.p, c->upload_player_count,
+                                       c->collisions.p, c->s.max_collisions, c->collision_count.p, c->s.delta_time, st));
+    if (c->upload_player_count > 0) VXB_CUDA(c, launch_players(w, c->players.p, c->upload_player_count, c->s.delta_time, st));
+    if (c->slice_to_unload >= 0) {
+        const int comp = c->slice_to_unload / 2;
+        const bool positive = (c->slice_to_unload % 2) == 0;
+        const int32_t unload_index = (int32_t)(positive ? start_pos[comp] + c->s.render_size[comp] - 1 : start_pos[comp]);  // :917-923
+        VXB_CUDA(c, launch_unload(w, c->table.p, unload_index, (uint32_t)comp, st));
+        c->slice_to_unload = -1;
+    }
+    if (worldgen_update_count > 0) {
+        VXB_CUDA(c, cudaMemcpyAsync(c->worldgen_updates.p, c->h_worldgen_updates.p, worldgen_update_count * 16, cudaMemcpyHostToDevice, st));
+        VXB_CUDA(c, cudaMemcpyAsync(c->worldgen_results.p, c->h_worldgen_results.p, c->last_worldgen_count * 4, cudaMemcpyHostToDevice, st));
+        VXB_CUDA(c, launch_worldgen(w, c->worldgen_updates.p, (uint32_t)worldgen_update_count, c->worldgen_results.p, (int)c->s.world_gen,
+                                    c->s.world_gen_seed, st));
+        VXB_CUDA(c, launch_complete_worldgen(w, c->table.p, c->worldgen_updates.p, c->worldgen_results.p, (uint32_t)c->last_worldgen_count, st));
+        VXB_CUDA(c, cudaMemcpyAsync(c->h_worldgen_results.p, c->worldgen_results.p, c->last_worldgen_count * 4, cudaMemcpyDeviceToHost, st));
+    }
+    if (voxel_write_count > 0) {
+        VXB_CUDA(c, cudaMemcpyAsync(c->voxel_writes.p, c->h_voxel_writes.p, voxel_write_count * 16, cudaMemcpyHostToDevice, st));
+        VXB_CUDA(c, launch_write_voxels(w, c->voxel_writes.p, (uint32_t)voxel_write_count, st));
+    }
+    if (chunk_update_count > 0) {
+        VXB_CUDA(c, cudaMemcpyAsync(c->chunk_updates.p, c->h_chunk_updates.p, chunk_update_count * 16, cudaMemcpyHostToDevice, st));
+        VXB_CUDA(c, launch_voxel_update(w, c->chunk_updates.p, (uint32_t)chunk_update_count, offset, c->update_flags.p, c->update_variant, st));
+        VXB_CUDA(c, cudaMemcpyAsync(c->h_update_flags.p, c->update_flags.p, chunk_update_count * 4, cudaMemcpyDeviceToHost, st));
+    }
+    c->results_pending = true;
+    return VXB_OK;
+}
+
+int vxb_push_updates_from_changed(vxb_ctx* c, const float (*player_positions)[3], uint32_t n_players) {  // :741-816
+    if (!c) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, n_players == 0 || player_positions, "vxb_push_updates_from_changed: player_positions is NULL");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    // The reference re-reads the mapped buffers on every call; a second call without a compute()
+    // in between would hand the same freed slots out twice, so results are consumed once here.
+    if (!c->results_pending) return VXB_OK;
+    const uint32_t* rs = c->s.render_size;
+    if (c->last_worldgen_count > 0) {
+        for (size_t i = 0; i < c->last_worldgen_count; i++) {
+            if (c->h_worldgen_results.p[i] == 1) {
+                const int32_t* lw = &c->h_worldgen_updates.p[8 * i * 4];
+                c->available_chunks.push_back((uint32_t)std::abs(lw[3]));
+                const uint32_t cp[3] = {(uint32_t)lw[0] / 2, (uint32_t)lw[1] / 2, (uint32_t)lw[2] / 2};
+                c->cpu_chunks_copy[((size_t)(cp[0] % rs[0]) * rs[1] + (cp[1] % rs[1])) * rs[2] + (cp[2] % rs[2])] = 1;
+                for (int x = -1; x <= 1; x++)
+                    for (int y = -1; y <= 1; y++)
+                        for (int z = -1; z <= 1; z++) {
+                            const uint32_t queued[3] = {(uint32_t)(lw[0] / 2 + x), (uint32_t)(lw[1] / 2 + y), (uint32_t)(lw[2] / 2 + z)};
+                            queue_chunk_update_impl(c, queued);
+                        }
+            }
+        }
+    }
+    for (size_t i = 0; i < c->last_update_count; i++) {
+        const uint32_t* ru = &c->h_chunk_updates.p[i * 4];
+        const uint32_t flags = c->h_update_flags.p[i];
+        if ((flags & 1) == 1) {
+            const float cpx = (float)(ru[0] * CHUNK_SIZE), cpy = (float)(ru[1] * CHUNK_SIZE), cpz = (float)(ru[2] * CHUNK_SIZE);
+            const int min_x = -(int)((flags >> 1) & 1), min_y = -(int)((flags >> 2) & 1), min_z = -(int)((flags >> 3) & 1);
+            const int max_x = (int)((flags >> 4) & 1), max_y = (int)((flags >> 5) & 1), max_z = (int)((flags >> 6) & 1);
+            // distance_weight does not depend on the offsets (:798-801); summed in f32 like the reference
+            float distance_weight = 0.0f;
+            for (uint32_t p = 0; p < n_players; p++) {
+                const float dx = player_positions[p][0] - cpx, dy = player_positions[p][1] - cpy, dz = player_positions[p][2] - cpz;
+                const float distance = std::sqrt(dx * dx + dy * dy + dz * dz);
+                distance_weight += 6.0f - distance;
+            }
+            // Rust `f32 as i32` saturates, NaN -> 0
+            int32_t dw;
+            if (distance_weight != distance_weight) dw = 0;
+            else if (distance_weight >= 2147483648.0f) dw = INT32_MAX;
+            else if (distance_weight <= -2147483648.0f) dw = INT32_MIN;
+            else dw = (int32_t)distance_weight;
+            // i32 arithmetic; debug builds of the reference would panic on overflow — saturate instead
+            int64_t pr64 = (int64_t)c->last_update_priorities[i] - 1 + dw;
+            const int32_t pr = (int32_t)std::max<int64_t>(INT32_MIN, std::min<int64_t>(INT32_MAX, pr64));
+            for (int xo = min_x; xo <= max_x; xo++)
+                for (int yo = min_y; yo <= max_y; yo++)
+                    for (int zo = min_z; zo <= max_z; zo++)
+                        c->chunk_update_queue.push_with_priority(Key3{{ru[0] + (uint32_t)xo, ru[1] + (uint32_t)yo, ru[2] + (uint32_t)zo}}, pr);
+        }
+    }
+    c->results_pending = false;
+    return VXB_OK;
+}
+
+static bool collision_less(const vxb_collision& a, const vxb_collision& b) {
+    if (a.id1 != b.id1) return a.id1 < b.id1;
+    return a.id2 < b.id2;
+}
+
+int vxb_download_projectiles(vxb_ctx* c, vxb_projectile* projectiles_out, vxb_collision* collisions_out, uint32_t* n_collisions,
+                             vxb_player* players_out) {  // :545-648
+    if (!c) return VXB_ERR_INVALID;
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    if (c->upload_projectile_count)
+        VXB_CUDA(c, cudaMemcpyAsync(c->h_projectiles.p, c->projectiles.p, (size_t)c->upload_projectile_count * sizeof(vxb_projectile),
+                                    cudaMemcpyDeviceToHost, st));
+    if (c->upload_player_count)
+        VXB_CUDA(c, cudaMemcpyAsync(c->h_players.p, c->players.p, (size_t)c->upload_player_count * sizeof(vxb_player),
+                                    cudaMemcpyDeviceToHost, st));
+    VXB_CUDA(c, cudaMemcpyAsync(c->h_collision_count.p, c->collision_count.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    VXB_CUDA(c, cudaStreamSynchronize(st));
+    const uint32_t n_coll = std::min(c->h_collision_count.p[0], c->s.max_collisions);
+    if (n_coll) {
+        VXB_CUDA(c, cudaMemcpyAsync(c->h_collisions.p, c->collisions.p, (size_t)n_coll * sizeof(vxb_collision), cudaMemcpyDeviceToHost, st));
+        VXB_CUDA(c, cudaStreamSynchronize(st));
+        std::sort(c->h_collisions.p, c->h_collisions.p + n_coll, collision_less);
+    }
+    for (uint32_t i = 0; i < c->upload_projectile_count; i++) {
+        const vxb_projectile& p = c->h_projectiles.p[i];
+        if (p.health == 0.0f && p.chunk_update_pos[3] == 1) {  // :558-578
+            const uint32_t chunk[3] = {p.chunk_update_pos[0] / CHUNK_SIZE, p.chunk_update_pos[1] / CHUNK_SIZE, p.chunk_update_pos[2] / CHUNK_SIZE};
+            const uint32_t chunk_idx = c->get_chunk(chunk);
+            if (chunk_idx == 0) c->worldgen_update_queue.push(Key3{{chunk[0], chunk[1], chunk[2]}}, false);
+            else if (chunk_idx != 1) c->chunk_update_queue.push_with_priority(Key3{{chunk[0], chunk[1], chunk[2]}}, 1);
+        }
+    }
+    if (projectiles_out && c->upload_projectile_count)
+        memcpy(projectiles_out, c->h_projectiles.p, (size_t)c->upload_projectile_count * sizeof(vxb_projectile));
+    if (players_out && c->upload_player_count) memcpy(players_out, c->h_players.p, (size_t)c->upload_player_count * sizeof(vxb_player));
+    if (collisions_out && n_coll) memcpy(collisions_out, c->h_collisions.p, (size_t)n_coll * sizeof(vxb_collision));
+    if (n_collisions) *n_collisions = n_coll;
+    return VXB_OK;
+}
+
+int vxb_device_ptrs(vxb_ctx* c, vxb_ptrs* out) {
+    if (!c || !out) return VXB_ERR_INVALID;
+    out->chunk_table = c->table.p;
+    out->voxel_pool = c->pool.p;
+    out->projectiles = c->projectiles.p;
+    out->players = c->players.p;
+    out->collisions = c->collisions.p;
+    out->pool_slots = c->s.max_loaded_chunks;
+    return VXB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// single dispatches on explicit lists
+
+int vxb_dispatch_worldgen(vxb_ctx* c, const uint32_t start_pos[3], const int32_t (*chunk_loads)[4], uint32_t n_workgroups, int complete,
+                          uint32_t* load_results_out) {
+    if (!c || !start_pos) return VXB_ERR_INVALID;
+    if (n_workgroups == 0) return VXB_OK;
+    VXB_REQUIRE(c, chunk_loads, "vxb_dispatch_worldgen: chunk_loads is NULL");
+    VXB_REQUIRE(c, n_workgroups % 8 == 0, "vxb_dispatch_worldgen: n_workgroups must be a multiple of 8 (8 workgroups per chunk)");
+    for (uint32_t i = 0; i < n_workgroups; i++) {
+        const uint32_t slot = (uint32_t)std::abs(chunk_loads[i][3]);
+        if (slot >= c->s.max_loaded_chunks) return fail(c, VXB_ERR_INVALID, "vxb_dispatch_worldgen: slot %u beyond max_loaded_chunks", slot);
+    }
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    const uint32_t n_chunks = n_workgroups / 8;
+    VXB_CUDA(c, c->worldgen_updates.ensure((size_t)n_workgroups * 4));
+    VXB_CUDA(c, c->worldgen_results.ensure(n_chunks));
+    VXB_CUDA(c, cudaMemcpyAsync(c->worldgen_updates.p, chunk_loads, (size_t)n_workgroups * 16, cudaMemcpyHostToDevice, st));
+    VXB_CUDA(c, launch_fill(c->worldgen_results.p, 1u, n_chunks, st));  // host pre-sets 1 (:1151-1154)
+    const World w = c->world(start_pos);
+    VXB_CUDA(c, launch_worldgen(w, c->worldgen_updates.p, n_workgroups, c->worldgen_results.p, (int)c->s.world_gen, c->s.world_gen_seed, st));
+    if (complete) VXB_CUDA(c, launch_complete_worldgen(w, c->table.p, c->worldgen_updates.p, c->worldgen_results.p, n_chunks, st));
+    if (load_results_out) {
+        VXB_CUDA(c, cudaMemcpyAsync(load_results_out, c->worldgen_results.p, (size_t)n_chunks * 4, cudaMemcpyDeviceToHost, st));
+        VXB_CUDA(c, cudaStreamSynchronize(st));
+    }
+    return VXB_OK;
+}
+
+int vxb_dispatch_voxel_update(vxb_ctx* c, const uint32_t start_pos[3], const uint32_t (*chunk_updates)[4], uint32_t n,
+                              const uint32_t offset[3], uint32_t* flags_out) {
+    if (!c || !start_pos || !offset) return VXB_ERR_INVALID;
+    if (n == 0) return VXB_OK;
+    VXB_REQUIRE(c, chunk_updates, "vxb_dispatch_voxel_update: chunk_updates is NULL");
+    VXB_REQUIRE(c, offset[0] < 2 && offset[1] < 2 && offset[2] < 2, "vxb_dispatch_voxel_update: offset must be in {0,1}^3");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    VXB_CUDA(c, c->chunk_updates.ensure((size_t)n * 4));
+    VXB_CUDA(c, c->update_flags.ensure(n));
+    VXB_CUDA(c, cudaMemcpyAsync(c->chunk_updates.p, chunk_updates, (size_t)n * 16, cudaMemcpyHostToDevice, st));
+    const World w = c->world(start_pos);
+    VXB_CUDA(c, launch_voxel_update(w, c->chunk_updates.p, n, offset, c->update_flags.p, c->update_variant, st));
+    if (flags_out) {
+        VXB_CUDA(c, cudaMemcpyAsync(flags_out, c->update_flags.p, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+        VXB_CUDA(c, cudaStreamSynchronize(st));
+    }
+    return VXB_OK;
+}
+
+int vxb_dispatch_write_voxels(vxb_ctx* c, const uint32_t start_pos[3], const uint32_t (*writes)[4], uint32_t n) {
+    if (!c || !start_pos) return VXB_ERR_INVALID;
+    if (n == 0) return VXB_OK;
+    VXB_REQUIRE(c, writes, "vxb_dispatch_write_voxels: writes is NULL");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, c->voxel_writes.ensure((size_t)n * 4));
+    VXB_CUDA(c, cudaMemcpyAsync(c->voxel_writes.p, writes, (size_t)n * 16, cudaMemcpyHostToDevice, c->stream));
+    VXB_CUDA(c, launch_write_voxels(c->world(start_pos), c->voxel_writes.p, n, c->stream));
+    return VXB_OK;
+}
+
+int vxb_dispatch_unload(vxb_ctx* c, int32_t unload_index, uint32_t unload_component) {
+    if (!c) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, unload_component < 3, "vxb_dispatch_unload: unload_component must be 0..2");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    const uint32_t zero[3] = {0, 0, 0};
+    VXB_CUDA(c, launch_unload(c->world(zero), c->table.p, unload_index, unload_component, c->stream));
+    return VXB_OK;
+}
+
+int vxb_dispatch_entities(vxb_ctx* c, const uint32_t start_pos[3], vxb_projectile* projectiles, uint32_t n_projectiles, vxb_player* players,
+                          uint32_t n_players, int run_projectiles, int run_players, vxb_collision* collisions_out, uint32_t* n_collisions) {
+    if (!c || !start_pos) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, n_projectiles == 0 || projectiles, "vxb_dispatch_entities: projectiles is NULL");
+    VXB_REQUIRE(c, n_players == 0 || players, "vxb_dispatch_entities: players is NULL");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    VXB_CUDA(c, c->projectiles.ensure(n_projectiles));
+    VXB_CUDA(c, c->players.ensure(n_players));
+    if (n_projectiles) VXB_CUDA(c, cudaMemcpyAsync(c->projectiles.p, projectiles, (size_t)n_projectiles * sizeof(vxb_projectile), cudaMemcpyHostToDevice, st));
+    if (n_players) VXB_CUDA(c, cudaMemcpyAsync(c->players.p, players, (size_t)n_players * sizeof(vxb_player), cudaMemcpyHostToDevice, st));
+    VXB_CUDA(c, cudaMemsetAsync(c->collisions.p, 0, (size_t)c->s.max_collisions * sizeof(vxb_collision), st));
+    VXB_CUDA(c, cudaMemsetAsync(c->collision_count.p, 0, sizeof(uint32_t), st));
+    const World w = c->world(start_pos);
+    if (run_projectiles && n_projectiles)
+        VXB_CUDA(c, launch_projectiles(w, c->projectiles.p, n_projectiles, c->players.p, n_players, c->collisions.p, c->s.max_collisions,
+                                       c->collision_count.p, c->s.delta_time, st));
+    if (run_players && n_players) VXB_CUDA(c, launch_players(w, c->players.p, n_players, c->s.delta_time, st));
+    if (n_projectiles) VXB_CUDA(c, cudaMemcpyAsync(projectiles, c->projectiles.p, (size_t)n_projectiles * sizeof(vxb_projectile), cudaMemcpyDeviceToHost, st));
+    if (n_players) VXB_CUDA(c, cudaMemcpyAsync(players, c->players.p, (size_t)n_players * sizeof(vxb_player), cudaMemcpyDeviceToHost, st));
+    uint32_t count = 0;
+    VXB_CUDA(c, cudaMemcpyAsync(&count, c->collision_count.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    VXB_CUDA(c, cudaStreamSynchronize(st));
+    count = std::min(count, c->s.max_collisions);
+    if (collisions_out && count) {
+        VXB_CUDA(c, cudaMemcpyAsync(collisions_out, c->collisions.p, (size_t)count * sizeof(vxb_collision), cudaMemcpyDeviceToHost, st));
+        VXB_CUDA(c, cudaStreamSynchronize(st));
+        std::sort(collisions_out, collisions_out + count, collision_less);
+    }
+    if (n_collisions) *n_collisions = count;
+    return VXB_OK;
+}
+
+int vxb_update_list_upload(vxb_ctx* c, const uint32_t (*chunk_updates)[4], uint32_t n) {
+    if (!c) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, n == 0 || chunk_updates, "vxb_update_list_upload: chunk_updates is NULL");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, c->res_list.ensure((size_t)n * 4));
+    VXB_CUDA(c, c->res_flags.ensure(n));
+    if (n) VXB_CUDA(c, cudaMemcpyAsync(c->res_list.p, chunk_updates, (size_t)n * 16, cudaMemcpyHostToDevice, c->stream));
+    c->res_n = n;
+    return VXB_OK;
+}
+
+int vxb_update_list_run(vxb_ctx* c, const uint32_t start_pos[3], const uint32_t offset[3]) {
+    if (!c || !start_pos || !offset) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, offset[0] < 2 && offset[1] < 2 && offset[2] < 2, "vxb_update_list_run: offset must be in {0,1}^3");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, launch_voxel_update(c->world(start_pos), c->res_list.p, c->res_n, offset, c->res_flags.p, c->update_variant, c->stream));
+    return VXB_OK;
+}
+
+int vxb_update_list_flags(vxb_ctx* c, uint32_t* flags_out, uint32_t n) {
+    if (!c || !flags_out) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, n <= c->res_n, "vxb_update_list_flags: n exceeds the resident list length");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    if (n) VXB_CUDA(c, cudaMemcpyAsync(flags_out, c->res_flags.p, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
+    VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VXB_OK;
+}
+
+int vxb_set_update_kernel(vxb_ctx* c, int variant) {
+    if (!c) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, variant >= 0 && variant <= 2, "vxb_set_update_kernel: variant must be 0, 1 or 2");
+    c->update_variant = variant;
+    return VXB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// rays
+
+static int ensure_ray_buffers(vxb_ctx* c, uint64_t n) {
+    VXB_CUDA(c, c->ray_pos.ensure(n * 15));
+    VXB_CUDA(c, c->ray_normal.ensure(n * 15));
+    VXB_CUDA(c, c->ray_voxel.ensure(n * 5));
+    VXB_CUDA(c, c->ray_ldist.ensure(n * 5));
+    VXB_CUDA(c, c->ray_leaving.ensure(n * 5));
+    VXB_CUDA(c, c->ray_count.ensure(n));
+    VXB_CUDA(c, c->ray_dist.ensure(n));
+    c->n_rays = n;
+    return VXB_OK;
+}
+static RayOut ray_out(vxb_ctx* c) {
+    RayOut o;
+    o.n_rays = c->n_rays;
+    o.pos = c->ray_pos.p; o.normal = c->ray_normal.p; o.voxel = c->ray_voxel.p; o.ldist = c->ray_ldist.p;
+    o.leaving = c->ray_leaving.p; o.layer_count = c->ray_count.p; o.dist = c->ray_dist.p;
+    o.total_iters = c->scalars.p;
+    return o;
+}
+
+int vxb_raymarch(vxb_ctx* c, const uint32_t start_pos[3], const vxb_player* cams, uint32_t n_views, uint32_t w, uint32_t h,
+                 const vxb_ray_caps* caps, const float* raster_depth) {
+    if (!c || !start_pos) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, cams && caps, "vxb_raymarch: cams / caps is NULL");
+    VXB_REQUIRE(c, n_views > 0 && w > 0 && h > 0, "vxb_raymarch: empty view");
+    VXB_REQUIRE(c, n_views <= 65535, "vxb_raymarch: at most 65535 views per call");
+    VXB_REQUIRE(c, caps->projectile_count <= c->projectiles.n, "vxb_raymarch: projectile_count exceeds the projectile buffer");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    const uint64_t n = (uint64_t)n_views * w * h;
+    int rc = ensure_ray_buffers(c, n);
+    if (rc) return rc;
+    VXB_CUDA(c, c->cams.ensure(n_views));
+    VXB_CUDA(c, cudaMemcpyAsync(c->cams.p, cams, (size_t)n_views * sizeof(vxb_player), cudaMemcpyHostToDevice, st));
+    const float* rd = nullptr;
+    if (raster_depth) {
+        VXB_CUDA(c, c->raster_depth.ensure(n));
+        VXB_CUDA(c, cudaMemcpyAsync(c->raster_depth.p, raster_depth, n * sizeof(float), cudaMemcpyHostToDevice, st));
+        rd = c->raster_depth.p;
+    }
+    VXB_CUDA(c, cudaMemsetAsync(c->scalars.p, 0, sizeof(unsigned long long), st));
+    VXB_CUDA(c, launch_raymarch_views(c->world(start_pos), c->cams.p, n_views, w, h, caps->primary_ray_dist, c->projectiles.p,
+                                      caps->projectile_count, rd, ray_out(c), st));
+    return VXB_OK;
+}
+
+int vxb_raymarch_rays(vxb_ctx* c, const uint32_t start_pos[3], const float (*pos)[3], const float (*dir)[3], uint64_t n, int kind,
+                      uint32_t max_iterations, uint32_t projectile_count) {
+    if (!c || !start_pos) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, n == 0 || (pos && dir), "vxb_raymarch_rays: pos / dir is NULL");
+    VXB_REQUIRE(c, kind >= 0 && kind <= 3, "vxb_raymarch_rays: kind must be 0..3");
+    VXB_REQUIRE(c, projectile_count <= c->projectiles.n, "vxb_raymarch_rays: projectile_count exceeds the projectile buffer");
+    VXB_REQUIRE(c, n < (1ull << 31) * 128ull, "vxb_raymarch_rays: too many rays");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    int rc = ensure_ray_buffers(c, n);
+    if (rc) return rc;
+    VXB_CUDA(c, c->ray_in_pos.ensure(n * 3));
+    VXB_CUDA(c, c->ray_in_dir.ensure(n * 3));
+    if (n) {
+        VXB_CUDA(c, cudaMemcpyAsync(c->ray_in_pos.p, pos, n * 12, cudaMemcpyHostToDevice, st));
+        VXB_CUDA(c, cudaMemcpyAsync(c->ray_in_dir.p, dir, n * 12, cudaMemcpyHostToDevice, st));
+    }
+    VXB_CUDA(c, cudaMemsetAsync(c->scalars.p, 0, sizeof(unsigned long long), st));
+    VXB_CUDA(c, launch_raymarch_rays(c->world(start_pos), c->ray_in_pos.p, c->ray_in_dir.p, n, kind, max_iterations, c->projectiles.p,
+                                     projectile_count, ray_out(c), st));
+    return VXB_OK;
+}
+
+int vxb_ray_results(vxb_ctx* c, vxb_ray_buffers* out) {
+    if (!c || !out) return VXB_ERR_INVALID;
+    out->n_rays = c->n_rays;
+    out->pos = c->ray_pos.p; out->normal = c->ray_normal.p; out->voxel = c->ray_voxel.p; out->ldist = c->ray_ldist.p;
+    out->leaving = c->ray_leaving.p; out->layer_count = c->ray_count.p; out->dist = c->ray_dist.p;
+    return VXB_OK;
+}
+
+int vxb_ray_download(vxb_ctx* c, float* pos, float* normal, uint32_t* voxel, float* ldist, uint32_t* leaving, uint32_t* layer_count,
+                     float* dist, uint64_t* total_iterations) {
+    if (!c) return VXB_ERR_INVALID;
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    const uint64_t n = c->n_rays;
+    if (pos) VXB_CUDA(c, cudaMemcpyAsync(pos, c->ray_pos.p, n * 15 * 4, cudaMemcpyDeviceToHost, st));
+    if (normal) VXB_CUDA(c, cudaMemcpyAsync(normal, c->ray_normal.p, n * 15 * 4, cudaMemcpyDeviceToHost, st));
+    if (voxel) VXB_CUDA(c, cudaMemcpyAsync(voxel, c->ray_voxel.p, n * 5 * 4, cudaMemcpyDeviceToHost, st));
+    if (ldist) VXB_CUDA(c, cudaMemcpyAsync(ldist, c->ray_ldist.p, n * 5 * 4, cudaMemcpyDeviceToHost, st));
+    if (leaving) VXB_CUDA(c, cudaMemcpyAsync(leaving, c->ray_leaving.p, n * 5 * 4, cudaMemcpyDeviceToHost, st));
+    if (layer_count) VXB_CUDA(c, cudaMemcpyAsync(layer_count, c->ray_count.p, n * 4, cudaMemcpyDeviceToHost, st));
+    if (dist) VXB_CUDA(c, cudaMemcpyAsync(dist, c->ray_dist.p, n * 4, cudaMemcpyDeviceToHost, st));
+    unsigned long long it = 0;
+    VXB_CUDA(c, cudaMemcpyAsync(&it, c->scalars.p, sizeof(it), cudaMemcpyDeviceToHost, st));
+    VXB_CUDA(c, cudaStreamSynchronize(st));
+    if (total_iterations) *total_iterations = it;
+    return VXB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// bulk hooks
+
+int vxb_read_pool(vxb_ctx* c, uint64_t first_slot, uint64_t n_slots, uint32_t* out) {
+    if (!c || !out) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, first_slot + n_slots <= c->s.max_loaded_chunks, "vxb_read_pool: slot range beyond the pool");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, cudaMemcpyAsync(out, c->pool.p + first_slot * CHUNK_VOLUME, n_slots * CHUNK_VOLUME * 4, cudaMemcpyDeviceToHost, c->stream));
+    VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VXB_OK;
+}
+int vxb_write_pool(vxb_ctx* c, uint64_t first_slot, uint64_t n_slots, const uint32_t* in) {
+    if (!c || !in) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, first_slot + n_slots <= c->s.max_loaded_chunks, "vxb_write_pool: slot range beyond the pool");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, cudaMemcpyAsync(c->pool.p + first_slot * CHUNK_VOLUME, in, n_slots * CHUNK_VOLUME * 4, cudaMemcpyHostToDevice, c->stream));
+    VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VXB_OK;
+}
+int vxb_read_table(vxb_ctx* c, uint32_t* out) {
+    if (!c || !out) return VXB_ERR_INVALID;
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, cudaMemcpyAsync(out, c->table.p, c->cpu_chunks_copy.size() * 4, cudaMemcpyDeviceToHost, c->stream));
+    VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VXB_OK;
+}
+int vxb_write_table(vxb_ctx* c, const uint32_t* in) {
+    if (!c || !in) return VXB_ERR_INVALID;
+    const size_t n = c->cpu_chunks_copy.size();
+    for (size_t i = 0; i < n; i++)
+        if (in[i] >= c->s.max_loaded_chunks) return fail(c, VXB_ERR_INVALID, "vxb_write_table: entry %zu names slot %u beyond the pool", i, in[i]);
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, cudaMemcpyAsync(c->table.p, in, n * 4, cudaMemcpyHostToDevice, c->stream));
+    VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->cpu_chunks_copy.assign(in, in + n);
+    std::vector<uint8_t> used(c->s.max_loaded_chunks, 0);
+    for (size_t i = 0; i < n; i++) used[in[i]] = 1;
+    c->available_chunks.clear();
+    for (uint32_t i = 2; i < c->s.max_loaded_chunks; i++)
+        if (!used[i]) c->available_chunks.push_back(i);
+    return VXB_OK;
+}
+int vxb_world_checksum(vxb_ctx* c, const uint32_t start_pos[3], uint64_t* out) {
+    if (!c || !start_pos || !out) return VXB_ERR_INVALID;
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, launch_checksum(c->world(start_pos), c->scalars.p + 1, c->stream));
+    unsigned long long v = 0;
+    VXB_CUDA(c, cudaMemcpyAsync(&v, c->scalars.p + 1, sizeof(v), cudaMemcpyDeviceToHost, c->stream));
+    VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    *out = v;
+    return VXB_OK;
+}
+
+}  // extern "C"
+#pragma GCC visibility pop

@@ -1,0 +1,57 @@
+// Host-callable launchers of the CUDA kernels (internal to libvoxelb200; the public boundary is
+// include/voxelb200.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/voxelb200.h"
+
+namespace vxb {
+
+struct World;
+
+// compute_voxel.glsl dispatch. variant 0 = tiled, 1 = reference-shaped gather, 2 = tiled + store elision.
+cudaError_t launch_voxel_update(const World& w, const uint32_t* chunk_updates, uint32_t n, const uint32_t offset[3],
+                                uint32_t* flags_out, int variant, cudaStream_t st);
+
+// maps/open_world.glsl (map 0) | maps/control.glsl (map 1) dispatch over n_workgroups 8^3 blocks.
+cudaError_t launch_worldgen(const World& w, const int32_t* chunk_loads, uint32_t n_workgroups, uint32_t* load_results, int map,
+                            uint32_t seed, cudaStream_t st);
+// complete_worldgen.glsl
+cudaError_t launch_complete_worldgen(const World& w, uint32_t* table, const int32_t* chunk_loads, const uint32_t* load_results,
+                                     uint32_t worldgen_count, cudaStream_t st);
+// write_voxels.glsl
+cudaError_t launch_write_voxels(const World& w, const uint32_t* writes, uint32_t n, cudaStream_t st);
+// unload_chunks.glsl
+cudaError_t launch_unload(const World& w, uint32_t* table, int32_t unload_index, uint32_t unload_component, cudaStream_t st);
+// fill n words
+cudaError_t launch_fill(uint32_t* dst, uint32_t value, uint64_t n, cudaStream_t st);
+// order-independent world checksum
+cudaError_t launch_checksum(const World& w, unsigned long long* out, cudaStream_t st);
+
+// frag.glsl raycast() for n_views * w * h pixels (cams on device) or for explicit rays.
+struct RayOut {
+    uint64_t n_rays;
+    float* pos;
+    float* normal;
+    uint32_t* voxel;
+    float* ldist;
+    uint32_t* leaving;
+    uint32_t* layer_count;
+    float* dist;
+    unsigned long long* total_iters;
+};
+cudaError_t launch_raymarch_views(const World& w, const vxb_player* cams_dev, uint32_t n_views, uint32_t width, uint32_t height,
+                                  uint32_t max_iterations, const vxb_projectile* projectiles, uint32_t projectile_count,
+                                  const float* raster_depth_dev, RayOut out, cudaStream_t st);
+cudaError_t launch_raymarch_rays(const World& w, const float* pos_dev, const float* dir_dev, uint64_t n, int kind,
+                                 uint32_t max_iterations, const vxb_projectile* projectiles, uint32_t projectile_count, RayOut out,
+                                 cudaStream_t st);
+
+// compute_projectile.glsl / compute_entity.glsl
+cudaError_t launch_projectiles(const World& w, vxb_projectile* projectiles, uint32_t n_projectiles, const vxb_player* players,
+                               uint32_t n_players, vxb_collision* collisions, uint32_t collision_capacity, uint32_t* collision_count,
+                               float dt, cudaStream_t st);
+cudaError_t launch_players(const World& w, vxb_player* players, uint32_t n_players, float dt, cudaStream_t st);
+
+}  // namespace vxb

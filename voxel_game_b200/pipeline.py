@@ -1,0 +1,362 @@
+"""Host-side mirror of the reference's interface for the voxel hot path, over the C ABI.
+
+`VoxelComputePipeline` keeps the method names and argument meaning of the reference's
+`VoxelComputePipeline` (client/src/voxel_sim_manager.rs:264-1207); `PointLightingSystem.draw`
+mirrors `PointLightingSystem::draw` (client/src/raytracer.rs:234-305). Everything here is a thin
+ctypes shim: the work happens in libvoxelb200.so (CUDA, sm_100a). No CPU fallback.
+"""
+import ctypes
+from dataclasses import dataclass, field
+from enum import IntEnum
+
+import numpy as np
+
+from . import _lib
+from ._lib import COLLISION_DTYPE, PLAYER_DTYPE, PROJECTILE_DTYPE, RayBuffers, RayCaps, Ptrs, Settings, VxbError, ptr
+
+CHUNK_SIZE = 16
+CHUNK_VOLUME = 4096
+
+# shaders/common.glsl:66-78
+MAT_AIR, MAT_STONE, MAT_OOB, MAT_DIRT, MAT_GRASS, MAT_PROJECTILE, MAT_ICE = 0, 1, 2, 3, 4, 5, 6
+MAT_WATER, MAT_PLAYER, MAT_AIR_OOB, MAT_WOOD, MAT_LEAF, MAT_UNBREAKABLE = 7, 8, 9, 10, 11, 12
+
+
+class Direction(IntEnum):
+    """client/src/utils.rs:9-17"""
+
+    PosX = 0
+    NegX = 1
+    PosY = 2
+    NegY = 3
+    PosZ = 4
+    NegZ = 5
+
+
+class WorldGen(IntEnum):
+    """WorldGenSettings, /src/lib.rs:4-23"""
+
+    Normal = 0
+    Control = 1
+
+
+@dataclass
+class GameSettings:
+    """The fields of GameSettings (/src/lib.rs:42-55) that the hot path reads, plus capacities."""
+
+    render_size: tuple = (8, 8, 8)
+    max_loaded_chunks: int = 512
+    max_worldgen_rate: int = 512
+    max_update_rate: int = 512
+    delta_time: float = 0.02
+    world_gen: WorldGen = WorldGen.Normal
+    world_gen_seed: int = 0
+    max_projectiles: int = 1024
+    max_players: int = 1024
+    max_voxel_writes: int = 1024
+    max_collisions: int = 1024
+
+    def to_c(self):
+        s = Settings()
+        s.render_size[:] = [int(v) for v in self.render_size]
+        s.max_loaded_chunks = int(self.max_loaded_chunks)
+        s.max_worldgen_rate = int(self.max_worldgen_rate)
+        s.max_update_rate = int(self.max_update_rate)
+        s.delta_time = float(self.delta_time)
+        s.world_gen = int(self.world_gen)
+        s.world_gen_seed = int(self.world_gen_seed)
+        s.max_projectiles = int(self.max_projectiles)
+        s.max_players = int(self.max_players)
+        s.max_voxel_writes = int(self.max_voxel_writes)
+        s.max_collisions = int(self.max_collisions)
+        return s
+
+
+@dataclass
+class GameState:
+    """GameState.start_pos (client/src/game_manager.rs:42-48), in chunks."""
+
+    start_pos: list = field(default_factory=lambda: [0, 0, 0])
+
+
+@dataclass
+class GraphicsSettings:
+    """client/src/settings_manager.rs:63-69 with the defaults of client/settings.yaml:15-19."""
+
+    primary_ray_dist: int = 100
+    shadow_ray_dist: int = 40
+    reflection_ray_dist: int = 20
+    ao_ray_dist: int = 15
+
+
+def initial_start_pos(center, render_size):
+    """game_manager.rs:42-48: spawn as u32 / CHUNK_SIZE - size / 2 per axis."""
+    return [int(c) // CHUNK_SIZE - int(s) // 2 for c, s in zip(center, render_size)]
+
+
+def _u32(vals, n):
+    a = np.ascontiguousarray(np.asarray(vals, dtype=np.uint32).reshape(-1))
+    if a.size != n:
+        raise ValueError("expected %d values" % n)
+    return a
+
+
+class VoxelComputePipeline:
+    """Mirror of VoxelComputePipeline (client/src/voxel_sim_manager.rs)."""
+
+    def __init__(self, game_settings: GameSettings, device: int = 0):
+        self._lib = _lib.load()
+        self.settings = game_settings
+        self._h = ctypes.c_void_p()
+        cs = game_settings.to_c()
+        rc = self._lib.vxb_create(ctypes.byref(cs), int(device), ctypes.byref(self._h))
+        if rc != 0:
+            raise VxbError("vxb_create failed (%d): %s" % (rc, self._lib.vxb_last_error(None).decode()))
+        self.device = device
+
+    # -- plumbing ---------------------------------------------------------------------------
+    def _check(self, rc):
+        if rc != 0:
+            raise VxbError("libvoxelb200 error %d: %s" % (rc, self._lib.vxb_last_error(self._h).decode()))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._lib.vxb_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def set_stream(self, cuda_stream_ptr):
+        self._check(self._lib.vxb_set_stream(self._h, ctypes.c_void_p(cuda_stream_ptr or 0)))
+
+    def synchronize(self):
+        self._check(self._lib.vxb_synchronize(self._h))
+
+    # -- the reference's public methods ----------------------------------------------------
+    def compute(self, game_state: GameState, projectiles=None, players=None):
+        """compute() (:830-1008). projectiles / players: numpy arrays of PROJECTILE_DTYPE / PLAYER_DTYPE."""
+        sp = _u32(game_state.start_pos, 3)
+        pr = np.ascontiguousarray(projectiles, dtype=PROJECTILE_DTYPE) if projectiles is not None else None
+        pl = np.ascontiguousarray(players, dtype=PLAYER_DTYPE) if players is not None else None
+        self._check(
+            self._lib.vxb_compute(self._h, ptr(sp), ptr(pr), 0 if pr is None else pr.size, ptr(pl), 0 if pl is None else pl.size)
+        )
+        self._n_proj = 0 if pr is None else min(pr.size, self.settings.max_projectiles)
+        self._n_players = 0 if pl is None else min(pl.size, self.settings.max_players)
+
+    def download_projectiles(self):
+        """download_projectiles() (:545-648) -> (projectiles, collisions, players)."""
+        pr = np.zeros(getattr(self, "_n_proj", 0), dtype=PROJECTILE_DTYPE)
+        pl = np.zeros(getattr(self, "_n_players", 0), dtype=PLAYER_DTYPE)
+        co = np.zeros(self.settings.max_collisions, dtype=COLLISION_DTYPE)
+        n = ctypes.c_uint32(0)
+        self._check(self._lib.vxb_download_projectiles(self._h, ptr(pr), ptr(co), ctypes.byref(n), ptr(pl)))
+        return pr, co[: n.value].copy(), pl
+
+    def push_updates_from_changed(self, player_locations=()):
+        """push_updates_from_changed() (:741-816)."""
+        pp = np.ascontiguousarray(np.asarray(player_locations, dtype=np.float32).reshape(-1, 3))
+        self._check(self._lib.vxb_push_updates_from_changed(self._h, ptr(pp) if pp.size else None, pp.shape[0]))
+
+    def queue_voxel_write(self, write):
+        self._check(self._lib.vxb_queue_voxel_write(self._h, ptr(_u32(write, 4))))
+
+    def queue_chunk_update(self, queued):
+        self._check(self._lib.vxb_queue_chunk_update(self._h, ptr(_u32(queued, 3))))
+
+    def queue_update_from_world_pos(self, pos):
+        p = np.ascontiguousarray(np.asarray(pos, dtype=np.float32).reshape(3))
+        self._check(self._lib.vxb_queue_update_from_world_pos(self._h, ptr(p)))
+
+    def ensure_chunk_loaded(self, chunk):
+        self._check(self._lib.vxb_ensure_chunk_loaded(self._h, ptr(_u32(chunk, 3))))
+
+    def queue_worldgen(self, chunk, forced=False):
+        self._check(self._lib.vxb_queue_worldgen(self._h, ptr(_u32(chunk, 3)), int(bool(forced))))
+
+    def move_start_pos(self, game_state: GameState, direction: Direction):
+        sp = _u32(game_state.start_pos, 3).copy()
+        self._check(self._lib.vxb_move_start_pos(self._h, ptr(sp), int(direction)))
+        game_state.start_pos = [int(v) for v in sp]
+
+    def update_count(self):
+        return int(self._lib.vxb_update_count(self._h))
+
+    def worldgen_count(self):
+        return int(self._lib.vxb_worldgen_count(self._h))
+
+    def worldgen_capacity(self):
+        return int(self._lib.vxb_worldgen_capacity(self._h))
+
+    def queue_set_idx(self):
+        out = np.zeros(3, np.uint32)
+        self._check(self._lib.vxb_queue_set_idx(self._h, ptr(out)))
+        return [int(v) for v in out]
+
+    def get_chunk(self, chunk):
+        return int(self._lib.vxb_get_chunk(self._h, ptr(_u32(chunk, 3))))
+
+    def last_dispatch_counts(self):
+        out = np.zeros(3, np.uint32)
+        self._check(self._lib.vxb_last_dispatch_counts(self._h, ptr(out)))
+        return [int(v) for v in out]
+
+    def device_ptrs(self):
+        """chunks()/voxels()/projectiles()/players() (:537-543, :650-656) as raw device pointers."""
+        p = Ptrs()
+        self._check(self._lib.vxb_device_ptrs(self._h, ctypes.byref(p)))
+        return p
+
+    # -- single dispatches on explicit work lists ------------------------------------------
+    def dispatch_worldgen(self, start_pos, chunk_loads, complete=True, want_results=True):
+        cl = np.ascontiguousarray(np.asarray(chunk_loads, dtype=np.int32).reshape(-1, 4))
+        res = np.zeros(cl.shape[0] // 8, np.uint32) if want_results else None
+        self._check(self._lib.vxb_dispatch_worldgen(self._h, ptr(_u32(start_pos, 3)), ptr(cl), cl.shape[0], int(complete), ptr(res)))
+        return res
+
+    def dispatch_voxel_update(self, start_pos, chunk_updates, offset, want_flags=True):
+        cu = np.ascontiguousarray(np.asarray(chunk_updates, dtype=np.uint32).reshape(-1, 4))
+        flags = np.zeros(cu.shape[0], np.uint32) if want_flags else None
+        self._check(
+            self._lib.vxb_dispatch_voxel_update(self._h, ptr(_u32(start_pos, 3)), ptr(cu), cu.shape[0], ptr(_u32(offset, 3)), ptr(flags))
+        )
+        return flags
+
+    def dispatch_write_voxels(self, start_pos, writes):
+        wr = np.ascontiguousarray(np.asarray(writes, dtype=np.uint32).reshape(-1, 4))
+        self._check(self._lib.vxb_dispatch_write_voxels(self._h, ptr(_u32(start_pos, 3)), ptr(wr), wr.shape[0]))
+
+    def dispatch_unload(self, unload_index, unload_component):
+        self._check(self._lib.vxb_dispatch_unload(self._h, int(unload_index), int(unload_component)))
+
+    def dispatch_entities(self, start_pos, projectiles=None, players=None, run_projectiles=True, run_players=True):
+        pr = np.ascontiguousarray(projectiles, dtype=PROJECTILE_DTYPE).copy() if projectiles is not None else np.zeros(0, PROJECTILE_DTYPE)
+        pl = np.ascontiguousarray(players, dtype=PLAYER_DTYPE).copy() if players is not None else np.zeros(0, PLAYER_DTYPE)
+        co = np.zeros(self.settings.max_collisions, dtype=COLLISION_DTYPE)
+        n = ctypes.c_uint32(0)
+        self._check(
+            self._lib.vxb_dispatch_entities(
+                self._h, ptr(_u32(start_pos, 3)), ptr(pr) if pr.size else None, pr.size, ptr(pl) if pl.size else None, pl.size,
+                int(run_projectiles), int(run_players), ptr(co), ctypes.byref(n),
+            )
+        )
+        return pr, pl, co[: n.value].copy(), int(n.value)
+
+    def update_list_upload(self, chunk_updates):
+        cu = np.ascontiguousarray(np.asarray(chunk_updates, dtype=np.uint32).reshape(-1, 4))
+        self._check(self._lib.vxb_update_list_upload(self._h, ptr(cu), cu.shape[0]))
+        self._res_n = cu.shape[0]
+
+    def update_list_run(self, start_pos, offset):
+        self._check(self._lib.vxb_update_list_run(self._h, ptr(_u32(start_pos, 3)), ptr(_u32(offset, 3))))
+
+    def update_list_flags(self):
+        out = np.zeros(self._res_n, np.uint32)
+        self._check(self._lib.vxb_update_list_flags(self._h, ptr(out), self._res_n))
+        return out
+
+    def set_update_kernel(self, variant):
+        self._check(self._lib.vxb_set_update_kernel(self._h, int(variant)))
+
+    # -- rays ---------------------------------------------------------------------------------
+    def raymarch(self, start_pos, cams, w, h, caps: RayCaps, raster_depth=None):
+        cams = np.ascontiguousarray(cams, dtype=PLAYER_DTYPE).reshape(-1)
+        rd = None if raster_depth is None else np.ascontiguousarray(raster_depth, dtype=np.float32)
+        self._check(self._lib.vxb_raymarch(self._h, ptr(_u32(start_pos, 3)), ptr(cams), cams.size, int(w), int(h), ctypes.byref(caps), ptr(rd)))
+
+    def raymarch_rays(self, start_pos, pos, dirs, kind, max_iterations, projectile_count=0):
+        p = np.ascontiguousarray(np.asarray(pos, dtype=np.float32).reshape(-1, 3))
+        d = np.ascontiguousarray(np.asarray(dirs, dtype=np.float32).reshape(-1, 3))
+        assert p.shape == d.shape
+        self._check(
+            self._lib.vxb_raymarch_rays(self._h, ptr(_u32(start_pos, 3)), ptr(p), ptr(d), p.shape[0], int(kind), int(max_iterations), int(projectile_count))
+        )
+
+    def ray_results(self):
+        rb = RayBuffers()
+        self._check(self._lib.vxb_ray_results(self._h, ctypes.byref(rb)))
+        return rb
+
+    def ray_download(self):
+        """-> dict of host arrays shaped [5,3,n] / [5,n] / [n] (see vxb_ray_buffers)."""
+        n = int(self.ray_results().n_rays)
+        out = {
+            "pos": np.zeros((5, 3, n), np.float32),
+            "normal": np.zeros((5, 3, n), np.float32),
+            "voxel": np.zeros((5, n), np.uint32),
+            "ldist": np.zeros((5, n), np.float32),
+            "leaving": np.zeros((5, n), np.uint32),
+            "layer_count": np.zeros(n, np.uint32),
+            "dist": np.zeros(n, np.float32),
+        }
+        it = ctypes.c_uint64(0)
+        self._check(
+            self._lib.vxb_ray_download(
+                self._h, ptr(out["pos"]), ptr(out["normal"]), ptr(out["voxel"]), ptr(out["ldist"]), ptr(out["leaving"]),
+                ptr(out["layer_count"]), ptr(out["dist"]), ctypes.byref(it),
+            )
+        )
+        out["total_iterations"] = int(it.value)
+        return out
+
+    # -- bulk hooks ---------------------------------------------------------------------------
+    def read_pool(self, first_slot, n_slots):
+        out = np.zeros((int(n_slots), CHUNK_VOLUME), np.uint32)
+        self._check(self._lib.vxb_read_pool(self._h, int(first_slot), int(n_slots), ptr(out)))
+        return out
+
+    def write_pool(self, first_slot, data):
+        d = np.ascontiguousarray(np.asarray(data, dtype=np.uint32).reshape(-1, CHUNK_VOLUME))
+        self._check(self._lib.vxb_write_pool(self._h, int(first_slot), d.shape[0], ptr(d)))
+
+    def read_table(self):
+        out = np.zeros(tuple(int(v) for v in self.settings.render_size), np.uint32)
+        self._check(self._lib.vxb_read_table(self._h, ptr(out)))
+        return out
+
+    def write_table(self, table):
+        t = np.ascontiguousarray(np.asarray(table, dtype=np.uint32).reshape(tuple(int(v) for v in self.settings.render_size)))
+        self._check(self._lib.vxb_write_table(self._h, ptr(t)))
+
+    def world_checksum(self, start_pos):
+        out = ctypes.c_uint64(0)
+        self._check(self._lib.vxb_world_checksum(self._h, ptr(_u32(start_pos, 3)), ctypes.byref(out)))
+        return int(out.value)
+
+
+class Game:
+    """The slice of `Game` (client/src/game_manager.rs:19-27) the ray pass reads."""
+
+    def __init__(self, voxel_compute: VoxelComputePipeline, game_state: GameState, players):
+        self.voxel_compute = voxel_compute
+        self.game_state = game_state
+        self.players = players  # PLAYER_DTYPE array; players[0] is the camera (frag.glsl:716)
+
+
+class PointLightingSystem:
+    """Mirror of PointLightingSystem (client/src/raytracer.rs). Headless: there is no colour
+    attachment; `draw` runs the primary DDA of frag.glsl for every pixel and leaves the
+    RaycastResult layers in device memory (download with `game.voxel_compute.ray_download()`)."""
+
+    def draw(self, viewport_dimensions, color_input, normals_input, depth_input, screen_to_world, game: Game,
+             graphics_settings: GraphicsSettings, rendered_projectile_count=0):
+        """Arguments as in raytracer.rs:234-243. color_input / normals_input / screen_to_world are
+        unused without a rasterised G-buffer; depth_input is None or a [h, w] array of max_depth
+        (world-space distance to the rasterised surface, frag.glsl:725-728)."""
+        w, h = int(viewport_dimensions[0]), int(viewport_dimensions[1])
+        caps = RayCaps(
+            graphics_settings.primary_ray_dist, graphics_settings.shadow_ray_dist, graphics_settings.reflection_ray_dist,
+            graphics_settings.ao_ray_dist, int(rendered_projectile_count),
+        )
+        cam = np.ascontiguousarray(game.players, dtype=PLAYER_DTYPE).reshape(-1)[:1]
+        game.voxel_compute.raymarch(game.game_state.start_pos, cam, w, h, caps, depth_input)
