@@ -1,0 +1,484 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the voxel hot path on B200 (contract: see the task prompt).
+
+Primary line (metric "voxel-updates/s"): BASELINE.json configs[2], the Margolus voxel update step
+over EVERY chunk of a 4096x256x4096-voxel open-world map (256x16x256 chunks, 17.18 GB of voxel
+state, far larger than L2), one phase per step, phases cycled; x-slab sharded over N GPUs with a
+one-voxel-plane halo exchange on phases whose x offset is 1 (strong scaling: the world is fixed).
+The same JSON line carries, under "rays", BASELINE.json configs[1]: 1920x1080 primary-ray DDA over a
+1024x256x1024-voxel world (rays/s, N=1 only), and "worldgen" (voxels generated/s, measured while
+building the worlds).
+
+  python bench.py --gpus 1 --steps 16 --warmup 3
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
+  python bench.py --impl reference ...    # the CPU restatement (oracle) on the host cores
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+C3_RS = (256, 16, 256)
+C3_SP = (497, 105, 497)  # (625,113,625) - (128,8,128), SURVEY §8d
+C2_RS = (64, 16, 64)
+C2_SP = (593, 105, 593)  # (625,113,625) - (32,8,32)
+PHASES = [(x, y, z) for z in (0, 1) for y in (0, 1) for x in (0, 1)]
+BYTES_PER_VOXEL_UPDATE = 8  # 4 B read + 4 B unconditional write (compute_voxel.glsl:87)
+
+
+def hbm_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def traffic_from_profiles(key):
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        return json.load(open(p)).get(key)
+    return None
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        for line in self.f.read().splitlines():
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        os.unlink(self.f.name)
+        if sm:
+            out["sm_mhz"] = float(np.median(sm))
+            out["sm_max_mhz"] = float(max(mx))
+            out["samples"] = len(sm)
+        out["reasons"] = sorted(reasons)
+        return out
+
+
+def chunk_grid(x0, x1, rs, sp):
+    """Global chunk coords of local window columns [x0, x1) in (x, y, z) order, z fastest."""
+    xs = np.arange(sp[0] + x0, sp[0] + x1, dtype=np.int64)
+    ys = np.arange(sp[1], sp[1] + rs[1], dtype=np.int64)
+    zs = np.arange(sp[2], sp[2] + rs[2], dtype=np.int64)
+    g = np.stack(np.meshgrid(xs, ys, zs, indexing="ij"), -1).reshape(-1, 3)
+    return g
+
+
+def loads_for(chunks, slots, forced):
+    ijk = np.array([(i, j, k) for i in range(2) for j in range(2) for k in range(2)], np.int64)
+    xyz = (2 * chunks[:, None, :] + ijk[None, :, :]).reshape(-1, 3)
+    w = np.repeat(np.asarray(slots, np.int64) * (-1 if forced else 1), 8)
+    return np.concatenate([xyz, w[:, None]], 1).astype(np.int32)
+
+
+def generate_world(gpu, sp, chunks, first_slot, forced, torch, batch=32768):
+    """Worldgen every chunk of `chunks` (slot = first_slot + i). Returns (seconds on device, voxels)."""
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for b in range(0, len(chunks), batch):
+        c = chunks[b:b + batch]
+        loads = loads_for(c, np.arange(first_slot + b, first_slot + b + len(c)), forced)
+        gpu.dispatch_worldgen(sp, loads, complete=True, want_results=False)
+    ev1.record()
+    torch.cuda.synchronize()
+    return ev0.elapsed_time(ev1) / 1e3, len(chunks) * 4096
+
+
+def pinned_u32(torch, shape):
+    t = torch.empty(shape, dtype=torch.int32, pin_memory=True)
+    return t, t.numpy().view(np.uint32)
+
+
+class DevView:
+    """Expose a raw device pointer to torch through __cuda_array_interface__ (int32 words)."""
+
+    def __init__(self, ptr, n_words):
+        self.__cuda_array_interface__ = {"shape": (int(n_words),), "typestr": "<i4", "data": (int(ptr), False), "version": 2}
+
+
+# ------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    import voxel_game_b200 as vg
+
+    world_size = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world_size != args.gpus:
+        if world_size == 1 and args.gpus > 1:
+            raise SystemExit("launch with torch.distributed.run --nproc-per-node %d for --gpus %d" % (args.gpus, args.gpus))
+    torch.cuda.set_device(local_rank)
+    if world_size > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    stream = torch.cuda.current_stream()
+    peak, peak_src = hbm_peak()
+
+    def barrier():
+        if world_size > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---------------- C3: slab of the 256x16x256-chunk world ----------------
+    RS, SP = tuple(args.world), C3_SP
+    assert RS[0] % world_size == 0, "x extent must divide by the GPU count"
+    cols = RS[0] // world_size
+    x0 = rank * cols
+    ghost = 1 if rank < world_size - 1 else 0
+    lrs = (cols + ghost, RS[1], RS[2])
+    lsp = (SP[0] + x0, SP[1], SP[2])
+    n_local = lrs[0] * lrs[1] * lrs[2]
+    n_own = cols * RS[1] * RS[2]
+    gs = vg.GameSettings(render_size=lrs, max_loaded_chunks=2 + n_local, max_worldgen_rate=8 * 32768, max_update_rate=1024)
+    gpu = vg.VoxelComputePipeline(gs, device=local_rank)
+    gpu.set_stream(stream.cuda_stream)
+    chunks = chunk_grid(0, lrs[0], lrs, lsp)
+    wg_s, wg_vox = generate_world(gpu, lsp, chunks, 2, True, torch)
+    own_list = np.concatenate([chunks[:n_own], np.zeros((n_own, 1), np.int64)], 1).astype(np.uint32)
+    gpu.update_list_upload(own_list)
+    gpu.set_update_kernel(args.variant)
+
+    # halo planes: x == 0 plane of a chunk is its first 256 words; column c of the local window
+    # holds slots 2 + c*plane_chunks ... (x-major slot assignment above)
+    plane_chunks = RS[1] * RS[2]
+    ptrs = gpu.device_ptrs()
+    pool_t = torch.as_tensor(DevView(ptrs.voxel_pool, (2 + n_local) * 4096), device="cuda").view(2 + n_local, 4096)
+    first_col = pool_t[2:2 + plane_chunks, :256]
+    ghost_col = pool_t[2 + cols * plane_chunks:2 + (cols + 1) * plane_chunks, :256] if ghost else None
+    sendbuf = torch.empty((plane_chunks, 256), dtype=torch.int32, device="cuda")
+    recvbuf = torch.empty((plane_chunks, 256), dtype=torch.int32, device="cuda")
+    launches = [0]
+
+    def exchange(pre):
+        """pre: owner of column 0 -> left neighbour's ghost; post: ghost -> owner (right neighbour)."""
+        ops = []
+        if pre:
+            if rank > 0:
+                sendbuf.copy_(first_col)
+                ops.append(dist.P2POp(dist.isend, sendbuf, rank - 1))
+            if ghost:
+                ops.append(dist.P2POp(dist.irecv, recvbuf, rank + 1))
+        else:
+            if ghost:
+                sendbuf.copy_(ghost_col)
+                ops.append(dist.P2POp(dist.isend, sendbuf, rank + 1))
+            if rank > 0:
+                ops.append(dist.P2POp(dist.irecv, recvbuf, rank - 1))
+        if ops:
+            for r in dist.batch_isend_irecv(ops):
+                r.wait()
+        if pre and ghost:
+            ghost_col.copy_(recvbuf)
+        if not pre and rank > 0:
+            first_col.copy_(recvbuf)
+        launches[0] += 2
+
+    def step(i):
+        off = PHASES[i % 8]
+        if world_size > 1 and off[0] == 1:
+            exchange(True)
+        gpu.update_list_run(lsp, off)
+        launches[0] += 1
+        if world_size > 1 and off[0] == 1:
+            exchange(False)
+
+    for i in range(args.warmup):
+        step(i)
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    launches[0] = 0
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    ev[0].record()
+    for i in range(args.steps):
+        step(args.warmup + i)
+        ev[i + 1].record()
+    barrier()
+    total_ms = ev[0].elapsed_time(ev[-1])
+    clocks = sampler.stop() if sampler else None
+    t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
+    if world_size > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+    n_total_vox = RS[0] * RS[1] * RS[2] * 4096
+    value = n_total_vox * args.steps / (total_ms / 1e3)
+    # dominant kernel: this rank's k_voxel_update launches (CUDA events on the launching stream)
+    per_step_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
+    kern_ms = float(np.mean(per_step_ms)) if world_size == 1 else None
+
+    # ---------------- e2e: the C-ABI dispatch with HOST work list in, flags out ----------------
+    e2e = None
+    if rank == 0 or world_size > 1:
+        lt, lnp = pinned_u32(torch, (n_own, 4))
+        ft, fnp = pinned_u32(torch, (n_own,))
+        lnp[:] = own_list
+        lib, h = gpu._lib, gpu._h
+        from voxel_game_b200._lib import ptr, u32x
+
+        spc, offs = u32x(lsp, 3), [u32x(o, 3) for o in PHASES]
+
+        def e2e_step(i):
+            off = PHASES[i % 8]
+            if world_size > 1 and off[0] == 1:
+                exchange(True)
+            rc = lib.vxb_dispatch_voxel_update(h, ptr(spc), ptr(lnp), n_own, ptr(offs[i % 8]), ptr(fnp))  # syncs: flags are host-visible
+            assert rc == 0
+            if world_size > 1 and off[0] == 1:
+                exchange(False)
+
+        for i in range(2):
+            e2e_step(i)
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(args.steps):
+            e2e_step(i)
+        barrier()
+        e2e_s = time.perf_counter() - t0
+        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+        if world_size > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e = {"value": n_total_vox * args.steps / float(t.item()), "unit": "voxel-updates/s",
+               "h2d_bytes_per_step": int(n_own * 16 * world_size), "d2h_bytes_per_step": int(n_own * 4 * world_size),
+               "api": "vxb_dispatch_voxel_update (host chunk_updates list in, chunk_updates[].w flags out)"}
+
+    result = None
+    if rank == 0:
+        achieved = BYTES_PER_VOXEL_UPDATE * n_own * 4096 / (kern_ms / 1e3) / 1e9 if kern_ms else None
+        result = {
+            "metric": "voxel-updates/s", "value": value, "unit": "voxel-updates/s", "n_gpus": world_size, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "u32", "data": "synthetic (seeded open-world worldgen, forced slots)",
+            "config": {"workload": "BASELINE configs[2]: voxel update step, %dx%dx%d-voxel world, all %d chunks per step, phase cycled"
+                                   % (RS[0] * 16, RS[1] * 16, RS[2] * 16, RS[0] * RS[1] * RS[2]),
+                       "sharding": "x-slab x%d, halo = one voxel plane per boundary on offset.x==1 phases" % world_size,
+                       "l2": "inputs larger than L2 (%.2f GB of voxel state per GPU vs 126 MB)" % (n_local * 16384 / 1e9),
+                       "update_kernel_variant": args.variant},
+            "gpu_launches": launches[0],
+            "clocks": clocks,
+            "e2e": e2e,
+            "worldgen": {"value": wg_vox / wg_s, "unit": "voxels-generated/s", "voxels": wg_vox, "map": "open_world", "gpus": 1,
+                         "note": "rank 0's slab, device time incl. per-batch list upload"},
+        }
+        if achieved is not None:
+            result["roofline"] = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                                  "traffic": traffic_from_profiles("k_voxel_update_bytes_per_launch"), "peak_source": peak_src,
+                                  "kernel": "k_voxel_update_tiled", "algorithmic_bytes_per_launch": BYTES_PER_VOXEL_UPDATE * n_own * 4096,
+                                  "avg_launch_ms": kern_ms}
+
+    # ---------------- cpu_baseline (rank 0, N == 1): oracle on a bounded sample of the same world ----
+    if rank == 0 and world_size == 1 and not args.no_cpu:
+        from tests.oracle_lib import CpuWorld, load as load_oracle
+
+        sx = min(args.cpu_sample_cols, RS[0])
+        n_s = sx * RS[1] * RS[2]
+        cw = CpuWorld((sx, RS[1], RS[2]), SP, 2 + n_s)
+        cw.pool[2:] = gpu.read_pool(2, n_s)
+        cw.load_all_chunks()  # slots follow global (x,y,z) order, as on the GPU
+        lst = np.concatenate([chunk_grid(0, sx, (sx, RS[1], RS[2]), SP), np.zeros((n_s, 1), np.int64)], 1).astype(np.uint32)
+        cw.voxel_update(lst, PHASES[0])  # warm-up (page faults, thread pool)
+        t0 = time.perf_counter()
+        reps = 0
+        while reps < 8 and (time.perf_counter() - t0 < 20 or reps < 2):
+            cw.voxel_update(lst, PHASES[(reps + 1) % 8])
+            reps += 1
+        cs = time.perf_counter() - t0
+        result["cpu_baseline"] = {"value": n_s * 4096 * reps / cs, "unit": "voxel-updates/s", "cores": load_oracle().orc_num_threads(),
+                                  "kind": "port",
+                                  "sample": "%d ticks over the first %d x-columns of the same world (%d chunks, %d voxels), OpenMP over chunks"
+                                            % (reps, sx, n_s, n_s * 4096)}
+    gpu.close()
+    del pool_t, first_col, ghost_col
+
+    # ---------------- C2: 1080p primary rays (N == 1) ----------------
+    if rank == 0 and world_size == 1 and not args.no_rays:
+        result["rays"] = bench_rays(args, torch, vg, peak)
+
+    if world_size > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(result))
+
+
+def bench_rays(args, torch, vg, peak):
+    from tests import scenes
+
+    RS, SP = C2_RS, C2_SP
+    n = RS[0] * RS[1] * RS[2]
+    gs = vg.GameSettings(render_size=RS, max_loaded_chunks=2 + n, max_worldgen_rate=8 * 32768, max_update_rate=1024)
+    gpu = vg.VoxelComputePipeline(gs, device=torch.cuda.current_device())
+    gpu.set_stream(torch.cuda.current_stream().cuda_stream)
+    chunks = chunk_grid(0, RS[0], RS, SP)
+    generate_world(gpu, SP, chunks, 2, False, torch)
+    table = gpu.read_table()
+    loaded = chunks[(table.reshape(-1)[((chunks[:, 0] % RS[0]) * RS[1] + chunks[:, 1] % RS[1]) * RS[2] + chunks[:, 2] % RS[2]]) >= 2]
+    lst = np.concatenate([loaded, np.zeros((len(loaded), 1), np.int64)], 1).astype(np.uint32)
+    gpu.update_list_upload(lst)
+    for t in range(64):  # 8 ticks per phase so the distance fields are populated
+        gpu.update_list_run(SP, PHASES[t % 8])
+    gpu.synchronize()
+    cx, cz = 16 * SP[0] + 8 * RS[0], 16 * SP[2] + 8 * RS[2]
+    # surface height at the world centre column: first non-air from the top (host scan of one column of chunks)
+    col_y = None
+    for cy in range(SP[1] + RS[1] - 1, SP[1] - 1, -1):
+        slot = int(table[(cx >> 4) % RS[0], cy % RS[1], (cz >> 4) % RS[2]])
+        if slot < 2:
+            continue
+        ch = gpu.read_pool(slot, 1)[0].reshape(16, 16, 16)[cx & 15, :, cz & 15] >> 24
+        solid = np.nonzero((ch != 0) & (ch != 9))[0]
+        if solid.size:
+            col_y = 16 * cy + int(solid.max())
+            break
+    if col_y is None:
+        col_y = 1800
+    cams = np.concatenate([scenes.camera((cx + 0.5, col_y + 4.5, cz + 0.5), k * np.pi / 4, -0.2) for k in range(8)])
+    W, H = 1920, 1080
+    caps = vg.RayCaps(100, 40, 20, 15, 0)
+    iters_total, layers_total = [], []
+    for k in range(max(args.warmup, 3)):
+        gpu.raymarch(SP, cams[k % 8:k % 8 + 1], W, H, caps)
+    torch.cuda.synchronize()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    ev[0].record()
+    for i in range(args.steps):
+        gpu.raymarch(SP, cams[i % 8:i % 8 + 1], W, H, caps)
+        ev[i + 1].record()
+    torch.cuda.synchronize()
+    ms = ev[0].elapsed_time(ev[-1])
+    # iteration / layer totals for the gather model (one pass per camera, untimed)
+    for k in range(8):
+        gpu.raymarch(SP, cams[k:k + 1], W, H, caps)
+        r = gpu.ray_download()
+        iters_total.append(r["total_iterations"])
+        layers_total.append(int(r["layer_count"].sum()))
+    mean_iters = float(np.mean([iters_total[i % 8] for i in range(args.steps)]))
+    mean_layers = float(np.mean([layers_total[i % 8] for i in range(args.steps)]))
+    alg_bytes = 8 * mean_iters + 16 * W * H + 24 * mean_layers
+    # e2e: camera in from host, layer_count + depth + first layer voxel out to host
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        gpu.raymarch(SP, cams[i % 8:i % 8 + 1], W, H, caps)
+        out_lc = np.empty(W * H, np.uint32)
+        out_d = np.empty(W * H, np.float32)
+        from voxel_game_b200._lib import ptr
+
+        assert gpu._lib.vxb_ray_download(gpu._h, None, None, None, None, None, ptr(out_lc), ptr(out_d), None) == 0
+    e2e_s = time.perf_counter() - t0
+    gpu.close()
+    achieved = alg_bytes / (ms / args.steps / 1e3) / 1e9
+    return {"metric": "rays/s", "value": W * H * args.steps / (ms / 1e3), "unit": "rays/s", "ms_per_frame": ms / args.steps,
+            "config": {"workload": "BASELINE configs[1]: 1920x1080 primary-ray DDA, 1024x256x1024-voxel open-world map, 8 cameras cycled",
+                       "primary_ray_dist": 100},
+            "mean_iterations_per_ray": mean_iters / (W * H), "mean_layers_per_ray": mean_layers / (W * H),
+            "roofline": {"bound": "hbm", "model": "gather: 8 B per DDA iteration + 16 B + 24 B x layers per ray", "achieved": achieved,
+                         "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic_from_profiles("k_raymarch_primary_bytes_per_launch")},
+            "e2e": {"value": W * H * args.steps / e2e_s, "unit": "rays/s", "h2d_bytes_per_step": 128, "d2h_bytes_per_step": W * H * 8}}
+
+
+# ------------------------------------------------------------------------------------------------
+def run_reference(args):
+    """The reference has no CPU implementation of this path and its shaders cannot run here (no
+    Vulkan / software renderer on the box): the reference arm is the CPU restatement of the shader
+    (oracle, kind "port") with all host threads, on a bounded sample of the same workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from tests.oracle_lib import CpuWorld, chunk_loads_for, load as load_oracle
+
+    lib = load_oracle()
+    cores = lib.orc_num_threads()
+    # sample: an 8x8x8-chunk open-world block generated by the oracle itself around the spawn, tiled 4x1x4
+    base_rs, tile = (8, 8, 8), (4, 1, 4)
+    sp = (621, 109, 621)
+    gen = CpuWorld(base_rs, sp, 2 + 512)
+    chunks = gen.load_all_chunks()
+    gen.worldgen(chunk_loads_for(chunks, range(2, 514), forced=True), 0, complete=False)
+    rs = tuple(b * t for b, t in zip(base_rs, tile))
+    n = rs[0] * rs[1] * rs[2]
+    cw = CpuWorld(rs, sp, 2 + n)
+    all_chunks = cw.load_all_chunks()
+    src = gen.pool[2:].reshape(8, 8, 8, 4096)
+    dst = cw.pool[2:].reshape(rs[0], rs[1], rs[2], 4096)
+    for tx in range(tile[0]):
+        for tz in range(tile[2]):
+            dst[8 * tx:8 * tx + 8, :, 8 * tz:8 * tz + 8] = src
+    lst = np.asarray([(c[0], c[1], c[2], 0) for c in all_chunks], np.uint32)
+    for i in range(args.warmup):
+        cw.voxel_update(lst, PHASES[i % 8])
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        cw.voxel_update(lst, PHASES[(args.warmup + i) % 8])
+    s = time.perf_counter() - t0
+    value = n * 4096 * args.steps / s
+    sample = "oracle-generated 8x8x8-chunk open-world block tiled 4x1x4 (%d chunks, %d voxels) per step; OpenMP over chunks" % (n, n * 4096)
+    print(json.dumps({
+        "impl": "reference", "metric": "voxel-updates/s", "value": value, "unit": "voxel-updates/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": s / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "u32", "data": "synthetic (oracle open-world worldgen, tiled)",
+        "config": {"workload": "BASELINE configs[2] voxel update step — bounded CPU sample", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "voxel-updates/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "voxel-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=16)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--world", type=int, nargs=3, default=list(C3_RS), help="update-step world size in chunks (default BASELINE configs[2])")
+    ap.add_argument("--variant", type=int, default=0, help="update kernel variant (0 tiled, 1 gather, 2 tiled+store elision)")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-rays", action="store_true")
+    ap.add_argument("--cpu-sample-cols", type=int, default=4)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -4,20 +4,27 @@
 // chunk_updates[] entry.
 //
 // Design (B200, HBM-bound, integer only; see DESIGN.md §"k_voxel_update"):
-//  * one CTA of 256 threads per work-list entry; thread = 2x2 (x,y) columns of 4 consecutive z =
-//    two Margolus blocks = 16 voxels in registers; no shared-memory tile is needed because a
-//    Margolus block has no neighbours outside itself — the "halo" is only the phase shift.
-//  * in-chunk layout is x*256 + y*16 + z, so 4 consecutive z are one aligned 16-byte vector and a
-//    warp covers 8 full 64-byte rows per load instruction (every 32-byte sector fully used).
-//  * phase shift in z (offset.z == 1) breaks the 16-byte alignment; instead of scalar accesses the
-//    thread still loads/stores its ALIGNED vector and exchanges the boundary element with the
-//    neighbouring lane by warp shuffle; only z == 0 of the row (owned by the -z neighbour's CTA in
-//    this phase) and z == 16 (first voxel of the +z neighbour chunk) use narrower accesses.
-//  * the 2x2x2 neighbourhood of chunk slots is resolved once per CTA (8 table lookups) instead of
-//    once per voxel; sentinel slots 0/1 (unloaded / all-air) and out-of-window chunks are folded to
-//    constants and are neither loaded nor stored.
+//  * persistent CTAs (grid = SMs x resident CTAs) of 256 threads walk the work list with stride
+//    gridDim; a chunk is 16 KiB, a thread owns 2x2 (x,y) columns x 4 consecutive z = two Margolus
+//    blocks = 16 voxels. A Margolus block has no neighbours outside itself, so the only "halo" is
+//    the phase shift: up to 8 source chunks per work item.
+//  * memory-level parallelism comes from a 4-stage cp.async (LDGSTS) ring in shared memory, not
+//    from registers or occupancy: every thread copies exactly the 4 aligned 16-byte vectors (+ one
+//    straddled word) it will consume, into a thread-private slot, up to 3 chunks ahead. No CTA
+//    barrier guards the data (thread-private); one barrier per chunk publishes the chunk-slot
+//    table and the change flags. The dependent chain list entry -> chunk table -> voxels is taken
+//    off the critical path: 8 lanes resolve the 2x2x2 slot neighbourhood 4 chunks ahead.
+//  * in-chunk layout is x*256 + y*16 + z: 4 consecutive z are one aligned 16-byte vector and a warp
+//    covers 8 full 64-byte rows per copy instruction (every 32-byte sector fully used).
+//  * phase shift in z (offset.z == 1) breaks the 16-byte alignment; the thread still copies/stores
+//    its ALIGNED vector and exchanges the boundary element with the neighbouring lane by warp
+//    shuffle; only z == 0 of the row (owned by the -z neighbour's work item in this phase) and
+//    z == 16 (first voxel of the +z neighbour chunk) use narrower accesses.
+//  * sentinel slots 0/1 (unloaded / all-air) and out-of-window chunks are folded to constants and
+//    are neither loaded nor stored.
 //  * the reference re-reads every voxel in set_data; here the original stays in registers.
-//  * change flags are reduced with __reduce_or_sync and one shared atomic per warp.
+//  * the shader's straight-line block logic (~200 instructions per voxel) would make the kernel
+//    issue-bound 5x over; margolus_block() classifies the block first (exact, see there).
 #include "vxb_device.cuh"
 #include "vxb_kernels.h"
 
@@ -25,87 +32,148 @@ namespace vxb {
 
 __device__ __forceinline__ constexpr int cidx(int i, int j, int k) { return i * 4 + j * 2 + k; }
 
+constexpr uint32_t BIT_AIR = 1u << MAT_AIR, BIT_OOB = 1u << MAT_OOB, BIT_WATER = 1u << MAT_WATER, BIT_AIR_OOB = 1u << MAT_AIR_OOB,
+                   BIT_LEAF = 1u << MAT_LEAF, BIT_OTHER = 1u << 31;
+
+__device__ __forceinline__ uint32_t umin3(uint32_t a, uint32_t b, uint32_t c) { return __vimin3_u32(a, b, c); }
+
 // compute_voxel.glsl:102-207 on one block held in registers; v[cidx(i,j,k)] are voxel words.
 // PY = pos.y % 2 (== offset.y, since 16*chunk.y + 2*lid.y is even).
+// Returns false when the block is provably a fixed point (v is left untouched).
+//
+// Every path is exact; none is approximate:
+//  F0  all 8 words identical and that word is a fixed point (solid below its damage threshold,
+//      or air/water/leaf whose 8 distance slots are all 7)            -> nothing changes
+//  F1  no air/water/leaf in the block and every data field < 5        -> nothing changes
+//  damage step only if some data field can reach a threshold (min 5)
+//  water steps only if the block holds both water and air
+//  distance step by case: with `present` = set of materials in the block,
+//      - a cell of class X in {air, water, leaf} is "blocked" (slot := 0) iff ANY other cell is
+//        outside X's pass set ({X, OOB} plus AIR_OOB for air). Since the cell itself is inside its
+//        pass set, that is a property of the whole block: present has a bit outside the pass set.
+//        So either the block is "pure" for one class, or every distance cell gets 0.
+//      - pure block: slot := min(7, own if the block has an OOB cell, 1 + min over the other cells
+//        of class X of their value in that slot); OOB / AIR_OOB cells take no part in the min.
+//        The 3-bit fields are compared in place (masked, not shifted): 1 AND + 1/2 VIMNMX3 per pair.
 template <int PY>
-__device__ __forceinline__ void margolus_block(uint32_t (&v)[8]) {
+__device__ __forceinline__ bool margolus_block(uint32_t (&v)[8]) {
+    uint32_t orv = v[0];
+    {
+        const uint32_t W = v[0];
+        uint32_t diff = 0;
+#pragma unroll
+        for (int c = 1; c < 8; c++) {
+            diff |= v[c] ^ W;
+            orv |= v[c];
+        }
+        if (diff == 0) {
+            const uint32_t m0 = W >> 24, d0 = W & 0xFFFFFFu;
+            const bool fixed = mat_in(MASK_DATA_DISTANCE, m0) ? (d0 == 0xFFFFFFu)
+                                                              : !(mat_in(MASK_DATA_DAMAGE, m0) && d0 >= (m0 == MAT_STONE ? 10u : 5u));
+            if (fixed) return false;
+        }
+    }
     uint32_t m[8], d[8];
+    // set of materials in the block; ids >= 32 (out of contract) shift out and are caught by orv
+    uint32_t present = (orv >> 29) ? BIT_OTHER : 0u;
 #pragma unroll
     for (int c = 0; c < 8; c++) {
         m[c] = v[c] >> 24;
         d[c] = v[c] & 0xFFFFFFu;
+        present |= 1u << m[c];
     }
+    const uint32_t ord = orv & 0xFFFFFFu;
+    if ((present & MASK_DATA_DISTANCE) == 0 && ord < 5u) return false;
+
     // :102-112 accumulated damage past the material's threshold -> air (stone 10, others 5)
+    if (ord >= 5u) {
+        bool any = false;
 #pragma unroll
-    for (int c = 0; c < 8; c++) {
-        if (mat_in(MASK_DATA_DAMAGE, m[c])) {
-            uint32_t thr = m[c] == MAT_STONE ? 10u : 5u;
-            if (d[c] >= thr) {
+        for (int c = 0; c < 8; c++) {
+            if (mat_in(MASK_DATA_DAMAGE, m[c]) && d[c] >= (m[c] == MAT_STONE ? 10u : 5u)) {
                 m[c] = MAT_AIR;
                 d[c] = 0;
+                any = true;
             }
         }
+        if (any) {
+            present &= BIT_OTHER;
+#pragma unroll
+            for (int c = 0; c < 8; c++) present |= 1u << m[c];
+        }
     }
+
+    if ((present & BIT_WATER) && (present & BIT_AIR)) {
 #define VXB_FALL(b, t)                              \
     if (m[b] == MAT_AIR && m[t] == MAT_WATER) {     \
         m[b] = MAT_WATER; d[b] = 0;                 \
         m[t] = MAT_AIR;   d[t] = 0;                 \
     }
-    // :114-123 straight down
+        // :114-123 straight down
 #pragma unroll
-    for (int i = 0; i < 2; i++)
+        for (int i = 0; i < 2; i++)
 #pragma unroll
-        for (int k = 0; k < 2; k++) VXB_FALL(cidx(i, 0, k), cidx(i, 1, k))
-    // :125-134 diagonally in x
+            for (int k = 0; k < 2; k++) VXB_FALL(cidx(i, 0, k), cidx(i, 1, k))
+        // :125-134 diagonally in x
 #pragma unroll
-    for (int i = 0; i < 2; i++)
+        for (int i = 0; i < 2; i++)
 #pragma unroll
-        for (int k = 0; k < 2; k++) VXB_FALL(cidx(1 - i, 0, k), cidx(i, 1, k))
-    // :136-145 diagonally in z
+            for (int k = 0; k < 2; k++) VXB_FALL(cidx(1 - i, 0, k), cidx(i, 1, k))
+        // :136-145 diagonally in z
 #pragma unroll
-    for (int i = 0; i < 2; i++)
+        for (int i = 0; i < 2; i++)
 #pragma unroll
-        for (int k = 0; k < 2; k++) VXB_FALL(cidx(i, 0, 1 - k), cidx(i, 1, k))
-    // :147-154 sideways in x inside the top layer; `to` = column pos.y%2, `from` = the other
+            for (int k = 0; k < 2; k++) VXB_FALL(cidx(i, 0, 1 - k), cidx(i, 1, k))
+        // :147-154 sideways in x inside the top layer; `to` = column pos.y%2, `from` = the other
 #pragma unroll
-    for (int i = 0; i < 2; i++) VXB_FALL(cidx(PY, 1, i), cidx(1 - PY, 1, i))
-    // :156-163 sideways in z
+        for (int i = 0; i < 2; i++) VXB_FALL(cidx(PY, 1, i), cidx(1 - PY, 1, i))
+        // :156-163 sideways in z
 #pragma unroll
-    for (int i = 0; i < 2; i++) VXB_FALL(cidx(i, 1, PY), cidx(i, 1, 1 - PY))
+        for (int i = 0; i < 2; i++) VXB_FALL(cidx(i, 1, PY), cidx(i, 1, 1 - PY))
 #undef VXB_FALL
+    }
+
     // :165-207 each cell refreshes ONE 3-bit slot of its distance field: the slot named by its own
-    // corner, looking into the block. A cell only writes its own slot and only reads that same slot
-    // of the others, so the sequential loop of the reference equals this snapshot evaluation.
-    uint32_t nd[8];
+    // corner. A cell only writes its own slot and only reads that same slot of the others, so the
+    // sequential loop of the reference equals an evaluation on the pre-step snapshot.
+    if (present & MASK_DATA_DISTANCE) {
+        const bool pure_air = (present & ~(BIT_AIR | BIT_OOB | BIT_AIR_OOB)) == 0;
+        const bool pure_water = (present & ~(BIT_WATER | BIT_OOB)) == 0;
+        const bool pure_leaf = (present & ~(BIT_LEAF | BIT_OOB)) == 0;
+        if (pure_air || pure_water || pure_leaf) {
+            const uint32_t X = pure_air ? MAT_AIR : (pure_water ? MAT_WATER : MAT_LEAF);
+            const bool has_oob = (present & BIT_OOB) != 0;
+            uint32_t deff[8];
 #pragma unroll
-    for (int c = 0; c < 8; c++) {
-        const int i = c >> 2, j = (c >> 1) & 1, k = c & 1;
-        const int shift = 3 * ((k << 2) | (j << 1) | i);
-        nd[c] = d[c];
-        const bool is_air = m[c] == MAT_AIR;
-        if (is_air || mat_in(MASK_DATA_DISTANCE, m[c])) {
-            uint32_t r = 7u;
-            bool blocked = false;
-            const uint32_t own = (d[c] >> shift) & 7u;
+            for (int c = 0; c < 8; c++) deff[c] = m[c] == X ? d[c] : 0xFFFFFFu;
+            uint32_t nd[8];
 #pragma unroll
-            for (int o = 0; o < 8; o++) {
-                if (o == c) continue;
-                const uint32_t mo = m[o];
-                if (mo == MAT_OOB) {
-                    r = min(r, own);
-                } else if (is_air ? (mo == MAT_AIR) : (mo == m[c])) {
-                    r = min(r, ((d[o] >> shift) & 7u) + 1u);
-                } else if (is_air && mo == MAT_AIR_OOB) {
-                } else {
-                    blocked = true;
-                }
+            for (int c = 0; c < 8; c++) {
+                const int i = c >> 2, j = (c >> 1) & 1, k = c & 1;
+                const uint32_t MK = 7u << (3 * ((k << 2) | (j << 1) | i));
+                uint32_t f[7];
+#pragma unroll
+                for (int o = 0, q = 0; o < 8; o++)
+                    if (o != c) f[q++] = deff[o] & MK;
+                const uint32_t t = umin3(umin3(f[0], f[1], f[2]), umin3(f[3], f[4], f[5]), f[6]);
+                const uint32_t cap = has_oob ? (d[c] & MK) : MK;
+                const uint32_t r = min(cap, t + (MK & (MK >> 2)));  // + 1 in the field; 8 overflows past MK and loses to cap
+                nd[c] = m[c] == X ? ((d[c] & ~MK) | r) : d[c];
             }
-            if (blocked) r = 0u;
-            nd[c] = (d[c] & ~(7u << shift)) | (r << shift);
+#pragma unroll
+            for (int c = 0; c < 8; c++) d[c] = nd[c];
+        } else {
+#pragma unroll
+            for (int c = 0; c < 8; c++) {
+                const int i = c >> 2, j = (c >> 1) & 1, k = c & 1;
+                const uint32_t MK = 7u << (3 * ((k << 2) | (j << 1) | i));
+                if (mat_in(MASK_DATA_DISTANCE, m[c])) d[c] &= ~MK;
+            }
         }
     }
 #pragma unroll
-    for (int c = 0; c < 8; c++) v[c] = (m[c] << 24) | nd[c];
+    for (int c = 0; c < 8; c++) v[c] = (m[c] << 24) | d[c];
+    return true;
 }
 
 // set_data's guard (:53-54): voxels whose ORIGINAL material is OOB / AIR_OOB are never modified.
@@ -114,10 +182,9 @@ __device__ __forceinline__ uint32_t keep_guard(uint32_t og, uint32_t nv) {
     return (om == MAT_OOB || om == MAT_AIR_OOB) ? og : nv;
 }
 
-// s_slot[n] of the tiled kernel: pool slot of neighbour chunk n (bit2 = +x, bit1 = +y, bit0 = +z), or
-// 0 / 1 for "every voxel is MAT_OOB<<24" (out of window, or table value 0) / "every voxel is
-// MAT_AIR_OOB<<24" (table value 1). Sentinel slots 0 and 1 are never written by any kernel, so they
-// are folded to constants: not loaded, not stored.
+// Slot of neighbour chunk, or 0 / 1 for "every voxel is MAT_OOB<<24" (out of window, or table value
+// 0) / "every voxel is MAT_AIR_OOB<<24" (table value 1). Sentinel slots 0 and 1 are never written
+// by any kernel, so they are folded to constants: not loaded, not stored.
 __device__ __forceinline__ uint32_t slot_const(uint32_t slot) { return slot == 1 ? VOX_AIR_OOB : VOX_OOB; }
 
 __device__ __forceinline__ uint32_t resolve_chunk(const World& w, uint32_t cx, uint32_t cy, uint32_t cz) {
@@ -127,21 +194,45 @@ __device__ __forceinline__ uint32_t resolve_chunk(const World& w, uint32_t cx, u
     return table_lookup(w, cx, cy, cz);
 }
 
+// ---- cp.async (LDGSTS) helpers ----
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async4(void* smem, const void* gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory");
+}
+
+constexpr int UPD_THREADS = 256;
+constexpr int UPD_STAGES = 4;            // chunks in flight per CTA = UPD_STAGES - 1
+constexpr int UPD_NSLOT = UPD_STAGES + 1;  // slot-table ring: chunks t .. t+STAGES-1 live, t+STAGES being written
+
+struct UpdStage {
+    uint4 a[4][UPD_THREADS];          // [(i,j)][thread]: the thread's aligned 16-byte vector of column (i,j)
+    uint32_t zx[4][UPD_THREADS / 4];  // [(i,j)][thread/4]: straddled voxel z == 16 (threads with tzq == 3, offset.z == 1)
+};
+struct UpdSmem {
+    UpdStage stage[UPD_STAGES];
+    uint32_t slot[UPD_NSLOT][8];
+    uint32_t flags[2];
+};
+
 // PHASE bit0 = offset.x, bit1 = offset.y, bit2 = offset.z. ELIDE: skip stores of unchanged vectors.
 template <int PHASE, bool ELIDE>
-__global__ void __launch_bounds__(256, 3) k_voxel_update_tiled(World w, const uint4* __restrict__ chunk_updates,
-                                                               uint32_t* __restrict__ flags_out) {
+__global__ void __launch_bounds__(UPD_THREADS, 3) k_voxel_update_tiled(World w, const uint4* __restrict__ chunk_updates, uint32_t n_items,
+                                                                       uint32_t* __restrict__ flags_out) {
     constexpr int OX = PHASE & 1, OY = (PHASE >> 1) & 1, OZ = (PHASE >> 2) & 1;
-    __shared__ uint32_t s_slot[8];
-    __shared__ uint32_t s_flags;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    UpdSmem& sm = *reinterpret_cast<UpdSmem*>(smem_raw);
 
     const uint32_t tid = threadIdx.x;
-    if (tid < 8) {
-        const uint4 e = chunk_updates[blockIdx.x];
-        s_slot[tid] = resolve_chunk(w, e.x + ((tid >> 2) & 1), e.y + ((tid >> 1) & 1), e.z + (tid & 1));
-    }
-    if (tid == 8) s_flags = 0;
-    __syncthreads();
+    const uint32_t G = gridDim.x;
+    if (blockIdx.x >= n_items) return;
+    const uint32_t T = (n_items - blockIdx.x + G - 1) / G;  // work items of this CTA: blockIdx.x + t*G
 
     const int tzq = tid & 3, ty = (tid >> 2) & 7, tx = tid >> 5;
     const int Z0 = 4 * tzq + OZ;
@@ -150,105 +241,205 @@ __global__ void __launch_bounds__(256, 3) k_voxel_update_tiled(World w, const ui
     auto rowoff = [&](int i, int j) { return (uint32_t)((((2 * tx + OX + i) & 15) << 8) | (((2 * ty + OY + j) & 15) << 4)); };
     auto slot_ptr = [&](uint32_t slot, uint32_t off) { return w.pool + ((size_t)slot << 12) + off; };
 
-    uint32_t v[2][2][4];  // originals
-
+    // resolve the 2x2x2 slot neighbourhood of work item t (lane n of 8): list entry -> table lookup
+    auto resolve = [&](uint32_t t, uint32_t n) -> uint32_t {
+        if (t >= T) return 0;
+        const uint4 e = chunk_updates[blockIdx.x + t * G];
+        return resolve_chunk(w, e.x + ((n >> 2) & 1), e.y + ((n >> 1) & 1), e.z + (n & 1));
+    };
+    // issue this thread's copies of work item t into its ring stage (always commits one group)
+    auto issue = [&](uint32_t t) {
+        if (t < T) {
+            UpdStage& st = sm.stage[t % UPD_STAGES];
+            const uint32_t* sl = sm.slot[t % UPD_NSLOT];
 #pragma unroll
-    for (int i = 0; i < 2; i++) {
+            for (int i = 0; i < 2; i++) {
 #pragma unroll
-        for (int j = 0; j < 2; j++) {
-            const int n = nsel(i, j);
-            const uint32_t row = rowoff(i, j);
-            const uint32_t slot = s_slot[n];
-            uint4 A;
-            if (slot >= 2) {
-                A = *reinterpret_cast<const uint4*>(slot_ptr(slot, row + 4 * tzq));
-            } else {
-                const uint32_t c = slot_const(slot);
-                A = make_uint4(c, c, c, c);
-            }
-            if (OZ == 0) {
-                v[i][j][0] = A.x; v[i][j][1] = A.y; v[i][j][2] = A.z; v[i][j][3] = A.w;
-            } else {
-                uint32_t next = __shfl_down_sync(0xFFFFFFFFu, A.x, 1);
-                if (tzq == 3) {  // z == 16: first voxel of the row in the +z neighbour chunk
-                    const uint32_t zslot = s_slot[n | 1];
-                    next = zslot >= 2 ? *slot_ptr(zslot, row) : slot_const(zslot);
-                }
-                v[i][j][0] = A.y; v[i][j][1] = A.z; v[i][j][2] = A.w; v[i][j][3] = next;
-            }
-        }
-    }
-
-    // two Margolus blocks per thread: z pairs (0,1) and (2,3); set_data's guard and change flags (:51-88)
-    uint32_t r[2][2][4];
-    uint32_t flags = 0;
-#pragma unroll
-    for (int b = 0; b < 2; b++) {
-        uint32_t blk[8];
-#pragma unroll
-        for (int c = 0; c < 8; c++) blk[c] = v[c >> 2][(c >> 1) & 1][2 * b + (c & 1)];
-        margolus_block<OY>(blk);
-#pragma unroll
-        for (int c = 0; c < 8; c++) {
-            const int i = c >> 2, j = (c >> 1) & 1, z = 2 * b + (c & 1);
-            const uint32_t og = v[i][j][z];
-            const uint32_t nv = keep_guard(og, blk[c]);
-            r[i][j][z] = nv;
-            if (nv != og) {
-                const int X = 2 * tx + OX + i, Y = 2 * ty + OY + j, Z = Z0 + z;
-                flags |= 1u | (X == 0 ? 2u : 0u) | (Y == 0 ? 4u : 0u) | (Z == 0 ? 8u : 0u) | (X >= 15 ? 0x10u : 0u) |
-                         (Y >= 15 ? 0x20u : 0u) | (Z >= 15 ? 0x40u : 0u);
-            }
-        }
-    }
-
-    // write-back (imageStore :87 is unconditional; constants/sentinels are never stored)
-#pragma unroll
-    for (int i = 0; i < 2; i++) {
-#pragma unroll
-        for (int j = 0; j < 2; j++) {
-            const int n = nsel(i, j);
-            const uint32_t row = rowoff(i, j);
-            const uint32_t slot = s_slot[n];
-            if (OZ == 0) {
-                if (slot >= 2) {
-                    const bool same = r[i][j][0] == v[i][j][0] && r[i][j][1] == v[i][j][1] && r[i][j][2] == v[i][j][2] &&
-                                      r[i][j][3] == v[i][j][3];
-                    if (!(ELIDE && same))
-                        *reinterpret_cast<uint4*>(slot_ptr(slot, row + 4 * tzq)) = make_uint4(r[i][j][0], r[i][j][1], r[i][j][2], r[i][j][3]);
-                }
-            } else {
-                // element z = 4*tzq of the aligned vector is the previous lane's last voxel
-                const uint32_t prev = __shfl_up_sync(0xFFFFFFFFu, r[i][j][3], 1);
-                bool prev_same = true;
-                if (ELIDE) prev_same = __shfl_up_sync(0xFFFFFFFFu, (int)(r[i][j][3] == v[i][j][3]), 1) != 0;
-                if (slot >= 2) {
-                    const bool same = r[i][j][0] == v[i][j][0] && r[i][j][1] == v[i][j][1] && r[i][j][2] == v[i][j][2];
-                    if (tzq > 0) {
-                        if (!(ELIDE && same && prev_same))
-                            *reinterpret_cast<uint4*>(slot_ptr(slot, row + 4 * tzq)) = make_uint4(prev, r[i][j][0], r[i][j][1], r[i][j][2]);
-                    } else if (!(ELIDE && same)) {
-                        // z == 0 of this row belongs to the -z neighbour's CTA in this phase
-                        *slot_ptr(slot, row + 1) = r[i][j][0];
-                        *reinterpret_cast<uint2*>(slot_ptr(slot, row + 2)) = make_uint2(r[i][j][1], r[i][j][2]);
+                for (int j = 0; j < 2; j++) {
+                    const int n = nsel(i, j);
+                    const uint32_t row = rowoff(i, j);
+                    const uint32_t slot = sl[n];
+                    if (slot >= 2) {
+                        cp_async16(&st.a[i * 2 + j][tid], slot_ptr(slot, row + 4 * tzq));
+                    } else {
+                        const uint32_t c = slot_const(slot);
+                        st.a[i * 2 + j][tid] = make_uint4(c, c, c, c);
+                    }
+                    if (OZ == 1 && tzq == 3) {  // z == 16: first voxel of the row in the +z neighbour chunk
+                        const uint32_t zslot = sl[n | 1];
+                        if (zslot >= 2) cp_async4(&st.zx[i * 2 + j][tid >> 2], slot_ptr(zslot, row));
+                        else st.zx[i * 2 + j][tid >> 2] = slot_const(zslot);
                     }
                 }
-                if (tzq == 3) {
-                    const uint32_t zslot = s_slot[n | 1];
-                    if (zslot >= 2 && !(ELIDE && r[i][j][3] == v[i][j][3])) *slot_ptr(zslot, row) = r[i][j][3];
+            }
+        }
+        cp_async_commit();
+    };
+
+    // ---- prologue: slot tables of the first STAGES items, copies of the first STAGES-1 ----
+    if (tid < 8 * UPD_STAGES) sm.slot[tid >> 3][tid & 7] = resolve(tid >> 3, tid & 7);
+    if (tid < 2) sm.flags[tid] = 0;
+    __syncthreads();
+#pragma unroll
+    for (int t = 0; t < UPD_STAGES - 1; t++) issue(t);
+
+    for (uint32_t t = 0; t < T; t++) {
+        // slots of item t+STAGES (consumed by issue() one iteration later): loads start now, the
+        // result is only touched at the end of the iteration
+        uint32_t pend = 0;
+        if (tid < 8) pend = resolve(t + UPD_STAGES, tid);
+        issue(t + UPD_STAGES - 1);
+        cp_async_wait<UPD_STAGES - 1>();  // this thread's copies of item t have landed
+
+        const UpdStage& st = sm.stage[t % UPD_STAGES];
+        const uint32_t* sl = sm.slot[t % UPD_NSLOT];
+        uint32_t v[2][2][4];  // originals
+#pragma unroll
+        for (int i = 0; i < 2; i++) {
+#pragma unroll
+            for (int j = 0; j < 2; j++) {
+                const uint4 A = st.a[i * 2 + j][tid];
+                if (OZ == 0) {
+                    v[i][j][0] = A.x; v[i][j][1] = A.y; v[i][j][2] = A.z; v[i][j][3] = A.w;
+                } else {
+                    uint32_t next = __shfl_down_sync(0xFFFFFFFFu, A.x, 1);
+                    if (tzq == 3) next = st.zx[i * 2 + j][tid >> 2];
+                    v[i][j][0] = A.y; v[i][j][1] = A.z; v[i][j][2] = A.w; v[i][j][3] = next;
                 }
             }
         }
-    }
 
-    flags = __reduce_or_sync(0xFFFFFFFFu, flags);
-    if ((tid & 31) == 0 && flags) atomicOr(&s_flags, flags);
-    __syncthreads();
-    if (tid == 0) flags_out[blockIdx.x] = s_flags;
+        // two Margolus blocks per thread: z pairs (0,1) and (2,3); set_data's guard and change flags (:51-88)
+        uint32_t r[2][2][4];
+        uint32_t flags = 0;
+#pragma unroll
+        for (int b = 0; b < 2; b++) {
+            uint32_t blk[8];
+#pragma unroll
+            for (int c = 0; c < 8; c++) blk[c] = v[c >> 2][(c >> 1) & 1][2 * b + (c & 1)];
+            const bool touched = margolus_block<OY>(blk);
+#pragma unroll
+            for (int c = 0; c < 8; c++) r[c >> 2][(c >> 1) & 1][2 * b + (c & 1)] = blk[c];
+            if (touched) {
+#pragma unroll
+                for (int c = 0; c < 8; c++) {
+                    const int i = c >> 2, j = (c >> 1) & 1, z = 2 * b + (c & 1);
+                    const uint32_t og = v[i][j][z];
+                    const uint32_t nv = keep_guard(og, blk[c]);
+                    r[i][j][z] = nv;
+                    if (nv != og) {
+                        const int X = 2 * tx + OX + i, Y = 2 * ty + OY + j, Z = Z0 + z;
+                        flags |= 1u | (X == 0 ? 2u : 0u) | (Y == 0 ? 4u : 0u) | (Z == 0 ? 8u : 0u) | (X >= 15 ? 0x10u : 0u) |
+                                 (Y >= 15 ? 0x20u : 0u) | (Z >= 15 ? 0x40u : 0u);
+                    }
+                }
+            }
+        }
+
+        // write-back (imageStore :87 is unconditional; constants/sentinels are never stored)
+#pragma unroll
+        for (int i = 0; i < 2; i++) {
+#pragma unroll
+            for (int j = 0; j < 2; j++) {
+                const int n = nsel(i, j);
+                const uint32_t row = rowoff(i, j);
+                const uint32_t slot = sl[n];
+                if (OZ == 0) {
+                    if (slot >= 2) {
+                        const bool same = r[i][j][0] == v[i][j][0] && r[i][j][1] == v[i][j][1] && r[i][j][2] == v[i][j][2] &&
+                                          r[i][j][3] == v[i][j][3];
+                        if (!(ELIDE && same))
+                            *reinterpret_cast<uint4*>(slot_ptr(slot, row + 4 * tzq)) = make_uint4(r[i][j][0], r[i][j][1], r[i][j][2], r[i][j][3]);
+                    }
+                } else {
+                    // element z = 4*tzq of the aligned vector is the previous lane's last voxel
+                    const uint32_t prev = __shfl_up_sync(0xFFFFFFFFu, r[i][j][3], 1);
+                    bool prev_same = true;
+                    if (ELIDE) prev_same = __shfl_up_sync(0xFFFFFFFFu, (int)(r[i][j][3] == v[i][j][3]), 1) != 0;
+                    if (slot >= 2) {
+                        const bool same = r[i][j][0] == v[i][j][0] && r[i][j][1] == v[i][j][1] && r[i][j][2] == v[i][j][2];
+                        if (tzq > 0) {
+                            if (!(ELIDE && same && prev_same))
+                                *reinterpret_cast<uint4*>(slot_ptr(slot, row + 4 * tzq)) = make_uint4(prev, r[i][j][0], r[i][j][1], r[i][j][2]);
+                        } else if (!(ELIDE && same)) {
+                            // z == 0 of this row belongs to the -z neighbour's work item in this phase
+                            *slot_ptr(slot, row + 1) = r[i][j][0];
+                            *reinterpret_cast<uint2*>(slot_ptr(slot, row + 2)) = make_uint2(r[i][j][1], r[i][j][2]);
+                        }
+                    }
+                    if (tzq == 3) {
+                        const uint32_t zslot = sl[n | 1];
+                        if (zslot >= 2 && !(ELIDE && r[i][j][3] == v[i][j][3])) *slot_ptr(zslot, row) = r[i][j][3];
+                    }
+                }
+            }
+        }
+
+        flags = __reduce_or_sync(0xFFFFFFFFu, flags);
+        if ((tid & 31) == 0 && flags) atomicOr(&sm.flags[t & 1], flags);
+        if (tid < 8) sm.slot[(t + UPD_STAGES) % UPD_NSLOT][tid] = pend;
+        __syncthreads();
+        if (tid == 0) {
+            flags_out[blockIdx.x + t * G] = sm.flags[t & 1];
+            sm.flags[t & 1] = 0;  // next written in iteration t+2, after the barrier of t+1
+        }
+    }
+    cp_async_wait<0>();
 }
 
 // Reference-shaped variant: one thread per 2x2x2 block, every voxel through get_data (window test
-// + table lookup + scalar load), as compute_voxel.glsl does. Kept as the profiling baseline.
+// + table lookup + scalar load) and the shader's straight-line block logic, as compute_voxel.glsl
+// does. Kept as the profiling baseline and as a second implementation for cross-checks.
+__device__ void margolus_block_reference(uint32_t (&v)[8], const uint32_t py) {
+    uint32_t m[8], d[8];
+    for (int c = 0; c < 8; c++) {
+        m[c] = v[c] >> 24;
+        d[c] = v[c] & 0xFFFFFFu;
+    }
+    for (int c = 0; c < 8; c++)
+        if (mat_in(MASK_DATA_DAMAGE, m[c]) && d[c] >= (m[c] == MAT_STONE ? 10u : 5u)) {
+            m[c] = MAT_AIR;
+            d[c] = 0;
+        }
+    auto fall = [&](int b, int t) {
+        if (m[b] == MAT_AIR && m[t] == MAT_WATER) {
+            m[b] = MAT_WATER; d[b] = 0;
+            m[t] = MAT_AIR; d[t] = 0;
+        }
+    };
+    for (int i = 0; i < 2; i++)
+        for (int k = 0; k < 2; k++) fall(cidx(i, 0, k), cidx(i, 1, k));
+    for (int i = 0; i < 2; i++)
+        for (int k = 0; k < 2; k++) fall(cidx(1 - i, 0, k), cidx(i, 1, k));
+    for (int i = 0; i < 2; i++)
+        for (int k = 0; k < 2; k++) fall(cidx(i, 0, 1 - k), cidx(i, 1, k));
+    for (int i = 0; i < 2; i++) fall(cidx(py, 1, i), cidx(1 - py, 1, i));
+    for (int i = 0; i < 2; i++) fall(cidx(i, 1, py), cidx(i, 1, 1 - py));
+    uint32_t nd[8];
+    for (int c = 0; c < 8; c++) {
+        const int i = c >> 2, j = (c >> 1) & 1, k = c & 1;
+        const int shift = 3 * ((k << 2) | (j << 1) | i);
+        nd[c] = d[c];
+        const bool is_air = m[c] == MAT_AIR;
+        if (is_air || mat_in(MASK_DATA_DISTANCE, m[c])) {
+            uint32_t r = 7u;
+            bool blocked = false;
+            const uint32_t own = (d[c] >> shift) & 7u;
+            for (int o = 0; o < 8; o++) {
+                if (o == c) continue;
+                const uint32_t mo = m[o];
+                if (mo == MAT_OOB) r = min(r, own);
+                else if (is_air ? (mo == MAT_AIR) : (mo == m[c])) r = min(r, ((d[o] >> shift) & 7u) + 1u);
+                else if (is_air && mo == MAT_AIR_OOB) {}
+                else blocked = true;
+            }
+            if (blocked) r = 0u;
+            nd[c] = (d[c] & ~(7u << shift)) | (r << shift);
+        }
+    }
+    for (int c = 0; c < 8; c++) v[c] = (m[c] << 24) | nd[c];
+}
+
 __global__ void __launch_bounds__(512) k_voxel_update_gather(World w, const uint4* __restrict__ chunk_updates,
                                                              uint32_t* __restrict__ flags_out, uint32_t ox, uint32_t oy, uint32_t oz) {
     __shared__ uint32_t s_flags;
@@ -264,7 +455,7 @@ __global__ void __launch_bounds__(512) k_voxel_update_gather(World w, const uint
         og[c] = get_data(w, px + (c >> 2), py + ((c >> 1) & 1), pz + (c & 1));
         blk[c] = og[c];
     }
-    if (oy) margolus_block<1>(blk); else margolus_block<0>(blk);
+    margolus_block_reference(blk, oy);
     uint32_t flags = 0;
 #pragma unroll
     for (int c = 0; c < 8; c++) {
@@ -284,17 +475,36 @@ __global__ void __launch_bounds__(512) k_voxel_update_gather(World w, const uint
     if (tid == 0) flags_out[blockIdx.x] = s_flags;
 }
 
+template <int PHASE, bool ELIDE>
+static cudaError_t launch_one(const World& w, const uint4* list, uint32_t n, uint32_t* flags, cudaStream_t st) {
+    static int grid_cap = 0;  // per instantiation: SMs x resident CTAs (one device model per process)
+    auto kern = k_voxel_update_tiled<PHASE, ELIDE>;
+    if (grid_cap == 0) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UpdSmem));
+        if (e != cudaSuccess) return e;
+        int dev = 0, sms = 0, per_sm = 0;
+        if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
+        if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+        if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, UPD_THREADS, sizeof(UpdSmem))) != cudaSuccess) return e;
+        if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+        grid_cap = sms * per_sm;
+    }
+    const uint32_t grid = n < (uint32_t)grid_cap ? n : (uint32_t)grid_cap;
+    kern<<<grid, UPD_THREADS, sizeof(UpdSmem), st>>>(w, list, n, flags);
+    return cudaGetLastError();
+}
+
 template <bool ELIDE>
-static void launch_tiled(int phase, const World& w, const uint4* list, uint32_t n, uint32_t* flags, cudaStream_t st) {
+static cudaError_t launch_tiled(int phase, const World& w, const uint4* list, uint32_t n, uint32_t* flags, cudaStream_t st) {
     switch (phase) {
-        case 0: k_voxel_update_tiled<0, ELIDE><<<n, 256, 0, st>>>(w, list, flags); break;
-        case 1: k_voxel_update_tiled<1, ELIDE><<<n, 256, 0, st>>>(w, list, flags); break;
-        case 2: k_voxel_update_tiled<2, ELIDE><<<n, 256, 0, st>>>(w, list, flags); break;
-        case 3: k_voxel_update_tiled<3, ELIDE><<<n, 256, 0, st>>>(w, list, flags); break;
-        case 4: k_voxel_update_tiled<4, ELIDE><<<n, 256, 0, st>>>(w, list, flags); break;
-        case 5: k_voxel_update_tiled<5, ELIDE><<<n, 256, 0, st>>>(w, list, flags); break;
-        case 6: k_voxel_update_tiled<6, ELIDE><<<n, 256, 0, st>>>(w, list, flags); break;
-        default: k_voxel_update_tiled<7, ELIDE><<<n, 256, 0, st>>>(w, list, flags); break;
+        case 0: return launch_one<0, ELIDE>(w, list, n, flags, st);
+        case 1: return launch_one<1, ELIDE>(w, list, n, flags, st);
+        case 2: return launch_one<2, ELIDE>(w, list, n, flags, st);
+        case 3: return launch_one<3, ELIDE>(w, list, n, flags, st);
+        case 4: return launch_one<4, ELIDE>(w, list, n, flags, st);
+        case 5: return launch_one<5, ELIDE>(w, list, n, flags, st);
+        case 6: return launch_one<6, ELIDE>(w, list, n, flags, st);
+        default: return launch_one<7, ELIDE>(w, list, n, flags, st);
     }
 }
 
@@ -305,12 +515,10 @@ cudaError_t launch_voxel_update(const World& w, const uint32_t* chunk_updates, u
     const int phase = (offset[0] & 1) | ((offset[1] & 1) << 1) | ((offset[2] & 1) << 2);
     if (variant == 1) {
         k_voxel_update_gather<<<n, 512, 0, st>>>(w, list, flags_out, offset[0] & 1, offset[1] & 1, offset[2] & 1);
-    } else if (variant == 2) {
-        launch_tiled<true>(phase, w, list, n, flags_out, st);
-    } else {
-        launch_tiled<false>(phase, w, list, n, flags_out, st);
+        return cudaGetLastError();
     }
-    return cudaGetLastError();
+    if (variant == 2) return launch_tiled<true>(phase, w, list, n, flags_out, st);
+    return launch_tiled<false>(phase, w, list, n, flags_out, st);
 }
 
 }  // namespace vxb
