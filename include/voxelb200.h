@@ -144,7 +144,8 @@ int vxb_create(const vxb_settings* settings, int device, vxb_ctx** out);
 void vxb_destroy(vxb_ctx* ctx);
 /* Message of the last failing call on this ctx (or of the last failing vxb_create when ctx is NULL). */
 const char* vxb_last_error(const vxb_ctx* ctx);
-/* Launch all further work of this ctx on `cuda_stream` (a cudaStream_t; NULL = the ctx's own stream). */
+/* Launch all further work of this ctx on `cuda_stream` (a cudaStream_t). A new ctx works on its own
+ * non-blocking stream; NULL here selects CUDA's legacy default stream. Synchronises the old stream. */
 int vxb_set_stream(vxb_ctx* ctx, void* cuda_stream);
 int vxb_synchronize(vxb_ctx* ctx);
 

@@ -1,0 +1,16 @@
+import csv, subprocess, sys
+rep=sys.argv[1]
+raw=subprocess.run(['ncu','-i',rep,'--page','raw','--csv'],capture_output=True,text=True).stdout
+rows=list(csv.reader(raw.splitlines()))
+hdr=rows[0]; units=rows[1]; idx={h:i for i,h in enumerate(hdr)}
+want=['gpu__time_duration.sum','dram__bytes_read.sum','dram__bytes_write.sum','gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed','smsp__inst_executed.sum','sm__inst_executed.avg.per_cycle_elapsed','sm__warps_active.avg.pct_of_peak_sustained_active','launch__registers_per_thread','launch__grid_size','launch__occupancy_limit_registers','launch__occupancy_limit_shared_mem','smsp__issue_active.avg.pct_of_peak_sustained_active','lts__t_sector_hit_rate.pct','l1tex__t_sector_hit_rate.pct','sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active','sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active','sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active','lts__throughput.avg.pct_of_peak_sustained_elapsed','l1tex__throughput.avg.pct_of_peak_sustained_elapsed','smsp__warps_eligible.avg.per_cycle_active','l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum','lts__t_sectors_srcunit_tex_op_read.sum','lts__t_sectors_srcunit_tex_op_write.sum']
+for r in rows[2:]:
+    print('====', r[idx['Kernel Name']][:90])
+    for w in want:
+        if w in idx: print('  %-70s %s %s'%(w, r[idx[w]], units[idx[w]]))
+    vals=[]
+    for h in hdr:
+        if h.startswith('smsp__average_warps_issue_stalled') and h.endswith('per_issue_active.ratio'):
+            try: vals.append((float(r[idx[h]]),h))
+            except: pass
+    print('  stalls:', ', '.join('%s=%.2f'%(h.replace('smsp__average_warps_issue_stalled_','').replace('_per_issue_active.ratio',''),v) for v,h in sorted(vals,reverse=True)[:7]))

@@ -2,7 +2,7 @@ import sys, numpy as np, torch
 sys.path.insert(0,'/root/repo')
 import voxel_game_b200 as vg
 import bench
-RS=(16,16,256); SP=bench.C3_SP
+RS=(32,16,256); SP=bench.C3_SP
 n=RS[0]*RS[1]*RS[2]
 gs=vg.GameSettings(render_size=RS,max_loaded_chunks=2+n,max_worldgen_rate=8*32768,max_update_rate=1024)
 gpu=vg.VoxelComputePipeline(gs)
@@ -11,7 +11,8 @@ bench.generate_world(gpu,SP,chunks,2,True,torch)
 lst=np.concatenate([chunks,np.zeros((n,1),np.int64)],1).astype(np.uint32)
 gpu.update_list_upload(lst)
 gpu.set_update_kernel(int(sys.argv[1]) if len(sys.argv)>1 else 0)
-for t in range(16): gpu.update_list_run(SP,bench.PHASES[t%8])
+settle=int(sys.argv[2]) if len(sys.argv)>2 else 96
+for t in range(settle): gpu.update_list_run(SP,bench.PHASES[t%8])
 gpu.update_list_run(SP,(0,0,0))
 gpu.update_list_run(SP,(1,1,1))
 gpu.synchronize()

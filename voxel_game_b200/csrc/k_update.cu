@@ -15,7 +15,8 @@
 //    table and the change flags. The dependent chain list entry -> chunk table -> voxels is taken
 //    off the critical path: 8 lanes resolve the 2x2x2 slot neighbourhood 4 chunks ahead.
 //  * in-chunk layout is x*256 + y*16 + z: 4 consecutive z are one aligned 16-byte vector and a warp
-//    covers 8 full 64-byte rows per copy instruction (every 32-byte sector fully used).
+//    covers 8 full 64-byte rows per copy instruction (every 32-byte sector fully used). A warp is a
+//    16 x 2 x 16-voxel horizontal slab so that mostly-horizontal surfaces touch few warps.
 //  * phase shift in z (offset.z == 1) breaks the 16-byte alignment; the thread still copies/stores
 //    its ALIGNED vector and exchanges the boundary element with the neighbouring lane by warp
 //    shuffle; only z == 0 of the row (owned by the -z neighbour's work item in this phase) and
@@ -234,7 +235,12 @@ __global__ void __launch_bounds__(UPD_THREADS, 3) k_voxel_update_tiled(World w, 
     if (blockIdx.x >= n_items) return;
     const uint32_t T = (n_items - blockIdx.x + G - 1) / G;  // work items of this CTA: blockIdx.x + t*G
 
-    const int tzq = tid & 3, ty = (tid >> 2) & 7, tx = tid >> 5;
+    // warp = one ty: a 16 x 2 x 16-voxel horizontal slab. Terrain and water surfaces are mostly
+    // horizontal, so few warps of a chunk contain them and leave the block fast paths.
+    // (Tried and rejected: per-warp slot tables + global flag atomics to drop the per-chunk CTA
+    // barrier — warps of a CTA drift apart, their partial-sector stores no longer merge in L2 and
+    // the y/z-shifted phases lose 15-20 %.)
+    const int tzq = tid & 3, tx = (tid >> 2) & 7, ty = tid >> 5;
     const int Z0 = 4 * tzq + OZ;
     // (i,j) column of this thread: neighbour-chunk selector and in-chunk row offset (z = 0)
     auto nsel = [&](int i, int j) { return (((2 * tx + OX + i) >> 4) << 2) | (((2 * ty + OY + j) >> 4) << 1); };

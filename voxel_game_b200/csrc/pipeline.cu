@@ -272,7 +272,7 @@ int vxb_set_stream(vxb_ctx* ctx, void* cuda_stream) {
     if (!ctx) return VXB_ERR_INVALID;
     VXB_CUDA(ctx, cudaSetDevice(ctx->device));
     VXB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+    ctx->stream = (cudaStream_t)cuda_stream;  // NULL is CUDA's legacy default stream, not the ctx's own
     return VXB_OK;
 }
 
