@@ -255,6 +255,27 @@ int vxb_ray_results(vxb_ctx* ctx, vxb_ray_buffers* out);
 int vxb_ray_download(vxb_ctx* ctx, float* pos, float* normal, uint32_t* voxel, float* ldist, uint32_t* leaving,
                      uint32_t* layer_count, float* dist, uint64_t* total_iterations);
 
+/* Has no counterpart in the reference. Same single-hit ray queries as vxb_raymarch_rays with kind
+ * 1, 2 or 3, for callers that must not allocate when they ask: a fixed-rate simulation thread (a
+ * cudaMalloc there stalls every stream of the device), a host that gave all device memory to its own
+ * pool at start-up, or code that runs while a stream is being captured. This entry point calls no
+ * cudaMalloc / cudaFree and no allocating library routine. Its device staging is a fixed array inside
+ * the library image (about 1.1 MB, held by every GPU that loads the library until the process
+ * exits), so one call takes at most VXB_NOALLOC_MAX_RAYS rays; more is rejected with VXB_ERR_INVALID.
+ *  - pos, dir: HOST arrays [n][3]. Outputs are HOST arrays and may each be NULL: out_pos and
+ *    out_normal are component-major ([c*n + i], c = 0..2; normal is only meaningful for kind 1),
+ *    out_voxel / out_ldist per ray, out_light = passthrough_light (kinds 2, 3).
+ *  - Synchronises the ctx stream before returning.
+ *  - The first call on a device looks up that device's address of the array; make that first call
+ *    before any stream capture begins.
+ *  - All calls share the one array per GPU and it keeps the previous call's contents (the call
+ *    clears the one counter that must start at zero). Two calls that overlap on the same GPU, from
+ *    different ctxs or streams, race on it: issue them one after the other. */
+#define VXB_NOALLOC_MAX_RAYS 16384u
+int vxb_raymarch_rays_noalloc(vxb_ctx* ctx, const uint32_t start_pos[3], const float (*pos)[3], const float (*dir)[3], uint32_t n,
+                              int kind, uint32_t max_iterations, uint32_t projectile_count, float* out_pos, float* out_normal,
+                              uint32_t* out_voxel, float* out_ldist, float* out_light);
+
 /* ---- bulk test / checkpoint hooks (no reference analogue) --------------------------------------- */
 int vxb_read_pool(vxb_ctx* ctx, uint64_t first_slot, uint64_t n_slots, uint32_t* out);
 int vxb_write_pool(vxb_ctx* ctx, uint64_t first_slot, uint64_t n_slots, const uint32_t* in);

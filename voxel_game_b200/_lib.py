@@ -143,6 +143,7 @@ SIGNATURES = {
     "vxb_raymarch_rays": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_u64, ctypes.c_int, c_u32, c_u32]),
     "vxb_ray_results": (ctypes.c_int, [c_vp, ctypes.POINTER(RayBuffers)]),
     "vxb_ray_download": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "vxb_raymarch_rays_noalloc": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_u32, ctypes.c_int, c_u32, c_u32, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "vxb_read_pool": (ctypes.c_int, [c_vp, c_u64, c_u64, c_vp]),
     "vxb_write_pool": (ctypes.c_int, [c_vp, c_u64, c_u64, c_vp]),
     "vxb_read_table": (ctypes.c_int, [c_vp, c_vp]),

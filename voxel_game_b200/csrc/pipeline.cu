@@ -950,3 +950,16 @@ int vxb_world_checksum(vxb_ctx* c, const uint32_t start_pos[3], uint64_t* out) {
 
 }  // extern "C"
 #pragma GCC visibility pop
+
+// Internal accessors for translation units that sit beside this one (the struct stays private here).
+namespace vxb {
+void ctx_view(const vxb_ctx* c, const uint32_t start_pos[3], World* w, cudaStream_t* st, const vxb_projectile** projectiles,
+              size_t* projectile_capacity, int* device) {
+    *w = c->world(start_pos);
+    *st = c->stream;
+    *projectiles = c->projectiles.p;
+    *projectile_capacity = c->projectiles.n;
+    *device = c->device;
+}
+int ctx_fail(vxb_ctx* c, int code, const char* msg) { return fail(c, code, "%s", msg); }
+}  // namespace vxb

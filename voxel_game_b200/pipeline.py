@@ -282,6 +282,24 @@ class VoxelComputePipeline:
             self._lib.vxb_raymarch_rays(self._h, ptr(_u32(start_pos, 3)), ptr(p), ptr(d), p.shape[0], int(kind), int(max_iterations), int(projectile_count))
         )
 
+    def raymarch_rays_noalloc(self, start_pos, pos, dirs, kind, max_iterations, projectile_count=0):
+        """vxb_raymarch_rays_noalloc: single-hit queries (kind 1..3) for callers that must not allocate
+        on the device when they ask (simulation tick, pooled-memory hosts, during stream capture).
+        At most 16384 rays per call. Returns a dict of host arrays: pos/normal [3, n], voxel, ldist, light [n]."""
+        p = np.ascontiguousarray(np.asarray(pos, dtype=np.float32).reshape(-1, 3))
+        d = np.ascontiguousarray(np.asarray(dirs, dtype=np.float32).reshape(-1, 3))
+        assert p.shape == d.shape
+        n = p.shape[0]
+        out = {"pos": np.zeros((3, n), np.float32), "normal": np.zeros((3, n), np.float32), "voxel": np.zeros(n, np.uint32),
+               "ldist": np.zeros(n, np.float32), "light": np.zeros(n, np.float32)}
+        self._check(
+            self._lib.vxb_raymarch_rays_noalloc(
+                self._h, ptr(_u32(start_pos, 3)), ptr(p) if n else None, ptr(d) if n else None, n, int(kind), int(max_iterations),
+                int(projectile_count), ptr(out["pos"]), ptr(out["normal"]), ptr(out["voxel"]), ptr(out["ldist"]), ptr(out["light"]),
+            )
+        )
+        return out
+
     def ray_results(self):
         rb = RayBuffers()
         self._check(self._lib.vxb_ray_results(self._h, ctypes.byref(rb)))
