@@ -163,15 +163,11 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     # ---------------- C3: slab of the 256x16x256-chunk world ----------------
+    from voxel_game_b200.sharding import SlabShard, halo_exchange
+
     RS, SP = tuple(args.world), C3_SP
-    assert RS[0] % world_size == 0, "x extent must divide by the GPU count"
-    cols = RS[0] // world_size
-    x0 = rank * cols
-    ghost = 1 if rank < world_size - 1 else 0
-    lrs = (cols + ghost, RS[1], RS[2])
-    lsp = (SP[0] + x0, SP[1], SP[2])
-    n_local = lrs[0] * lrs[1] * lrs[2]
-    n_own = cols * RS[1] * RS[2]
+    shard = SlabShard(RS, SP, rank, world_size)
+    cols, ghost, lrs, lsp, n_local, n_own = shard.cols, shard.ghost, shard.local_render_size, shard.local_start_pos, shard.n_local, shard.n_own
     gs = vg.GameSettings(render_size=lrs, max_loaded_chunks=2 + n_local, max_worldgen_rate=8 * 32768, max_update_rate=1024)
     gpu = vg.VoxelComputePipeline(gs, device=local_rank)
     gpu.set_stream(stream.cuda_stream)
@@ -180,46 +176,31 @@ def run_ours(args):
     own_list = np.concatenate([chunks[:n_own], np.zeros((n_own, 1), np.int64)], 1).astype(np.uint32)
     gpu.update_list_upload(own_list)
     gpu.set_update_kernel(args.variant)
-    # settle: run the automaton until the distance fields have propagated (<= 7 per 8 phases) so the
-    # timed steps see the steady state of a running game, not the first ticks after worldgen
-    for i in range(args.settle):
-        gpu.update_list_run(lsp, PHASES[i % 8])
-    torch.cuda.synchronize()
 
-    # halo planes: x == 0 plane of a chunk is its first 256 words; column c of the local window
-    # holds slots 2 + c*plane_chunks ... (x-major slot assignment above)
-    plane_chunks = RS[1] * RS[2]
+    # halo planes as strided views of the pool (slots follow the local window in (x,y,z) order)
     ptrs = gpu.device_ptrs()
     pool_t = torch.as_tensor(DevView(ptrs.voxel_pool, (2 + n_local) * 4096), device="cuda").view(2 + n_local, 4096)
-    first_col = pool_t[2:2 + plane_chunks, :256]
-    ghost_col = pool_t[2 + cols * plane_chunks:2 + (cols + 1) * plane_chunks, :256] if ghost else None
-    sendbuf = torch.empty((plane_chunks, 256), dtype=torch.int32, device="cuda")
-    recvbuf = torch.empty((plane_chunks, 256), dtype=torch.int32, device="cuda")
+    first_col, ghost_col = shard.views(pool_t)
+    sendbuf = torch.empty((shard.plane_chunks, 256), dtype=torch.int32, device="cuda")
+    recvbuf = torch.empty((shard.plane_chunks, 256), dtype=torch.int32, device="cuda")
     launches = [0]
 
     def exchange(pre):
-        """pre: owner of column 0 -> left neighbour's ghost; post: ghost -> owner (right neighbour)."""
-        ops = []
-        if pre:
-            if rank > 0:
-                sendbuf.copy_(first_col)
-                ops.append(dist.P2POp(dist.isend, sendbuf, rank - 1))
-            if ghost:
-                ops.append(dist.P2POp(dist.irecv, recvbuf, rank + 1))
-        else:
-            if ghost:
-                sendbuf.copy_(ghost_col)
-                ops.append(dist.P2POp(dist.isend, sendbuf, rank + 1))
-            if rank > 0:
-                ops.append(dist.P2POp(dist.irecv, recvbuf, rank - 1))
-        if ops:
-            for r in dist.batch_isend_irecv(ops):
-                r.wait()
-        if pre and ghost:
-            ghost_col.copy_(recvbuf)
-        if not pre and rank > 0:
-            first_col.copy_(recvbuf)
-        launches[0] += 2
+        launches[0] += halo_exchange(dist, shard, first_col, ghost_col, sendbuf, recvbuf, pre)
+
+    # settle: run the automaton until the distance fields have propagated (<= 7 per 8 phases) so the
+    # timed steps see the steady state of a running game, not the first ticks after worldgen
+    def settle_step(i):
+        off = PHASES[i % 8]
+        if world_size > 1 and off[0] == 1:
+            exchange(True)
+        gpu.update_list_run(lsp, off)
+        if world_size > 1 and off[0] == 1:
+            exchange(False)
+
+    for i in range(args.settle):
+        settle_step(i)
+    torch.cuda.synchronize()
 
     def step(i):
         off = PHASES[i % 8]
