@@ -150,6 +150,8 @@ def run_ours(args):
         if world_size == 1 and args.gpus > 1:
             raise SystemExit("launch with torch.distributed.run --nproc-per-node %d for --gpus %d" % (args.gpus, args.gpus))
     torch.cuda.set_device(local_rank)
+    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"  # the image's default prints a banner on stdout; stdout carries ONE JSON line
     if world_size > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     # everything (our kernels, torch copies, NCCL, timing events) runs on ONE explicit stream
