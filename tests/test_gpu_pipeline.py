@@ -1,0 +1,94 @@
+"""GPU: the whole compute pass (vxb_compute + host queues + read-back) against the Python restatement
+of the reference's host logic driving the shader oracle, tick by tick: chunk table (device and host
+mirror), voxel pool, queue lengths, dispatch counts, Margolus phase, entities and collisions."""
+import numpy as np
+import pytest
+
+from tests import scenes
+from tests.host_oracle import HostOracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _compare(gpu, ho, tick):
+    assert gpu.last_dispatch_counts() == ho.last_counts, "tick %d counts" % tick
+    assert gpu.queue_set_idx() == list(ho.update_queue.active), "tick %d phase" % tick
+    assert gpu.update_count() == ho.update_count(), "tick %d update_count" % tick
+    assert gpu.worldgen_count() == ho.worldgen_count(), "tick %d worldgen_count" % tick
+    assert gpu.worldgen_capacity() == ho.worldgen_capacity(), "tick %d capacity" % tick
+    assert np.array_equal(gpu.read_table(), ho.world.table), "tick %d device table" % tick
+    rs = ho.rs
+    for x in range(rs[0]):
+        for y in range(rs[1]):
+            for z in range(rs[2]):
+                assert gpu.get_chunk((x, y, z)) == int(ho.cpu_chunks[x, y, z])
+    used = sorted(set(int(v) for v in ho.world.table.reshape(-1) if v >= 2))
+    pool = gpu.read_pool(0, ho.world.pool.shape[0])
+    for s in [0, 1] + used:
+        assert np.array_equal(pool[s], ho.world.pool[s]), "tick %d slot %d" % (tick, s)
+
+
+@pytest.mark.parametrize("world_gen,seed,center", [(0, 0, (10000, 1804, 10000)), (1, 3646, (10040, 1800, 10020))])
+def test_compute_pass_tick_by_tick(world_gen, seed, center):
+    import voxel_game_b200 as vg
+
+    rs = (4, 4, 4)
+    n_slots = 2 + 40  # fewer slots than chunks (64): exercises slot exhaustion and recycling
+    kw = dict(max_worldgen_rate=64, max_update_rate=12)
+    gs = vg.GameSettings(render_size=rs, max_loaded_chunks=n_slots, world_gen=vg.WorldGen(world_gen), world_gen_seed=seed, **kw)
+    gpu = vg.VoxelComputePipeline(gs)
+    ho = HostOracle(rs, n_slots, kw["max_worldgen_rate"], kw["max_update_rate"], world_gen=world_gen, seed=seed)
+    state = vg.GameState(start_pos=vg.initial_start_pos(center, rs))
+    sp = list(state.start_pos)
+    player_pos = [(center[0] + 0.5, center[1] + 6.0, center[2] + 0.5)]
+    players = scenes.players_grid(1, center, 1.0, center[1] + 6.0, seed=1)
+    players["vel"][0, :3] = (1.5, -3.0, 0.5)
+    rng = np.random.RandomState(7)
+
+    gpu.queue_update_from_world_pos(center)  # Game::new, game_manager.rs:63
+    ho.queue_update_from_world_pos(center)
+    for tick in range(40):
+        gpu.push_updates_from_changed(player_pos)  # main.rs:487
+        ho.push_updates_from_changed(player_pos)
+        pc = [int(v) // 16 for v in player_pos[0]]
+        for dx in (-1, 0, 1):                      # main.rs:497-510 (radius 1 here)
+            for dy in (-1, 0, 1):
+                for dz in (-1, 0, 1):
+                    c = (pc[0] + dx, pc[1] + dy, pc[2] + dz)
+                    gpu.ensure_chunk_loaded(c)
+                    ho.ensure_chunk_loaded(c)
+        if tick > 0:
+            g_pr, g_co, g_pl = gpu.download_projectiles()  # main.rs:513
+            o_pr, o_co, o_pl = ho.download_projectiles()
+            if o_pr is not None:
+                assert np.array_equal(g_pr.view(np.uint8), o_pr.view(np.uint8)), "tick %d projectiles" % tick
+                assert np.array_equal(g_co[["id1", "id2", "properties"]], o_co[["id1", "id2", "properties"]])
+            if o_pl is not None:
+                assert np.array_equal(g_pl.view(np.uint8), o_pl.view(np.uint8)), "tick %d players" % tick
+                players = o_pl.copy()
+        if tick in (5, 6, 9, 17):                   # cpu_simulation.rs:580 -> queue_voxel_write
+            for _ in range(5):
+                v = [int(16 * sp[a] + rng.randint(0, 16 * rs[a])) for a in range(3)] + [int(rng.choice([0, 1, 7, 3])) << 24]
+                gpu.queue_voxel_write(v)
+                ho.queue_voxel_write(v)
+            edge = [16 * (sp[0] + 1), 16 * (sp[1] + 1) + 3, 16 * (sp[2] + 2) + 15, 7 << 24]  # on chunk faces: neighbour updates
+            gpu.queue_voxel_write(edge)
+            ho.queue_voxel_write(edge)
+        if tick in (12, 25):                        # main.rs:539-573 -> move_start_pos
+            d = vg.Direction.PosX if tick == 12 else vg.Direction.NegZ
+            gpu.move_start_pos(state, d)
+            sp = ho.move_start_pos(sp, int(d))
+            assert list(state.start_pos) == sp
+        projectiles = None
+        if tick in (8, 9, 20):
+            lo = (16 * sp[0] + 8, center[1] - 6, 16 * sp[2] + 8)
+            hi = (16 * (sp[0] + rs[0]) - 8, center[1] + 12, 16 * (sp[2] + rs[2]) - 8)
+            projectiles = scenes.random_projectiles(200, lo, hi, seed=tick)
+            projectiles["pos"][:20, :3] = players["pos"][0, :3] + rng.randn(20, 3).astype(np.float32)
+        gpu.compute(state, projectiles, players)   # main.rs:575
+        off = ho.compute(sp, projectiles, players)
+        gpu.synchronize()
+        _compare(gpu, ho, tick)
+    # the run exercised every dispatch kind
+    assert ho.worldgen_capacity() < n_slots - 2
+    gpu.close()
