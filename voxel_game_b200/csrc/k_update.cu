@@ -21,8 +21,8 @@
 //    its ALIGNED vector and exchanges the boundary element with the neighbouring lane by warp
 //    shuffle; only z == 0 of the row (owned by the -z neighbour's work item in this phase) and
 //    z == 16 (first voxel of the +z neighbour chunk) use narrower accesses.
-//  * sentinel slots 0/1 (unloaded / all-air) and out-of-window chunks are folded to constants and
-//    are neither loaded nor stored.
+//  * sentinel slots 0/1 (unloaded / all-air; out-of-window resolves to 0) are read like any chunk
+//    (they stay cache-resident) and never stored.
 //  * the reference re-reads every voxel in set_data; here the original stays in registers.
 //  * the shader's straight-line block logic (~200 instructions per voxel) would make the kernel
 //    issue-bound 5x over; margolus_block() classifies the block first (exact, see there).
@@ -38,9 +38,53 @@ constexpr uint32_t BIT_AIR = 1u << MAT_AIR, BIT_OOB = 1u << MAT_OOB, BIT_WATER =
 
 __device__ __forceinline__ uint32_t umin3(uint32_t a, uint32_t b, uint32_t c) { return __vimin3_u32(a, b, c); }
 
-// compute_voxel.glsl:102-207 on one block held in registers; v[cidx(i,j,k)] are voxel words.
-// PY = pos.y % 2 (== offset.y, since 16*chunk.y + 2*lid.y is even).
-// Returns false when the block is provably a fixed point (v is left untouched).
+// :114-163 the five water moves of one block, on bit masks: bit cidx(i,j,k) of `air` / `water`
+// says that the cell holds MAT_AIR / MAT_WATER. A move swaps an air cell b below / beside a water
+// cell t (both lose their data); on the masks that flips bits b and t in both. Returns the new air
+// mask in bits 0-7, the new water mask in bits 8-15 and, in bits 16-23, every cell that took part in
+// a move (a cell can move twice and end as it started, its data is reset all the same).
+// Kept out of line and on scalars: only blocks
+// holding both water and air come here, and inlined on the voxel arrays the moves are if-converted
+// into ~90 always-executed selects.
+template <int PY>
+__device__ __noinline__ uint32_t margolus_water(uint32_t air, uint32_t water) {
+    uint32_t touched = 0;
+#define VXB_FALL(b, t)                                              \
+    {                                                               \
+        const uint32_t c = (air >> (b)) & (water >> (t)) & 1u;      \
+        const uint32_t f = (c << (b)) | (c << (t));                 \
+        air ^= f;                                                   \
+        water ^= f;                                                 \
+        touched |= f;                                               \
+    }
+    // :114-123 straight down
+#pragma unroll
+    for (int i = 0; i < 2; i++)
+#pragma unroll
+        for (int k = 0; k < 2; k++) VXB_FALL(cidx(i, 0, k), cidx(i, 1, k))
+    // :125-134 diagonally in x
+#pragma unroll
+    for (int i = 0; i < 2; i++)
+#pragma unroll
+        for (int k = 0; k < 2; k++) VXB_FALL(cidx(1 - i, 0, k), cidx(i, 1, k))
+    // :136-145 diagonally in z
+#pragma unroll
+    for (int i = 0; i < 2; i++)
+#pragma unroll
+        for (int k = 0; k < 2; k++) VXB_FALL(cidx(i, 0, 1 - k), cidx(i, 1, k))
+    // :147-154 sideways in x inside the top layer; `to` = column pos.y%2, `from` = the other
+#pragma unroll
+    for (int i = 0; i < 2; i++) VXB_FALL(cidx(PY, 1, i), cidx(1 - PY, 1, i))
+    // :156-163 sideways in z
+#pragma unroll
+    for (int i = 0; i < 2; i++) VXB_FALL(cidx(i, 1, PY), cidx(i, 1, 1 - PY))
+#undef VXB_FALL
+    return air | (water << 8) | (touched << 16);
+}
+
+// compute_voxel.glsl:102-207 + set_data's guard (:53-54) on one block held in registers;
+// v[cidx(i,j,k)] are voxel words. PY = pos.y % 2 (== offset.y, since 16*chunk.y + 2*lid.y is even).
+// Updates v in place and returns the 8-bit mask of cells whose word changed (bit = cidx).
 //
 // Every path is exact; none is approximate:
 //  F0  all 8 words identical and that word is a fixed point (solid below its damage threshold,
@@ -56,8 +100,10 @@ __device__ __forceinline__ uint32_t umin3(uint32_t a, uint32_t b, uint32_t c) { 
 //      - pure block: slot := min(7, own if the block has an OOB cell, 1 + min over the other cells
 //        of class X of their value in that slot); OOB / AIR_OOB cells take no part in the min.
 //        The 3-bit fields are compared in place (masked, not shifted): 1 AND + 1/2 VIMNMX3 per pair.
+//  guard: cells whose ORIGINAL material is OOB / AIR_OOB keep their word (only looked at when the
+//      block holds such a cell).
 template <int PY>
-__device__ __forceinline__ bool margolus_block(uint32_t (&v)[8]) {
+__device__ __forceinline__ uint32_t margolus_block(uint32_t (&v)[8]) {
     uint32_t orv = v[0];
     {
         const uint32_t W = v[0];
@@ -71,7 +117,7 @@ __device__ __forceinline__ bool margolus_block(uint32_t (&v)[8]) {
             const uint32_t m0 = W >> 24, d0 = W & 0xFFFFFFu;
             const bool fixed = mat_in(MASK_DATA_DISTANCE, m0) ? (d0 == 0xFFFFFFu)
                                                               : !(mat_in(MASK_DATA_DAMAGE, m0) && d0 >= (m0 == MAT_STONE ? 10u : 5u));
-            if (fixed) return false;
+            if (fixed) return 0;
         }
     }
     uint32_t m[8], d[8];
@@ -84,10 +130,11 @@ __device__ __forceinline__ bool margolus_block(uint32_t (&v)[8]) {
         present |= 1u << m[c];
     }
     const uint32_t ord = orv & 0xFFFFFFu;
-    if ((present & MASK_DATA_DISTANCE) == 0 && ord < 5u) return false;
+    if ((present & MASK_DATA_DISTANCE) == 0 && ord < 5u) return 0;
+    const uint32_t present0 = present;  // materials of the ORIGINAL words (for the store guard)
 
     // :102-112 accumulated damage past the material's threshold -> air (stone 10, others 5)
-    if (ord >= 5u) {
+    if (ord >= 5u && (present & MASK_DATA_DAMAGE)) {
         bool any = false;
 #pragma unroll
         for (int c = 0; c < 8; c++) {
@@ -105,33 +152,21 @@ __device__ __forceinline__ bool margolus_block(uint32_t (&v)[8]) {
     }
 
     if ((present & BIT_WATER) && (present & BIT_AIR)) {
-#define VXB_FALL(b, t)                              \
-    if (m[b] == MAT_AIR && m[t] == MAT_WATER) {     \
-        m[b] = MAT_WATER; d[b] = 0;                 \
-        m[t] = MAT_AIR;   d[t] = 0;                 \
-    }
-        // :114-123 straight down
+        uint32_t air = 0, water = 0;
 #pragma unroll
-        for (int i = 0; i < 2; i++)
+        for (int c = 0; c < 8; c++) {
+            air |= (m[c] == MAT_AIR ? 1u : 0u) << c;
+            water |= (m[c] == MAT_WATER ? 1u : 0u) << c;
+        }
+        const uint32_t aw = margolus_water<PY>(air, water);
+        const uint32_t moved = (aw >> 16) & 0xFFu;  // cells that took part in a swap: new material, data reset
 #pragma unroll
-            for (int k = 0; k < 2; k++) VXB_FALL(cidx(i, 0, k), cidx(i, 1, k))
-        // :125-134 diagonally in x
-#pragma unroll
-        for (int i = 0; i < 2; i++)
-#pragma unroll
-            for (int k = 0; k < 2; k++) VXB_FALL(cidx(1 - i, 0, k), cidx(i, 1, k))
-        // :136-145 diagonally in z
-#pragma unroll
-        for (int i = 0; i < 2; i++)
-#pragma unroll
-            for (int k = 0; k < 2; k++) VXB_FALL(cidx(i, 0, 1 - k), cidx(i, 1, k))
-        // :147-154 sideways in x inside the top layer; `to` = column pos.y%2, `from` = the other
-#pragma unroll
-        for (int i = 0; i < 2; i++) VXB_FALL(cidx(PY, 1, i), cidx(1 - PY, 1, i))
-        // :156-163 sideways in z
-#pragma unroll
-        for (int i = 0; i < 2; i++) VXB_FALL(cidx(i, 1, PY), cidx(i, 1, 1 - PY))
-#undef VXB_FALL
+        for (int c = 0; c < 8; c++) {
+            if (moved & (1u << c)) {
+                m[c] = (aw & (1u << c)) ? MAT_AIR : MAT_WATER;
+                d[c] = 0;
+            }
+        }
     }
 
     // :165-207 each cell refreshes ONE 3-bit slot of its distance field: the slot named by its own
@@ -144,9 +179,10 @@ __device__ __forceinline__ bool margolus_block(uint32_t (&v)[8]) {
         if (pure_air || pure_water || pure_leaf) {
             const uint32_t X = pure_air ? MAT_AIR : (pure_water ? MAT_WATER : MAT_LEAF);
             const bool has_oob = (present & BIT_OOB) != 0;
+            const bool all_x = (present & (BIT_OOB | BIT_AIR_OOB)) == 0;  // every cell is of class X
             uint32_t deff[8];
 #pragma unroll
-            for (int c = 0; c < 8; c++) deff[c] = m[c] == X ? d[c] : 0xFFFFFFu;
+            for (int c = 0; c < 8; c++) deff[c] = (all_x || m[c] == X) ? d[c] : 0xFFFFFFu;
             uint32_t nd[8];
 #pragma unroll
             for (int c = 0; c < 8; c++) {
@@ -159,7 +195,7 @@ __device__ __forceinline__ bool margolus_block(uint32_t (&v)[8]) {
                 const uint32_t t = umin3(umin3(f[0], f[1], f[2]), umin3(f[3], f[4], f[5]), f[6]);
                 const uint32_t cap = has_oob ? (d[c] & MK) : MK;
                 const uint32_t r = min(cap, t + (MK & (MK >> 2)));  // + 1 in the field; 8 overflows past MK and loses to cap
-                nd[c] = m[c] == X ? ((d[c] & ~MK) | r) : d[c];
+                nd[c] = (all_x || m[c] == X) ? ((d[c] & ~MK) | r) : d[c];
             }
 #pragma unroll
             for (int c = 0; c < 8; c++) d[c] = nd[c];
@@ -172,21 +208,20 @@ __device__ __forceinline__ bool margolus_block(uint32_t (&v)[8]) {
             }
         }
     }
+    uint32_t chg = 0;
+    const bool guard = (present0 & (BIT_OOB | BIT_AIR_OOB)) != 0;
 #pragma unroll
-    for (int c = 0; c < 8; c++) v[c] = (m[c] << 24) | d[c];
-    return true;
+    for (int c = 0; c < 8; c++) {
+        uint32_t nv = (m[c] << 24) | d[c];
+        if (guard) {
+            const uint32_t om = v[c] >> 24;
+            if (om == MAT_OOB || om == MAT_AIR_OOB) nv = v[c];
+        }
+        if (nv != v[c]) chg |= 1u << c;
+        v[c] = nv;
+    }
+    return chg;
 }
-
-// set_data's guard (:53-54): voxels whose ORIGINAL material is OOB / AIR_OOB are never modified.
-__device__ __forceinline__ uint32_t keep_guard(uint32_t og, uint32_t nv) {
-    const uint32_t om = og >> 24;
-    return (om == MAT_OOB || om == MAT_AIR_OOB) ? og : nv;
-}
-
-// Slot of neighbour chunk, or 0 / 1 for "every voxel is MAT_OOB<<24" (out of window, or table value
-// 0) / "every voxel is MAT_AIR_OOB<<24" (table value 1). Sentinel slots 0 and 1 are never written
-// by any kernel, so they are folded to constants: not loaded, not stored.
-__device__ __forceinline__ uint32_t slot_const(uint32_t slot) { return slot == 1 ? VOX_AIR_OOB : VOX_OOB; }
 
 __device__ __forceinline__ uint32_t resolve_chunk(const World& w, uint32_t cx, uint32_t cy, uint32_t cz) {
     if (!(cx >= w.sp[0] && cy >= w.sp[1] && cz >= w.sp[2] && cx - w.sp[0] < w.rs[0] && cy - w.sp[1] < w.rs[1] &&
@@ -209,7 +244,7 @@ __device__ __forceinline__ void cp_async_wait() {
 }
 
 constexpr int UPD_THREADS = 256;
-constexpr int UPD_STAGES = 4;            // chunks in flight per CTA = UPD_STAGES - 1
+constexpr int UPD_STAGES = 3;            // chunks in flight per CTA = UPD_STAGES - 1
 constexpr int UPD_NSLOT = UPD_STAGES + 1;  // slot-table ring: chunks t .. t+STAGES-1 live, t+STAGES being written
 
 struct UpdStage {
@@ -223,8 +258,14 @@ struct UpdSmem {
 };
 
 // PHASE bit0 = offset.x, bit1 = offset.y, bit2 = offset.z. ELIDE: skip stores of unchanged vectors.
+//
+// Neighbour slot n (bit2 = +x, bit1 = +y, bit0 = +z) of a work item is a pool slot, or 0 / 1 for
+// "out of window or unloaded" / "all air". Slots 0 and 1 are real 16 KiB pool entries holding
+// MAT_OOB<<24 / MAT_AIR_OOB<<24 and no kernel ever writes them, so LOADS need no special case (they
+// read the sentinel chunk, which stays in L1/L2); only STORES are predicated on slot >= 2, which is
+// exactly set_data's guard for those two materials.
 template <int PHASE, bool ELIDE>
-__global__ void __launch_bounds__(UPD_THREADS, 3) k_voxel_update_tiled(World w, const uint4* __restrict__ chunk_updates, uint32_t n_items,
+__global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, const uint4* __restrict__ chunk_updates, uint32_t n_items,
                                                                        uint32_t* __restrict__ flags_out) {
     constexpr int OX = PHASE & 1, OY = (PHASE >> 1) & 1, OZ = (PHASE >> 2) & 1;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -241,11 +282,23 @@ __global__ void __launch_bounds__(UPD_THREADS, 3) k_voxel_update_tiled(World w, 
     // barrier — warps of a CTA drift apart, their partial-sector stores no longer merge in L2 and
     // the y/z-shifted phases lose 15-20 %.)
     const int tzq = tid & 3, tx = (tid >> 2) & 7, ty = tid >> 5;
-    const int Z0 = 4 * tzq + OZ;
-    // (i,j) column of this thread: neighbour-chunk selector and in-chunk row offset (z = 0)
+    // (i,j) column of this thread: neighbour-chunk selector and in-chunk word offset of its vector
     auto nsel = [&](int i, int j) { return (((2 * tx + OX + i) >> 4) << 2) | (((2 * ty + OY + j) >> 4) << 1); };
     auto rowoff = [&](int i, int j) { return (uint32_t)((((2 * tx + OX + i) & 15) << 8) | (((2 * ty + OY + j) & 15) << 4)); };
     auto slot_ptr = [&](uint32_t slot, uint32_t off) { return w.pool + ((size_t)slot << 12) + off; };
+    // change-flag bits of set_data (:56-84) by local coordinate: bit1-3 low faces, bit4-6 high faces
+    uint32_t fx[2], fy[2], fz[4];
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+        const int X = 2 * tx + OX + i, Y = 2 * ty + OY + i;
+        fx[i] = (X == 0 ? 2u : 0u) | (X >= 15 ? 0x10u : 0u);
+        fy[i] = (Y == 0 ? 4u : 0u) | (Y >= 15 ? 0x20u : 0u);
+    }
+#pragma unroll
+    for (int z = 0; z < 4; z++) {
+        const int Z = 4 * tzq + OZ + z;
+        fz[z] = (Z == 0 ? 8u : 0u) | (Z >= 15 ? 0x40u : 0u);
+    }
 
     // resolve the 2x2x2 slot neighbourhood of work item t (lane n of 8): list entry -> table lookup
     auto resolve = [&](uint32_t t, uint32_t n) -> uint32_t {
@@ -264,18 +317,9 @@ __global__ void __launch_bounds__(UPD_THREADS, 3) k_voxel_update_tiled(World w, 
                 for (int j = 0; j < 2; j++) {
                     const int n = nsel(i, j);
                     const uint32_t row = rowoff(i, j);
-                    const uint32_t slot = sl[n];
-                    if (slot >= 2) {
-                        cp_async16(&st.a[i * 2 + j][tid], slot_ptr(slot, row + 4 * tzq));
-                    } else {
-                        const uint32_t c = slot_const(slot);
-                        st.a[i * 2 + j][tid] = make_uint4(c, c, c, c);
-                    }
-                    if (OZ == 1 && tzq == 3) {  // z == 16: first voxel of the row in the +z neighbour chunk
-                        const uint32_t zslot = sl[n | 1];
-                        if (zslot >= 2) cp_async4(&st.zx[i * 2 + j][tid >> 2], slot_ptr(zslot, row));
-                        else st.zx[i * 2 + j][tid >> 2] = slot_const(zslot);
-                    }
+                    cp_async16(&st.a[i * 2 + j][tid], slot_ptr(sl[n], row + 4 * tzq));
+                    if (OZ == 1 && tzq == 3)  // z == 16: first voxel of the row in the +z neighbour chunk
+                        cp_async4(&st.zx[i * 2 + j][tid >> 2], slot_ptr(sl[n | 1], row));
                 }
             }
         }
@@ -315,34 +359,36 @@ __global__ void __launch_bounds__(UPD_THREADS, 3) k_voxel_update_tiled(World w, 
             }
         }
 
-        // two Margolus blocks per thread: z pairs (0,1) and (2,3); set_data's guard and change flags (:51-88)
+        // two Margolus blocks per thread: z pairs (0,1) and (2,3); change flags of set_data (:55-86)
         uint32_t r[2][2][4];
         uint32_t flags = 0;
+        uint32_t chg16 = 0;  // bit (i*2+j)*4 + z: voxel changed
 #pragma unroll
         for (int b = 0; b < 2; b++) {
             uint32_t blk[8];
 #pragma unroll
             for (int c = 0; c < 8; c++) blk[c] = v[c >> 2][(c >> 1) & 1][2 * b + (c & 1)];
-            const bool touched = margolus_block<OY>(blk);
+            const uint32_t chg = margolus_block<OY>(blk);
 #pragma unroll
             for (int c = 0; c < 8; c++) r[c >> 2][(c >> 1) & 1][2 * b + (c & 1)] = blk[c];
-            if (touched) {
+            if (chg) {
+                // chg bit c = i*4 + j*2 + k
+                flags |= 1u;
+                if (chg & 0x0Fu) flags |= fx[0];
+                if (chg & 0xF0u) flags |= fx[1];
+                if (chg & 0x33u) flags |= fy[0];
+                if (chg & 0xCCu) flags |= fy[1];
+                if (chg & 0x55u) flags |= fz[2 * b];
+                if (chg & 0xAAu) flags |= fz[2 * b + 1];
+                if (ELIDE) {
 #pragma unroll
-                for (int c = 0; c < 8; c++) {
-                    const int i = c >> 2, j = (c >> 1) & 1, z = 2 * b + (c & 1);
-                    const uint32_t og = v[i][j][z];
-                    const uint32_t nv = keep_guard(og, blk[c]);
-                    r[i][j][z] = nv;
-                    if (nv != og) {
-                        const int X = 2 * tx + OX + i, Y = 2 * ty + OY + j, Z = Z0 + z;
-                        flags |= 1u | (X == 0 ? 2u : 0u) | (Y == 0 ? 4u : 0u) | (Z == 0 ? 8u : 0u) | (X >= 15 ? 0x10u : 0u) |
-                                 (Y >= 15 ? 0x20u : 0u) | (Z >= 15 ? 0x40u : 0u);
-                    }
+                    for (int c = 0; c < 8; c++)
+                        if (chg & (1u << c)) chg16 |= 1u << (((c >> 2) * 2 + ((c >> 1) & 1)) * 4 + 2 * b + (c & 1));
                 }
             }
         }
 
-        // write-back (imageStore :87 is unconditional; constants/sentinels are never stored)
+        // write-back (imageStore :87 is unconditional; sentinel slots are never stored)
 #pragma unroll
         for (int i = 0; i < 2; i++) {
 #pragma unroll
@@ -350,32 +396,30 @@ __global__ void __launch_bounds__(UPD_THREADS, 3) k_voxel_update_tiled(World w, 
                 const int n = nsel(i, j);
                 const uint32_t row = rowoff(i, j);
                 const uint32_t slot = sl[n];
+                const uint32_t c4 = (chg16 >> ((i * 2 + j) * 4)) & 0xFu;  // only meaningful under ELIDE
                 if (OZ == 0) {
-                    if (slot >= 2) {
-                        const bool same = r[i][j][0] == v[i][j][0] && r[i][j][1] == v[i][j][1] && r[i][j][2] == v[i][j][2] &&
-                                          r[i][j][3] == v[i][j][3];
-                        if (!(ELIDE && same))
-                            *reinterpret_cast<uint4*>(slot_ptr(slot, row + 4 * tzq)) = make_uint4(r[i][j][0], r[i][j][1], r[i][j][2], r[i][j][3]);
-                    }
+                    if (slot >= 2 && !(ELIDE && c4 == 0))
+                        *reinterpret_cast<uint4*>(slot_ptr(slot, row + 4 * tzq)) = make_uint4(r[i][j][0], r[i][j][1], r[i][j][2], r[i][j][3]);
                 } else {
                     // element z = 4*tzq of the aligned vector is the previous lane's last voxel
                     const uint32_t prev = __shfl_up_sync(0xFFFFFFFFu, r[i][j][3], 1);
-                    bool prev_same = true;
-                    if (ELIDE) prev_same = __shfl_up_sync(0xFFFFFFFFu, (int)(r[i][j][3] == v[i][j][3]), 1) != 0;
-                    if (slot >= 2) {
-                        const bool same = r[i][j][0] == v[i][j][0] && r[i][j][1] == v[i][j][1] && r[i][j][2] == v[i][j][2];
-                        if (tzq > 0) {
-                            if (!(ELIDE && same && prev_same))
-                                *reinterpret_cast<uint4*>(slot_ptr(slot, row + 4 * tzq)) = make_uint4(prev, r[i][j][0], r[i][j][1], r[i][j][2]);
-                        } else if (!(ELIDE && same)) {
-                            // z == 0 of this row belongs to the -z neighbour's work item in this phase
-                            *slot_ptr(slot, row + 1) = r[i][j][0];
-                            *reinterpret_cast<uint2*>(slot_ptr(slot, row + 2)) = make_uint2(r[i][j][1], r[i][j][2]);
-                        }
+                    uint32_t prev_chg = 1;
+                    if (ELIDE) prev_chg = __shfl_up_sync(0xFFFFFFFFu, c4 & 8u, 1);
+                    if (tzq > 0) {
+                        if (slot >= 2 && !(ELIDE && (c4 & 7u) == 0 && prev_chg == 0))
+                            *reinterpret_cast<uint4*>(slot_ptr(slot, row + 4 * tzq)) = make_uint4(prev, r[i][j][0], r[i][j][1], r[i][j][2]);
+                    } else if (slot >= 2 && !(ELIDE && (c4 & 6u) == 0)) {
+                        // z == 0 of this row belongs to the -z neighbour's work item in this phase
+                        *reinterpret_cast<uint2*>(slot_ptr(slot, row + 2)) = make_uint2(r[i][j][1], r[i][j][2]);
                     }
-                    if (tzq == 3) {
-                        const uint32_t zslot = sl[n | 1];
-                        if (zslot >= 2 && !(ELIDE && r[i][j][3] == v[i][j][3])) *slot_ptr(zslot, row) = r[i][j][3];
+                    // one 4-byte store instruction serves both row ends: z == 1 (lanes tzq == 0) and
+                    // z == 16, the first voxel of the +z neighbour chunk (lanes tzq == 3)
+                    if (tzq == 0 || tzq == 3) {
+                        const uint32_t eslot = tzq == 0 ? slot : sl[n | 1];
+                        const uint32_t eoff = tzq == 0 ? row + 1 : row;
+                        const uint32_t eval = tzq == 0 ? r[i][j][0] : r[i][j][3];
+                        const uint32_t echg = tzq == 0 ? (c4 & 1u) : (c4 & 8u);
+                        if (eslot >= 2 && !(ELIDE && echg == 0)) *slot_ptr(eslot, eoff) = eval;
                     }
                 }
             }
