@@ -213,10 +213,10 @@ def run_ours(args):
         if world_size > 1 and off[0] == 1:
             exchange(False)
 
+    sampler = ClockSampler(local_rank) if rank == 0 else None  # samples under load: warm-up + timed region
     for i in range(args.warmup):
         step(i)
     barrier()
-    sampler = ClockSampler(local_rank) if rank == 0 else None
     launches[0] = 0
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     ev[0].record()
@@ -235,6 +235,25 @@ def run_ours(args):
     # dominant kernel: this rank's k_voxel_update launches (CUDA events on the launching stream)
     per_step_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
     kern_ms = float(np.mean(per_step_ms)) if world_size == 1 else None
+
+    # ---------------- same steps with the reference's unconditional stores (variant 0), for comparison ----------------
+    alt = None
+    if world_size == 1 and args.variant == 2:
+        gpu.set_update_kernel(0)
+        for i in range(args.warmup):
+            gpu.update_list_run(lsp, PHASES[i % 8])
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for i in range(args.steps):
+            gpu.update_list_run(lsp, PHASES[(args.warmup + i) % 8])
+        a1.record()
+        torch.cuda.synchronize()
+        alt_ms = a0.elapsed_time(a1) / args.steps
+        alt = {"update_kernel_variant": 0, "stores": "unconditional, as compute_voxel.glsl:87", "ms_per_step": alt_ms,
+               "value": n_total_vox / (alt_ms / 1e3), "unit": "voxel-updates/s",
+               "achieved_GBps": BYTES_PER_VOXEL_UPDATE * n_own * 4096 / (alt_ms / 1e3) / 1e9,
+               "frac": BYTES_PER_VOXEL_UPDATE * n_own * 4096 / (alt_ms / 1e3) / 1e9 / peak}
+        gpu.set_update_kernel(args.variant)
 
     # ---------------- e2e: the C-ABI dispatch with HOST work list in, flags out ----------------
     e2e = None
@@ -289,11 +308,15 @@ def run_ours(args):
             "worldgen": {"value": wg_vox / wg_s, "unit": "voxels-generated/s", "voxels": wg_vox, "map": "open_world", "gpus": 1,
                          "note": "rank 0's slab, device time incl. per-batch list upload"},
         }
+        if alt is not None:
+            result["unconditional_store_variant"] = alt
         if achieved is not None:
             result["roofline"] = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                                   "traffic": traffic_from_profiles("k_voxel_update_bytes_per_launch"), "peak_source": peak_src,
                                   "kernel": "k_voxel_update_tiled", "algorithmic_bytes_per_launch": BYTES_PER_VOXEL_UPDATE * n_own * 4096,
-                                  "avg_launch_ms": kern_ms}
+                                  "avg_launch_ms": kern_ms,
+                                  "note": "algorithmic bytes = 8 B per voxel-update (4 B read + 4 B write) as SURVEY 8(d) fixes it, whether or not "
+                                          "unchanged vectors are stored; `traffic` is the measured DRAM bytes of one launch"}
 
     # ---------------- cpu_baseline (rank 0, N == 1): oracle on a bounded sample of the same world ----
     if rank == 0 and world_size == 1 and not args.no_cpu:
@@ -458,7 +481,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--world", type=int, nargs=3, default=list(C3_RS), help="update-step world size in chunks (default BASELINE configs[2])")
-    ap.add_argument("--variant", type=int, default=0, help="update kernel variant (0 tiled, 1 gather, 2 tiled+store elision)")
+    ap.add_argument("--variant", type=int, default=2, help="update kernel variant: 2 = tiled + unchanged-store elision (product default), 0 = tiled with the reference's unconditional stores, 1 = reference-shaped gather")
     ap.add_argument("--settle", type=int, default=96, help="untimed update ticks after worldgen (world preparation)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-rays", action="store_true")

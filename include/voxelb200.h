@@ -230,8 +230,10 @@ int vxb_dispatch_entities(vxb_ctx* ctx, const uint32_t start_pos[3], vxb_project
 int vxb_update_list_upload(vxb_ctx* ctx, const uint32_t (*chunk_updates)[4], uint32_t n);
 int vxb_update_list_run(vxb_ctx* ctx, const uint32_t start_pos[3], const uint32_t offset[3]);
 int vxb_update_list_flags(vxb_ctx* ctx, uint32_t* flags_out, uint32_t n);
-/* Selects the update kernel: 0 = default (register-tiled, vectorised), 1 = per-voxel gather that
- * follows the reference's access pattern (kept for profiling comparisons). */
+/* Selects the update kernel: 2 = default (persistent cp.async-pipelined, vectorised; 16-byte vectors
+ * whose four voxels did not change are not stored back — results are identical), 0 = the same kernel
+ * with the reference's unconditional stores (compute_voxel.glsl:87), 1 = per-voxel gather that follows
+ * the reference's access pattern (kept as profiling baseline and cross-check). */
 int vxb_set_update_kernel(vxb_ctx* ctx, int variant);
 
 /* ---- the ray pass (src/raytracer.rs, shaders/frag.glsl) --------------------------------------- */

@@ -1,5 +1,5 @@
 import sys, os, time, numpy as np, torch
-sys.path.insert(0,'/root/repo')
+import os; sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import voxel_game_b200 as vg
 import bench
 RS=(64,16,256); SP=bench.C3_SP

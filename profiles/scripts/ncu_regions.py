@@ -6,7 +6,7 @@ for r in rows:
     if r and r[0]=="Kernel Name": cur={'name':r[1],'rows':[]}; ks.append(cur); continue
     if r and r[0]=="Address": cur['hdr']=r; continue
     if cur is not None and r: cur['rows'].append(r)
-k=[x for x in ks if x['rows']][which]
+kk=[x for x in ks if x["rows"]]; k=kk[min(which*2,len(kk)-1)] if len(kk)>2 else kk[which]
 h={n:i for i,n in enumerate(k['hdr'])}
 tot=sum(int(r[h['Instructions Executed']]) for r in k['rows'])
 print(k['name'][:60], 'static', len(k['rows']), 'warp instr per chunk', tot/nchunks)

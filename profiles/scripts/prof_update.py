@@ -1,5 +1,5 @@
 import sys, numpy as np, torch
-sys.path.insert(0,'/root/repo')
+import os; sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import voxel_game_b200 as vg
 import bench
 RS=(32,16,256); SP=bench.C3_SP
@@ -14,6 +14,6 @@ gpu.set_update_kernel(int(sys.argv[1]) if len(sys.argv)>1 else 0)
 settle=int(sys.argv[2]) if len(sys.argv)>2 else 96
 for t in range(settle): gpu.update_list_run(SP,bench.PHASES[t%8])
 gpu.update_list_run(SP,(0,0,0))
-gpu.update_list_run(SP,(1,1,1))
+gpu.update_list_run(SP,(0,0,1))
 gpu.synchronize()
 print("done")

@@ -253,8 +253,14 @@ struct UpdStage {
 };
 struct UpdSmem {
     UpdStage stage[UPD_STAGES];
-    uint32_t slot[UPD_NSLOT][8];
+    __align__(16) uint32_t slot[UPD_NSLOT][8];
     uint32_t flags[2];
+};
+
+// The 2x2x2 neighbour slots of one work item, picked apart for one thread: s[i*2+j] is the slot of
+// the chunk holding column (i,j), z[i*2+j] the slot of its +z neighbour (only used when offset.z == 1).
+struct ThreadSlots {
+    uint32_t s[4], z[4];
 };
 
 // PHASE bit0 = offset.x, bit1 = offset.y, bit2 = offset.z. ELIDE: skip stores of unchanged vectors.
@@ -282,8 +288,21 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
     // barrier — warps of a CTA drift apart, their partial-sector stores no longer merge in L2 and
     // the y/z-shifted phases lose 15-20 %.)
     const int tzq = tid & 3, tx = (tid >> 2) & 7, ty = tid >> 5;
-    // (i,j) column of this thread: neighbour-chunk selector and in-chunk word offset of its vector
-    auto nsel = [&](int i, int j) { return (((2 * tx + OX + i) >> 4) << 2) | (((2 * ty + OY + j) >> 4) << 1); };
+    // (i,j) column of this thread: in-chunk word offset of its vector, and which neighbour chunk holds it.
+    // Only the last thread column / row straddles (x or y == 16), and only for i / j == 1.
+    const bool bx = OX == 1 && tx == 7, by = OY == 1 && ty == 7;
+    // read the item's 8 slots with two 16-byte shared loads BEFORE any cp.async (their asm memory clobber
+    // would otherwise force a reload per use; 32 LDS per item made the z-shifted phases MIO-bound)
+    auto thread_slots = [&](const uint32_t* sl) {
+        const uint4 lo = *reinterpret_cast<const uint4*>(sl), hi = *reinterpret_cast<const uint4*>(sl + 4);
+        // lo = slots 0..3 (x+0: y+0 z+0, y+0 z+1, y+1 z+0, y+1 z+1), hi = slots 4..7 (x+1: same)
+        ThreadSlots r;
+        r.s[0] = lo.x;                              r.z[0] = lo.y;
+        r.s[1] = by ? lo.z : lo.x;                  r.z[1] = by ? lo.w : lo.y;
+        r.s[2] = bx ? hi.x : lo.x;                  r.z[2] = bx ? hi.y : lo.y;
+        r.s[3] = bx ? (by ? hi.z : hi.x) : r.s[1];  r.z[3] = bx ? (by ? hi.w : hi.y) : r.z[1];
+        return r;
+    };
     auto rowoff = [&](int i, int j) { return (uint32_t)((((2 * tx + OX + i) & 15) << 8) | (((2 * ty + OY + j) & 15) << 4)); };
     auto slot_ptr = [&](uint32_t slot, uint32_t off) { return w.pool + ((size_t)slot << 12) + off; };
     // change-flag bits of set_data (:56-84) by local coordinate: bit1-3 low faces, bit4-6 high faces
@@ -310,16 +329,15 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
     auto issue = [&](uint32_t t) {
         if (t < T) {
             UpdStage& st = sm.stage[t % UPD_STAGES];
-            const uint32_t* sl = sm.slot[t % UPD_NSLOT];
+            const ThreadSlots ts = thread_slots(sm.slot[t % UPD_NSLOT]);
 #pragma unroll
             for (int i = 0; i < 2; i++) {
 #pragma unroll
                 for (int j = 0; j < 2; j++) {
-                    const int n = nsel(i, j);
                     const uint32_t row = rowoff(i, j);
-                    cp_async16(&st.a[i * 2 + j][tid], slot_ptr(sl[n], row + 4 * tzq));
+                    cp_async16(&st.a[i * 2 + j][tid], slot_ptr(ts.s[i * 2 + j], row + 4 * tzq));
                     if (OZ == 1 && tzq == 3)  // z == 16: first voxel of the row in the +z neighbour chunk
-                        cp_async4(&st.zx[i * 2 + j][tid >> 2], slot_ptr(sl[n | 1], row));
+                        cp_async4(&st.zx[i * 2 + j][tid >> 2], slot_ptr(ts.z[i * 2 + j], row));
                 }
             }
         }
@@ -342,7 +360,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
         cp_async_wait<UPD_STAGES - 1>();  // this thread's copies of item t have landed
 
         const UpdStage& st = sm.stage[t % UPD_STAGES];
-        const uint32_t* sl = sm.slot[t % UPD_NSLOT];
+        const ThreadSlots ts = thread_slots(sm.slot[t % UPD_NSLOT]);
         uint32_t v[2][2][4];  // originals
 #pragma unroll
         for (int i = 0; i < 2; i++) {
@@ -393,9 +411,8 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
         for (int i = 0; i < 2; i++) {
 #pragma unroll
             for (int j = 0; j < 2; j++) {
-                const int n = nsel(i, j);
                 const uint32_t row = rowoff(i, j);
-                const uint32_t slot = sl[n];
+                const uint32_t slot = ts.s[i * 2 + j];
                 const uint32_t c4 = (chg16 >> ((i * 2 + j) * 4)) & 0xFu;  // only meaningful under ELIDE
                 if (OZ == 0) {
                     if (slot >= 2 && !(ELIDE && c4 == 0))
@@ -415,7 +432,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
                     // one 4-byte store instruction serves both row ends: z == 1 (lanes tzq == 0) and
                     // z == 16, the first voxel of the +z neighbour chunk (lanes tzq == 3)
                     if (tzq == 0 || tzq == 3) {
-                        const uint32_t eslot = tzq == 0 ? slot : sl[n | 1];
+                        const uint32_t eslot = tzq == 0 ? slot : ts.z[i * 2 + j];
                         const uint32_t eoff = tzq == 0 ? row + 1 : row;
                         const uint32_t eval = tzq == 0 ? r[i][j][0] : r[i][j][3];
                         const uint32_t echg = tzq == 0 ? (c4 & 1u) : (c4 & 8u);

@@ -121,7 +121,7 @@ struct vxb_ctx {
     uint32_t last_counts[3] = {0, 0, 0};
     uint32_t last_start_pos[3] = {0, 0, 0};
     bool results_pending = false;  // flags / worldgen_results D2H enqueued by the last compute
-    int update_variant = 0;
+    int update_variant = 2;  // tiled kernel with unchanged-store elision (identical results, fewer bytes)
 
     World world(const uint32_t start_pos[3]) const {
         World w;
