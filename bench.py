@@ -150,8 +150,6 @@ def run_ours(args):
         if world_size == 1 and args.gpus > 1:
             raise SystemExit("launch with torch.distributed.run --nproc-per-node %d for --gpus %d" % (args.gpus, args.gpus))
     torch.cuda.set_device(local_rank)
-    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
-        os.environ["NCCL_DEBUG"] = "WARN"  # the image's default prints a banner on stdout; stdout carries ONE JSON line
     if world_size > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     # everything (our kernels, torch copies, NCCL, timing events) runs on ONE explicit stream
@@ -350,7 +348,7 @@ def run_ours(args):
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
-        print(json.dumps(result))
+        OUT.emit(result)
 
 
 def bench_rays(args, torch, vg, peak):
@@ -464,17 +462,36 @@ def run_reference(args):
     s = time.perf_counter() - t0
     value = n * 4096 * args.steps / s
     sample = "oracle-generated 8x8x8-chunk open-world block tiled 4x1x4 (%d chunks, %d voxels) per step; OpenMP over chunks" % (n, n * 4096)
-    print(json.dumps({
+    OUT.emit({
         "impl": "reference", "metric": "voxel-updates/s", "value": value, "unit": "voxel-updates/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": s / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "u32", "data": "synthetic (oracle open-world worldgen, tiled)",
         "config": {"workload": "BASELINE configs[2] voxel update step — bounded CPU sample", "sample": sample},
         "cpu_baseline": {"value": value, "unit": "voxel-updates/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "voxel-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
+
+
+class OneLineStdout:
+    """stdout carries exactly ONE JSON line: everything any library prints to fd 1 during the run (the
+    image sets NCCL_DEBUG=VERSION, which makes NCCL print a banner there) is sent to stderr instead."""
+
+    def __init__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+
+    def emit(self, obj):
+        sys.stdout.flush()
+        os.write(self.saved, (json.dumps(obj) + "\n").encode())
+
+
+OUT = None
 
 
 def main():
+    global OUT
+    OUT = OneLineStdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=16)
