@@ -104,10 +104,31 @@ __device__ __forceinline__ SlabHit projectile_slabs(const vxb_projectile& p, f3 
     return s;
 }
 
+__device__ __forceinline__ void store_layer(const RayOut& o, uint64_t i, uint32_t l, const Layer& L) {
+    const uint64_t n = o.n_rays;
+    o.pos[(l * 3 + 0) * n + i] = L.pos.x;
+    o.pos[(l * 3 + 1) * n + i] = L.pos.y;
+    o.pos[(l * 3 + 2) * n + i] = L.pos.z;
+    o.normal[(l * 3 + 0) * n + i] = L.normal.x;
+    o.normal[(l * 3 + 1) * n + i] = L.normal.y;
+    o.normal[(l * 3 + 2) * n + i] = L.normal.z;
+    o.voxel[l * n + i] = L.voxel;
+    o.ldist[l * n + i] = L.dist;
+    o.leaving[l * n + i] = L.leaving;
+}
+
 // frag.glsl:348-486. layers[] must be zero-initialised by the caller (GLSL leaves them undefined;
 // the oracle zeroes them too: the reference's insertion quirk at layer_idx 0 -> 1 exposes layer 0).
+// DIRECT (no projectiles to insert): layers go straight to the output arrays as they are produced and
+// the local layers[] array is never touched (it would live in local memory: dynamic indexing).
+template <bool DIRECT>
 __device__ uint32_t raycast(const World& w, f3 pos, f3 ray, uint32_t max_iterations, const vxb_projectile* projectiles,
-                            uint32_t projectile_count, float raster_depth, Layer (&layers)[5], float& out_depth, uint32_t& iters) {
+                            uint32_t projectile_count, float raster_depth, Layer (&layers)[5], float& out_depth, uint32_t& iters,
+                            const RayOut& out, uint64_t ray_index) {
+    auto push = [&](uint32_t idx, const Layer& L) {
+        if (DIRECT) store_layer(out, ray_index, idx, L);
+        else layers[idx] = L;
+    };
     const uint32_t offset = ray_octant(ray);
     f3 ray_pos = pos;
     f3 normal = -ray;
@@ -122,7 +143,7 @@ __device__ uint32_t raycast(const World& w, f3 pos, f3 ray, uint32_t max_iterati
         f3 v_min, v_max;
         if (voxel_material == MAT_AIR || voxel_material == MAT_AIR_OOB) {
             if (medium != MAT_AIR) {
-                layers[layer_idx] = Layer{ray_pos, normal, medium << 24, depth, 1u};
+                push(layer_idx, Layer{ray_pos, normal, medium << 24, depth, 1u});
                 layer_idx++;
                 if (layer_idx >= 5) break;
             }
@@ -137,13 +158,13 @@ __device__ uint32_t raycast(const World& w, f3 pos, f3 ray, uint32_t max_iterati
             v_min = floor_pos;
             v_max = floor_pos + mk3(1.0f, 1.0f, 1.0f);
             if (medium != voxel_material) {
-                layers[layer_idx] = Layer{ray_pos, normal, voxel_data, depth, 0u};
+                push(layer_idx, Layer{ray_pos, normal, voxel_data, depth, 0u});
                 layer_idx++;
                 if (layer_idx >= 5) break;
             }
             medium = voxel_material;
         } else {
-            layers[layer_idx] = Layer{ray_pos, normal, voxel_data, depth, 0u};
+            push(layer_idx, Layer{ray_pos, normal, voxel_data, depth, 0u});
             layer_idx++;
             break;
         }
@@ -170,13 +191,13 @@ __device__ uint32_t raycast(const World& w, f3 pos, f3 ray, uint32_t max_iterati
 
     if (raster_depth > 0.0f && layer_idx < 5) {
         // headless: no rasterised G-buffer; u_normals = (0,1,0), u_diffuse.x = 1 (MAT_PLAYER)
-        layers[layer_idx] = Layer{ray_pos, norm3(mk3(0.0f, 1.0f, 0.0f)), MAT_PLAYER << 24, raster_depth, 0u};
+        push(layer_idx, Layer{ray_pos, norm3(mk3(0.0f, 1.0f, 0.0f)), MAT_PLAYER << 24, raster_depth, 0u});
         layer_idx++;
     }
 
     // :439-484 projectile boxes, inserted by distance
     f3 pnormal = mk3(0, 0, 0);
-    for (uint32_t i = 0; i < projectile_count; i++) {
+    for (uint32_t i = 0; !DIRECT && i < projectile_count; i++) {
         const vxb_projectile& p = projectiles[i];
         const SlabHit s = projectile_slabs(p, pos, ray, depth);
         const float dist = gmax(gmax(s.tx0, s.ty0), s.tz0);
@@ -314,19 +335,6 @@ __device__ Layer simple_raycast(const World& w, f3 pos, f3 ray, uint32_t max_ite
     return Layer{ray_pos, mk3(0, 0, 0), voxel_data, depth, 0u};
 }
 
-__device__ __forceinline__ void store_layer(const RayOut& o, uint64_t i, uint32_t l, const Layer& L) {
-    const uint64_t n = o.n_rays;
-    o.pos[(l * 3 + 0) * n + i] = L.pos.x;
-    o.pos[(l * 3 + 1) * n + i] = L.pos.y;
-    o.pos[(l * 3 + 2) * n + i] = L.pos.z;
-    o.normal[(l * 3 + 0) * n + i] = L.normal.x;
-    o.normal[(l * 3 + 1) * n + i] = L.normal.y;
-    o.normal[(l * 3 + 2) * n + i] = L.normal.z;
-    o.voxel[l * n + i] = L.voxel;
-    o.ldist[l * n + i] = L.dist;
-    o.leaving[l * n + i] = L.leaving;
-}
-
 __device__ __forceinline__ void count_iters(const RayOut& o, uint32_t iters) {
     // one atomic per warp
     uint32_t s = iters;
@@ -355,15 +363,20 @@ __global__ void __launch_bounds__(64) k_raymarch_primary(World w, const vxb_play
         const f3 pos = mk3(cam.pos[0], cam.pos[1], cam.pos[2]);
         const float max_depth = raster_depth ? raster_depth[i] : 0.0f;
         Layer layers[5];
-#pragma unroll
-        for (int l = 0; l < 5; l++) layers[l] = Layer{mk3(0, 0, 0), mk3(0, 0, 0), 0u, 0.0f, 0u};
         float depth;
-        const uint32_t count = raycast(w, pos, ray, max_iterations, projectiles, projectile_count, max_depth, layers, depth, iters);
+        uint32_t count;
+        if (projectile_count == 0) {
+            count = raycast<true>(w, pos, ray, max_iterations, projectiles, 0, max_depth, layers, depth, iters, out, i);
+        } else {
+#pragma unroll
+            for (int l = 0; l < 5; l++) layers[l] = Layer{mk3(0, 0, 0), mk3(0, 0, 0), 0u, 0.0f, 0u};
+            count = raycast<false>(w, pos, ray, max_iterations, projectiles, projectile_count, max_depth, layers, depth, iters, out, i);
+#pragma unroll
+            for (uint32_t l = 0; l < 5; l++)
+                if (l < count) store_layer(out, i, l, layers[l]);
+        }
         out.layer_count[i] = count;
         out.dist[i] = depth;
-#pragma unroll
-        for (uint32_t l = 0; l < 5; l++)
-            if (l < count) store_layer(out, i, l, layers[l]);
     }
     count_iters(out, iters);
 }
@@ -379,15 +392,20 @@ __global__ void __launch_bounds__(128) k_raymarch_rays(World w, const float* __r
         const f3 ray = mk3(rdir[3 * i], rdir[3 * i + 1], rdir[3 * i + 2]);
         if (kind == 0) {
             Layer layers[5];
-#pragma unroll
-            for (int l = 0; l < 5; l++) layers[l] = Layer{mk3(0, 0, 0), mk3(0, 0, 0), 0u, 0.0f, 0u};
             float depth;
-            const uint32_t count = raycast(w, pos, ray, max_iterations, projectiles, projectile_count, 0.0f, layers, depth, iters);
+            uint32_t count;
+            if (projectile_count == 0) {
+                count = raycast<true>(w, pos, ray, max_iterations, projectiles, 0, 0.0f, layers, depth, iters, out, i);
+            } else {
+#pragma unroll
+                for (int l = 0; l < 5; l++) layers[l] = Layer{mk3(0, 0, 0), mk3(0, 0, 0), 0u, 0.0f, 0u};
+                count = raycast<false>(w, pos, ray, max_iterations, projectiles, projectile_count, 0.0f, layers, depth, iters, out, i);
+#pragma unroll
+                for (uint32_t l = 0; l < 5; l++)
+                    if (l < count) store_layer(out, i, l, layers[l]);
+            }
             out.layer_count[i] = count;
             out.dist[i] = depth;
-#pragma unroll
-            for (uint32_t l = 0; l < 5; l++)
-                if (l < count) store_layer(out, i, l, layers[l]);
         } else {
             float light = 0.0f;
             Layer L;

@@ -227,7 +227,7 @@ __device__ __forceinline__ uint32_t resolve_chunk(const World& w, uint32_t cx, u
     if (!(cx >= w.sp[0] && cy >= w.sp[1] && cz >= w.sp[2] && cx - w.sp[0] < w.rs[0] && cy - w.sp[1] < w.rs[1] &&
           cz - w.sp[2] < w.rs[2]))
         return 0;
-    return table_lookup(w, cx, cy, cz);
+    return table_lookup_in_window(w, cx, cy, cz);
 }
 
 // ---- cp.async (LDGSTS) helpers ----

@@ -63,6 +63,8 @@ extern "C" int vxb_raymarch_rays_noalloc(vxb_ctx* ctx, const uint32_t start_pos[
     if (kind < 1 || kind > 3) return ctx_fail(ctx, VXB_ERR_INVALID, "vxb_raymarch_rays_noalloc: kind must be 1, 2 or 3 (single-hit queries)");
     if (n == 0) return VXB_OK;
     if (!pos || !dir) return ctx_fail(ctx, VXB_ERR_INVALID, "vxb_raymarch_rays_noalloc: pos / dir is NULL");
+    for (int a = 0; a < 3; a++)
+        if (start_pos[a] > (1u << 27)) return ctx_fail(ctx, VXB_ERR_INVALID, "vxb_raymarch_rays_noalloc: start_pos out of range");
 
     World w;
     cudaStream_t st;

@@ -131,6 +131,7 @@ struct vxb_ctx {
             w.rs[i] = s.render_size[i];
             w.sp[i] = start_pos[i];
         }
+        world_derive(w);
         return w;
     }
     size_t table_index(const uint32_t pos[3]) const {
@@ -159,6 +160,16 @@ static int fail(vxb_ctx* ctx, int code, const char* fmt, ...) {
     do {                                                                                           \
         cudaError_t _e = (expr);                                                                   \
         if (_e != cudaSuccess) return fail(ctx, VXB_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(_e)); \
+    } while (0)
+// the kernels' one-compare window test needs 16 * (start_pos + render_size) to fit in u32
+static bool window_ok(const vxb_ctx* c, const uint32_t start_pos[3]) {
+    for (int a = 0; a < 3; a++)
+        if ((uint64_t)start_pos[a] + c->s.render_size[a] > (1ull << 28) - 1) return false;
+    return true;
+}
+#define VXB_WINDOW(ctx, sp)                                                                                              \
+    do {                                                                                                                 \
+        if (!window_ok(ctx, sp)) return fail(ctx, VXB_ERR_INVALID, "start_pos + render_size exceeds 2^28 chunks");        \
     } while (0)
 #define VXB_REQUIRE(ctx, cond, msg)                                  \
     do {                                                             \
@@ -480,6 +491,7 @@ static size_t load_chunk_updates(vxb_ctx* c, const uint32_t start_pos[3]) {  // 
 int vxb_compute(vxb_ctx* c, const uint32_t start_pos[3], const vxb_projectile* projectiles, uint32_t n_projectiles,
                 const vxb_player* players, uint32_t n_players) {
     if (!c || !start_pos) return VXB_ERR_INVALID;
+    VXB_WINDOW(c, start_pos);
     VXB_REQUIRE(c, n_projectiles == 0 || projectiles, "vxb_compute: projectiles is NULL");
     VXB_REQUIRE(c, n_players == 0 || players, "vxb_compute: players is NULL");
     VXB_CUDA(c, cudaSetDevice(c->device));
@@ -663,6 +675,7 @@ int vxb_device_ptrs(vxb_ctx* c, vxb_ptrs* out) {
 int vxb_dispatch_worldgen(vxb_ctx* c, const uint32_t start_pos[3], const int32_t (*chunk_loads)[4], uint32_t n_workgroups, int complete,
                           uint32_t* load_results_out) {
     if (!c || !start_pos) return VXB_ERR_INVALID;
+    VXB_WINDOW(c, start_pos);
     if (n_workgroups == 0) return VXB_OK;
     VXB_REQUIRE(c, chunk_loads, "vxb_dispatch_worldgen: chunk_loads is NULL");
     VXB_REQUIRE(c, n_workgroups % 8 == 0, "vxb_dispatch_worldgen: n_workgroups must be a multiple of 8 (8 workgroups per chunk)");
@@ -690,6 +703,7 @@ int vxb_dispatch_worldgen(vxb_ctx* c, const uint32_t start_pos[3], const int32_t
 int vxb_dispatch_voxel_update(vxb_ctx* c, const uint32_t start_pos[3], const uint32_t (*chunk_updates)[4], uint32_t n,
                               const uint32_t offset[3], uint32_t* flags_out) {
     if (!c || !start_pos || !offset) return VXB_ERR_INVALID;
+    VXB_WINDOW(c, start_pos);
     if (n == 0) return VXB_OK;
     VXB_REQUIRE(c, chunk_updates, "vxb_dispatch_voxel_update: chunk_updates is NULL");
     VXB_REQUIRE(c, offset[0] < 2 && offset[1] < 2 && offset[2] < 2, "vxb_dispatch_voxel_update: offset must be in {0,1}^3");
@@ -709,6 +723,7 @@ int vxb_dispatch_voxel_update(vxb_ctx* c, const uint32_t start_pos[3], const uin
 
 int vxb_dispatch_write_voxels(vxb_ctx* c, const uint32_t start_pos[3], const uint32_t (*writes)[4], uint32_t n) {
     if (!c || !start_pos) return VXB_ERR_INVALID;
+    VXB_WINDOW(c, start_pos);
     if (n == 0) return VXB_OK;
     VXB_REQUIRE(c, writes, "vxb_dispatch_write_voxels: writes is NULL");
     VXB_CUDA(c, cudaSetDevice(c->device));
@@ -730,6 +745,7 @@ int vxb_dispatch_unload(vxb_ctx* c, int32_t unload_index, uint32_t unload_compon
 int vxb_dispatch_entities(vxb_ctx* c, const uint32_t start_pos[3], vxb_projectile* projectiles, uint32_t n_projectiles, vxb_player* players,
                           uint32_t n_players, int run_projectiles, int run_players, vxb_collision* collisions_out, uint32_t* n_collisions) {
     if (!c || !start_pos) return VXB_ERR_INVALID;
+    VXB_WINDOW(c, start_pos);
     VXB_REQUIRE(c, n_projectiles == 0 || projectiles, "vxb_dispatch_entities: projectiles is NULL");
     VXB_REQUIRE(c, n_players == 0 || players, "vxb_dispatch_entities: players is NULL");
     VXB_CUDA(c, cudaSetDevice(c->device));
@@ -773,6 +789,7 @@ int vxb_update_list_upload(vxb_ctx* c, const uint32_t (*chunk_updates)[4], uint3
 
 int vxb_update_list_run(vxb_ctx* c, const uint32_t start_pos[3], const uint32_t offset[3]) {
     if (!c || !start_pos || !offset) return VXB_ERR_INVALID;
+    VXB_WINDOW(c, start_pos);
     VXB_REQUIRE(c, offset[0] < 2 && offset[1] < 2 && offset[2] < 2, "vxb_update_list_run: offset must be in {0,1}^3");
     VXB_CUDA(c, cudaSetDevice(c->device));
     VXB_CUDA(c, launch_voxel_update(c->world(start_pos), c->res_list.p, c->res_n, offset, c->res_flags.p, c->update_variant, c->stream));
@@ -821,6 +838,7 @@ static RayOut ray_out(vxb_ctx* c) {
 int vxb_raymarch(vxb_ctx* c, const uint32_t start_pos[3], const vxb_player* cams, uint32_t n_views, uint32_t w, uint32_t h,
                  const vxb_ray_caps* caps, const float* raster_depth) {
     if (!c || !start_pos) return VXB_ERR_INVALID;
+    VXB_WINDOW(c, start_pos);
     VXB_REQUIRE(c, cams && caps, "vxb_raymarch: cams / caps is NULL");
     VXB_REQUIRE(c, n_views > 0 && w > 0 && h > 0, "vxb_raymarch: empty view");
     VXB_REQUIRE(c, n_views <= 65535, "vxb_raymarch: at most 65535 views per call");
@@ -847,6 +865,7 @@ int vxb_raymarch(vxb_ctx* c, const uint32_t start_pos[3], const vxb_player* cams
 int vxb_raymarch_rays(vxb_ctx* c, const uint32_t start_pos[3], const float (*pos)[3], const float (*dir)[3], uint64_t n, int kind,
                       uint32_t max_iterations, uint32_t projectile_count) {
     if (!c || !start_pos) return VXB_ERR_INVALID;
+    VXB_WINDOW(c, start_pos);
     VXB_REQUIRE(c, n == 0 || (pos && dir), "vxb_raymarch_rays: pos / dir is NULL");
     VXB_REQUIRE(c, kind >= 0 && kind <= 3, "vxb_raymarch_rays: kind must be 0..3");
     VXB_REQUIRE(c, projectile_count <= c->projectiles.n, "vxb_raymarch_rays: projectile_count exceeds the projectile buffer");
@@ -939,6 +958,7 @@ int vxb_write_table(vxb_ctx* c, const uint32_t* in) {
 }
 int vxb_world_checksum(vxb_ctx* c, const uint32_t start_pos[3], uint64_t* out) {
     if (!c || !start_pos || !out) return VXB_ERR_INVALID;
+    VXB_WINDOW(c, start_pos);
     VXB_CUDA(c, cudaSetDevice(c->device));
     VXB_CUDA(c, launch_checksum(c->world(start_pos), c->scalars.p + 1, c->stream));
     unsigned long long v = 0;

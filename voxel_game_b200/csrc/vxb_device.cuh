@@ -35,25 +35,49 @@ struct World {
     uint32_t* __restrict__ pool;         // [slot][4096]
     uint32_t rs[3];                      // render_size (chunks)
     uint32_t sp[3];                      // start_pos (chunks)
+    // derived on the host (make_world): window origin and extent in voxels, start_pos % render_size
+    uint32_t wmin[3], wext[3], spm[3];
 };
+
+// Fills the derived fields. The window must not wrap around u32: 16*(start_pos + render_size) < 2^32
+// (the reference assumes the same); callers validate it.
+__host__ __device__ inline void world_derive(World& w) {
+    for (int a = 0; a < 3; a++) {
+        w.wmin[a] = CHUNK_SIZE * w.sp[a];
+        w.wext[a] = CHUNK_SIZE * w.rs[a];
+        w.spm[a] = w.sp[a] % w.rs[a];
+    }
+}
 
 // get_data of every shader (e.g. compute_voxel.glsl:43-49) on the linear pool.
 __device__ __forceinline__ uint32_t table_lookup(const World& w, uint32_t cx, uint32_t cy, uint32_t cz) {
     return __ldg(&w.table[((uint64_t)(cx % w.rs[0]) * w.rs[1] + (cy % w.rs[1])) * w.rs[2] + (cz % w.rs[2])]);
 }
 __device__ __forceinline__ bool in_window(const World& w, uint32_t x, uint32_t y, uint32_t z) {
-    // !(any(lessThan(pos, 16*start)) || any(greaterThanEqual(pos - 16*start, 16*render_size)))
-    const uint32_t sx = CHUNK_SIZE * w.sp[0], sy = CHUNK_SIZE * w.sp[1], sz = CHUNK_SIZE * w.sp[2];
-    return x >= sx && y >= sy && z >= sz && (x - sx) < CHUNK_SIZE * w.rs[0] && (y - sy) < CHUNK_SIZE * w.rs[1] &&
-           (z - sz) < CHUNK_SIZE * w.rs[2];
+    // !(any(lessThan(pos, 16*start)) || any(greaterThanEqual(pos - 16*start, 16*render_size))).
+    // One unsigned compare per axis: for pos < 16*start the difference wraps to >= 2^32 - 16*start,
+    // which is >= the extent because the window does not wrap around u32 (validated on the host).
+    return (x - w.wmin[0]) < w.wext[0] && (y - w.wmin[1]) < w.wext[1] && (z - w.wmin[2]) < w.wext[2];
 }
 __device__ __forceinline__ uint64_t voxel_index(const World& w, uint32_t x, uint32_t y, uint32_t z) {
     uint32_t slot = table_lookup(w, x >> 4, y >> 4, z >> 4);
     return (uint64_t)slot * CHUNK_VOLUME + ((x & 15u) << 8 | (y & 15u) << 4 | (z & 15u));
 }
+// (chunk % render_size) for a chunk coordinate INSIDE the window, without an integer division:
+// c - sp lies in [0, rs), so (c - sp) + (sp % rs) lies in [0, 2 rs).
+__device__ __forceinline__ uint32_t wrap_in_window(uint32_t c, uint32_t sp, uint32_t spm, uint32_t rs) {
+    const uint32_t q = (c - sp) + spm;
+    return q >= rs ? q - rs : q;
+}
+__device__ __forceinline__ uint32_t table_lookup_in_window(const World& w, uint32_t cx, uint32_t cy, uint32_t cz) {
+    const uint32_t tx = wrap_in_window(cx, w.sp[0], w.spm[0], w.rs[0]), ty = wrap_in_window(cy, w.sp[1], w.spm[1], w.rs[1]),
+                   tz = wrap_in_window(cz, w.sp[2], w.spm[2], w.rs[2]);
+    return __ldg(&w.table[((uint64_t)tx * w.rs[1] + ty) * w.rs[2] + tz]);
+}
 __device__ __forceinline__ uint32_t get_data(const World& w, uint32_t x, uint32_t y, uint32_t z) {
     if (!in_window(w, x, y, z)) return VOX_OOB;
-    return w.pool[voxel_index(w, x, y, z)];
+    const uint32_t slot = table_lookup_in_window(w, x >> 4, y >> 4, z >> 4);
+    return w.pool[(uint64_t)slot * CHUNK_VOLUME + ((x & 15u) << 8 | (y & 15u) << 4 | (z & 15u))];
 }
 
 // ---- strict GLSL-style scalar helpers (same positions as the oracle's shim) ----
@@ -102,8 +126,13 @@ __device__ __forceinline__ void quat_inverse(const float q[4], float out[4]) {
     out[0] = -q[0] / d; out[1] = -q[1] / d; out[2] = -q[2] / d; out[3] = q[3] / d;
 }
 
-// frag.glsl:66-70 per axis
+// frag.glsl:66-70 per axis: max((vmin - pos) / ray, (vmax - pos) / ray).
+// With vmin < vmax and ray strictly positive (negative) the second (first) quotient is the larger one
+// — IEEE division by a fixed divisor is monotonic — so one division gives the same bits as two and a
+// max. ray == +-0 (quotients are +-inf or NaN) and NaN take the literal form.
 __device__ __forceinline__ float ray_box_axis(float pos, float ray, float vmin, float vmax) {
+    if (ray > 0.0f) return (vmax - pos) / ray;
+    if (ray < 0.0f) return (vmin - pos) / ray;
     return gmax((vmin - pos) / ray, (vmax - pos) / ray);
 }
 
