@@ -356,7 +356,8 @@ def bench_rays(args, torch, vg, peak):
 
     RS, SP = C2_RS, C2_SP
     n = RS[0] * RS[1] * RS[2]
-    gs = vg.GameSettings(render_size=RS, max_loaded_chunks=2 + n, max_worldgen_rate=8 * 32768, max_update_rate=1024)
+    gs = vg.GameSettings(render_size=RS, max_loaded_chunks=2 + n, max_worldgen_rate=8 * 32768, max_update_rate=1024,
+                         max_collisions=1 << 22)
     gpu = vg.VoxelComputePipeline(gs, device=torch.cuda.current_device())
     gpu.set_stream(torch.cuda.current_stream().cuda_stream)  # the explicit stream set in run_ours
     chunks = chunk_grid(0, RS[0], RS, SP)
@@ -415,15 +416,74 @@ def bench_rays(args, torch, vg, peak):
 
         assert gpu._lib.vxb_ray_download(gpu._h, None, None, None, None, None, ptr(out_lc), ptr(out_d), None) == 0
     e2e_s = time.perf_counter() - t0
+    collisions = None if args.no_collisions else bench_collisions(args, torch, vg, gpu, SP, RS, (cx, col_y, cz), peak)
     gpu.close()
     achieved = alg_bytes / (ms / args.steps / 1e3) / 1e9
-    return {"metric": "rays/s", "value": W * H * args.steps / (ms / 1e3), "unit": "rays/s", "ms_per_frame": ms / args.steps,
+    return {"collisions": collisions,"metric": "rays/s", "value": W * H * args.steps / (ms / 1e3), "unit": "rays/s", "ms_per_frame": ms / args.steps,
             "config": {"workload": "BASELINE configs[1]: 1920x1080 primary-ray DDA, 1024x256x1024-voxel open-world map, 8 cameras cycled",
                        "primary_ray_dist": 100},
             "mean_iterations_per_ray": mean_iters / (W * H), "mean_layers_per_ray": mean_layers / (W * H),
             "roofline": {"bound": "hbm", "model": "gather: 8 B per DDA iteration + 16 B + 24 B x layers per ray", "achieved": achieved,
                          "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic_from_profiles("k_raymarch_primary_bytes_per_launch")},
             "e2e": {"value": W * H * args.steps / e2e_s, "unit": "rays/s", "h2d_bytes_per_step": 128, "d2h_bytes_per_step": W * H * 8}}
+
+
+def bench_collisions(args, torch, vg, gpu, SP, RS, centre, peak):
+    """BASELINE configs[3]: 1M projectiles + 64 player hulls vs the (replicated) config-2 world, one tick."""
+    from tests import scenes
+    from tests.oracle_lib import CpuWorld
+
+    cx, col_y, cz = centre
+    n_proj, n_side = args.projectiles, 8
+    lo = (16 * SP[0] + 8, 16 * SP[1] + 8, 16 * SP[2] + 8)
+    hi = (16 * (SP[0] + RS[0]) - 8, 16 * (SP[1] + RS[1]) - 8, 16 * (SP[2] + RS[2]) - 8)
+    pr = scenes.random_projectiles(n_proj, lo, hi, seed=0x5EED0001 & 0x7FFFFFFF)
+    pl = scenes.players_grid(n_side, (cx, col_y, cz), 48.0, col_y + 4.0, seed=64)
+    gpu.dispatch_entities(SP, projectiles=pr, players=pl, run_projectiles=False, run_players=False)  # upload only
+    ptrs = gpu.device_ptrs()
+    proj_t = torch.as_tensor(DevView(ptrs.projectiles, n_proj * 28), device="cuda")
+    play_t = torch.as_tensor(DevView(ptrs.players, n_side * n_side * 32), device="cuda")
+    proj0, play0 = proj_t.clone(), play_t.clone()
+    steps = max(4, min(args.steps, 16))
+    total_ms, n_coll = 0.0, 0
+    for i in range(3 + steps):
+        proj_t.copy_(proj0)  # the kernels update entities in place: every step starts from the same batch
+        play_t.copy_(play0)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        gpu.entities_resident_run(SP, n_proj, n_side * n_side)
+        e1.record()
+        torch.cuda.synchronize()
+        if i >= 3:
+            total_ms += e0.elapsed_time(e1)
+    proj_t.copy_(proj0)
+    play_t.copy_(play0)
+    n_coll = gpu.entities_resident_run(SP, n_proj, n_side * n_side, want_count=True)
+    ms = total_ms / steps
+    out = {"metric": "projectiles/s", "value": n_proj / (ms / 1e3), "unit": "projectiles/s", "ms_per_tick": ms, "collisions_found": n_coll,
+           "config": {"workload": "BASELINE configs[3]: %d projectiles + %d player hulls vs the config-2 world, one tick (dt 0.02)" % (n_proj, n_side * n_side),
+                      "note": "device time of k_projectiles + k_players; entity arrays restored by a device copy between steps (untimed)"}}
+    if not args.no_cpu:
+        # oracle on a bounded sample of the same batch, same world (downloaded); counters from a sequential pass
+        n_s = min(65536, n_proj)
+        n = RS[0] * RS[1] * RS[2]
+        cw = CpuWorld(RS, SP, 2 + n)
+        cw.table[:] = gpu.read_table()
+        cw.pool[:] = gpu.read_pool(0, 2 + n)
+        _, _, counters = cw.projectiles(pr[:n_s], pl, capacity=1 << 20, parallel=False)
+        t0 = time.perf_counter()
+        cw.projectiles(pr[:n_s], pl, capacity=1 << 20, parallel=True)
+        cw.entities(pl)
+        cs = time.perf_counter() - t0
+        scale = n_proj / n_s
+        alg = 224.0 * n_proj + 8.0 * float(counters[1]) * scale + 8.0 * float(counters[2]) * scale + 16.0 * n_coll + 2 * 128 * n_side * n_side
+        out["cpu_baseline"] = {"value": n_s / cs, "unit": "projectiles/s", "cores": int(cw.lib.orc_num_threads()), "kind": "port",
+                               "sample": "first %d projectiles of the same batch against the same world, OpenMP over projectiles" % n_s}
+        out["roofline"] = {"bound": "hbm", "model": "gather: 224 B per projectile + 8 B per terrain sample + 8 B per LOS iteration + 16 B per collision "
+                           "(sample / LOS counts from the oracle on the CPU sample, scaled)", "achieved": alg / (ms / 1e3) / 1e9, "peak": peak,
+                           "unit": "GB/s", "frac": alg / (ms / 1e3) / 1e9 / peak, "traffic": None,
+                           "terrain_samples_per_projectile": float(counters[1]) / n_s, "los_iterations_per_projectile": float(counters[2]) / n_s}
+    return out
 
 
 # ------------------------------------------------------------------------------------------------
@@ -502,6 +562,8 @@ def main():
     ap.add_argument("--settle", type=int, default=96, help="untimed update ticks after worldgen (world preparation)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-rays", action="store_true")
+    ap.add_argument("--no-collisions", action="store_true")
+    ap.add_argument("--projectiles", type=int, default=1 << 20)
     ap.add_argument("--cpu-sample-cols", type=int, default=4)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -225,6 +225,13 @@ int vxb_dispatch_entities(vxb_ctx* ctx, const uint32_t start_pos[3], vxb_project
                           vxb_player* players, uint32_t n_players, int run_projectiles, int run_players,
                           vxb_collision* collisions_out, uint32_t* n_collisions);
 
+/* Re-runs compute_projectile.glsl / compute_entity.glsl on the projectiles and players already in
+ * the ctx's device buffers (uploaded by the last vxb_dispatch_entities / vxb_compute), without any
+ * host traffic; the collision list and its counter are reset first. For benchmark config 4.
+ * n_collisions_out (nullable) synchronises and receives the collision count. */
+int vxb_entities_resident_run(vxb_ctx* ctx, const uint32_t start_pos[3], uint32_t n_projectiles, uint32_t n_players,
+                              int run_projectiles, int run_players, uint32_t* n_collisions_out);
+
 /* Resident work list for repeated full sweeps (benchmark configs 3 and 5): upload once, then run
  * the update dispatch on it any number of times without host traffic. */
 int vxb_update_list_upload(vxb_ctx* ctx, const uint32_t (*chunk_updates)[4], uint32_t n);

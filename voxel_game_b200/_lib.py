@@ -135,6 +135,7 @@ SIGNATURES = {
     "vxb_dispatch_write_voxels": (ctypes.c_int, [c_vp, c_vp, c_vp, c_u32]),
     "vxb_dispatch_unload": (ctypes.c_int, [c_vp, c_i32, c_u32]),
     "vxb_dispatch_entities": (ctypes.c_int, [c_vp, c_vp, c_vp, c_u32, c_vp, c_u32, ctypes.c_int, ctypes.c_int, c_vp, c_vp]),
+    "vxb_entities_resident_run": (ctypes.c_int, [c_vp, c_vp, c_u32, c_u32, ctypes.c_int, ctypes.c_int, c_vp]),
     "vxb_update_list_upload": (ctypes.c_int, [c_vp, c_vp, c_u32]),
     "vxb_update_list_run": (ctypes.c_int, [c_vp, c_vp, c_vp]),
     "vxb_update_list_flags": (ctypes.c_int, [c_vp, c_vp, c_u32]),

@@ -776,6 +776,27 @@ int vxb_dispatch_entities(vxb_ctx* c, const uint32_t start_pos[3], vxb_projectil
     return VXB_OK;
 }
 
+int vxb_entities_resident_run(vxb_ctx* c, const uint32_t start_pos[3], uint32_t n_projectiles, uint32_t n_players, int run_projectiles,
+                              int run_players, uint32_t* n_collisions_out) {
+    if (!c || !start_pos) return VXB_ERR_INVALID;
+    VXB_WINDOW(c, start_pos);
+    VXB_REQUIRE(c, n_projectiles <= c->projectiles.n && n_players <= c->players.n, "vxb_entities_resident_run: count exceeds the resident buffers");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    VXB_CUDA(c, cudaMemsetAsync(c->collisions.p, 0, (size_t)c->s.max_collisions * sizeof(vxb_collision), st));
+    VXB_CUDA(c, cudaMemsetAsync(c->collision_count.p, 0, sizeof(uint32_t), st));
+    const World w = c->world(start_pos);
+    if (run_projectiles && n_projectiles)
+        VXB_CUDA(c, launch_projectiles(w, c->projectiles.p, n_projectiles, c->players.p, n_players, c->collisions.p, c->s.max_collisions,
+                                       c->collision_count.p, c->s.delta_time, st));
+    if (run_players && n_players) VXB_CUDA(c, launch_players(w, c->players.p, n_players, c->s.delta_time, st));
+    if (n_collisions_out) {
+        VXB_CUDA(c, cudaMemcpyAsync(n_collisions_out, c->collision_count.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+        VXB_CUDA(c, cudaStreamSynchronize(st));
+    }
+    return VXB_OK;
+}
+
 int vxb_update_list_upload(vxb_ctx* c, const uint32_t (*chunk_updates)[4], uint32_t n) {
     if (!c) return VXB_ERR_INVALID;
     VXB_REQUIRE(c, n == 0 || chunk_updates, "vxb_update_list_upload: chunk_updates is NULL");

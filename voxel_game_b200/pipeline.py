@@ -252,6 +252,16 @@ class VoxelComputePipeline:
         )
         return pr, pl, co[: n.value].copy(), int(n.value)
 
+    def entities_resident_run(self, start_pos, n_projectiles, n_players, run_projectiles=True, run_players=True, want_count=False):
+        n = ctypes.c_uint32(0)
+        self._check(
+            self._lib.vxb_entities_resident_run(
+                self._h, ptr(_u32(start_pos, 3)), int(n_projectiles), int(n_players), int(run_projectiles), int(run_players),
+                ctypes.byref(n) if want_count else None,
+            )
+        )
+        return int(n.value)
+
     def update_list_upload(self, chunk_updates):
         cu = np.ascontiguousarray(np.asarray(chunk_updates, dtype=np.uint32).reshape(-1, 4))
         self._check(self._lib.vxb_update_list_upload(self._h, ptr(cu), cu.shape[0]))
