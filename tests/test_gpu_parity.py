@@ -112,6 +112,25 @@ def test_worldgen(world_gen, seed, center):
     gpu.close()
 
 
+def test_worldgen_scattered_chunks():
+    # chunks far apart (different lattice cells, large coordinates): exercises the per-block candidate
+    # culling of the open-world kernel against the oracle's full 5x5x5 loops
+    rng = np.random.RandomState(12)
+    n = 24
+    for world_gen, seed in ((0, 0), (1, 77)):
+        for k in range(n // 8):
+            base = (int(rng.randint(8, 4000)), int(rng.randint(108, 116)), int(rng.randint(8, 4000)))
+            if world_gen == 1:
+                base = (int(rng.randint(610, 640)), int(rng.randint(110, 114)), int(rng.randint(618, 632)))
+            rs = (2, 2, 2)
+            gpu, cpu = make_pair(rs, base, 2 + 8, world_gen=world_gen, seed=seed)
+            chunks = [(base[0] + x, base[1] + y, base[2] + z) for x in range(2) for y in range(2) for z in range(2)]
+            loads = chunk_loads_for(chunks, range(2, 10), forced=True)
+            assert np.array_equal(gpu.dispatch_worldgen(base, loads), cpu.worldgen(loads, world_gen))
+            assert_world_equal(gpu, cpu)
+            gpu.close()
+
+
 def test_worldgen_sky_chunk_is_all_air():
     sp = (625, 125, 625)  # y = 2000: far above SEA_LEVEL
     gpu, cpu = make_pair((1, 1, 1), sp, 4)

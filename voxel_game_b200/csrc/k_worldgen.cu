@@ -12,6 +12,8 @@
 //  * zero-weight skip: a cell with |d|^2 >= 2 has smoothstep == 1 exactly, hence weight w == +0 and
 //    its contributions are +-0; adding +-0 to an accumulator that started at +0 never changes it,
 //    so the sqrt/divide/polynomial are only executed for the ~10-15 % of cells that matter.
+//  * per-CTA candidate lists: of the 216 staged cells only those whose jittered point can be within
+//    sqrt(2) of the block (conservatively) are visited at all, in the shader's loop order.
 //  * only the y and w lanes of the gradient vec4s feed the material decision tree; x/z lanes of
 //    the reference are dead code and are not computed.
 //  * the density field has y-scale exactly 0, so it only depends on the (x,z) column; it is
@@ -51,34 +53,76 @@ __device__ __forceinline__ void stage_field(FieldStage& fs, int (&base)[3], cons
     }
 }
 
-// common.glsl:332-355 voronoise(p, 1.0, 1.0) -> (dir.y / a.y, a.x / a.y) from staged jitters.
-__device__ __forceinline__ yw voronoise_staged(const FieldStage& fs, const int (&base)[3], float px, float py, float pz) {
+// Candidate cells of one field for one 8^3 block, in ascending (z, y, x) order — the order of the
+// shader's loops. A lattice cell can only contribute to SOME voxel of the block if its jittered point
+// lies within sqrt(2) of the block's extent in lattice space; the test below is conservative (a margin
+// far above float rounding), every voxel still applies the exact |d|^2 < 2 test, and a culled cell
+// would have contributed exactly +-0. Typically ~20-30 of the 216 staged cells survive.
+struct FieldCand {
+    uint32_t n;
+    uint32_t e[216];  // cx | cy << 3 | cz << 6 | c << 16  (c = staged index)
+};
+
+__device__ __forceinline__ void build_candidates(FieldCand& fc, const FieldStage& fs, const int (&base)[3], const uint32_t origin[3],
+                                                 float sx, float sy, float sz, uint32_t tid, uint32_t* s_wcount) {
+    bool flag = false;
+    uint32_t packed = 0;
+    if (tid < 216) {
+        const int cx = tid % 6, cy = (tid / 6) % 6, cz = tid / 36;
+        const float4 o = fs.o[tid];
+        const float q[3] = {(float)(base[0] + cx) + o.x, (float)(base[1] + cy) + o.y, (float)(base[2] + cz) + o.z};
+        const float sc[3] = {sx, sy, sz};
+        float d2 = 0.0f, pabs = 0.0f;
+#pragma unroll
+        for (int a = 0; a < 3; a++) {
+            const float lo = sc[a] * (float)origin[a], hi = sc[a] * (float)(origin[a] + 7u);
+            const float e = fmaxf(fmaxf(lo - q[a], q[a] - hi), 0.0f);
+            d2 += e * e;
+            pabs = fmaxf(pabs, fabsf(hi));
+        }
+        const float r = 1.4143f + 0.01f + 8e-7f * pabs;  // sqrt(2) + margin + rounding of p at this magnitude
+        flag = d2 < r * r;
+        packed = (uint32_t)cx | ((uint32_t)cy << 3) | ((uint32_t)cz << 6) | (tid << 16);
+    }
+    const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, flag);
+    const uint32_t warp = tid >> 5, lane = tid & 31;
+    if (lane == 0 && warp < 8) s_wcount[warp] = __popc(ballot);
+    __syncthreads();
+    if (tid < 216) {
+        uint32_t off = __popc(ballot & ((1u << lane) - 1u));
+        for (uint32_t w2 = 0; w2 < warp; w2++) off += s_wcount[w2];
+        if (flag) fc.e[off] = packed;
+    }
+    if (tid == 0) {
+        uint32_t total = 0;
+        for (int w2 = 0; w2 < 7; w2++) total += s_wcount[w2];
+        fc.n = total;
+    }
+    __syncthreads();
+}
+
+// common.glsl:332-355 voronoise(p, 1.0, 1.0) -> (dir.y / a.y, a.x / a.y) from staged jitters, visiting
+// only the block's candidate cells (same order, same arithmetic for every cell that is visited).
+__device__ __forceinline__ yw voronoise_staged(const FieldStage& fs, const FieldCand& fc, const int (&base)[3], float px, float py, float pz) {
     const int ix = f2i(px) - base[0], iy = f2i(py) - base[1], iz = f2i(pz) - base[2];  // in [2,3]
     const float fx = gfract(px), fy = gfract(py), fz = gfract(pz);
     float ax = 0.0f, ay = 0.0f, diry = 0.0f;
-    float gfx[5], gfy[5], gfz[5];
-#pragma unroll
-    for (int t = 0; t < 5; t++) {
-        gfx[t] = (float)(t - 2) - fx;
-        gfy[t] = (float)(t - 2) - fy;
-        gfz[t] = (float)(t - 2) - fz;
-    }
-    for (int z = 0; z < 5; z++) {
-        for (int y = 0; y < 5; y++) {
-            const float4* row = &fs.o[((iz + z - 2) * 6 + (iy + y - 2)) * 6 + (ix - 2)];
-#pragma unroll
-            for (int x = 0; x < 5; x++) {
-                const float4 o = row[x];
-                const float dx = gfx[x] + o.x, dy = gfy[y] + o.y, dz = gfz[z] + o.z;
-                const float dsq = dx * dx + dy * dy + dz * dz;
-                if (dsq < 2.0f) {
-                    float t = gclamp(sqrtf(dsq) / 1.414f, 0.0f, 1.0f);
-                    const float w = 1.0f - t * t * (3.0f - 2.0f * t);
-                    ax += o.w * w;
-                    ay += w;
-                    diry += dy * (2.0f * o.w - 1.0f) * w;
-                }
-            }
+    const uint32_t n = fc.n;
+    for (uint32_t k = 0; k < n; k++) {
+        const uint32_t e = fc.e[k];
+        // offset of the cell relative to this voxel's own cell: the shader only visits -2..2 per axis
+        const int kx = (int)(e & 7u) - ix, ky = (int)((e >> 3) & 7u) - iy, kz = (int)((e >> 6) & 7u) - iz;
+        if ((uint32_t)(kx + 2) > 4u || (uint32_t)(ky + 2) > 4u || (uint32_t)(kz + 2) > 4u) continue;
+        const float4 o = fs.o[e >> 16];
+        // vec3 d = g - f + o.xyz with g = vec3(x, y, z)
+        const float dx = ((float)kx - fx) + o.x, dy = ((float)ky - fy) + o.y, dz = ((float)kz - fz) + o.z;
+        const float dsq = dx * dx + dy * dy + dz * dz;
+        if (dsq < 2.0f) {
+            float t = gclamp(sqrtf(dsq) / 1.414f, 0.0f, 1.0f);
+            const float w = 1.0f - t * t * (3.0f - 2.0f * t);
+            ax += o.w * w;
+            ay += w;
+            diry += dy * (2.0f * o.w - 1.0f) * w;
         }
     }
     return yw{diry / ay, ax / ay};
@@ -159,6 +203,8 @@ __device__ __forceinline__ uint32_t open_world_decide(uint32_t gx, uint32_t gy, 
 __global__ void __launch_bounds__(512) k_worldgen_open(uint32_t* __restrict__ pool, const int4* __restrict__ chunk_loads,
                                                        uint32_t* __restrict__ load_results) {
     __shared__ FieldStage s_macro, s_dens, s_temp, s_cave;
+    __shared__ FieldCand c_macro, c_dens, c_temp, c_cave;
+    __shared__ uint32_t s_wcount[8];
     __shared__ int s_base[4][3];
     __shared__ yw s_density[64];
 
@@ -178,6 +224,17 @@ __global__ void __launch_bounds__(512) k_worldgen_open(uint32_t* __restrict__ po
         if (tid == 0) { s_base[3][0] = b[0]; s_base[3][1] = b[1]; s_base[3][2] = b[2]; }
     }
     __syncthreads();
+    {
+        int b[3];
+        b[0] = s_base[0][0]; b[1] = s_base[0][1]; b[2] = s_base[0][2];
+        build_candidates(c_macro, s_macro, b, origin, 0.01f, 0.00001f, 0.01f, tid, s_wcount);
+        b[0] = s_base[1][0]; b[1] = s_base[1][1]; b[2] = s_base[1][2];
+        build_candidates(c_dens, s_dens, b, origin, 0.04f, 0.0f, 0.04f, tid, s_wcount);
+        b[0] = s_base[2][0]; b[1] = s_base[2][1]; b[2] = s_base[2][2];
+        build_candidates(c_temp, s_temp, b, origin, 0.005f, 0.0005f, 0.005f, tid, s_wcount);
+        b[0] = s_base[3][0]; b[1] = s_base[3][1]; b[2] = s_base[3][2];
+        build_candidates(c_cave, s_cave, b, origin, 0.06f, 0.035f, 0.06f, tid, s_wcount);
+    }
 
     const uint32_t lz = tid & 7, ly = (tid >> 3) & 7, lx = tid >> 6;
     const uint32_t gx = origin[0] + lx, gy = origin[1] + ly, gz = origin[2] + lz;
@@ -190,14 +247,14 @@ __global__ void __launch_bounds__(512) k_worldgen_open(uint32_t* __restrict__ po
         const uint32_t cx = tid >> 3, cz = tid & 7;
         base[0] = s_base[1][0]; base[1] = s_base[1][1]; base[2] = s_base[1][2];
         // p.y = 0.0 * y is +0 for every finite y
-        s_density[tid] = voronoise_staged(s_dens, base, 0.04f * (float)(origin[0] + cx), 0.0f * ty, 0.04f * (float)(origin[2] + cz));
+        s_density[tid] = voronoise_staged(s_dens, c_dens, base, 0.04f * (float)(origin[0] + cx), 0.0f * ty, 0.04f * (float)(origin[2] + cz));
     }
     base[0] = s_base[0][0]; base[1] = s_base[0][1]; base[2] = s_base[0][2];
-    const yw Vmacro = voronoise_staged(s_macro, base, 0.01f * tx, 0.00001f * ty, 0.01f * tz);
+    const yw Vmacro = voronoise_staged(s_macro, c_macro, base, 0.01f * tx, 0.00001f * ty, 0.01f * tz);
     base[0] = s_base[2][0]; base[1] = s_base[2][1]; base[2] = s_base[2][2];
-    const yw Vtemp = voronoise_staged(s_temp, base, 0.005f * tx, 0.0005f * ty, 0.005f * tz);
+    const yw Vtemp = voronoise_staged(s_temp, c_temp, base, 0.005f * tx, 0.0005f * ty, 0.005f * tz);
     base[0] = s_base[3][0]; base[1] = s_base[3][1]; base[2] = s_base[3][2];
-    const yw Vcave = voronoise_staged(s_cave, base, 0.06f * tx, 0.035f * ty, 0.06f * tz);
+    const yw Vcave = voronoise_staged(s_cave, c_cave, base, 0.06f * tx, 0.035f * ty, 0.06f * tz);
     __syncthreads();
     const yw Vdens = s_density[lx * 8 + lz];
 
