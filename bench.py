@@ -416,10 +416,24 @@ def bench_rays(args, torch, vg, peak):
 
         assert gpu._lib.vxb_ray_download(gpu._h, None, None, None, None, None, ptr(out_lc), ptr(out_d), None) == 0
     e2e_s = time.perf_counter() - t0
+    # full fragment shader (primary DDA + get_color: shadow, reflection, 2 AO rays, PBR) at 1080p
+    for k in range(3):
+        gpu.render(SP, cams[k % 8:k % 8 + 1], W, H, caps, time=1.0)
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    for i in range(args.steps):
+        gpu.render(SP, cams[i % 8:i % 8 + 1], W, H, caps, time=1.0 + 0.02 * i)
+    f1.record()
+    torch.cuda.synchronize()
+    shade_ms = f0.elapsed_time(f1) / args.steps
+    shaded_iters = gpu.ray_download()["total_iterations"]  # DDA iterations (primary + secondary) of the last frame
+    shaded = {"metric": "shaded pixels/s", "value": W * H / (shade_ms / 1e3), "unit": "pixels/s", "ms_per_frame": shade_ms,
+              "dda_iterations_per_pixel": shaded_iters / (W * H),
+              "config": {"workload": "frag.glsl main (primary DDA + get_color) at 1920x1080 on the config-2 world, caps 100/40/20/15"}}
     collisions = None if args.no_collisions else bench_collisions(args, torch, vg, gpu, SP, RS, (cx, col_y, cz), peak)
     gpu.close()
     achieved = alg_bytes / (ms / args.steps / 1e3) / 1e9
-    return {"collisions": collisions,"metric": "rays/s", "value": W * H * args.steps / (ms / 1e3), "unit": "rays/s", "ms_per_frame": ms / args.steps,
+    return {"collisions": collisions, "shaded_frame": shaded,"metric": "rays/s", "value": W * H * args.steps / (ms / 1e3), "unit": "rays/s", "ms_per_frame": ms / args.steps,
             "config": {"workload": "BASELINE configs[1]: 1920x1080 primary-ray DDA, 1024x256x1024-voxel open-world map, 8 cameras cycled",
                        "primary_ray_dist": 100},
             "mean_iterations_per_ray": mean_iters / (W * H), "mean_layers_per_ray": mean_layers / (W * H),

@@ -252,6 +252,20 @@ int vxb_set_update_kernel(vxb_ctx* ctx, int variant);
  * Results stay on the device (vxb_ray_results). Asynchronous. */
 int vxb_raymarch(vxb_ctx* ctx, const uint32_t start_pos[3], const vxb_player* cams, uint32_t n_views, uint32_t w, uint32_t h,
                  const vxb_ray_caps* caps, const float* raster_depth);
+/* The whole fragment shader of the ray pass, frag.glsl main (:715-741): primary DDA (raycast) plus
+ * get_color (:650-713) — material noise, neighbour-voxel blending, sun shadow, reflection and two
+ * ambient-occlusion rays, Cook-Torrance lighting, depth transparency — for every pixel of n_views
+ * w x h views. `time` = PushConstants.time (src/raytracer.rs:247). The colour attachment becomes a
+ * device buffer of float RGBA ([view][py][px][4]); read it with vxb_color_download or borrow it with
+ * vxb_color_buffer. Pixels whose primary ray produced no layer are (1,0,0,1) as in :735-738.
+ * Asynchronous. raster_depth as in vxb_raymarch. */
+int vxb_render(vxb_ctx* ctx, const uint32_t start_pos[3], const vxb_player* cams, uint32_t n_views, uint32_t w, uint32_t h,
+               const vxb_ray_caps* caps, float time, const float* raster_depth);
+/* Synchronises and copies the last vxb_render result to a HOST array of n_pixels * 4 floats. */
+int vxb_color_download(vxb_ctx* ctx, float* rgba_out, uint64_t n_pixels);
+/* Device pointer and pixel count of the colour buffer (borrowed; valid until the next vxb_render that grows it). */
+int vxb_color_buffer(vxb_ctx* ctx, float** rgba_dev, uint64_t* n_pixels);
+
 /* Arbitrary rays (collision / visibility queries): pos, dir are HOST arrays [n][3].
  * kind 0 = raycast (primary, multi-layer), 1 = single_raycast (frag.glsl:93), 2 = simple_raycast
  * (:275), 3 = simple_raycast_w_projectiles (:161). For kinds 1-3 the result uses layer 0:

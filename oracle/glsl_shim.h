@@ -24,6 +24,8 @@
 //   pow(x,1.0)    = x   (voronoise is only ever called with v = 1.0 → k = 1.0)
 //   float→int     = truncate, saturating, NaN→0   (CUDA cvt.rzi semantics)
 //   float→uint    = truncate, saturating at 0 and 2^32-1, NaN→0
+//   pow(x, n)     = x*x*...*x for the integer exponents 3, 5, 20 of the shading code
+//   pow(b, e)     = (float)exp((double)e * log((double)b)) for the one real exponent (frag.glsl:703)
 #pragma once
 #include <cmath>
 #include <cstdint>
@@ -192,6 +194,14 @@ inline vec4 normalize(vec4 v) { return v / length(v); }
 inline vec3 cross(vec3 x, vec3 y) {
     return vec3(x.y * y.z - y.y * x.z, x.z * y.x - y.z * x.x, x.x * y.y - y.x * x.y);
 }
+inline vec3 mix(vec3 x, vec3 y, float a) { return x * (1.0f - a) + y * a; }
+inline vec3 reflect(vec3 I, vec3 N) { return I - 2.0f * dot(N, I) * N; }  // GLSL 4.50 8.5
+inline vec3& operator*=(vec3& a, float b) { a = a * b; return a; }
+// pow with a small positive integer exponent: repeated multiplication, left to right (shim position;
+// a GLSL pow(x, 20.0) is exp2(20 * log2(x)) on real drivers and undefined for x < 0)
+inline float ipow(float x, int n) { float r = x; for (int i = 1; i < n; i++) r = r * x; return r; }
+// pow with a real exponent (frag.glsl:703 only): evaluated in double, rounded to float (shim position)
+inline float rpow(float b, float e) { return (float)::exp((double)e * ::log((double)b)); }
 inline uint bitfieldExtract(uint value, int offset, int bits) {
     return (value >> offset) & ((1u << bits) - 1u);
 }

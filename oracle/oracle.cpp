@@ -14,6 +14,7 @@
 #include "compute_voxel.h"
 #include "entities.h"
 #include "raycast.h"
+#include "shading.h"
 #include "worldgen.h"
 
 using namespace orc;
@@ -146,6 +147,21 @@ void orc_raycast_image(uint32_t* chunks, uint32_t* voxels, const SimData* sim, c
         iters_sum += iters;
     }
     if (total_iters) *total_iters = iters_sum;
+}
+
+// frag.glsl:main for every pixel: primary DDA + get_color. out_rgba [w*h][4]. caps = {primary, shadow, reflection, ao}.
+void orc_render_image(uint32_t* chunks, uint32_t* voxels, const SimData* sim, const Player* cam, uint32_t w, uint32_t h, const uint32_t* caps,
+                      float time, const Projectile* projectiles, const float* raster_depth, float* out_rgba) {
+    float aspect_ratio = (float)w / (float)h;
+#pragma omp parallel for schedule(dynamic, 2)
+    for (int64_t py = 0; py < (int64_t)h; py++) {
+        frag::ShadeEnv e{frag::Env{Images{chunks, voxels}, *sim, projectiles, nullptr}, time, caps[0], caps[1], caps[2], caps[3], h};
+        for (uint32_t px = 0; px < w; px++) {
+            uint64_t i = (uint64_t)py * w + px;
+            vec4 c = frag::shade_pixel(e, *cam, aspect_ratio, px, (uint32_t)py, w, h, raster_depth ? raster_depth[i] : 0.0f);
+            out_rgba[4 * i + 0] = c.x; out_rgba[4 * i + 1] = c.y; out_rgba[4 * i + 2] = c.z; out_rgba[4 * i + 3] = c.w;
+        }
+    }
 }
 
 // Arbitrary ray batch through raycast(): pos/ray are [n][3].

@@ -140,6 +140,17 @@ class CpuWorld:
         o["total_iterations"] = int(it.value)
         return o
 
+    def render_image(self, cam, w, h, caps=(100, 40, 20, 15), time=0.0, projectiles=None, raster_depth=None):
+        """frag.glsl main for every pixel (primary DDA + get_color) -> float32 [h, w, 4]."""
+        cam = np.ascontiguousarray(cam, dtype=PLAYER_DTYPE).reshape(-1)[:1]
+        pr = None if projectiles is None else np.ascontiguousarray(projectiles, dtype=PROJECTILE_DTYPE)
+        s = self.sim(projectile_count=0 if pr is None else pr.size)
+        out = np.zeros((h, w, 4), np.float32)
+        capsa = np.asarray(caps, np.uint32)
+        rd = None if raster_depth is None else np.ascontiguousarray(raster_depth, np.float32)
+        self.lib.orc_render_image(p(self.table), p(self.pool), ctypes.byref(s), p(cam), u32(w), u32(h), p(capsa), f32(time), p(pr), p(rd), p(out))
+        return out
+
     def raycast_batch(self, pos, ray, max_iterations, projectiles=None):
         pos = np.ascontiguousarray(np.asarray(pos, np.float32).reshape(-1, 3))
         ray = np.ascontiguousarray(np.asarray(ray, np.float32).reshape(-1, 3))

@@ -325,3 +325,31 @@ def test_projectiles_and_players():
     # voxel damage written by projectiles (imageAtomicAdd): world state equal
     assert_world_equal(gpu, cpu)
     gpu.close()
+
+
+@pytest.mark.parametrize("world_gen,seed,yaw,pitch,t", [(0, 0, 0.3, -0.2, 0.0), (0, 0, 2.5, 0.15, 3.25), (1, 3646, 1.2, -0.35, 1.5)])
+def test_render_full_fragment_shader(world_gen, seed, yaw, pitch, t):
+    """frag.glsl main = primary DDA + get_color. One transcendental (depth_transparency ^ dist) and long
+    float chains: colours are compared at the north-star tolerance, not bit-exactly."""
+    import voxel_game_b200 as vg
+
+    rs = (6, 4, 6)
+    center = (10000, 1820 if world_gen == 0 else 1816, 10000)
+    sp = vg.initial_start_pos(center, rs)
+    gpu, cpu = _generated_world(rs, sp, world_gen, seed, update_ticks=16)
+    sy = _surface_y(cpu, center[0], center[2], 16 * (sp[1] + rs[1]) - 1)
+    cam = scenes.camera((center[0] + 0.5, sy + 4.3, center[2] + 0.5), yaw, pitch)
+    w, h = 128, 72
+    projectiles = scenes.random_projectiles(4, (center[0] - 8, sy + 2, center[2] - 8), (center[0] + 8, sy + 8, center[2] + 8), 21)
+    gpu.dispatch_entities(sp, projectiles=projectiles, players=cam, run_projectiles=False, run_players=False)
+    caps = vg.RayCaps(100, 40, 20, 15, 4)
+    game = vg.Game(gpu, vg.GameState(start_pos=list(sp)), cam)
+    vg.PointLightingSystem().draw((w, h), None, None, None, None, game, vg.GraphicsSettings(), rendered_projectile_count=4, time=t)
+    g = gpu.color_download()[0]
+    c = cpu.render_image(cam, w, h, caps=(100, 40, 20, 15), time=t, projectiles=projectiles)
+    assert np.isfinite(c).all() and g.shape == c.shape
+    close = np.isclose(g, c, rtol=RTOL, atol=1e-5).all(axis=2)
+    # a ray that grazes a voxel face can flip a branch under a 1-ulp difference of the pow: allow 0.1 % of pixels
+    assert close.mean() > 0.999, "only %.4f of the pixels agree" % close.mean()
+    assert c[..., :3].std() > 0.02  # a real picture, not a constant
+    gpu.close()

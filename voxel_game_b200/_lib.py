@@ -141,6 +141,9 @@ SIGNATURES = {
     "vxb_update_list_flags": (ctypes.c_int, [c_vp, c_vp, c_u32]),
     "vxb_set_update_kernel": (ctypes.c_int, [c_vp, ctypes.c_int]),
     "vxb_raymarch": (ctypes.c_int, [c_vp, c_vp, c_vp, c_u32, c_u32, c_u32, ctypes.POINTER(RayCaps), c_vp]),
+    "vxb_render": (ctypes.c_int, [c_vp, c_vp, c_vp, c_u32, c_u32, c_u32, ctypes.POINTER(RayCaps), c_f32, c_vp]),
+    "vxb_color_download": (ctypes.c_int, [c_vp, c_vp, c_u64]),
+    "vxb_color_buffer": (ctypes.c_int, [c_vp, ctypes.POINTER(c_vp), ctypes.POINTER(c_u64)]),
     "vxb_raymarch_rays": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_u64, ctypes.c_int, c_u32, c_u32]),
     "vxb_ray_results": (ctypes.c_int, [c_vp, ctypes.POINTER(RayBuffers)]),
     "vxb_ray_download": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),

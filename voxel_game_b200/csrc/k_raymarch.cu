@@ -335,6 +335,10 @@ __device__ Layer simple_raycast(const World& w, f3 pos, f3 ray, uint32_t max_ite
     return Layer{ray_pos, mk3(0, 0, 0), voxel_data, depth, 0u};
 }
 
+}  // namespace vxb
+#include "shade.cuh"
+namespace vxb {
+
 __device__ __forceinline__ void count_iters(const RayOut& o, uint32_t iters) {
     // one atomic per warp
     uint32_t s = iters;
@@ -377,6 +381,42 @@ __global__ void __launch_bounds__(64) k_raymarch_primary(World w, const vxb_play
         }
         out.layer_count[i] = count;
         out.dist[i] = depth;
+    }
+    count_iters(out, iters);
+}
+
+// frag.glsl main (:715-741) fused: primary DDA + get_color, one thread per pixel, f_color as float4.
+__global__ void __launch_bounds__(64) k_render(World w, const vxb_player* __restrict__ cams, uint32_t width, uint32_t height,
+                                               uint32_t max_iterations, ShadeParams sp, const float* __restrict__ raster_depth,
+                                               float4* __restrict__ color_out, RayOut out) {
+    const uint32_t lane_tile = threadIdx.x;
+    const uint32_t px = blockIdx.x * 8 + (lane_tile & 7), py = blockIdx.y * 8 + (lane_tile >> 3);
+    const uint32_t view = blockIdx.z;
+    uint32_t iters = 0;
+    if (px < width && py < height) {
+        const vxb_player& cam = cams[view];
+        const uint64_t i = ((uint64_t)view * height + py) * width + px;
+        const float aspect_ratio = (float)width / (float)height;
+        const float sx = (((float)px + 0.5f) / (float)width * 2.0f - 1.0f) * aspect_ratio;
+        const float sy = (((float)py + 0.5f) / (float)height * 2.0f - 1.0f) * 1.0f;
+        const f3 dir = mk3(cam.dir[0], cam.dir[1], cam.dir[2]), right = mk3(cam.right[0], cam.right[1], cam.right[2]),
+                 up = mk3(cam.up[0], cam.up[1], cam.up[2]);
+        const f3 ray = norm3(dir + sx * right - sy * up);
+        const f3 pos = mk3(cam.pos[0], cam.pos[1], cam.pos[2]);
+        const float max_depth = raster_depth ? raster_depth[i] : 0.0f;
+        Layer layers[5];
+#pragma unroll
+        for (int l = 0; l < 5; l++) layers[l] = Layer{mk3(0, 0, 0), mk3(0, 0, 0), 0u, 0.0f, 0u};
+        float depth;
+        const uint32_t count = raycast<false>(w, pos, ray, max_iterations, sp.projectiles, sp.projectile_count, max_depth, layers, depth, iters, out, i);
+        float4 c;
+        if (count == 0) {
+            c = make_float4(1.0f, 0.0f, 0.0f, 1.0f);  // :735-738
+        } else {
+            const f3 col = get_color(w, sp, ray, layers, count, depth, iters);
+            c = make_float4(col.x, col.y, col.z, 1.0f);
+        }
+        color_out[i] = c;
     }
     count_iters(out, iters);
 }
@@ -426,6 +466,25 @@ cudaError_t launch_raymarch_views(const World& w, const vxb_player* cams_dev, ui
     if (n_views == 0 || width == 0 || height == 0) return cudaSuccess;
     dim3 grid((width + 7) / 8, (height + 7) / 8, n_views);
     k_raymarch_primary<<<grid, 64, 0, st>>>(w, cams_dev, width, height, max_iterations, projectiles, projectile_count, raster_depth_dev, out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_render(const World& w, const vxb_player* cams_dev, uint32_t n_views, uint32_t width, uint32_t height,
+                          const vxb_ray_caps& caps, float time, const vxb_projectile* projectiles, const float* raster_depth_dev,
+                          float* color_out, unsigned long long* total_iters, cudaStream_t st) {
+    if (n_views == 0 || width == 0 || height == 0) return cudaSuccess;
+    ShadeParams sp;
+    sp.time = time;
+    sp.shadow_ray_dist = caps.shadow_ray_dist;
+    sp.reflection_ray_dist = caps.reflection_ray_dist;
+    sp.ao_ray_dist = caps.ao_ray_dist;
+    sp.vertical_resolution = height;  // raytracer.rs:252
+    sp.projectiles = projectiles;
+    sp.projectile_count = caps.projectile_count;
+    RayOut out{};
+    out.total_iters = total_iters;
+    dim3 grid((width + 7) / 8, (height + 7) / 8, n_views);
+    k_render<<<grid, 64, 0, st>>>(w, cams_dev, width, height, caps.primary_ray_dist, sp, raster_depth_dev, reinterpret_cast<float4*>(color_out), out);
     return cudaGetLastError();
 }
 

@@ -93,6 +93,8 @@ struct vxb_ctx {
     DevBuf<float> ray_pos, ray_normal, ray_ldist, ray_dist, ray_in_pos, ray_in_dir, raster_depth;
     DevBuf<uint32_t> ray_voxel, ray_leaving, ray_count;
     DevBuf<vxb_player> cams;
+    DevBuf<float> color;  // float4 per pixel of the last vxb_render
+    uint64_t n_color = 0;
     uint64_t n_rays = 0;
 
     // pinned staging
@@ -184,7 +186,7 @@ static void free_ctx(vxb_ctx* c) {
     c->update_flags.release(); c->voxel_writes.release(); c->scalars.release(); c->res_list.release(); c->res_flags.release();
     c->ray_pos.release(); c->ray_normal.release(); c->ray_ldist.release(); c->ray_dist.release(); c->ray_in_pos.release();
     c->ray_in_dir.release(); c->raster_depth.release(); c->ray_voxel.release(); c->ray_leaving.release(); c->ray_count.release();
-    c->cams.release();
+    c->cams.release(); c->color.release();
     c->h_projectiles.release(); c->h_players.release(); c->h_collisions.release(); c->h_collision_count.release();
     c->h_worldgen_updates.release(); c->h_worldgen_results.release(); c->h_chunk_updates.release(); c->h_update_flags.release();
     c->h_voxel_writes.release();
@@ -880,6 +882,48 @@ int vxb_raymarch(vxb_ctx* c, const uint32_t start_pos[3], const vxb_player* cams
     VXB_CUDA(c, cudaMemsetAsync(c->scalars.p, 0, sizeof(unsigned long long), st));
     VXB_CUDA(c, launch_raymarch_views(c->world(start_pos), c->cams.p, n_views, w, h, caps->primary_ray_dist, c->projectiles.p,
                                       caps->projectile_count, rd, ray_out(c), st));
+    return VXB_OK;
+}
+
+int vxb_render(vxb_ctx* c, const uint32_t start_pos[3], const vxb_player* cams, uint32_t n_views, uint32_t w, uint32_t h,
+               const vxb_ray_caps* caps, float time, const float* raster_depth) {
+    if (!c || !start_pos) return VXB_ERR_INVALID;
+    VXB_WINDOW(c, start_pos);
+    VXB_REQUIRE(c, cams && caps, "vxb_render: cams / caps is NULL");
+    VXB_REQUIRE(c, n_views > 0 && w > 0 && h > 0, "vxb_render: empty view");
+    VXB_REQUIRE(c, n_views <= 65535, "vxb_render: at most 65535 views per call");
+    VXB_REQUIRE(c, caps->projectile_count <= c->projectiles.n, "vxb_render: projectile_count exceeds the projectile buffer");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    const uint64_t n = (uint64_t)n_views * w * h;
+    VXB_CUDA(c, c->color.ensure(n * 4));
+    c->n_color = n;
+    VXB_CUDA(c, c->cams.ensure(n_views));
+    VXB_CUDA(c, cudaMemcpyAsync(c->cams.p, cams, (size_t)n_views * sizeof(vxb_player), cudaMemcpyHostToDevice, st));
+    const float* rd = nullptr;
+    if (raster_depth) {
+        VXB_CUDA(c, c->raster_depth.ensure(n));
+        VXB_CUDA(c, cudaMemcpyAsync(c->raster_depth.p, raster_depth, n * sizeof(float), cudaMemcpyHostToDevice, st));
+        rd = c->raster_depth.p;
+    }
+    VXB_CUDA(c, cudaMemsetAsync(c->scalars.p, 0, sizeof(unsigned long long), st));
+    VXB_CUDA(c, launch_render(c->world(start_pos), c->cams.p, n_views, w, h, *caps, time, c->projectiles.p, rd, c->color.p, c->scalars.p, st));
+    return VXB_OK;
+}
+
+int vxb_color_download(vxb_ctx* c, float* rgba_out, uint64_t n_pixels) {
+    if (!c || !rgba_out) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, n_pixels <= c->n_color, "vxb_color_download: more pixels than the last vxb_render produced");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    if (n_pixels) VXB_CUDA(c, cudaMemcpyAsync(rgba_out, c->color.p, n_pixels * 16, cudaMemcpyDeviceToHost, c->stream));
+    VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VXB_OK;
+}
+
+int vxb_color_buffer(vxb_ctx* c, float** rgba_dev, uint64_t* n_pixels) {
+    if (!c || !rgba_dev || !n_pixels) return VXB_ERR_INVALID;
+    *rgba_dev = c->color.p;
+    *n_pixels = c->n_color;
     return VXB_OK;
 }
 

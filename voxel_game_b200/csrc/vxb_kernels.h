@@ -44,6 +44,10 @@ struct RayOut {
 cudaError_t launch_raymarch_views(const World& w, const vxb_player* cams_dev, uint32_t n_views, uint32_t width, uint32_t height,
                                   uint32_t max_iterations, const vxb_projectile* projectiles, uint32_t projectile_count,
                                   const float* raster_depth_dev, RayOut out, cudaStream_t st);
+// frag.glsl main: primary DDA + shading (get_color) -> float4 colour per pixel
+cudaError_t launch_render(const World& w, const vxb_player* cams_dev, uint32_t n_views, uint32_t width, uint32_t height,
+                          const vxb_ray_caps& caps, float time, const vxb_projectile* projectiles, const float* raster_depth_dev,
+                          float* color_out, unsigned long long* total_iters, cudaStream_t st);
 cudaError_t launch_raymarch_rays(const World& w, const float* pos_dev, const float* dir_dev, uint64_t n, int kind,
                                  uint32_t max_iterations, const vxb_projectile* projectiles, uint32_t projectile_count, RayOut out,
                                  cudaStream_t st);

@@ -284,6 +284,18 @@ class VoxelComputePipeline:
         rd = None if raster_depth is None else np.ascontiguousarray(raster_depth, dtype=np.float32)
         self._check(self._lib.vxb_raymarch(self._h, ptr(_u32(start_pos, 3)), ptr(cams), cams.size, int(w), int(h), ctypes.byref(caps), ptr(rd)))
 
+    def render(self, start_pos, cams, w, h, caps: RayCaps, time=0.0, raster_depth=None):
+        """vxb_render: frag.glsl main (primary DDA + get_color) for every pixel; result stays on the device."""
+        cams = np.ascontiguousarray(cams, dtype=PLAYER_DTYPE).reshape(-1)
+        rd = None if raster_depth is None else np.ascontiguousarray(raster_depth, dtype=np.float32)
+        self._check(self._lib.vxb_render(self._h, ptr(_u32(start_pos, 3)), ptr(cams), cams.size, int(w), int(h), ctypes.byref(caps), float(time), ptr(rd)))
+        self._render_shape = (cams.size, int(h), int(w), 4)
+
+    def color_download(self):
+        out = np.zeros(self._render_shape, np.float32)
+        self._check(self._lib.vxb_color_download(self._h, ptr(out), out.size // 4))
+        return out
+
     def raymarch_rays(self, start_pos, pos, dirs, kind, max_iterations, projectile_count=0):
         p = np.ascontiguousarray(np.asarray(pos, dtype=np.float32).reshape(-1, 3))
         d = np.ascontiguousarray(np.asarray(dirs, dtype=np.float32).reshape(-1, 3))
@@ -377,14 +389,20 @@ class PointLightingSystem:
     RaycastResult layers in device memory (download with `game.voxel_compute.ray_download()`)."""
 
     def draw(self, viewport_dimensions, color_input, normals_input, depth_input, screen_to_world, game: Game,
-             graphics_settings: GraphicsSettings, rendered_projectile_count=0):
+             graphics_settings: GraphicsSettings, rendered_projectile_count=0, time=None):
         """Arguments as in raytracer.rs:234-243. color_input / normals_input / screen_to_world are
         unused without a rasterised G-buffer; depth_input is None or a [h, w] array of max_depth
-        (world-space distance to the rasterised surface, frag.glsl:725-728)."""
+        (world-space distance to the rasterised surface, frag.glsl:725-728).
+        With `time` (PushConstants.time) the full fragment shader runs (primary DDA + get_color) and the
+        colour buffer is left on the device (`game.voxel_compute.color_download()`); without it only the
+        primary DDA runs and the RaycastResult layers are left on the device."""
         w, h = int(viewport_dimensions[0]), int(viewport_dimensions[1])
         caps = RayCaps(
             graphics_settings.primary_ray_dist, graphics_settings.shadow_ray_dist, graphics_settings.reflection_ray_dist,
             graphics_settings.ao_ray_dist, int(rendered_projectile_count),
         )
         cam = np.ascontiguousarray(game.players, dtype=PLAYER_DTYPE).reshape(-1)[:1]
-        game.voxel_compute.raymarch(game.game_state.start_pos, cam, w, h, caps, depth_input)
+        if time is not None:
+            game.voxel_compute.render(game.game_state.start_pos, cam, w, h, caps, time, depth_input)
+        else:
+            game.voxel_compute.raymarch(game.game_state.start_pos, cam, w, h, caps, depth_input)
