@@ -340,9 +340,11 @@ def run_ours(args):
     gpu.close()
     del pool_t, first_col, ghost_col
 
-    # ---------------- C2: 1080p primary rays (N == 1) ----------------
-    if rank == 0 and world_size == 1 and not args.no_rays:
-        result["rays"] = bench_rays(args, torch, vg, peak)
+    # ---------------- C2: 1080p primary rays; view-range sharded over a replicated world for N > 1 ----------------
+    if not args.no_rays:
+        rays = bench_rays(args, torch, vg, peak, rank, world_size, dist)
+        if rank == 0:
+            result["rays"] = rays
 
     if world_size > 1:
         dist.barrier()
@@ -351,7 +353,7 @@ def run_ours(args):
         OUT.emit(result)
 
 
-def bench_rays(args, torch, vg, peak):
+def bench_rays(args, torch, vg, peak, rank=0, world_size=1, dist=None):
     from tests import scenes
 
     RS, SP = C2_RS, C2_SP
@@ -386,6 +388,32 @@ def bench_rays(args, torch, vg, peak):
     cams = np.concatenate([scenes.camera((cx + 0.5, col_y + 4.5, cz + 0.5), k * np.pi / 4, -0.2) for k in range(8)])
     W, H = 1920, 1080
     caps = vg.RayCaps(100, 40, 20, 15, 0)
+    # view-range sharding: one step = the 8 camera views (16.6 M rays), rank r renders views [8r/N, 8(r+1)/N)
+    # of its own replica of the world; no data-path collective
+    assert 8 % world_size == 0
+    mine = cams[rank * 8 // world_size:(rank + 1) * 8 // world_size]
+    for k in range(3):
+        gpu.raymarch(SP, mine, W, H, caps)
+    if world_size > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    b0.record()
+    for i in range(args.steps):
+        gpu.raymarch(SP, mine, W, H, caps)
+    b1.record()
+    if world_size > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    tb = torch.tensor([b0.elapsed_time(b1)], dtype=torch.float64, device="cuda")
+    if world_size > 1:
+        dist.all_reduce(tb, op=dist.ReduceOp.MAX)
+    batch_ms = float(tb.item()) / args.steps
+    batch8 = {"metric": "rays/s", "value": 8 * W * H / (batch_ms / 1e3), "unit": "rays/s", "ms_per_step": batch_ms, "n_gpus": world_size,
+              "scaling": "strong", "config": {"workload": "8 camera views x 1920x1080 per step, view-range sharded over a replicated config-2 world"}}
+    if world_size > 1:
+        gpu.close()
+        return {"batch8": batch8}
     iters_total, layers_total = [], []
     for k in range(max(args.warmup, 3)):
         gpu.raymarch(SP, cams[k % 8:k % 8 + 1], W, H, caps)
@@ -433,7 +461,7 @@ def bench_rays(args, torch, vg, peak):
     collisions = None if args.no_collisions else bench_collisions(args, torch, vg, gpu, SP, RS, (cx, col_y, cz), peak)
     gpu.close()
     achieved = alg_bytes / (ms / args.steps / 1e3) / 1e9
-    return {"collisions": collisions, "shaded_frame": shaded,"metric": "rays/s", "value": W * H * args.steps / (ms / 1e3), "unit": "rays/s", "ms_per_frame": ms / args.steps,
+    return {"batch8": batch8, "collisions": collisions, "shaded_frame": shaded,"metric": "rays/s", "value": W * H * args.steps / (ms / 1e3), "unit": "rays/s", "ms_per_frame": ms / args.steps,
             "config": {"workload": "BASELINE configs[1]: 1920x1080 primary-ray DDA, 1024x256x1024-voxel open-world map, 8 cameras cycled",
                        "primary_ray_dist": 100},
             "mean_iterations_per_ray": mean_iters / (W * H), "mean_layers_per_ray": mean_layers / (W * H),

@@ -103,6 +103,13 @@ __global__ void __launch_bounds__(128) k_projectiles(World w, vxb_projectile* __
         adj = mk3(pr.size[0], pr.size[1], pr.size[2]);
         adj.z += dt * pr.vel / 2.0f;
     }
+    // Conservative early-out per player (exact results): all six hitsphere centres lie within 1.9*size of
+    // the point 1.9*size below the player position and have radius <= 0.9*size; a sphere can only pass
+    // the three axis tests if its centre is within the half-diagonal of the box grown by the radius
+    // (the axes are orthonormal for a unit quaternion — otherwise no culling). 10 % + 1e-3 slack covers
+    // rounding; a NaN anywhere fails the comparison and falls through to the full test.
+    const float qn = pr.dir[0] * pr.dir[0] + pr.dir[1] * pr.dir[1] + pr.dir[2] * pr.dir[2] + pr.dir[3] * pr.dir[3];
+    const bool cull_ok = active && qn > 0.99f && qn < 1.01f;
     const float hs_off[6] = {0.0f, -1.3f, -1.9f, -2.6f, -3.3f, -3.8f};
     const float hs_rad[6] = {0.6f, 0.6f, 0.9f, 0.8f, 0.6f, 0.6f};
 
@@ -117,7 +124,16 @@ __global__ void __launch_bounds__(128) k_projectiles(World w, vxb_projectile* __
         for (uint32_t t = 0; t < tile_n; t++) {
             uint32_t collision = 0;
             f3 prev_collision = mk3(0.0f, 0.0f, 0.0f);
-            if (active) {
+            bool maybe = active;
+            if (cull_ok) {
+                const float4 pl = s_players[t];
+                const float sz = fabsf(pl.w), r9 = 0.9f * sz;
+                const float bx = adj.x + r9, by = adj.y + r9, bz = adj.z + r9;
+                const float bound = 1.1f * sqrtf(bx * bx + by * by + bz * bz) + 1.9f * sz + 1e-3f;
+                const float mx = pl.x - ppos.x, my = (pl.y - 1.9f * pl.w) - ppos.y, mz = pl.z - ppos.z;
+                if (mx * mx + my * my + mz * mz > bound * bound) maybe = false;
+            }
+            if (maybe) {
                 const float4 pl = s_players[t];
                 const f3 plpos = mk3(pl.x, pl.y, pl.z);
 #pragma unroll
