@@ -83,12 +83,33 @@ __device__ void quaternion_from_arc(f3 src, f3 dst, float out[4]) {
 }
 
 constexpr int PLAYER_TILE = 64;  // 64 x 128 B = 8 KiB of shared memory
+constexpr int PROJ_BLOCK = 128;
+constexpr uint64_t LATTICE_COOP_MAX = 1u << 20;  // sample indices stay exact in a float quotient
 
-__global__ void __launch_bounds__(128) k_projectiles(World w, vxb_projectile* __restrict__ projectiles, uint32_t n_projectiles,
+// per-projectile lattice of the terrain test, parked in shared memory for the warp-cooperative search
+struct LatticeRow {
+    float4 start, dgz, rgx, ugy;  // start corner; dir*grid_dist.z, right*grid_dist.x, up*grid_dist.y
+    int4 g;                       // grid_iteration_count
+    uint4 c0;                     // chunk of the lattice's low corner
+};
+struct LatticeHit {
+    bool found;
+    int i, j, k;
+    uint32_t data;
+};
+// mapped_i of compute_projectile.glsl:190-192: centre first, then alternating outwards
+// (g >= 0 and i >= 0 wherever it is called, so /2 and %2 are a shift and a mask)
+__device__ __forceinline__ int lattice_map(int g, int i) {
+    const int h = (i + 1) >> 1;
+    return (g >> 1) + ((i & 1) ? h : -h);
+}
+
+__global__ void __launch_bounds__(PROJ_BLOCK, 6) k_projectiles(World w, vxb_projectile* __restrict__ projectiles, uint32_t n_projectiles,
                                                      const vxb_player* __restrict__ players, uint32_t n_players,
                                                      vxb_collision* __restrict__ collisions, uint32_t collision_capacity,
                                                      uint32_t* __restrict__ collision_count, float dt) {
     __shared__ float4 s_players[PLAYER_TILE];  // (pos.xyz, size) is all the hit test reads
+    __shared__ float2 s_cull[PLAYER_TILE];     // (y of the hitsphere column's midpoint, its reach)
     const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
     const bool active = idx < n_projectiles;
     vxb_projectile pr;
@@ -103,11 +124,14 @@ __global__ void __launch_bounds__(128) k_projectiles(World w, vxb_projectile* __
         adj = mk3(pr.size[0], pr.size[1], pr.size[2]);
         adj.z += dt * pr.vel / 2.0f;
     }
-    // Conservative early-out per player (exact results): all six hitsphere centres lie within 1.9*size of
-    // the point 1.9*size below the player position and have radius <= 0.9*size; a sphere can only pass
-    // the three axis tests if its centre is within the half-diagonal of the box grown by the radius
-    // (the axes are orthonormal for a unit quaternion — otherwise no culling). 10 % + 1e-3 slack covers
-    // rounding; a NaN anywhere fails the comparison and falls through to the full test.
+    // Conservative early-out per player (exact results): all six hitsphere centres lie within 1.9*|size| of
+    // the point 1.9*size below the player position and have radius <= 0.9*|size|; a sphere can only pass
+    // the three axis tests if its centre is within the half-diagonal of the box grown by the radius, which
+    // is at most |adj| + sqrt(3)*0.9*|size| (the axes are orthonormal for a unit quaternion — otherwise
+    // no culling). So: skip when |midpoint - pos| > 1.1*|adj| + 1e-3 + 3.62*|size|  (3.62 > 1.1*1.559 + 1.9;
+    // the 10 % + 1e-3 slack covers rounding). A NaN anywhere fails the comparison and falls through to
+    // the full test.
+    const float cull_a = 1.1f * sqrtf(adj.x * adj.x + adj.y * adj.y + adj.z * adj.z) + 1e-3f;
     const float qn = pr.dir[0] * pr.dir[0] + pr.dir[1] * pr.dir[1] + pr.dir[2] * pr.dir[2] + pr.dir[3] * pr.dir[3];
     const bool cull_ok = active && qn > 0.99f && qn < 1.01f;
     const float hs_off[6] = {0.0f, -1.3f, -1.9f, -2.6f, -3.3f, -3.8f};
@@ -118,6 +142,7 @@ __global__ void __launch_bounds__(128) k_projectiles(World w, vxb_projectile* __
         for (uint32_t t = threadIdx.x; t < PLAYER_TILE && tile + t < n_players; t += blockDim.x) {
             const vxb_player& pl = players[tile + t];
             s_players[t] = make_float4(pl.pos[0], pl.pos[1], pl.pos[2], pl.size);
+            s_cull[t] = make_float2(pl.pos[1] - 1.9f * pl.size, 3.62f * fabsf(pl.size));
         }
         __syncthreads();
         const uint32_t tile_n = min((uint32_t)PLAYER_TILE, n_players - tile);
@@ -127,10 +152,9 @@ __global__ void __launch_bounds__(128) k_projectiles(World w, vxb_projectile* __
             bool maybe = active;
             if (cull_ok) {
                 const float4 pl = s_players[t];
-                const float sz = fabsf(pl.w), r9 = 0.9f * sz;
-                const float bx = adj.x + r9, by = adj.y + r9, bz = adj.z + r9;
-                const float bound = 1.1f * sqrtf(bx * bx + by * by + bz * bz) + 1.9f * sz + 1e-3f;
-                const float mx = pl.x - ppos.x, my = (pl.y - 1.9f * pl.w) - ppos.y, mz = pl.z - ppos.z;
+                const float2 cu = s_cull[t];
+                const float bound = cull_a + cu.y;
+                const float mx = pl.x - ppos.x, my = cu.x - ppos.y, mz = pl.z - ppos.z;
                 if (mx * mx + my * my + mz * mz > bound * bound) maybe = false;
             }
             if (maybe) {
@@ -172,66 +196,208 @@ __global__ void __launch_bounds__(128) k_projectiles(World w, vxb_projectile* __
         }
     }
 
-    if (!active) return;
-    if (pr.should_collide_with_terrain != 1) return;
-
-    // terrain part (:181-243)
+    // terrain part (:181-243). The reference walks a lattice of (gic0+1)(gic1+1)(gic2+1) sample points
+    // centre-out and reacts to the FIRST non-fluid voxel. Lattice sizes differ a lot between neighbouring
+    // projectiles (and most end at the first sample or never), so the search is done by the whole warp for
+    // one projectile at a time: lane l takes sample base+l of the reference's i-major/k-minor order, a
+    // ballot finds the first non-fluid one. The reaction runs afterwards on every lane for its own projectile.
     const float SQRT2 = 1.41421356237309504880f;  // sqrt(2.0) folded to the nearest float
-    int gic[3];
-    gic[0] = f2i(ceilf(2.0f * pr.size[0] * SQRT2));
-    gic[1] = f2i(ceilf(2.0f * pr.size[1] * SQRT2));
-    gic[2] = f2i(ceilf((2.0f * pr.size[2] + dt * pr.vel) * SQRT2));
-    f3 grid_dist = mk3(2.0f * pr.size[0] / (float)gic[0], 2.0f * pr.size[1] / (float)gic[1], 0.0f);
-    grid_dist.z = (2.0f * pr.size[2] + dt * pr.vel) / (float)gic[2];
-    const f3 start = ppos - dir * pr.size[2] - right * pr.size[0] - up * pr.size[1];
-    for (int i = 0; i <= gic[0]; i++) {
-        for (int j = 0; j <= gic[1]; j++) {
-            for (int k = 0; k <= gic[2]; k++) {
-                const int mapped_i = gic[0] / 2 + (2 * (i % 2) - 1) * ((i + 1) / 2);
-                const int mapped_j = gic[1] / 2 + (2 * (j % 2) - 1) * ((j + 1) / 2);
-                const int mapped_k = gic[2] / 2 + (2 * (k % 2) - 1) * ((k + 1) / 2);
-                const f3 pos = start + dir * grid_dist.z * (float)mapped_k + right * grid_dist.x * (float)mapped_i +
-                               up * grid_dist.y * (float)mapped_j;
-                const int vx = f2i(pos.x), vy = f2i(pos.y), vz = f2i(pos.z);
-                const uint32_t data = get_data(w, (uint32_t)vx, (uint32_t)vy, (uint32_t)vz);
-                const uint32_t voxel_mat = data >> 24;
-                if (mat_in(MASK_FLUID, voxel_mat)) {
-                    continue;
-                } else if (voxel_mat == MAT_OOB) {
-                    pr.health = 0.0f;
-                    pr.chunk_update_pos[3] = 0;
-                    projectiles[idx] = pr;
-                    return;
-                }
-                const float dist_past_bb = grid_dist.z * (float)mapped_k - 2.0f * pr.size[2];
-                const f3 ndir = -dir;
-                const f3 delta{ray_box_axis(pos.x, ndir.x, (float)vx, (float)(vx + 1)), ray_box_axis(pos.y, ndir.y, (float)vy, (float)(vy + 1)),
-                               ray_box_axis(pos.z, ndir.z, (float)vz, (float)(vz + 1))};
-                const float dist_diff = gmin(delta.x, gmin(delta.y, delta.z));
-                if (dist_past_bb > 0.0f) {
-                    const f3 mv = dir * (dist_past_bb - dist_diff);
-                    pr.pos[0] += mv.x; pr.pos[1] += mv.y; pr.pos[2] += mv.z; pr.pos[3] += 0.0f;
-                }
-                if (pr.wall_bounce == 1) {
-                    f3 new_dir = dir;
-                    if (delta.x == dist_diff) new_dir.x *= -1.0f;
-                    else if (delta.y == dist_diff) new_dir.y *= -1.0f;
-                    else if (delta.z == dist_diff) new_dir.z *= -1.0f;
-                    quaternion_from_arc(mk3(0.0f, 0.0f, 1.0f), new_dir, pr.dir);
-                    projectiles[idx] = pr;
-                    return;
-                }
-                if (pr.damage > 0) {
-                    // imageAtomicAdd(voxels, get_index(voxel_pos), int(projectile.damage)) (:230-233)
-                    atomicAdd(&w.pool[voxel_index(w, (uint32_t)vx, (uint32_t)vy, (uint32_t)vz)], (uint32_t)f2i(pr.damage));
-                }
-                pr.chunk_update_pos[0] = (uint32_t)vx; pr.chunk_update_pos[1] = (uint32_t)vy; pr.chunk_update_pos[2] = (uint32_t)vz;
-                pr.chunk_update_pos[3] = 1;
-                pr.health = 0.0f;
-                projectiles[idx] = pr;
-                return;
+    const bool want = active && pr.should_collide_with_terrain == 1;
+    const uint32_t lane = threadIdx.x & 31u, warp_row = threadIdx.x & ~31u;
+    int gic[3] = {-1, -1, -1};
+    f3 grid_dist = mk3(0, 0, 0), start = mk3(0, 0, 0);
+    if (want) {
+        gic[0] = f2i(ceilf(2.0f * pr.size[0] * SQRT2));
+        gic[1] = f2i(ceilf(2.0f * pr.size[1] * SQRT2));
+        gic[2] = f2i(ceilf((2.0f * pr.size[2] + dt * pr.vel) * SQRT2));
+        grid_dist = mk3(2.0f * pr.size[0] / (float)gic[0], 2.0f * pr.size[1] / (float)gic[1], 0.0f);
+        grid_dist.z = (2.0f * pr.size[2] + dt * pr.vel) / (float)gic[2];
+        start = ppos - dir * pr.size[2] - right * pr.size[0] - up * pr.size[1];
+    }
+    const float size_z = want ? pr.size[2] : 0.0f, pos_w = want ? pr.pos[3] : 0.0f, damage = want ? pr.damage : 0.0f;
+    const uint32_t wall_bounce = want ? pr.wall_bounce : 0u;
+    const f3 dgz = dir * grid_dist.z, rgx = right * grid_dist.x, ugy = up * grid_dist.y;
+    const bool empty = gic[0] < 0 || gic[1] < 0 || gic[2] < 0;
+    const bool small = !empty && gic[0] < 1024 && gic[1] < 1024 && gic[2] < 1024 &&
+                       (uint64_t)(gic[0] + 1) * (uint32_t)(gic[1] + 1) * (uint32_t)(gic[2] + 1) <= LATTICE_COOP_MAX;
+    LatticeHit hit;
+    hit.found = false;
+
+    __shared__ LatticeRow s_lat[PROJ_BLOCK];
+    __shared__ uint32_t s_slots[PROJ_BLOCK][8];
+    bool skip_air = false;
+    {
+        // chunk of the lattice's low corner: the 2x2x2 chunks from there are resolved once per projectile
+        const float lx = start.x + fminf(0.0f, dgz.x * (float)gic[2]) + fminf(0.0f, rgx.x * (float)gic[0]) + fminf(0.0f, ugy.x * (float)gic[1]);
+        const float ly = start.y + fminf(0.0f, dgz.y * (float)gic[2]) + fminf(0.0f, rgx.y * (float)gic[0]) + fminf(0.0f, ugy.y * (float)gic[1]);
+        const float lz = start.z + fminf(0.0f, dgz.z * (float)gic[2]) + fminf(0.0f, rgx.z * (float)gic[0]) + fminf(0.0f, ugy.z * (float)gic[1]);
+        const uint32_t c0x = (uint32_t)f2i(lx) >> 4, c0y = (uint32_t)f2i(ly) >> 4, c0z = (uint32_t)f2i(lz) >> 4;
+        const uint32_t n2 = gic[2] + 1, n12 = (gic[1] + 1) * n2;
+        LatticeRow& r = s_lat[threadIdx.x];
+        r.start = make_float4(start.x, start.y, start.z, 1.0f / (float)n2);
+        r.dgz = make_float4(dgz.x, dgz.y, dgz.z, 1.0f / (float)n12);
+        r.rgx = make_float4(rgx.x, rgx.y, rgx.z, 0.0f);
+        r.ugy = make_float4(ugy.x, ugy.y, ugy.z, 0.0f);
+        r.g = make_int4(gic[0], gic[1], gic[2], 0);
+        r.c0 = make_uint4(c0x, c0y, c0z, 0u);
+        if (want && small) {
+            uint32_t all_air = 1;
+#pragma unroll
+            for (uint32_t c = 0; c < 8; c++) {
+                const uint32_t cx = c0x + (c & 1u), cy = c0y + ((c >> 1) & 1u), cz = c0z + (c >> 2);
+                uint32_t slot = 0;  // slot 0 holds MAT_OOB, what get_data returns outside the window
+                if (cx - w.sp[0] < w.rs[0] && cy - w.sp[1] < w.rs[1] && cz - w.sp[2] < w.rs[2]) slot = table_lookup_in_window(w, cx, cy, cz);
+                s_slots[threadIdx.x][c] = slot;
+                all_air &= (slot == 1u);
+            }
+            // Every sample lies inside [low, high] grown by a rounding margin. If that box stays within the
+            // 2x2x2 chunks and all of them are all-air chunks (table entry 1: every voxel MAT_AIR_OOB, a
+            // fluid), no sample can be non-fluid and the whole lattice is skipped.
+            const float hx = start.x + fmaxf(0.0f, dgz.x * (float)gic[2]) + fmaxf(0.0f, rgx.x * (float)gic[0]) + fmaxf(0.0f, ugy.x * (float)gic[1]);
+            const float hy = start.y + fmaxf(0.0f, dgz.y * (float)gic[2]) + fmaxf(0.0f, rgx.y * (float)gic[0]) + fmaxf(0.0f, ugy.y * (float)gic[1]);
+            const float hz = start.z + fmaxf(0.0f, dgz.z * (float)gic[2]) + fmaxf(0.0f, rgx.z * (float)gic[0]) + fmaxf(0.0f, ugy.z * (float)gic[1]);
+            const float mgx = 0.01f + 4e-6f * fmaxf(fabsf(lx), fabsf(hx)), mgy = 0.01f + 4e-6f * fmaxf(fabsf(ly), fabsf(hy)),
+                        mgz = 0.01f + 4e-6f * fmaxf(fabsf(lz), fabsf(hz));
+            const bool inside = lx - mgx >= 16.0f * (float)c0x && hx + mgx < 16.0f * (float)c0x + 32.0f && ly - mgy >= 16.0f * (float)c0y &&
+                                hy + mgy < 16.0f * (float)c0y + 32.0f && lz - mgz >= 16.0f * (float)c0z && hz + mgz < 16.0f * (float)c0z + 32.0f &&
+                                hx < 2.0e6f && hy < 2.0e6f && hz < 2.0e6f;
+            skip_air = all_air && inside;
+        }
+    }
+    __syncwarp();
+    // Flat walk over (projectile, 32-sample batch) steps with the NEXT step's voxel loads issued before
+    // the current step's ballot, so a warp keeps two gathers in flight. The next step is speculative: it
+    // assumes the current batch has no hit; on a hit the rest of that projectile is dropped and the
+    // cursor restarts at the next projectile. Every cursor variable is warp-uniform.
+    uint32_t pend = __ballot_sync(0xFFFFFFFFu, want && small && !skip_air);
+    uint32_t curL = 0, base = 0, total = 0, n2 = 1, n12 = 1, myslot = 0;
+    float4 rs_ = make_float4(0, 0, 0, 0), rd = rs_, rr = rs_, ru = rs_;
+    int4 g = make_int4(0, 0, 0, 0);
+    uint4 c0 = make_uint4(0, 0, 0, 0);
+    bool have = false;
+    struct Step {
+        uint32_t data, L;
+        int i, j, k;
+        bool valid;
+    };
+    auto advance = [&](bool next_projectile) {
+        if (!next_projectile && base + 32 < total) {
+            base += 32;
+            return;
+        }
+        have = pend != 0;
+        if (!have) return;
+        curL = __ffs(pend) - 1;
+        pend &= pend - 1;
+        const LatticeRow& r = s_lat[warp_row + curL];
+        rs_ = r.start; rd = r.dgz; rr = r.rgx; ru = r.ugy; g = r.g; c0 = r.c0;
+        n2 = g.z + 1; n12 = (g.y + 1) * n2; total = (g.x + 1) * n12;
+        myslot = s_slots[warp_row + curL][lane & 7u];
+        base = 0;
+    };
+    auto issue = [&](Step& nxt) {
+        const uint32_t sidx = base + lane;
+        nxt.valid = sidx < total;
+        nxt.L = curL;
+        // sidx = (i * (g1+1) + j) * (g2+1) + k; quotients by a float reciprocal, corrected by one
+        uint32_t i = __float2uint_rz((float)sidx * rd.w);
+        int rem = (int)(sidx - i * n12);
+        if (rem < 0) { i--; rem += (int)n12; } else if (rem >= (int)n12) { i++; rem -= (int)n12; }
+        uint32_t j = __float2uint_rz((float)rem * rs_.w);
+        int k = rem - (int)(j * n2);
+        if (k < 0) { j--; k += (int)n2; } else if (k >= (int)n2) { j++; k -= (int)n2; }
+        nxt.i = (int)i; nxt.j = (int)j; nxt.k = k;
+        const int mi = lattice_map(g.x, (int)i), mj = lattice_map(g.y, (int)j), mk = lattice_map(g.z, k);
+        const float px = rs_.x + rd.x * (float)mk + rr.x * (float)mi + ru.x * (float)mj;
+        const float py = rs_.y + rd.y * (float)mk + rr.y * (float)mi + ru.y * (float)mj;
+        const float pz = rs_.z + rd.z * (float)mk + rr.z * (float)mi + ru.z * (float)mj;
+        const uint32_t vx = (uint32_t)f2i(px), vy = (uint32_t)f2i(py), vz = (uint32_t)f2i(pz);
+        const uint32_t dx = (vx >> 4) - c0.x, dy = (vy >> 4) - c0.y, dz = (vz >> 4) - c0.z;
+        const bool fast = (dx | dy | dz) <= 1u;
+        const uint32_t slot = __shfl_sync(0xFFFFFFFFu, myslot, fast ? (dx | dy << 1 | dz << 2) : 0u);
+        nxt.data = 0;
+        if (nxt.valid)
+            nxt.data = fast ? w.pool[(uint64_t)slot * CHUNK_VOLUME + ((vx & 15u) << 8 | (vy & 15u) << 4 | (vz & 15u))] : get_data(w, vx, vy, vz);
+    };
+    // one step: issue the following step's loads into `nxt`, then judge `cur` (two named buffers that
+    // swap roles, so the loaded word is never copied — a copy would wait for the load)
+    auto process = [&](const Step& cur, Step& nxt) {
+        advance(false);
+        if (have) issue(nxt);
+        const uint32_t m = __ballot_sync(0xFFFFFFFFu, cur.valid && !mat_in(MASK_FLUID, cur.data >> 24));
+        if (m) {
+            const uint32_t hl = __ffs(m) - 1;
+            const int hi = __shfl_sync(0xFFFFFFFFu, cur.i, hl), hj = __shfl_sync(0xFFFFFFFFu, cur.j, hl), hk = __shfl_sync(0xFFFFFFFFu, cur.k, hl);
+            const uint32_t hd = __shfl_sync(0xFFFFFFFFu, cur.data, hl);
+            if (lane == cur.L) { hit.found = true; hit.i = hi; hit.j = hj; hit.k = hk; hit.data = hd; }
+            if (have && nxt.L == cur.L) {  // the speculative step belongs to the projectile that just ended
+                advance(true);
+                if (have) issue(nxt);
             }
         }
+    };
+    Step sa{0, 0, 0, 0, 0, false}, sb{0, 0, 0, 0, 0, false};
+    advance(true);
+    if (have) issue(sa);
+    while (have) {
+        process(sa, sb);
+        if (!have) break;
+        process(sb, sa);
+    }
+    // lattices too large for the 32-bit sample index: the reference's own loop, one thread per projectile
+    if (want && !empty && !small) {
+        for (int i = 0; i <= gic[0] && !hit.found; i++)
+            for (int j = 0; j <= gic[1] && !hit.found; j++)
+                for (int k = 0; k <= gic[2]; k++) {
+                    const int mi = lattice_map(gic[0], i), mj = lattice_map(gic[1], j), mk = lattice_map(gic[2], k);
+                    const f3 pos = start + dgz * (float)mk + rgx * (float)mi + ugy * (float)mj;
+                    const uint32_t data = get_data(w, (uint32_t)f2i(pos.x), (uint32_t)f2i(pos.y), (uint32_t)f2i(pos.z));
+                    if (mat_in(MASK_FLUID, data >> 24)) continue;
+                    hit.found = true; hit.i = i; hit.j = j; hit.k = k; hit.data = data;
+                    break;
+                }
+    }
+    if (!hit.found) return;
+
+    {
+        const int mapped_i = lattice_map(gic[0], hit.i), mapped_j = lattice_map(gic[1], hit.j), mapped_k = lattice_map(gic[2], hit.k);
+        const f3 pos = start + dgz * (float)mapped_k + rgx * (float)mapped_i + ugy * (float)mapped_j;
+        const int vx = f2i(pos.x), vy = f2i(pos.y), vz = f2i(pos.z);
+        const uint32_t voxel_mat = hit.data >> 24;
+        // Only the fields the reaction changes are written back (the reference stores the whole struct,
+        // whose other fields are unchanged); nothing of `pr` stays live across the search above.
+        vxb_projectile& out = projectiles[idx];
+        if (voxel_mat == MAT_OOB) {
+            out.health = 0.0f;
+            out.chunk_update_pos[3] = 0;
+            return;
+        }
+        const float dist_past_bb = grid_dist.z * (float)mapped_k - 2.0f * size_z;
+        const f3 ndir = -dir;
+        const f3 delta{ray_box_axis(pos.x, ndir.x, (float)vx, (float)(vx + 1)), ray_box_axis(pos.y, ndir.y, (float)vy, (float)(vy + 1)),
+                       ray_box_axis(pos.z, ndir.z, (float)vz, (float)(vz + 1))};
+        const float dist_diff = gmin(delta.x, gmin(delta.y, delta.z));
+        if (dist_past_bb > 0.0f) {
+            const f3 mv = dir * (dist_past_bb - dist_diff);
+            out.pos[0] = ppos.x + mv.x; out.pos[1] = ppos.y + mv.y; out.pos[2] = ppos.z + mv.z; out.pos[3] = pos_w + 0.0f;
+        }
+        if (wall_bounce == 1) {
+            f3 new_dir = dir;
+            if (delta.x == dist_diff) new_dir.x *= -1.0f;
+            else if (delta.y == dist_diff) new_dir.y *= -1.0f;
+            else if (delta.z == dist_diff) new_dir.z *= -1.0f;
+            float q[4];
+            quaternion_from_arc(mk3(0.0f, 0.0f, 1.0f), new_dir, q);
+            out.dir[0] = q[0]; out.dir[1] = q[1]; out.dir[2] = q[2]; out.dir[3] = q[3];
+            return;
+        }
+        if (damage > 0) {
+            // imageAtomicAdd(voxels, get_index(voxel_pos), int(projectile.damage)) (:230-233)
+            atomicAdd(&w.pool[voxel_index(w, (uint32_t)vx, (uint32_t)vy, (uint32_t)vz)], (uint32_t)f2i(damage));
+        }
+        out.chunk_update_pos[0] = (uint32_t)vx; out.chunk_update_pos[1] = (uint32_t)vy; out.chunk_update_pos[2] = (uint32_t)vz;
+        out.chunk_update_pos[3] = 1;
+        out.health = 0.0f;
     }
 }
 
@@ -434,7 +600,7 @@ cudaError_t launch_projectiles(const World& w, vxb_projectile* projectiles, uint
                                uint32_t n_players, vxb_collision* collisions, uint32_t collision_capacity, uint32_t* collision_count,
                                float dt, cudaStream_t st) {
     if (n_projectiles == 0) return cudaSuccess;
-    k_projectiles<<<(n_projectiles + 127) / 128, 128, 0, st>>>(w, projectiles, n_projectiles, players, n_players, collisions,
+    k_projectiles<<<(n_projectiles + PROJ_BLOCK - 1) / PROJ_BLOCK, PROJ_BLOCK, 0, st>>>(w, projectiles, n_projectiles, players, n_players, collisions,
                                                                collision_capacity, collision_count, dt);
     return cudaGetLastError();
 }
