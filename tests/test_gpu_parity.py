@@ -327,6 +327,61 @@ def test_projectiles_and_players():
     gpu.close()
 
 
+def test_projectile_lattice_edge_cases():
+    """The terrain lattice of compute_projectile.glsl:181-243 at its corners: lattices that straddle the
+    window border or lie outside it, sit in all-air chunks, span chunk corners, have zero / negative /
+    NaN extents, and one too large for the warp-cooperative search (falls back to the per-thread loop)."""
+    import voxel_game_b200 as vg
+
+    rs = (6, 4, 6)
+    center = (10000, 1820, 10000)
+    sp = vg.initial_start_pos(center, rs)
+    gpu, cpu = _generated_world(rs, sp, 0, 0, update_ticks=4)
+    sy = _surface_y(cpu, center[0], center[2], 16 * (sp[1] + rs[1]) - 1)
+    players = scenes.players_grid(2, center, 9.0, sy + 5.0, seed=2)
+    wlo = np.array([16 * sp[0], 16 * sp[1], 16 * sp[2]], np.float32)
+    whi = np.array([16 * (sp[0] + rs[0]), 16 * (sp[1] + rs[1]), 16 * (sp[2] + rs[2])], np.float32)
+    n = 3000
+    pr = scenes.random_projectiles(n, wlo - 6, whi + 6, seed=77)  # in, across and outside the window
+    rng = np.random.RandomState(5)
+    # chunk corners: lattices that touch 8 chunks
+    k = np.arange(0, 600)
+    pr["pos"][k, :3] = (np.round(pr["pos"][k, :3] / 16) * 16 + rng.randn(600, 3) * 0.4).astype(np.float32)
+    # the sky (all-air chunks) and just above the surface
+    pr["pos"][600:900, 1] = whi[1] - 1 - rng.rand(300).astype(np.float32) * 30
+    pr["pos"][900:1200, 1] = sy + rng.rand(300).astype(np.float32) * 8 - 2
+    pr["pos"][900:1200, 0] = center[0] + rng.rand(300).astype(np.float32) * 40 - 20
+    pr["pos"][900:1200, 2] = center[2] + rng.rand(300).astype(np.float32) * 40 - 20
+    # degenerate extents
+    pr["size"][1200:1230, 0] = 0.0
+    pr["size"][1230:1260, 1] = -0.5
+    pr["size"][1260:1290, 2] = -3.0
+    pr["size"][1290:1300, 0] = np.nan
+    pr["vel"][1300:1320] = -400.0
+    pr["pos"][1320:1330, 0] = np.nan
+    pr["dir"][1330:1360] *= 1.7  # non-unit quaternions: no player culling, sheared lattice
+    # long, fast boxes (many batches), and one lattice beyond 2^20 samples
+    pr["size"][1360:1400, :3] = (3.0, 2.5, 6.0)
+    pr["vel"][1360:1400] = 300.0
+    pr["size"][1400, :3] = (38.0, 38.0, 38.0)
+    pr["pos"][1400, :3] = ((whi[0] + wlo[0]) / 2, whi[1] - 20, (whi[2] + wlo[2]) / 2)
+    pr["pos"][1401:1500, :3] = players["pos"][rng.randint(0, 4, 99), :3] + rng.randn(99, 3).astype(np.float32) * 1.2 + (0, -1.5, 0)
+    g_pr, _, g_co, g_n = gpu.dispatch_entities(sp, projectiles=pr, players=players, run_players=False)
+    c_pr, c_co, _ = cpu.projectiles(pr, players, capacity=1024)
+    assert g_n == len(c_co)
+    order_g = np.lexsort((g_co["id2"], g_co["id1"]))
+    order_c = np.lexsort((c_co["id2"], c_co["id1"]))
+    assert np.array_equal(g_co[["id1", "id2", "properties"]][order_g], c_co[["id1", "id2", "properties"]][order_c])
+    for f in ("chunk_update_pos", "wall_bounce", "owner"):
+        assert np.array_equal(g_pr[f], c_pr[f]), f
+    assert np.array_equal(g_pr["health"], c_pr["health"], equal_nan=True)
+    np.testing.assert_allclose(g_pr["pos"], c_pr["pos"], rtol=RTOL, atol=0, equal_nan=True)
+    np.testing.assert_allclose(g_pr["dir"], c_pr["dir"], rtol=RTOL, atol=1e-7, equal_nan=True)
+    assert (c_pr["health"] == 0).sum() > 200 and (c_pr["chunk_update_pos"][:, 3] == 1).sum() > 100
+    assert_world_equal(gpu, cpu)
+    gpu.close()
+
+
 @pytest.mark.parametrize("world_gen,seed,yaw,pitch,t", [(0, 0, 0.3, -0.2, 0.0), (0, 0, 2.5, 0.15, 3.25), (1, 3646, 1.2, -0.35, 1.5)])
 def test_render_full_fragment_shader(world_gen, seed, yaw, pitch, t):
     """frag.glsl main = primary DDA + get_color. One transcendental (depth_transparency ^ dist) and long
