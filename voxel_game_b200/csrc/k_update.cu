@@ -120,6 +120,36 @@ __device__ __forceinline__ uint32_t margolus_block(uint32_t (&v)[8]) {
             if (fixed) return 0;
         }
     }
+    // F2  all eight cells are MAT_AIR (id 0, so the word IS the data): the pure-air distance case below
+    //     without the material bookkeeping. The 3-bit slot of each other cell is moved to the top of
+    //     the word by a left shift (multiply pipe) instead of being masked in place (ALU pipe); the
+    //     lower slots that come along only break ties between equal slot values.
+    static_assert(MAT_AIR == 0, "the all-air test reads the material byte of the OR of the words");
+    if ((orv >> 24) == 0) {
+        uint32_t nv[8], anyc = 0;
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+            const int i = c >> 2, j = (c >> 1) & 1, k = c & 1;
+            const int SH = 29 - 3 * ((k << 2) | (j << 1) | i);
+            uint32_t f[7];
+#pragma unroll
+            for (int o = 0, q = 0; o < 8; o++)
+                if (o != c) f[q++] = v[o] << SH;
+            const uint32_t t = umin3(umin3(f[0], f[1], f[2]), umin3(f[3], f[4], f[5]), f[6]);
+            // min(7, slot + 1) in the top three bits: cap the slot at 6, then add one
+            const uint32_t r = (min(t, 0xDFFFFFFFu) & 0xE0000000u) + 0x20000000u;
+            nv[c] = (v[c] & ~(7u << (29 - SH))) | (r >> SH);
+            anyc |= nv[c] ^ v[c];
+        }
+        if (anyc == 0) return 0;
+        uint32_t chg = 0;
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+            if (nv[c] != v[c]) chg |= 1u << c;
+            v[c] = nv[c];
+        }
+        return chg;
+    }
     uint32_t m[8], d[8];
     // set of materials in the block; ids >= 32 (out of contract) shift out and are caught by orv
     uint32_t present = (orv >> 29) ? BIT_OTHER : 0u;
@@ -208,17 +238,23 @@ __device__ __forceinline__ uint32_t margolus_block(uint32_t (&v)[8]) {
             }
         }
     }
-    uint32_t chg = 0;
     const bool guard = (present0 & (BIT_OOB | BIT_AIR_OOB)) != 0;
+    uint32_t nv[8], anyc = 0;
 #pragma unroll
     for (int c = 0; c < 8; c++) {
-        uint32_t nv = (m[c] << 24) | d[c];
+        nv[c] = (m[c] << 24) | d[c];
         if (guard) {
             const uint32_t om = v[c] >> 24;
-            if (om == MAT_OOB || om == MAT_AIR_OOB) nv = v[c];
+            if (om == MAT_OOB || om == MAT_AIR_OOB) nv[c] = v[c];
         }
-        if (nv != v[c]) chg |= 1u << c;
-        v[c] = nv;
+        anyc |= nv[c] ^ v[c];
+    }
+    if (anyc == 0) return 0;
+    uint32_t chg = 0;
+#pragma unroll
+    for (int c = 0; c < 8; c++) {
+        if (nv[c] != v[c]) chg |= 1u << c;
+        v[c] = nv[c];
     }
     return chg;
 }
@@ -406,7 +442,9 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
             }
         }
 
-        // write-back (imageStore :87 is unconditional; sentinel slots are never stored)
+        // write-back (imageStore :87 is unconditional; sentinel slots are never stored). Under ELIDE a
+        // warp in which no voxel changed has nothing to store and skips the whole section.
+        if (!ELIDE || __any_sync(0xFFFFFFFFu, chg16 != 0)) {
 #pragma unroll
         for (int i = 0; i < 2; i++) {
 #pragma unroll
@@ -440,6 +478,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
                     }
                 }
             }
+        }
         }
 
         flags = __reduce_or_sync(0xFFFFFFFFu, flags);
