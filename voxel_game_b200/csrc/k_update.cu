@@ -104,22 +104,23 @@ __device__ __noinline__ uint32_t margolus_water(uint32_t air, uint32_t water) {
 //      block holds such a cell).
 template <int PY>
 __device__ __forceinline__ uint32_t margolus_block(uint32_t (&v)[8]) {
-    uint32_t orv = v[0];
     {
         const uint32_t W = v[0];
         uint32_t diff = 0;
 #pragma unroll
-        for (int c = 1; c < 8; c++) {
-            diff |= v[c] ^ W;
-            orv |= v[c];
-        }
+        for (int c = 1; c < 8; c++) diff |= v[c] ^ W;
         if (diff == 0) {
+            // the two words nearly every uniform block holds, then the general test
+            if (W == 0x00FFFFFFu || W == (MAT_STONE << 24)) return 0;
             const uint32_t m0 = W >> 24, d0 = W & 0xFFFFFFu;
             const bool fixed = mat_in(MASK_DATA_DISTANCE, m0) ? (d0 == 0xFFFFFFu)
                                                               : !(mat_in(MASK_DATA_DAMAGE, m0) && d0 >= (m0 == MAT_STONE ? 10u : 5u));
             if (fixed) return 0;
         }
     }
+    uint32_t orv = v[0];
+#pragma unroll
+    for (int c = 1; c < 8; c++) orv |= v[c];
     // F2  all eight cells are MAT_AIR (id 0, so the word IS the data): the pure-air distance case below
     //     without the material bookkeeping. The 3-bit slot of each other cell is moved to the top of
     //     the word by a left shift (multiply pipe) instead of being masked in place (ALU pipe); the
@@ -156,11 +157,40 @@ __device__ __forceinline__ uint32_t margolus_block(uint32_t (&v)[8]) {
 #pragma unroll
     for (int c = 0; c < 8; c++) {
         m[c] = v[c] >> 24;
-        d[c] = v[c] & 0xFFFFFFu;
         present |= 1u << m[c];
     }
     const uint32_t ord = orv & 0xFFFFFFu;
     if ((present & MASK_DATA_DISTANCE) == 0 && ord < 5u) return 0;
+    // F3  air next to solids (terrain surface), no water / leaf / unknown ids, and no non-air cell with
+    //     data >= 4: the damage step cannot fire (thresholds >= 5), there is no water step, the block is
+    //     not pure for any class, so every air cell just clears its own distance slot and nothing else
+    //     changes (OOB / AIR_OOB cells are not touched, which is all set_data's guard asks).
+    if ((present & (BIT_OTHER | BIT_WATER | BIT_LEAF)) == 0 && (present & BIT_AIR) && (present & ~(BIT_AIR | BIT_OOB | BIT_AIR_OOB))) {
+        uint32_t nonair = 0, slots = 0;
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+            const int i = c >> 2, j = (c >> 1) & 1, k = c & 1;
+            const uint32_t MK = 7u << (3 * ((k << 2) | (j << 1) | i));
+            nonair |= m[c] == MAT_AIR ? 0u : v[c];
+            slots |= m[c] == MAT_AIR ? (v[c] & MK) : 0u;
+        }
+        if ((nonair & 0xFFFFFCu) == 0) {
+            if (slots == 0) return 0;
+            uint32_t chg = 0;
+#pragma unroll
+            for (int c = 0; c < 8; c++) {
+                const int i = c >> 2, j = (c >> 1) & 1, k = c & 1;
+                const uint32_t MK = 7u << (3 * ((k << 2) | (j << 1) | i));
+                if (m[c] == MAT_AIR && (v[c] & MK)) {
+                    v[c] &= ~MK;
+                    chg |= 1u << c;
+                }
+            }
+            return chg;
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < 8; c++) d[c] = v[c] & 0xFFFFFFu;
     const uint32_t present0 = present;  // materials of the ORIGINAL words (for the store guard)
 
     // :102-112 accumulated damage past the material's threshold -> air (stone 10, others 5)
@@ -320,9 +350,10 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
 
     // warp = one ty: a 16 x 2 x 16-voxel horizontal slab. Terrain and water surfaces are mostly
     // horizontal, so few warps of a chunk contain them and leave the block fast paths.
-    // (Tried and rejected: per-warp slot tables + global flag atomics to drop the per-chunk CTA
-    // barrier — warps of a CTA drift apart, their partial-sector stores no longer merge in L2 and
-    // the y/z-shifted phases lose 15-20 %.)
+    // (Tried and rejected, twice: per-warp slot tables + global flag atomics to drop the per-chunk CTA
+    // barrier. Warps of a CTA drift apart; with unconditional stores their partial-sector stores no
+    // longer merge in L2 (y/z-shifted phases lose 15-20 %), and even with stores elided the CTA no
+    // longer reads one chunk's 16 KiB together, which costs DRAM page locality: 808 -> 731 G/s.)
     const int tzq = tid & 3, tx = (tid >> 2) & 7, ty = tid >> 5;
     // (i,j) column of this thread: in-chunk word offset of its vector, and which neighbour chunk holds it.
     // Only the last thread column / row straddles (x or y == 16), and only for i / j == 1.
