@@ -353,7 +353,9 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
     // (Tried and rejected, twice: per-warp slot tables + global flag atomics to drop the per-chunk CTA
     // barrier. Warps of a CTA drift apart; with unconditional stores their partial-sector stores no
     // longer merge in L2 (y/z-shifted phases lose 15-20 %), and even with stores elided the CTA no
-    // longer reads one chunk's 16 KiB together, which costs DRAM page locality: 808 -> 731 G/s.)
+    // longer reads one chunk's 16 KiB together, which costs DRAM page locality: 808 -> 731 G/s.
+    // A bounded version — mbarrier arrive at the end of iteration t, wait for t-2 at the start of t, so a
+    // warp runs at most one chunk ahead — measured +0.7 % elided / -2 % with stores: not kept.)
     const int tzq = tid & 3, tx = (tid >> 2) & 7, ty = tid >> 5;
     // (i,j) column of this thread: in-chunk word offset of its vector, and which neighbour chunk holds it.
     // Only the last thread column / row straddles (x or y == 16), and only for i / j == 1.
