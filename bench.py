@@ -41,10 +41,13 @@ def hbm_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def traffic_from_profiles(key):
+def traffic_from_profiles(key, scale=1.0):
+    """Measured DRAM bytes (ncu dram__bytes_read.sum + dram__bytes_write.sum) recorded in profiles/traffic.json
+    by an earlier profiling run of this same command; `scale` turns a per-chunk figure into a per-launch one."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(p):
-        return json.load(open(p)).get(key)
+        v = json.load(open(p)).get(key)
+        return None if v is None else v * scale
     return None
 
 
@@ -310,11 +313,17 @@ def run_ours(args):
             result["unconditional_store_variant"] = alt
         if achieved is not None:
             result["roofline"] = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                                  "traffic": traffic_from_profiles("k_voxel_update_bytes_per_launch"), "peak_source": peak_src,
+                                  "traffic": traffic_from_profiles("k_voxel_update_elide_dram_bytes_per_chunk" if (args.variant & 0xFF) == 2
+                                                                   else "k_voxel_update_store_dram_bytes_per_chunk", n_own), "peak_source": peak_src,
                                   "kernel": "k_voxel_update_tiled", "algorithmic_bytes_per_launch": BYTES_PER_VOXEL_UPDATE * n_own * 4096,
                                   "avg_launch_ms": kern_ms,
                                   "note": "algorithmic bytes = 8 B per voxel-update (4 B read + 4 B write) as SURVEY 8(d) fixes it, whether or not "
-                                          "unchanged vectors are stored; `traffic` is the measured DRAM bytes of one launch"}
+                                          "unchanged vectors are stored, so frac can exceed 1 for the store-eliding default on a settled world; "
+                                          "`traffic` is the measured DRAM bytes of one launch (profiles/traffic.json), `read_once` rates the same "
+                                          "launch against reading every voxel once (4 B/voxel), the floor of the eliding kernel"}
+            if (args.variant & 0xFF) == 2:
+                rd = 4 * n_own * 4096 / (kern_ms / 1e3) / 1e9
+                result["roofline"]["read_once"] = {"achieved": rd, "frac": rd / peak, "unit": "GB/s"}
 
     # ---------------- cpu_baseline (rank 0, N == 1): oracle on a bounded sample of the same world ----
     if rank == 0 and world_size == 1 and not args.no_cpu:

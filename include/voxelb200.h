@@ -240,7 +240,10 @@ int vxb_update_list_flags(vxb_ctx* ctx, uint32_t* flags_out, uint32_t n);
 /* Selects the update kernel: 2 = default (persistent cp.async-pipelined, vectorised; 16-byte vectors
  * whose four voxels did not change are not stored back — results are identical), 0 = the same kernel
  * with the reference's unconditional stores (compute_voxel.glsl:87), 1 = per-voxel gather that follows
- * the reference's access pattern (kept as profiling baseline and cross-check). */
+ * the reference's access pattern (kept as profiling baseline and cross-check).
+ * Bits 8-11 of `variant` optionally force how many consecutive list entries one thread block visits
+ * back to back (0 = automatic: 8 for long lists, 1 otherwise; code k = 2^(k-1) entries, k <= 9); the
+ * results do not depend on it. */
 int vxb_set_update_kernel(vxb_ctx* ctx, int variant);
 
 /* ---- the ray pass (src/raytracer.rs, shaders/frag.glsl) --------------------------------------- */

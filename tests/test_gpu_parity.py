@@ -57,6 +57,34 @@ def test_voxel_update_random(variant, seed):
     gpu.close()
 
 
+@pytest.mark.parametrize("variant", [0 | (3 << 8), 2 | (3 << 8), 2 | (5 << 8), 0 | (2 << 8)])
+def test_voxel_update_z_runs(variant):
+    """Thread blocks that visit runs of consecutive list entries hand the z == 16 voxels of one entry over to
+    the next when that is its +z neighbour (offset.z == 1). Forced run lengths 2 / 4 / 16 on a world that is
+    long in z; the list is z-fastest for its first part and shuffled for the rest (links and non-links)."""
+    rs, sp = (2, 2, 9), (200, 30, 41)
+    n_slots = 2 + 36
+    gpu, cpu = make_pair(rs, sp, n_slots)
+    table, chunks, _ = scenes.full_table(rs, sp, holes=0.12, seed=11)
+    cpu.table[:] = table
+    cpu.pool[2:] = scenes.random_pool(n_slots, 11)
+    sync_world_to_gpu(gpu, cpu)
+    gpu.set_update_kernel(variant)
+    chunks = np.asarray(chunks)
+    order = np.lexsort((chunks[:, 2], chunks[:, 1], chunks[:, 0]))  # z fastest
+    chunks = chunks[order]
+    rng = np.random.RandomState(3)
+    cut = 2 * len(chunks) // 3
+    chunks = np.concatenate([chunks[:cut], chunks[cut:][rng.permutation(len(chunks) - cut)]])
+    lst = scenes.update_list(chunks)
+    for tick, off in enumerate(scenes.PHASES * 2):
+        f_gpu = gpu.dispatch_voxel_update(sp, lst, off)
+        f_cpu = cpu.voxel_update(lst, off)
+        assert np.array_equal(f_gpu, f_cpu), "flags differ at tick %d phase %s" % (tick, off)
+        assert_world_equal(gpu, cpu)
+    gpu.close()
+
+
 def test_voxel_update_clustered_toroidal():
     # start_pos not a multiple of render_size: the table is addressed modulo render_size
     rs, sp = (4, 3, 2), (497, 106, 501)

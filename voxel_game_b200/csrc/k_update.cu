@@ -320,7 +320,10 @@ struct UpdStage {
 struct UpdSmem {
     UpdStage stage[UPD_STAGES];
     __align__(16) uint32_t slot[UPD_NSLOT][8];
+    uint32_t link[UPD_NSLOT];               // offset.z == 1: the CTA's next item is this item's +z neighbour
     uint32_t flags[2];
+    uint32_t cz[4][UPD_THREADS / 4];        // z-run carry: updated voxel z == 16 of column (i,j), kept for the next item
+    uint32_t cc[UPD_THREADS / 4];           // ... and whether it changed (bit i*2+j), for ELIDE
 };
 
 // The 2x2x2 neighbour slots of one work item, picked apart for one thread: s[i*2+j] is the slot of
@@ -338,15 +341,24 @@ struct ThreadSlots {
 // exactly set_data's guard for those two materials.
 template <int PHASE, bool ELIDE>
 __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, const uint4* __restrict__ chunk_updates, uint32_t n_items,
-                                                                       uint32_t* __restrict__ flags_out) {
+                                                                       uint32_t* __restrict__ flags_out, uint32_t run_log2) {
     constexpr int OX = PHASE & 1, OY = (PHASE >> 1) & 1, OZ = (PHASE >> 2) & 1;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     UpdSmem& sm = *reinterpret_cast<UpdSmem*>(smem_raw);
 
     const uint32_t tid = threadIdx.x;
     const uint32_t G = gridDim.x;
-    if (blockIdx.x >= n_items) return;
-    const uint32_t T = (n_items - blockIdx.x + G - 1) / G;  // work items of this CTA: blockIdx.x + t*G
+    // Work distribution: the list is cut into runs of R = 2^run_log2 consecutive entries and the runs are
+    // dealt round-robin to the CTAs, so a CTA walks R list neighbours back to back (in a z-fastest list:
+    // R chunks along z, which is what the z-run carry below feeds on) while heavy regions of the list
+    // still spread over all CTAs. The launcher picks R = 1 for short lists.
+    const uint32_t R = 1u << run_log2;
+    const uint32_t n_runs = (n_items + R - 1) >> run_log2;
+    if (blockIdx.x >= n_runs) return;
+    const uint32_t runs_mine = (n_runs - blockIdx.x + G - 1) / G;
+    const uint32_t last_start = (blockIdx.x + (runs_mine - 1) * G) << run_log2;
+    const uint32_t T = ((runs_mine - 1) << run_log2) + min(R, n_items - last_start);  // only the list's last run is short
+    auto item = [&](uint32_t t) { return ((blockIdx.x + (t >> run_log2) * G) << run_log2) + (t & (R - 1)); };
 
     // warp = one ty: a 16 x 2 x 16-voxel horizontal slab. Terrain and water surfaces are mostly
     // horizontal, so few warps of a chunk contain them and leave the block fast paths.
@@ -391,8 +403,16 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
     // resolve the 2x2x2 slot neighbourhood of work item t (lane n of 8): list entry -> table lookup
     auto resolve = [&](uint32_t t, uint32_t n) -> uint32_t {
         if (t >= T) return 0;
-        const uint4 e = chunk_updates[blockIdx.x + t * G];
+        const uint4 e = chunk_updates[item(t)];
         return resolve_chunk(w, e.x + ((n >> 2) & 1), e.y + ((n >> 1) & 1), e.z + (n & 1));
+    };
+    // offset.z == 1: is item t+1 of this CTA the +z neighbour of item t? Then item t does not store its
+    // z == 16 voxels (first word of each row of the +z chunk, a 4-byte store into a sector that item t+1
+    // writes the rest of) but hands them over, and item t+1 stores full aligned vectors.
+    auto resolve_link = [&](uint32_t t) -> uint32_t {
+        if (OZ == 0 || t + 1 >= T) return 0;
+        const uint4 a = chunk_updates[item(t)], b = chunk_updates[item(t + 1)];
+        return (a.x == b.x && a.y == b.y && a.z + 1 == b.z) ? 1u : 0u;
     };
     // issue this thread's copies of work item t into its ring stage (always commits one group)
     auto issue = [&](uint32_t t) {
@@ -415,8 +435,10 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
 
     // ---- prologue: slot tables of the first STAGES items, copies of the first STAGES-1 ----
     if (tid < 8 * UPD_STAGES) sm.slot[tid >> 3][tid & 7] = resolve(tid >> 3, tid & 7);
+    if (tid >= 32 && tid < 32 + UPD_STAGES) sm.link[tid - 32] = resolve_link(tid - 32);
     if (tid < 2) sm.flags[tid] = 0;
     __syncthreads();
+    uint32_t link_prev = 0;  // CTA-uniform: the previous item handed its z == 16 voxels over
 #pragma unroll
     for (int t = 0; t < UPD_STAGES - 1; t++) issue(t);
 
@@ -425,6 +447,8 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
         // result is only touched at the end of the iteration
         uint32_t pend = 0;
         if (tid < 8) pend = resolve(t + UPD_STAGES, tid);
+        else if (OZ == 1 && tid == 32) pend = resolve_link(t + UPD_STAGES);
+        const uint32_t link_out = OZ == 1 ? sm.link[t % UPD_NSLOT] : 0u;
         issue(t + UPD_STAGES - 1);
         cp_async_wait<UPD_STAGES - 1>();  // this thread's copies of item t have landed
 
@@ -477,7 +501,9 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
 
         // write-back (imageStore :87 is unconditional; sentinel slots are never stored). Under ELIDE a
         // warp in which no voxel changed has nothing to store and skips the whole section.
-        if (!ELIDE || __any_sync(0xFFFFFFFFu, chg16 != 0)) {
+        uint32_t cin_chg = 0;  // ELIDE: change bits of the handed-over z == 0 voxels (lanes tzq == 0)
+        if (OZ == 1 && ELIDE && link_prev && tzq == 0) cin_chg = sm.cc[tid >> 2];
+        if (!ELIDE || __any_sync(0xFFFFFFFFu, (chg16 | cin_chg) != 0)) {
 #pragma unroll
         for (int i = 0; i < 2; i++) {
 #pragma unroll
@@ -496,13 +522,19 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
                     if (tzq > 0) {
                         if (slot >= 2 && !(ELIDE && (c4 & 7u) == 0 && prev_chg == 0))
                             *reinterpret_cast<uint4*>(slot_ptr(slot, row + 4 * tzq)) = make_uint4(prev, r[i][j][0], r[i][j][1], r[i][j][2]);
+                    } else if (link_prev) {
+                        // z == 0 of this row was computed by the previous item of this CTA (the -z neighbour)
+                        // and handed over: the row start is one full vector like the others
+                        if (slot >= 2 && !(ELIDE && (c4 & 7u) == 0 && (cin_chg & (1u << (i * 2 + j))) == 0))
+                            *reinterpret_cast<uint4*>(slot_ptr(slot, row)) = make_uint4(sm.cz[i * 2 + j][tid >> 2], r[i][j][0], r[i][j][1], r[i][j][2]);
                     } else if (slot >= 2 && !(ELIDE && (c4 & 6u) == 0)) {
                         // z == 0 of this row belongs to the -z neighbour's work item in this phase
                         *reinterpret_cast<uint2*>(slot_ptr(slot, row + 2)) = make_uint2(r[i][j][1], r[i][j][2]);
                     }
                     // one 4-byte store instruction serves both row ends: z == 1 (lanes tzq == 0) and
-                    // z == 16, the first voxel of the +z neighbour chunk (lanes tzq == 3)
-                    if (tzq == 0 || tzq == 3) {
+                    // z == 16, the first voxel of the +z neighbour chunk (lanes tzq == 3) — each only
+                    // when it is not covered by a hand-over
+                    if ((tzq == 0 && !link_prev) || (tzq == 3 && !link_out)) {
                         const uint32_t eslot = tzq == 0 ? slot : ts.z[i * 2 + j];
                         const uint32_t eoff = tzq == 0 ? row + 1 : row;
                         const uint32_t eval = tzq == 0 ? r[i][j][0] : r[i][j][3];
@@ -514,12 +546,23 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
         }
         }
 
+        if (OZ == 1) {
+            __syncwarp();  // the hand-over words of the previous item have been read by lanes tzq == 0
+            if (link_out && tzq == 3) {
+#pragma unroll
+                for (int q = 0; q < 4; q++) sm.cz[q][tid >> 2] = r[q >> 1][q & 1][3];
+                if (ELIDE) sm.cc[tid >> 2] = ((chg16 >> 3) & 1u) | ((chg16 >> 6) & 2u) | ((chg16 >> 9) & 4u) | ((chg16 >> 12) & 8u);
+            }
+            link_prev = link_out;
+        }
+
         flags = __reduce_or_sync(0xFFFFFFFFu, flags);
         if ((tid & 31) == 0 && flags) atomicOr(&sm.flags[t & 1], flags);
         if (tid < 8) sm.slot[(t + UPD_STAGES) % UPD_NSLOT][tid] = pend;
+        else if (OZ == 1 && tid == 32) sm.link[(t + UPD_STAGES) % UPD_NSLOT] = pend;
         __syncthreads();
         if (tid == 0) {
-            flags_out[blockIdx.x + t * G] = sm.flags[t & 1];
+            flags_out[item(t)] = sm.flags[t & 1];
             sm.flags[t & 1] = 0;  // next written in iteration t+2, after the barrier of t+1
         }
     }
@@ -615,7 +658,7 @@ __global__ void __launch_bounds__(512) k_voxel_update_gather(World w, const uint
 }
 
 template <int PHASE, bool ELIDE>
-static cudaError_t launch_one(const World& w, const uint4* list, uint32_t n, uint32_t* flags, cudaStream_t st) {
+static cudaError_t launch_one(const World& w, const uint4* list, uint32_t n, uint32_t* flags, int run_code, cudaStream_t st) {
     static int grid_cap = 0;  // per instantiation: SMs x resident CTAs (one device model per process)
     auto kern = k_voxel_update_tiled<PHASE, ELIDE>;
     if (grid_cap == 0) {
@@ -628,22 +671,27 @@ static cudaError_t launch_one(const World& w, const uint4* list, uint32_t n, uin
         if (per_sm < 1) return cudaErrorLaunchOutOfResources;
         grid_cap = sms * per_sm;
     }
-    const uint32_t grid = n < (uint32_t)grid_cap ? n : (uint32_t)grid_cap;
-    kern<<<grid, UPD_THREADS, sizeof(UpdSmem), st>>>(w, list, n, flags);
+    // runs of 8 list neighbours per CTA visit once the list is long enough to keep every CTA busy with them.
+    // (config 3, G voxel-updates/s, all stores / elided: R=1 424/888, R=4 530/881, R=8 547/885, R=16 554/869, R=32 557/857)
+    // (run_code != 0 forces 2^(run_code-1): tests use it to drive the hand-over path with small worlds)
+    const uint32_t run_log2 = run_code ? (uint32_t)(run_code - 1) : (n >= 8u * 8u * (uint32_t)grid_cap ? 3u : 0u);
+    const uint32_t n_runs = (n + (1u << run_log2) - 1) >> run_log2;
+    const uint32_t grid = n_runs < (uint32_t)grid_cap ? n_runs : (uint32_t)grid_cap;
+    kern<<<grid, UPD_THREADS, sizeof(UpdSmem), st>>>(w, list, n, flags, run_log2);
     return cudaGetLastError();
 }
 
 template <bool ELIDE>
-static cudaError_t launch_tiled(int phase, const World& w, const uint4* list, uint32_t n, uint32_t* flags, cudaStream_t st) {
+static cudaError_t launch_tiled(int phase, const World& w, const uint4* list, uint32_t n, uint32_t* flags, int run_code, cudaStream_t st) {
     switch (phase) {
-        case 0: return launch_one<0, ELIDE>(w, list, n, flags, st);
-        case 1: return launch_one<1, ELIDE>(w, list, n, flags, st);
-        case 2: return launch_one<2, ELIDE>(w, list, n, flags, st);
-        case 3: return launch_one<3, ELIDE>(w, list, n, flags, st);
-        case 4: return launch_one<4, ELIDE>(w, list, n, flags, st);
-        case 5: return launch_one<5, ELIDE>(w, list, n, flags, st);
-        case 6: return launch_one<6, ELIDE>(w, list, n, flags, st);
-        default: return launch_one<7, ELIDE>(w, list, n, flags, st);
+        case 0: return launch_one<0, ELIDE>(w, list, n, flags, run_code, st);
+        case 1: return launch_one<1, ELIDE>(w, list, n, flags, run_code, st);
+        case 2: return launch_one<2, ELIDE>(w, list, n, flags, run_code, st);
+        case 3: return launch_one<3, ELIDE>(w, list, n, flags, run_code, st);
+        case 4: return launch_one<4, ELIDE>(w, list, n, flags, run_code, st);
+        case 5: return launch_one<5, ELIDE>(w, list, n, flags, run_code, st);
+        case 6: return launch_one<6, ELIDE>(w, list, n, flags, run_code, st);
+        default: return launch_one<7, ELIDE>(w, list, n, flags, run_code, st);
     }
 }
 
@@ -652,12 +700,14 @@ cudaError_t launch_voxel_update(const World& w, const uint32_t* chunk_updates, u
     if (n == 0) return cudaSuccess;
     const uint4* list = reinterpret_cast<const uint4*>(chunk_updates);
     const int phase = (offset[0] & 1) | ((offset[1] & 1) << 1) | ((offset[2] & 1) << 2);
+    const int run_code = (variant >> 8) & 0xF;
+    variant &= 0xFF;
     if (variant == 1) {
         k_voxel_update_gather<<<n, 512, 0, st>>>(w, list, flags_out, offset[0] & 1, offset[1] & 1, offset[2] & 1);
         return cudaGetLastError();
     }
-    if (variant == 2) return launch_tiled<true>(phase, w, list, n, flags_out, st);
-    return launch_tiled<false>(phase, w, list, n, flags_out, st);
+    if (variant == 2) return launch_tiled<true>(phase, w, list, n, flags_out, run_code, st);
+    return launch_tiled<false>(phase, w, list, n, flags_out, run_code, st);
 }
 
 }  // namespace vxb

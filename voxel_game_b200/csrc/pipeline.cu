@@ -830,7 +830,8 @@ int vxb_update_list_flags(vxb_ctx* c, uint32_t* flags_out, uint32_t n) {
 
 int vxb_set_update_kernel(vxb_ctx* c, int variant) {
     if (!c) return VXB_ERR_INVALID;
-    VXB_REQUIRE(c, variant >= 0 && variant <= 2, "vxb_set_update_kernel: variant must be 0, 1 or 2");
+    VXB_REQUIRE(c, (variant & 0xFF) <= 2 && (variant >> 8) >= 0 && (variant >> 8) <= 9,
+                "vxb_set_update_kernel: variant must be 0, 1 or 2 (+ optional run length code in bits 8-11: 0 auto, 1..9 = 2^(code-1))");
     c->update_variant = variant;
     return VXB_OK;
 }
