@@ -232,6 +232,21 @@ int vxb_dispatch_entities(vxb_ctx* ctx, const uint32_t start_pos[3], vxb_project
 int vxb_entities_resident_run(vxb_ctx* ctx, const uint32_t start_pos[3], uint32_t n_projectiles, uint32_t n_players,
                               int run_projectiles, int run_players, uint32_t* n_collisions_out);
 
+/* Sharded collision batches (no counterpart in the reference, which runs on one GPU): the
+ * world is replicated, every GPU runs compute_projectile.glsl on its own range of the projectile array,
+ * and the voxel damage it adds (imageAtomicAdd, compute_projectile.glsl:230-233) is logged as
+ * (x, y, z, amount) records so that the other replicas can replay it; integer adds commute, so every
+ * replica ends bit-identical to a single-GPU run.
+ *   vxb_damage_log_enable   capacity > 0 turns the log on (device buffer of `capacity` records), 0 off.
+ *                           The log is cleared at the start of every projectile dispatch.
+ *   vxb_damage_log_device   device addresses of the records and of their u32 counter (for NCCL).
+ *   vxb_damage_log_read     synchronises and copies the records to the host; fails if the log overflowed.
+ *   vxb_damage_apply        replays n records (host array, or device array if records_on_device != 0). */
+int vxb_damage_log_enable(vxb_ctx* ctx, uint32_t capacity);
+int vxb_damage_log_device(vxb_ctx* ctx, void** records_dev, void** count_dev, uint32_t* capacity);
+int vxb_damage_log_read(vxb_ctx* ctx, uint32_t (*records_out)[4], uint32_t capacity, uint32_t* n_out);
+int vxb_damage_apply(vxb_ctx* ctx, const uint32_t start_pos[3], const uint32_t (*records)[4], uint32_t n, int records_on_device);
+
 /* Resident work list for repeated full sweeps (benchmark configs 3 and 5): upload once, then run
  * the update dispatch on it any number of times without host traffic. */
 int vxb_update_list_upload(vxb_ctx* ctx, const uint32_t (*chunk_updates)[4], uint32_t n);

@@ -410,6 +410,60 @@ def test_projectile_lattice_edge_cases():
     gpu.close()
 
 
+def test_sharded_collision_batch_damage_log():
+    """Two replicas of one world each run half of a projectile batch with the voxel damage log on, then
+    replay the other's log (one through a host array, one straight from the device log): both pools must
+    equal a single context's run of the whole batch and the oracle's."""
+    import voxel_game_b200 as vg
+
+    rs = (6, 4, 6)
+    center = (10000, 1820, 10000)
+    sp = vg.initial_start_pos(center, rs)
+    gpu_a, cpu = _generated_world(rs, sp, 0, 0, update_ticks=4)
+    gpu_b, _ = _generated_world(rs, sp, 0, 0, update_ticks=4)
+    gpu_s, _ = _generated_world(rs, sp, 0, 0, update_ticks=4)
+    sy = _surface_y(cpu, center[0], center[2], 16 * (sp[1] + rs[1]) - 1)
+    players = scenes.players_grid(2, center, 9.0, sy + 5.0, seed=2)
+    lo = (16 * sp[0] + 8, sy - 8, 16 * sp[2] + 8)
+    hi = (16 * (sp[0] + rs[0]) - 8, sy + 6, 16 * (sp[2] + rs[2]) - 8)
+    pr = scenes.random_projectiles(4000, lo, hi, seed=21, bounce_frac=0.05)
+    pr["damage"] = np.array([0, 1, 5, 7], np.float32)[np.arange(len(pr)) % 4]
+    half = len(pr) // 2
+    for g in (gpu_a, gpu_b):
+        g.damage_log_enable(half)
+    pa, _, ca, na = gpu_a.dispatch_entities(sp, projectiles=pr[:half], players=players, run_players=False)
+    pb, _, cb, nb = gpu_b.dispatch_entities(sp, projectiles=pr[half:], players=players, run_players=False)
+    rec_a = gpu_a.damage_log_read(half)
+    rec_b = gpu_b.damage_log_read(half)
+    assert len(rec_a) > 50 and len(rec_b) > 50
+    gpu_a.damage_apply(sp, records=rec_b)
+    ptr_a, _, cap = gpu_a.damage_log_device()
+    assert cap == half
+    gpu_b.damage_apply(sp, n=len(rec_a), device_ptr=ptr_a)
+    gpu_b.synchronize()
+    ps, _, cs, ns = gpu_s.dispatch_entities(sp, projectiles=pr, players=players, run_players=False)
+    c_pr, c_co, _ = cpu.projectiles(pr, players, capacity=1024)
+    assert_world_equal(gpu_s, cpu)
+    assert_world_equal(gpu_a, cpu)
+    assert_world_equal(gpu_b, cpu)
+    both = np.concatenate([pa, pb])
+    for f in ("chunk_update_pos", "health", "wall_bounce"):
+        assert np.array_equal(both[f], ps[f]) and np.array_equal(both[f], c_pr[f]), f
+    cb = cb.copy()
+    cb["id1"] += half  # the second rank's projectile indices are local to its range
+    merged = np.concatenate([ca, cb])
+    merged = merged[np.lexsort((merged["id2"], merged["id1"]))]
+    assert na + nb == ns == len(c_co)
+    assert np.array_equal(merged[["id1", "id2", "properties"]], cs[["id1", "id2", "properties"]])
+    # an overflowing log is an error, not a silent truncation
+    gpu_a.damage_log_enable(4)
+    gpu_a.dispatch_entities(sp, projectiles=pr[:half], players=players, run_players=False)
+    with pytest.raises(vg.VxbError):
+        gpu_a.damage_log_read(4)
+    for g in (gpu_a, gpu_b, gpu_s):
+        g.close()
+
+
 @pytest.mark.parametrize("world_gen,seed,yaw,pitch,t", [(0, 0, 0.3, -0.2, 0.0), (0, 0, 2.5, 0.15, 3.25), (1, 3646, 1.2, -0.35, 1.5)])
 def test_render_full_fragment_shader(world_gen, seed, yaw, pitch, t):
     """frag.glsl main = primary DDA + get_color. One transcendental (depth_transparency ^ dist) and long

@@ -107,7 +107,7 @@ __device__ __forceinline__ int lattice_map(int g, int i) {
 __global__ void __launch_bounds__(PROJ_BLOCK, 6) k_projectiles(World w, vxb_projectile* __restrict__ projectiles, uint32_t n_projectiles,
                                                      const vxb_player* __restrict__ players, uint32_t n_players,
                                                      vxb_collision* __restrict__ collisions, uint32_t collision_capacity,
-                                                     uint32_t* __restrict__ collision_count, float dt) {
+                                                     uint32_t* __restrict__ collision_count, float dt, DamageLog dlog) {
     __shared__ float4 s_players[PLAYER_TILE];  // (pos.xyz, size) is all the hit test reads
     __shared__ float2 s_cull[PLAYER_TILE];     // (y of the hitsphere column's midpoint, its reach)
     const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -394,6 +394,10 @@ __global__ void __launch_bounds__(PROJ_BLOCK, 6) k_projectiles(World w, vxb_proj
         if (damage > 0) {
             // imageAtomicAdd(voxels, get_index(voxel_pos), int(projectile.damage)) (:230-233)
             atomicAdd(&w.pool[voxel_index(w, (uint32_t)vx, (uint32_t)vy, (uint32_t)vz)], (uint32_t)f2i(damage));
+            if (dlog.records) {  // sharded batches: the other replicas of the world replay this add
+                const uint32_t at = atomicAdd(dlog.count, 1u);
+                if (at < dlog.capacity) dlog.records[at] = make_uint4((uint32_t)vx, (uint32_t)vy, (uint32_t)vz, (uint32_t)f2i(damage));
+            }
         }
         out.chunk_update_pos[0] = (uint32_t)vx; out.chunk_update_pos[1] = (uint32_t)vy; out.chunk_update_pos[2] = (uint32_t)vz;
         out.chunk_update_pos[3] = 1;
@@ -598,12 +602,26 @@ __global__ void __launch_bounds__(128) k_players(World w, vxb_player* __restrict
 
 cudaError_t launch_projectiles(const World& w, vxb_projectile* projectiles, uint32_t n_projectiles, const vxb_player* players,
                                uint32_t n_players, vxb_collision* collisions, uint32_t collision_capacity, uint32_t* collision_count,
-                               float dt, cudaStream_t st) {
+                               float dt, DamageLog dlog, cudaStream_t st) {
     if (n_projectiles == 0) return cudaSuccess;
     k_projectiles<<<(n_projectiles + PROJ_BLOCK - 1) / PROJ_BLOCK, PROJ_BLOCK, 0, st>>>(w, projectiles, n_projectiles, players, n_players, collisions,
-                                                               collision_capacity, collision_count, dt);
+                                                               collision_capacity, collision_count, dt, dlog);
     return cudaGetLastError();
 }
+// replays logged voxel damage (x, y, z, amount) on this replica: the same add k_projectiles made on its own
+__global__ void k_apply_damage(World w, const uint4* __restrict__ records, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4 r = records[i];
+    atomicAdd(&w.pool[voxel_index(w, r.x, r.y, r.z)], r.w);
+}
+
+cudaError_t launch_apply_damage(const World& w, const uint32_t* records, uint32_t n, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    k_apply_damage<<<(n + 255) / 256, 256, 0, st>>>(w, reinterpret_cast<const uint4*>(records), n);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_players(const World& w, vxb_player* players, uint32_t n_players, float dt, cudaStream_t st) {
     if (n_players == 0) return cudaSuccess;
     k_players<<<(n_players + 127) / 128, 128, 0, st>>>(w, players, n_players, dt);

@@ -80,6 +80,8 @@ struct vxb_ctx {
     DevBuf<vxb_player> players;
     DevBuf<vxb_collision> collisions;
     DevBuf<uint32_t> collision_count;
+    DevBuf<uint32_t> dmg_log, dmg_count;  // voxel damage adds of the last projectile dispatch (vxb_damage_log_enable)
+    uint32_t dmg_cap = 0;
     DevBuf<int32_t> worldgen_updates;   // ivec4 per 8^3 workgroup
     DevBuf<uint32_t> worldgen_results;  // one per chunk
     DevBuf<uint32_t> chunk_updates;     // uvec4 per chunk
@@ -124,6 +126,8 @@ struct vxb_ctx {
     uint32_t last_start_pos[3] = {0, 0, 0};
     bool results_pending = false;  // flags / worldgen_results D2H enqueued by the last compute
     int update_variant = 2;  // tiled kernel with unchanged-store elision (identical results, fewer bytes)
+
+    DamageLog dlog() const { return DamageLog{dmg_cap ? reinterpret_cast<uint4*>(dmg_log.p) : nullptr, dmg_cap, dmg_count.p}; }
 
     World world(const uint32_t start_pos[3]) const {
         World w;
@@ -186,7 +190,7 @@ static void free_ctx(vxb_ctx* c) {
     c->update_flags.release(); c->voxel_writes.release(); c->scalars.release(); c->res_list.release(); c->res_flags.release();
     c->ray_pos.release(); c->ray_normal.release(); c->ray_ldist.release(); c->ray_dist.release(); c->ray_in_pos.release();
     c->ray_in_dir.release(); c->raster_depth.release(); c->ray_voxel.release(); c->ray_leaving.release(); c->ray_count.release();
-    c->cams.release(); c->color.release();
+    c->cams.release(); c->color.release(); c->dmg_log.release(); c->dmg_count.release();
     c->h_projectiles.release(); c->h_players.release(); c->h_collisions.release(); c->h_collision_count.release();
     c->h_worldgen_updates.release(); c->h_worldgen_results.release(); c->h_chunk_updates.release(); c->h_update_flags.release();
     c->h_voxel_writes.release();
@@ -515,6 +519,7 @@ int vxb_compute(vxb_ctx* c, const uint32_t start_pos[3], const vxb_projectile* p
     }
     VXB_CUDA(c, cudaMemsetAsync(c->collisions.p, 0, (size_t)c->s.max_collisions * sizeof(vxb_collision), st));
     VXB_CUDA(c, cudaMemsetAsync(c->collision_count.p, 0, sizeof(uint32_t), st));
+    if (c->dmg_cap) VXB_CUDA(c, cudaMemsetAsync(c->dmg_count.p, 0, sizeof(uint32_t), st));
 
     const size_t worldgen_update_count = load_worldgen_updates(c, start_pos);  // :871
     const size_t voxel_write_count = load_voxel_writes(c, start_pos);          // :874
@@ -531,7 +536,7 @@ int vxb_compute(vxb_ctx* c, const uint32_t start_pos[3], const vxb_projectile* p
     // dispatch order of :944-1000
     if (c->upload_projectile_count > 0)
         VXB_CUDA(c, launch_projectiles(w, c->projectiles.p, c->upload_projectile_count, c->players.p, c->upload_player_count,
-                                       c->collisions.p, c->s.max_collisions, c->collision_count.p, c->s.delta_time, st));
+                                       c->collisions.p, c->s.max_collisions, c->collision_count.p, c->s.delta_time, c->dlog(), st));
     if (c->upload_player_count > 0) VXB_CUDA(c, launch_players(w, c->players.p, c->upload_player_count, c->s.delta_time, st));
     if (c->slice_to_unload >= 0) {
         const int comp = c->slice_to_unload / 2;
@@ -758,10 +763,11 @@ int vxb_dispatch_entities(vxb_ctx* c, const uint32_t start_pos[3], vxb_projectil
     if (n_players) VXB_CUDA(c, cudaMemcpyAsync(c->players.p, players, (size_t)n_players * sizeof(vxb_player), cudaMemcpyHostToDevice, st));
     VXB_CUDA(c, cudaMemsetAsync(c->collisions.p, 0, (size_t)c->s.max_collisions * sizeof(vxb_collision), st));
     VXB_CUDA(c, cudaMemsetAsync(c->collision_count.p, 0, sizeof(uint32_t), st));
+    if (c->dmg_cap) VXB_CUDA(c, cudaMemsetAsync(c->dmg_count.p, 0, sizeof(uint32_t), st));
     const World w = c->world(start_pos);
     if (run_projectiles && n_projectiles)
         VXB_CUDA(c, launch_projectiles(w, c->projectiles.p, n_projectiles, c->players.p, n_players, c->collisions.p, c->s.max_collisions,
-                                       c->collision_count.p, c->s.delta_time, st));
+                                       c->collision_count.p, c->s.delta_time, c->dlog(), st));
     if (run_players && n_players) VXB_CUDA(c, launch_players(w, c->players.p, n_players, c->s.delta_time, st));
     if (n_projectiles) VXB_CUDA(c, cudaMemcpyAsync(projectiles, c->projectiles.p, (size_t)n_projectiles * sizeof(vxb_projectile), cudaMemcpyDeviceToHost, st));
     if (n_players) VXB_CUDA(c, cudaMemcpyAsync(players, c->players.p, (size_t)n_players * sizeof(vxb_player), cudaMemcpyDeviceToHost, st));
@@ -787,10 +793,11 @@ int vxb_entities_resident_run(vxb_ctx* c, const uint32_t start_pos[3], uint32_t 
     cudaStream_t st = c->stream;
     VXB_CUDA(c, cudaMemsetAsync(c->collisions.p, 0, (size_t)c->s.max_collisions * sizeof(vxb_collision), st));
     VXB_CUDA(c, cudaMemsetAsync(c->collision_count.p, 0, sizeof(uint32_t), st));
+    if (c->dmg_cap) VXB_CUDA(c, cudaMemsetAsync(c->dmg_count.p, 0, sizeof(uint32_t), st));
     const World w = c->world(start_pos);
     if (run_projectiles && n_projectiles)
         VXB_CUDA(c, launch_projectiles(w, c->projectiles.p, n_projectiles, c->players.p, n_players, c->collisions.p, c->s.max_collisions,
-                                       c->collision_count.p, c->s.delta_time, st));
+                                       c->collision_count.p, c->s.delta_time, c->dlog(), st));
     if (run_players && n_players) VXB_CUDA(c, launch_players(w, c->players.p, n_players, c->s.delta_time, st));
     if (n_collisions_out) {
         VXB_CUDA(c, cudaMemcpyAsync(n_collisions_out, c->collision_count.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
@@ -825,6 +832,63 @@ int vxb_update_list_flags(vxb_ctx* c, uint32_t* flags_out, uint32_t n) {
     VXB_CUDA(c, cudaSetDevice(c->device));
     if (n) VXB_CUDA(c, cudaMemcpyAsync(flags_out, c->res_flags.p, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
     VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VXB_OK;
+}
+
+// ---- sharded collision batches: log of voxel damage adds, replayed on the other replicas ----
+int vxb_damage_log_enable(vxb_ctx* c, uint32_t capacity) {
+    if (!c) return VXB_ERR_INVALID;
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->dmg_cap = 0;
+    if (capacity == 0) return VXB_OK;
+    VXB_CUDA(c, c->dmg_log.ensure((size_t)capacity * 4));
+    VXB_CUDA(c, c->dmg_count.ensure(1));
+    VXB_CUDA(c, cudaMemsetAsync(c->dmg_count.p, 0, sizeof(uint32_t), c->stream));
+    c->dmg_cap = capacity;
+    return VXB_OK;
+}
+
+int vxb_damage_log_device(vxb_ctx* c, void** records_dev, void** count_dev, uint32_t* capacity) {
+    if (!c) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, c->dmg_cap > 0, "vxb_damage_log_device: the log is not enabled");
+    if (records_dev) *records_dev = c->dmg_log.p;
+    if (count_dev) *count_dev = c->dmg_count.p;
+    if (capacity) *capacity = c->dmg_cap;
+    return VXB_OK;
+}
+
+int vxb_damage_log_read(vxb_ctx* c, uint32_t (*records_out)[4], uint32_t capacity, uint32_t* n_out) {
+    if (!c || !n_out) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, c->dmg_cap > 0, "vxb_damage_log_read: the log is not enabled");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    uint32_t n = 0;
+    VXB_CUDA(c, cudaMemcpyAsync(&n, c->dmg_count.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    VXB_REQUIRE(c, n <= c->dmg_cap, "vxb_damage_log_read: the log overflowed (more damage adds than its capacity)");
+    *n_out = n;
+    VXB_REQUIRE(c, n == 0 || (records_out && capacity >= n), "vxb_damage_log_read: records_out too small");
+    if (n) {
+        VXB_CUDA(c, cudaMemcpyAsync(records_out, c->dmg_log.p, (size_t)n * 16, cudaMemcpyDeviceToHost, c->stream));
+        VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return VXB_OK;
+}
+
+int vxb_damage_apply(vxb_ctx* c, const uint32_t start_pos[3], const uint32_t (*records)[4], uint32_t n, int records_on_device) {
+    if (!c || !start_pos) return VXB_ERR_INVALID;
+    VXB_WINDOW(c, start_pos);
+    if (n == 0) return VXB_OK;
+    VXB_REQUIRE(c, records != nullptr, "vxb_damage_apply: records is NULL");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    const uint32_t* dev = reinterpret_cast<const uint32_t*>(records);
+    if (!records_on_device) {
+        VXB_CUDA(c, c->voxel_writes.ensure((size_t)n * 4));  // staging shared with write_voxels (stream-ordered)
+        VXB_CUDA(c, cudaMemcpyAsync(c->voxel_writes.p, records, (size_t)n * 16, cudaMemcpyHostToDevice, c->stream));
+        dev = c->voxel_writes.p;
+    }
+    VXB_CUDA(c, launch_apply_damage(c->world(start_pos), dev, n, c->stream));
+    if (!records_on_device) VXB_CUDA(c, cudaStreamSynchronize(c->stream));  // the host array may be reused on return
     return VXB_OK;
 }
 

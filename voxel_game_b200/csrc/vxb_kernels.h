@@ -53,9 +53,17 @@ cudaError_t launch_raymarch_rays(const World& w, const float* pos_dev, const flo
                                  cudaStream_t st);
 
 // compute_projectile.glsl / compute_entity.glsl
+// Optional log of the voxel damage adds of one k_projectiles launch (records == nullptr: off); sharded
+// collision batches replay it on the other replicas of the world with launch_apply_damage.
+struct DamageLog {
+    uint4* records;  // (x, y, z, amount)
+    uint32_t capacity;
+    uint32_t* count;
+};
 cudaError_t launch_projectiles(const World& w, vxb_projectile* projectiles, uint32_t n_projectiles, const vxb_player* players,
                                uint32_t n_players, vxb_collision* collisions, uint32_t collision_capacity, uint32_t* collision_count,
-                               float dt, cudaStream_t st);
+                               float dt, DamageLog dlog, cudaStream_t st);
+cudaError_t launch_apply_damage(const World& w, const uint32_t* records, uint32_t n, cudaStream_t st);
 cudaError_t launch_players(const World& w, vxb_player* players, uint32_t n_players, float dt, cudaStream_t st);
 
 }  // namespace vxb

@@ -275,6 +275,30 @@ class VoxelComputePipeline:
         self._check(self._lib.vxb_update_list_flags(self._h, ptr(out), self._res_n))
         return out
 
+    # -- sharded collision batches (voxel damage log, see include/voxelb200.h) ----------------
+    def damage_log_enable(self, capacity):
+        self._check(self._lib.vxb_damage_log_enable(self._h, int(capacity)))
+
+    def damage_log_device(self):
+        """(records device address, counter device address, capacity)"""
+        r, c, cap = ctypes.c_void_p(), ctypes.c_void_p(), ctypes.c_uint32()
+        self._check(self._lib.vxb_damage_log_device(self._h, ctypes.byref(r), ctypes.byref(c), ctypes.byref(cap)))
+        return r.value, c.value, cap.value
+
+    def damage_log_read(self, capacity):
+        rec = np.zeros((int(capacity), 4), np.uint32)
+        n = ctypes.c_uint32(0)
+        self._check(self._lib.vxb_damage_log_read(self._h, ptr(rec), int(capacity), ctypes.byref(n)))
+        return rec[: n.value].copy()
+
+    def damage_apply(self, start_pos, records=None, n=None, device_ptr=None):
+        """Replays (x, y, z, amount) records: a host array, or n records at a device address."""
+        if device_ptr is not None:
+            self._check(self._lib.vxb_damage_apply(self._h, ptr(_u32(start_pos, 3)), ctypes.c_void_p(int(device_ptr)), int(n), 1))
+            return
+        rec = np.ascontiguousarray(np.asarray(records, dtype=np.uint32).reshape(-1, 4))
+        self._check(self._lib.vxb_damage_apply(self._h, ptr(_u32(start_pos, 3)), ptr(rec) if rec.size else None, rec.shape[0], 0))
+
     def set_update_kernel(self, variant):
         self._check(self._lib.vxb_set_update_kernel(self._h, int(variant)))
 
