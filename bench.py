@@ -346,6 +346,12 @@ def run_ours(args):
                                   "kind": "port",
                                   "sample": "%d ticks over the first %d x-columns of the same world (%d chunks, %d voxels), OpenMP over chunks"
                                             % (reps, sx, n_s, n_s * 4096)}
+    # ---------------- C5: full tick (worldgen stream + sharded update + replica refresh + 64 views) ----------------
+    tick = None
+    if args.tick or (world_size == 8 and not args.no_tick):
+        tick = bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp, chunks, exchange)
+        if rank == 0:
+            result["tick"] = tick
     gpu.close()
     del pool_t, first_col, ghost_col
 
@@ -360,6 +366,115 @@ def run_ours(args):
         dist.destroy_process_group()
     if rank == 0:
         OUT.emit(result)
+
+
+def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp, chunks, exchange):
+    """BASELINE configs[4]: one game tick on the config-3 world —
+      1. worldgen: 512 chunks regenerated in place (512 / N per rank, in its own slab; forced, so that slots
+         and the table stay put and only chunk payloads travel to the replicas),
+      2. the update step over all chunks (x-slab sharded, halo exchange on offset.x == 1 phases),
+      3. replica refresh: chunks whose change flag is set (plus the regenerated ones) are all-gathered into
+         every rank's full replica of the world (replicas.gather_changed_chunks),
+      4. 64 camera views x 1920x1080 primary rays against the replica, 64 / N views per rank.
+    Device time per phase (CUDA events on the one stream everything runs on), max over ranks."""
+    from tests import scenes
+    from voxel_game_b200.replicas import changed_chunk_mask, exchange_ghost_mask, gather_changed_chunks
+
+    RS, SP = tuple(args.world), C3_SP
+    n_total = RS[0] * RS[1] * RS[2]
+    n_own, pc = shard.n_own, shard.plane_chunks
+    dev = torch.cuda.current_device()
+    gs = vg.GameSettings(render_size=RS, max_loaded_chunks=2 + n_total, max_worldgen_rate=8 * 32768, max_update_rate=1024)
+    rep = vg.VoxelComputePipeline(gs, device=dev)
+    rep.set_stream(torch.cuda.current_stream().cuda_stream)
+    all_chunks = chunk_grid(0, RS[0], RS, SP)
+    generate_world(rep, SP, all_chunks, 2, True, torch)
+    rep_pool = torch.as_tensor(DevView(rep.device_ptrs().voxel_pool, (2 + n_total) * 4096), device="cuda").view(2 + n_total, 4096)[2:]
+    own_pool = pool_t[2:2 + n_own]
+    first_global = shard.x0 * pc
+    cap = min(n_own, 16384)
+    idx_buf = torch.empty(cap, dtype=torch.int64, device="cuda")
+    chunk_buf = torch.empty((cap, 4096), dtype=torch.int32, device="cuda")
+    # the replica's table and slots come from its own worldgen; its voxels are then taken from the slabs'
+    # current (settled) state: the same gather as the per-tick refresh, with every chunk marked
+    mark = torch.zeros(n_own, dtype=torch.bool, device="cuda")
+    for b in range(0, n_own, cap):
+        mark[b:b + cap] = True
+        gather_changed_chunks(dist, torch, mark, own_pool, first_global, rep_pool, idx_buf, chunk_buf, rank, world_size)
+        mark[b:b + cap] = False
+    del mark
+    same0 = bool(torch.equal(rep_pool[first_global:first_global + n_own], own_pool))
+    flags_t = torch.as_tensor(DevView(gpu.update_list_flags_device()[0], n_own), device="cuda")
+    # regenerated chunks: first column of the slab, all y, the first 32/N z  (512 / N chunks)
+    per_rank = max(1, 512 // world_size)
+    nz = max(1, per_rank // RS[1])
+    regen_idx = np.array([y * RS[2] + z for y in range(RS[1]) for z in range(nz)], np.int64)[:per_rank]
+    regen_loads = loads_for(chunks[regen_idx], 2 + regen_idx, True)
+    regen_t = torch.as_tensor(regen_idx, device="cuda")
+    # cameras: the 64 players of config 4 around the world centre, yaw = idx * 2 pi / 64
+    cx, cz = 16 * SP[0] + 8 * RS[0], 16 * SP[2] + 8 * RS[2]
+    cam_y = 16 * (SP[1] + RS[1] // 2) + 40.0
+    grid = scenes.players_grid(8, (cx, cam_y, cz), 48.0, cam_y, seed=64)
+    cams = np.concatenate([scenes.camera(tuple(grid["pos"][k, :3]), k * 2 * np.pi / 64, -0.2) for k in range(64)])
+    mine = cams[rank * 64 // world_size:(rank + 1) * 64 // world_size]
+    W, H = 1920, 1080
+    caps = vg.RayCaps(100, 40, 20, 15, 0)
+    names = ("worldgen", "update", "replica_refresh", "rays")
+    acc = {k: 0.0 for k in names}
+    moved = 0
+    n_ticks = max(4, min(args.steps, 16))
+
+    def one_tick(i, timed):
+        nonlocal moved
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+        off = PHASES[i % 8]
+        ev[0].record()
+        gpu.dispatch_worldgen(lsp, regen_loads, complete=True, want_results=False)
+        ev[1].record()
+        if world_size > 1 and off[0] == 1:
+            exchange(True)
+        gpu.update_list_run(lsp, off)
+        if world_size > 1 and off[0] == 1:
+            exchange(False)
+        ev[2].record()
+        mask, ghost_mask = changed_chunk_mask(torch, flags_t, shard.cols, RS[1], RS[2], off, bool(shard.ghost))
+        mask[regen_t] = True
+        if off[0] == 1:
+            got = exchange_ghost_mask(dist, torch, ghost_mask, rank, world_size, pc)
+            if got is not None:
+                mask[:pc] |= got
+        m = gather_changed_chunks(dist, torch, mask, own_pool, first_global, rep_pool, idx_buf, chunk_buf, rank, world_size)
+        ev[3].record()
+        for b in range(0, len(mine), 8):
+            rep.raymarch(SP, mine[b:b + 8], W, H, caps)
+        ev[4].record()
+        torch.cuda.synchronize()
+        if timed:
+            moved += m
+            for k in range(4):
+                acc[names[k]] += ev[k].elapsed_time(ev[k + 1])
+
+    for i in range(3):
+        one_tick(i, False)
+    if world_size > 1:
+        dist.barrier()
+    for i in range(n_ticks):
+        one_tick(3 + i, True)
+    if world_size > 1:
+        dist.barrier()
+    same1 = bool(torch.equal(rep_pool[first_global:first_global + n_own], own_pool))
+    t = torch.tensor([acc[k] / n_ticks for k in names] + [sum(acc.values()) / n_ticks, 0.0 if (same0 and same1) else 1.0], dtype=torch.float64, device="cuda")
+    if world_size > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    t = t.tolist()
+    rep.close()
+    return {"metric": "ticks/s", "value": 1e3 / t[4], "unit": "ticks/s", "ms_per_tick": t[4], "n_gpus": world_size, "ticks": n_ticks,
+            "phases_ms": {names[k]: t[k] for k in range(4)}, "replica_matches_slab": t[5] == 0.0,
+            "chunks_refreshed_per_tick": moved / n_ticks,
+            "config": {"workload": "BASELINE configs[4]: %d chunks regenerated + update over all %d chunks + 64 views x 1920x1080 primary rays per tick"
+                                   % (per_rank * world_size, n_total),
+                       "note": "regeneration is forced (slots keep their place) instead of forced = false; per-phase times are the max over ranks, "
+                               "their sum is the max over ranks of the per-rank sum"}}
 
 
 def bench_rays(args, torch, vg, peak, rank=0, world_size=1, dist=None):
@@ -421,8 +536,9 @@ def bench_rays(args, torch, vg, peak, rank=0, world_size=1, dist=None):
     batch8 = {"metric": "rays/s", "value": 8 * W * H / (batch_ms / 1e3), "unit": "rays/s", "ms_per_step": batch_ms, "n_gpus": world_size,
               "scaling": "strong", "config": {"workload": "8 camera views x 1920x1080 per step, view-range sharded over a replicated config-2 world"}}
     if world_size > 1:
+        coll = None if args.no_collisions else bench_collisions_sharded(args, torch, vg, dist, gpu, SP, RS, (cx, col_y, cz), rank, world_size)
         gpu.close()
-        return {"batch8": batch8}
+        return {"batch8": batch8, "collisions": coll}
     iters_total, layers_total = [], []
     for k in range(max(args.warmup, 3)):
         gpu.raymarch(SP, cams[k % 8:k % 8 + 1], W, H, caps)
@@ -537,6 +653,62 @@ def bench_collisions(args, torch, vg, gpu, SP, RS, centre, peak):
     return out
 
 
+def bench_collisions_sharded(args, torch, vg, dist, gpu, SP, RS, centre, rank, world_size):
+    """BASELINE configs[3] on N GPUs: replicated config-2 world, projectile index ranges per rank,
+    players replicated; the voxel damage each rank adds is logged, all-gathered and replayed on the other
+    replicas inside the timed region. Ends with a checksum comparison of the replicas."""
+    from tests import scenes
+    from voxel_game_b200.replicas import exchange_damage
+
+    cx, col_y, cz = centre
+    n_proj, n_side = args.projectiles, 8
+    lo = (16 * SP[0] + 8, 16 * SP[1] + 8, 16 * SP[2] + 8)
+    hi = (16 * (SP[0] + RS[0]) - 8, 16 * (SP[1] + RS[1]) - 8, 16 * (SP[2] + RS[2]) - 8)
+    pr = scenes.random_projectiles(n_proj, lo, hi, seed=0x5EED0001 & 0x7FFFFFFF)
+    pl = scenes.players_grid(n_side, (cx, col_y, cz), 48.0, col_y + 4.0, seed=64)
+    per = n_proj // world_size
+    mine = pr[rank * per:(rank + 1) * per]
+    gpu.damage_log_enable(per)
+    gpu.dispatch_entities(SP, projectiles=mine, players=pl, run_projectiles=False, run_players=False)  # upload only
+    ptrs = gpu.device_ptrs()
+    proj_t = torch.as_tensor(DevView(ptrs.projectiles, per * 28), device="cuda")
+    play_t = torch.as_tensor(DevView(ptrs.players, n_side * n_side * 32), device="cuda")
+    proj0, play0 = proj_t.clone(), play_t.clone()
+    rec_ptr, cnt_ptr, cap = gpu.damage_log_device()
+    rec_t = torch.as_tensor(DevView(rec_ptr, cap * 4), device="cuda").view(cap, 4)
+    cnt_t = torch.as_tensor(DevView(cnt_ptr, 1), device="cuda")
+    steps = max(4, min(args.steps, 16))
+    total_ms, foreign = 0.0, 0
+
+    def apply_fn(rows):
+        gpu.damage_apply(SP, n=rows.shape[0], device_ptr=rows.data_ptr())
+
+    for i in range(3 + steps):
+        proj_t.copy_(proj0)
+        play_t.copy_(play0)
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        gpu.entities_resident_run(SP, per, n_side * n_side)
+        got = exchange_damage(dist, torch, rec_t, int(cnt_t.item()), rank, world_size, apply_fn)
+        e1.record()
+        torch.cuda.synchronize()
+        if i >= 3:
+            total_ms += e0.elapsed_time(e1)
+            foreign += got
+    ck = torch.tensor([gpu.world_checksum(SP) & 0x7FFFFFFFFFFFFFFF], dtype=torch.int64, device="cuda")
+    cks = torch.zeros(world_size, dtype=torch.int64, device="cuda")
+    dist.all_gather_into_tensor(cks, ck)
+    t = torch.tensor([total_ms / steps], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    return {"metric": "projectiles/s", "value": n_proj / (ms / 1e3), "unit": "projectiles/s", "ms_per_tick": ms, "n_gpus": world_size, "scaling": "strong",
+            "replicas_identical": bool((cks == cks[0]).all().item()), "foreign_damage_records_per_tick": foreign / steps,
+            "config": {"workload": "BASELINE configs[3]: %d projectiles (index ranges per rank) + %d player hulls vs replicas of the config-2 world; "
+                                   "voxel damage all-gathered and replayed inside the timed region" % (n_proj, n_side * n_side)}}
+
+
 # ------------------------------------------------------------------------------------------------
 def run_reference(args):
     """The reference has no CPU implementation of this path and its shaders cannot run here (no
@@ -614,6 +786,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-rays", action="store_true")
     ap.add_argument("--no-collisions", action="store_true")
+    ap.add_argument("--tick", action="store_true", help="also run BASELINE configs[4], the full tick (default on at 8 GPUs)")
+    ap.add_argument("--no-tick", action="store_true")
     ap.add_argument("--projectiles", type=int, default=1 << 20)
     ap.add_argument("--cpu-sample-cols", type=int, default=4)
     args = ap.parse_args()

@@ -252,6 +252,9 @@ int vxb_damage_apply(vxb_ctx* ctx, const uint32_t start_pos[3], const uint32_t (
 int vxb_update_list_upload(vxb_ctx* ctx, const uint32_t (*chunk_updates)[4], uint32_t n);
 int vxb_update_list_run(vxb_ctx* ctx, const uint32_t start_pos[3], const uint32_t offset[3]);
 int vxb_update_list_flags(vxb_ctx* ctx, uint32_t* flags_out, uint32_t n);
+/* Device address of the resident list's change flags (chunk_updates[].w of the last vxb_update_list_run,
+ * one u32 per entry, stream-ordered), for consumers that stay on the device (replica refresh). */
+int vxb_update_list_flags_device(vxb_ctx* ctx, void** flags_dev, uint32_t* n);
 /* Selects the update kernel: 2 = default (persistent cp.async-pipelined, vectorised; 16-byte vectors
  * whose four voxels did not change are not stored back — results are identical), 0 = the same kernel
  * with the reference's unconditional stores (compute_voxel.glsl:87), 1 = per-voxel gather that follows

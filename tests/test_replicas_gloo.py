@@ -15,14 +15,30 @@ from tests import scenes
 from tests.oracle_lib import CpuWorld
 
 RS, SP = (4, 2, 3), (100, 50, 70)
-TICKS = 12
+TICKS = 24
 
 
 def _global_world(seed):
+    """A mostly settled world (saturated air) with a few stones and water cells at chunk corners, faces and on
+    the slab boundary: distance fields and water then change a few chunks per tick, often only the neighbour
+    of the work item that made the change — what the change-flag dilation has to get right."""
     n = RS[0] * RS[1] * RS[2]
     w = CpuWorld(RS, SP, 2 + n)
     chunks = w.load_all_chunks()
-    w.pool[2:] = scenes.random_pool(2 + n, seed, water=0.2, air=0.5)
+    w.pool[2:] = 0x00FFFFFF
+    grid = w.pool[2:].reshape(RS[0], RS[1], RS[2], 16, 16, 16)
+    stone, water = np.uint32(1 << 24), np.uint32(7 << 24)
+    grid[1, 0, 1, 15, 15, 15] = stone   # corner: touches 8 chunks, on the slab boundary (x = 1 | 2)
+    grid[2, 1, 0, 0, 0, 0] = stone      # first voxel of rank 1's first column
+    grid[0, 0, 2, 8, 15, 0] = stone
+    grid[3, 1, 2, 15, 3, 15] = stone
+    grid[1, 1, 1, 15, 8, 7] = water     # falls and spreads across the slab boundary
+    grid[2, 1, 1, 0, 9, 7] = water
+    grid[0, 1, 0, 5, 0, 5] = water      # falls into the chunk below
+    rng = np.random.RandomState(seed)
+    for _ in range(6):
+        c = tuple(rng.randint(0, r) for r in RS)
+        grid[c][tuple(rng.randint(0, 16, 3))] = stone
     return w, chunks
 
 
@@ -46,7 +62,7 @@ def _worker(rank, world_size, port, out_dir):
     import torch
     import torch.distributed as dist
 
-    from voxel_game_b200.replicas import exchange_damage, gather_changed_chunks
+    from voxel_game_b200.replicas import changed_chunk_mask, exchange_damage, exchange_ghost_mask, gather_changed_chunks
     from voxel_game_b200.sharding import SlabShard, halo_exchange
 
     os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -80,8 +96,12 @@ def _worker(rank, world_size, port, out_dir):
             flags = w.voxel_update(lst, off)
             if off[0] == 1:
                 halo_exchange(dist, sh, first, ghost, sendbuf, recvbuf, pre=False)
-            moved += gather_changed_chunks(dist, torch, torch.from_numpy(flags.astype(np.int32)), own_pool, sh.x0 * pc, replica_t, idx_buf,
-                                           chunk_buf, rank, world_size)
+            mask, ghost_mask = changed_chunk_mask(torch, torch.from_numpy(flags.astype(np.int32)), sh.cols, RS[1], RS[2], off, bool(sh.ghost))
+            if off[0] == 1:
+                got = exchange_ghost_mask(dist, torch, ghost_mask, rank, world_size, pc)
+                if got is not None:
+                    mask[:pc] |= got
+            moved += gather_changed_chunks(dist, torch, mask, own_pool, sh.x0 * pc, replica_t, idx_buf, chunk_buf, rank, world_size)
             states.append(replica.pool[2:].copy())
 
         # ---- sharded collision batch on the (now identical) replicas ----
@@ -123,7 +143,8 @@ def test_two_rank_replicas_follow_the_single_world(tmp_path):
         changed_total += int((f & 1).sum())
         assert np.array_equal(r0["states"][t], g.pool[2:]), "replica 0 differs after tick %d" % t
         assert np.array_equal(r1["states"][t], g.pool[2:]), "replica 1 differs after tick %d" % t
-    assert int(r0["moved"]) == int(r1["moved"]) == changed_total > 0
+    # the refresh is selective: it moved at least the flagged chunks and not everything
+    assert int(r0["moved"]) == int(r1["moved"]) and 0 < changed_total <= int(r0["moved"]) < TICKS * len(chunks)
     # the whole batch on the single world
     pr = _batch(17)
     out_pr, _, _ = g.projectiles(pr, scenes.players_grid(1, (0, 0, 0), 1.0, -1000.0, seed=1)[:0], capacity=16)

@@ -835,6 +835,14 @@ int vxb_update_list_flags(vxb_ctx* c, uint32_t* flags_out, uint32_t n) {
     return VXB_OK;
 }
 
+int vxb_update_list_flags_device(vxb_ctx* c, void** flags_dev, uint32_t* n) {
+    if (!c || !flags_dev) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, c->res_n > 0, "vxb_update_list_flags_device: no resident list uploaded");
+    *flags_dev = c->res_flags.p;
+    if (n) *n = c->res_n;
+    return VXB_OK;
+}
+
 // ---- sharded collision batches: log of voxel damage adds, replayed on the other replicas ----
 int vxb_damage_log_enable(vxb_ctx* c, uint32_t capacity) {
     if (!c) return VXB_ERR_INVALID;

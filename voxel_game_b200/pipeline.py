@@ -275,6 +275,12 @@ class VoxelComputePipeline:
         self._check(self._lib.vxb_update_list_flags(self._h, ptr(out), self._res_n))
         return out
 
+    def update_list_flags_device(self):
+        """(device address of the resident list's change flags, number of entries)"""
+        a, n = ctypes.c_void_p(), ctypes.c_uint32()
+        self._check(self._lib.vxb_update_list_flags_device(self._h, ctypes.byref(a), ctypes.byref(n)))
+        return a.value, n.value
+
     # -- sharded collision batches (voxel damage log, see include/voxelb200.h) ----------------
     def damage_log_enable(self, capacity):
         self._check(self._lib.vxb_damage_log_enable(self._h, int(capacity)))

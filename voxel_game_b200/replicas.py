@@ -9,10 +9,10 @@ gloo on CPU tensors (tests):
   and each rank replays the OTHER ranks' records on its replica. Integer adds commute, so all replicas
   end bit-identical to a single-GPU run of the whole batch.
 
-* `gather_changed_chunks` — sharded update + replicated rays (config 5): after the update step every
-  rank owns the new state of its slab; chunks whose change flag (bit 0 of chunk_updates[].w,
-  compute_voxel.glsl:55-86) is set are all-gathered as (global chunk index, 16 KiB payload) and
-  written into every rank's replica pool.
+* `changed_chunk_mask` / `exchange_ghost_mask` / `gather_changed_chunks` — sharded update + replicated
+  rays (config 5): after the update step every rank owns the new state of its slab; the chunks whose
+  payload changed (from the change flags chunk_updates[].w, compute_voxel.glsl:55-86) are all-gathered
+  as (global chunk index, 16 KiB payload) and written into every rank's replica pool.
 """
 
 
@@ -51,14 +51,60 @@ def exchange_damage(dist, torch, records, count, rank, world_size, apply_fn):
     return applied
 
 
-def gather_changed_chunks(dist, torch, flags, own_pool, own_first_global, replica_pool, idx_buf, chunk_buf, rank, world_size):
-    """flags: [n_own] int32 change flags of this rank's chunks (list order == pool order).
-    own_pool: [n_own, 4096] view of this rank's slab chunks; own_first_global: global index of its
-    first chunk in the replica's chunk order; replica_pool: [n_total, 4096] view of the replica's
-    chunks. idx_buf [cap] int64 / chunk_buf [cap, 4096] int32: exchange scratch on the same device.
-    Every rank's changed chunks (bit 0) end up in every replica. Returns the total number of chunks
-    written into this replica."""
-    changed = torch.nonzero(flags & 1, as_tuple=False).flatten()
+def changed_chunk_mask(torch, flags, cols, ry, rz, offset, has_ghost):
+    """Which chunk PAYLOADS did one update dispatch change? flags: [cols*ry*rz] int32, the change flags of a
+    work list that is the full (x, y, z)-ordered grid of this rank's own columns. An item's region is the
+    16^3 box at `offset` inside its chunk, so with offset components of 1 it reaches one voxel plane into
+    the +x / +y / +z neighbours (and edge / corner neighbours); set_data (compute_voxel.glsl:55-86) says so
+    through the high-face bits 0x10 / 0x20 / 0x40 next to bit 0. The mask is therefore bit 0 dilated along
+    the shifted axes where those bits are set (conservative: local coordinate 15 sets them too).
+    Returns (own mask [cols*ry*rz] bool, ghost-column mask [ry*rz] bool or None): the ghost column is the
+    first column of the next rank, which has to be told (exchange_ghost_mask)."""
+    g = flags.view(cols, ry, rz)
+    base = (g & 1) != 0
+    hi = [base & ((g & bit) != 0) if offset[a] else None for a, bit in enumerate((0x10, 0x20, 0x40))]
+    changed = base.clone()
+    ghost = torch.zeros((ry, rz), dtype=torch.bool, device=flags.device) if has_ghost else None
+    for d in ((1, 0, 0), (0, 1, 0), (0, 0, 1), (1, 1, 0), (1, 0, 1), (0, 1, 1), (1, 1, 1)):
+        if any(d[a] and hi[a] is None for a in range(3)):
+            continue
+        m = None
+        for a in range(3):
+            if d[a]:
+                m = hi[a] if m is None else (m & hi[a])
+        src = m[: cols - d[0], : ry - d[1], : rz - d[2]]
+        changed[d[0]:, d[1]:, d[2]:] |= src
+        if d[0] and ghost is not None:
+            ghost[d[1]:, d[2]:] |= m[cols - 1, : ry - d[1], : rz - d[2]]
+    return changed.reshape(-1), (ghost.reshape(-1) if ghost is not None else None)
+
+
+def exchange_ghost_mask(dist, torch, ghost_mask, rank, world_size, plane_chunks):
+    """Rank g tells rank g+1 which chunks of g+1's first column it changed through its ghost column.
+    Returns the mask received from rank g-1 ([plane_chunks] bool) or None for rank 0."""
+    if world_size == 1:
+        return None
+    ops, recv = [], None
+    if ghost_mask is not None:
+        send = ghost_mask.to(torch.uint8).contiguous()
+        ops.append(dist.P2POp(dist.isend, send, rank + 1))
+    if rank > 0:
+        recv = torch.empty(plane_chunks, dtype=torch.uint8, device=(ghost_mask.device if ghost_mask is not None else None))
+        ops.append(dist.P2POp(dist.irecv, recv, rank - 1))
+    if ops:
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+    return None if recv is None else recv.bool()
+
+
+def gather_changed_chunks(dist, torch, mask, own_pool, own_first_global, replica_pool, idx_buf, chunk_buf, rank, world_size):
+    """mask: [n_own] bool, the chunks of this rank's slab whose payload changed (changed_chunk_mask, plus what
+    the caller knows: regenerated chunks, the neighbour's ghost mask). own_pool: [n_own, 4096] view of this
+    rank's slab chunks; own_first_global: global index of its first chunk in the replica's chunk order;
+    replica_pool: [n_total, 4096] view of the replica's chunks. idx_buf [cap] int64 / chunk_buf [cap, 4096]
+    int32: exchange scratch on the same device. Every rank's marked chunks end up in every replica.
+    Returns the total number of chunks written into this replica."""
+    changed = torch.nonzero(mask, as_tuple=False).flatten()
     n = int(changed.numel())
     if n > idx_buf.shape[0]:
         raise ValueError("%d changed chunks but the exchange buffer holds %d" % (n, idx_buf.shape[0]))
