@@ -440,7 +440,7 @@ def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp,
         mask, ghost_mask = changed_chunk_mask(torch, flags_t, shard.cols, RS[1], RS[2], off, bool(shard.ghost))
         mask[regen_t] = True
         if off[0] == 1:
-            got = exchange_ghost_mask(dist, torch, ghost_mask, rank, world_size, pc)
+            got = exchange_ghost_mask(dist, torch, ghost_mask, rank, world_size, pc, flags_t.device)
             if got is not None:
                 mask[:pc] |= got
         m = gather_changed_chunks(dist, torch, mask, own_pool, first_global, rep_pool, idx_buf, chunk_buf, rank, world_size)

@@ -98,7 +98,7 @@ def _worker(rank, world_size, port, out_dir):
                 halo_exchange(dist, sh, first, ghost, sendbuf, recvbuf, pre=False)
             mask, ghost_mask = changed_chunk_mask(torch, torch.from_numpy(flags.astype(np.int32)), sh.cols, RS[1], RS[2], off, bool(sh.ghost))
             if off[0] == 1:
-                got = exchange_ghost_mask(dist, torch, ghost_mask, rank, world_size, pc)
+                got = exchange_ghost_mask(dist, torch, ghost_mask, rank, world_size, pc, torch.device("cpu"))
                 if got is not None:
                     mask[:pc] |= got
             moved += gather_changed_chunks(dist, torch, mask, own_pool, sh.x0 * pc, replica_t, idx_buf, chunk_buf, rank, world_size)

@@ -79,7 +79,7 @@ def changed_chunk_mask(torch, flags, cols, ry, rz, offset, has_ghost):
     return changed.reshape(-1), (ghost.reshape(-1) if ghost is not None else None)
 
 
-def exchange_ghost_mask(dist, torch, ghost_mask, rank, world_size, plane_chunks):
+def exchange_ghost_mask(dist, torch, ghost_mask, rank, world_size, plane_chunks, device):
     """Rank g tells rank g+1 which chunks of g+1's first column it changed through its ghost column.
     Returns the mask received from rank g-1 ([plane_chunks] bool) or None for rank 0."""
     if world_size == 1:
@@ -89,7 +89,7 @@ def exchange_ghost_mask(dist, torch, ghost_mask, rank, world_size, plane_chunks)
         send = ghost_mask.to(torch.uint8).contiguous()
         ops.append(dist.P2POp(dist.isend, send, rank + 1))
     if rank > 0:
-        recv = torch.empty(plane_chunks, dtype=torch.uint8, device=(ghost_mask.device if ghost_mask is not None else None))
+        recv = torch.empty(plane_chunks, dtype=torch.uint8, device=device)
         ops.append(dist.P2POp(dist.irecv, recv, rank - 1))
     if ops:
         for req in dist.batch_isend_irecv(ops):
