@@ -166,7 +166,7 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     # ---------------- C3: slab of the 256x16x256-chunk world ----------------
-    from voxel_game_b200.sharding import SlabShard, halo_exchange
+    from voxel_game_b200.sharding import SlabShard, halo_exchange, sharded_update
 
     RS, SP = tuple(args.world), C3_SP
     shard = SlabShard(RS, SP, rank, world_size)
@@ -193,26 +193,17 @@ def run_ours(args):
 
     # settle: run the automaton until the distance fields have propagated (<= 7 per 8 phases) so the
     # timed steps see the steady state of a running game, not the first ticks after worldgen
+    side = torch.cuda.Stream()  # halo exchange + boundary column, hidden behind the slab's interior
+
     def settle_step(i):
-        off = PHASES[i % 8]
-        if world_size > 1 and off[0] == 1:
-            exchange(True)
-        gpu.update_list_run(lsp, off)
-        if world_size > 1 and off[0] == 1:
-            exchange(False)
+        sharded_update(torch, gpu, shard, lsp, PHASES[i % 8], exchange, stream, side)
 
     for i in range(args.settle):
         settle_step(i)
     torch.cuda.synchronize()
 
     def step(i):
-        off = PHASES[i % 8]
-        if world_size > 1 and off[0] == 1:
-            exchange(True)
-        gpu.update_list_run(lsp, off)
-        launches[0] += 1
-        if world_size > 1 and off[0] == 1:
-            exchange(False)
+        launches[0] += sharded_update(torch, gpu, shard, lsp, PHASES[i % 8], exchange, stream, side)
 
     sampler = ClockSampler(local_rank) if rank == 0 else None  # samples under load: warm-up + timed region
     for i in range(args.warmup):
@@ -349,7 +340,7 @@ def run_ours(args):
     # ---------------- C5: full tick (worldgen stream + sharded update + replica refresh + 64 views) ----------------
     tick = None
     if args.tick or (world_size == 8 and not args.no_tick):
-        tick = bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp, chunks, exchange)
+        tick = bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp, chunks, exchange, stream, side)
         if rank == 0:
             result["tick"] = tick
     gpu.close()
@@ -368,7 +359,7 @@ def run_ours(args):
         OUT.emit(result)
 
 
-def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp, chunks, exchange):
+def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp, chunks, exchange, main, side):
     """BASELINE configs[4]: one game tick on the config-3 world —
       1. worldgen: 512 chunks regenerated in place (512 / N per rank, in its own slab; forced, so that slots
          and the table stay put and only chunk payloads travel to the replicas),
@@ -379,6 +370,7 @@ def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp,
     Device time per phase (CUDA events on the one stream everything runs on), max over ranks."""
     from tests import scenes
     from voxel_game_b200.replicas import changed_chunk_mask, exchange_ghost_mask, gather_changed_chunks
+    from voxel_game_b200.sharding import sharded_update
 
     RS, SP = tuple(args.world), C3_SP
     n_total = RS[0] * RS[1] * RS[2]
@@ -431,11 +423,7 @@ def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp,
         ev[0].record()
         gpu.dispatch_worldgen(lsp, regen_loads, complete=True, want_results=False)
         ev[1].record()
-        if world_size > 1 and off[0] == 1:
-            exchange(True)
-        gpu.update_list_run(lsp, off)
-        if world_size > 1 and off[0] == 1:
-            exchange(False)
+        sharded_update(torch, gpu, shard, lsp, off, exchange, main, side)
         ev[2].record()
         mask, ghost_mask = changed_chunk_mask(torch, flags_t, shard.cols, RS[1], RS[2], off, bool(shard.ghost))
         mask[regen_t] = True

@@ -251,6 +251,12 @@ int vxb_damage_apply(vxb_ctx* ctx, const uint32_t start_pos[3], const uint32_t (
  * the update dispatch on it any number of times without host traffic. */
 int vxb_update_list_upload(vxb_ctx* ctx, const uint32_t (*chunk_updates)[4], uint32_t n);
 int vxb_update_list_run(vxb_ctx* ctx, const uint32_t start_pos[3], const uint32_t offset[3]);
+/* The same dispatch over entries [first, first + count) of the resident list only (their flags land at
+ * the same positions), on *cuda_stream if cuda_stream is not NULL, else on the ctx's stream. Lets a
+ * caller put the part of a sweep that depends on a halo exchange on another stream than the rest;
+ * entries of one phase are independent of each other. Ordering between the streams is the caller's. */
+int vxb_update_list_run_range(vxb_ctx* ctx, const uint32_t start_pos[3], const uint32_t offset[3], uint32_t first, uint32_t count,
+                              void* const* cuda_stream);
 int vxb_update_list_flags(vxb_ctx* ctx, uint32_t* flags_out, uint32_t n);
 /* Device address of the resident list's change flags (chunk_updates[].w of the last vxb_update_list_run,
  * one u32 per entry, stream-ordered), for consumers that stay on the device (replica refresh). */

@@ -85,6 +85,35 @@ def test_voxel_update_z_runs(variant):
     gpu.close()
 
 
+def test_update_list_run_range_equals_full_sweep():
+    """vxb_update_list_run_range over two halves of the resident list (the second on another stream, as the
+    sharded step does for its boundary column) gives the world and flags of one full dispatch."""
+    import torch
+
+    rs, sp = (3, 2, 4), (100, 50, 70)
+    n_slots = 2 + 24
+    gpu, cpu = make_pair(rs, sp, n_slots)
+    table, chunks, _ = scenes.full_table(rs, sp, holes=0.1, seed=4)
+    cpu.table[:] = table
+    cpu.pool[2:] = scenes.random_pool(n_slots, 4)
+    sync_world_to_gpu(gpu, cpu)
+    lst = scenes.update_list(chunks)
+    gpu.update_list_upload(lst)
+    side = torch.cuda.Stream()
+    half = len(lst) // 2
+    for off in scenes.PHASES:
+        gpu.update_list_run_range(sp, off, 0, half)
+        gpu.update_list_run_range(sp, off, half, len(lst) - half, cuda_stream=side.cuda_stream)
+        side.synchronize()
+        f_gpu = gpu.update_list_flags()
+        f_cpu = cpu.voxel_update(lst, off)
+        assert np.array_equal(f_gpu, f_cpu), off
+        assert_world_equal(gpu, cpu)
+    with pytest.raises(Exception):
+        gpu.update_list_run_range(sp, (0, 0, 0), half, len(lst))
+    gpu.close()
+
+
 def test_voxel_update_clustered_toroidal():
     # start_pos not a multiple of render_size: the table is addressed modulo render_size
     rs, sp = (4, 3, 2), (497, 106, 501)

@@ -140,6 +140,7 @@ SIGNATURES = {
     "vxb_update_list_run": (ctypes.c_int, [c_vp, c_vp, c_vp]),
     "vxb_update_list_flags": (ctypes.c_int, [c_vp, c_vp, c_u32]),
     "vxb_set_update_kernel": (ctypes.c_int, [c_vp, ctypes.c_int]),
+    "vxb_update_list_run_range": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_uint32, ctypes.c_uint32, ctypes.POINTER(ctypes.c_void_p)]),
     "vxb_update_list_flags_device": (ctypes.c_int, [c_vp, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_uint32)]),
     "vxb_damage_log_enable": (ctypes.c_int, [c_vp, ctypes.c_uint32]),
     "vxb_damage_log_device": (ctypes.c_int, [c_vp, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_uint32)]),

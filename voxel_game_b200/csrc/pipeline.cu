@@ -826,6 +826,18 @@ int vxb_update_list_run(vxb_ctx* c, const uint32_t start_pos[3], const uint32_t 
     return VXB_OK;
 }
 
+int vxb_update_list_run_range(vxb_ctx* c, const uint32_t start_pos[3], const uint32_t offset[3], uint32_t first, uint32_t count,
+                              void* const* cuda_stream) {
+    if (!c || !start_pos || !offset) return VXB_ERR_INVALID;
+    VXB_WINDOW(c, start_pos);
+    VXB_REQUIRE(c, offset[0] < 2 && offset[1] < 2 && offset[2] < 2, "vxb_update_list_run_range: offset must be in {0,1}^3");
+    VXB_REQUIRE(c, (uint64_t)first + count <= c->res_n, "vxb_update_list_run_range: range exceeds the resident list");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, launch_voxel_update(c->world(start_pos), c->res_list.p + (size_t)first * 4, count, offset, c->res_flags.p + first, c->update_variant,
+                                    cuda_stream ? (cudaStream_t)*cuda_stream : c->stream));
+    return VXB_OK;
+}
+
 int vxb_update_list_flags(vxb_ctx* c, uint32_t* flags_out, uint32_t n) {
     if (!c || !flags_out) return VXB_ERR_INVALID;
     VXB_REQUIRE(c, n <= c->res_n, "vxb_update_list_flags: n exceeds the resident list length");

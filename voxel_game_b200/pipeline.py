@@ -275,6 +275,11 @@ class VoxelComputePipeline:
         self._check(self._lib.vxb_update_list_flags(self._h, ptr(out), self._res_n))
         return out
 
+    def update_list_run_range(self, start_pos, offset, first, count, cuda_stream=None):
+        """Entries [first, first + count) of the resident list; cuda_stream: raw handle, None = the ctx's stream."""
+        st = None if cuda_stream is None else ctypes.byref(ctypes.c_void_p(int(cuda_stream)))
+        self._check(self._lib.vxb_update_list_run_range(self._h, ptr(_u32(start_pos, 3)), ptr(_u32(offset, 3)), int(first), int(count), st))
+
     def update_list_flags_device(self):
         """(device address of the resident list's change flags, number of entries)"""
         a, n = ctypes.c_void_p(), ctypes.c_uint32()

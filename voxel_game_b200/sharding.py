@@ -75,3 +75,35 @@ def halo_exchange(dist, shard, first_col, ghost_col, sendbuf, recvbuf, pre):
         first_col.copy_(recvbuf)
         launches += 1
     return launches
+
+
+def sharded_update(torch, gpu, shard, local_start_pos, offset, exchange, main, side):
+    """One update dispatch of rank `shard.rank`'s resident list (its own columns in (x, y, z) order) with the
+    halo exchange hidden behind the interior of the slab. `exchange(pre)` performs one direction of the halo
+    exchange on the CURRENT torch stream; main / side are torch CUDA streams, main being the ctx's stream.
+    Phases with offset.x == 0 need no exchange. With offset.x == 1 only the LAST own column reads and writes
+    the ghost column, and nothing this rank computes touches the x == 0 planes of its FIRST column (its
+    items cover x = 1..16), which is what travels to and from the left neighbour. So:
+        main:  every column but the last
+        side:  exchange(pre) -> last column -> exchange(post)
+    and main waits for side at the end. Returns the number of update kernels launched."""
+    if shard.world_size == 1 or offset[0] == 0:
+        gpu.update_list_run(local_start_pos, offset)
+        return 1
+    side.wait_stream(main)
+    if not shard.ghost:  # last rank: nothing to wait for, only its first-column planes travel
+        with torch.cuda.stream(side):
+            exchange(True)
+            exchange(False)
+        gpu.update_list_run(local_start_pos, offset)
+        main.wait_stream(side)
+        return 1
+    n_int = shard.n_own - shard.plane_chunks
+    if n_int:
+        gpu.update_list_run_range(local_start_pos, offset, 0, n_int)
+    with torch.cuda.stream(side):
+        exchange(True)
+        gpu.update_list_run_range(local_start_pos, offset, n_int, shard.plane_chunks, cuda_stream=side.cuda_stream)
+        exchange(False)
+    main.wait_stream(side)
+    return 2 if n_int else 1
