@@ -220,4 +220,40 @@ void orc_entities(uint32_t* chunks, uint32_t* voxels, const SimData* sim, Player
     compute_entity::dispatch(e);
 }
 
+// ---- arithmetic property used by the CUDA DDA (not a restatement of the reference) ----
+// The kernels replace the per-step division by a ray component with a multiplication by its rounded
+// reciprocal plus one exact-remainder refinement (vxb_device.cuh: ray_box_axis_rcp). This counts, over n
+// pseudo-random pairs from the guarded range (|b| in [2^-60, 2], |a| in [2^-24, 2^60), mantissas biased
+// towards all-ones / all-zeros), how often that differs from the IEEE quotient a / b. Expected: 0.
+uint64_t orc_reciprocal_division_mismatches(uint64_t n, uint64_t seed) {
+    uint64_t bad = 0;
+#pragma omp parallel reduction(+ : bad)
+    {
+        uint64_t s = seed ^ (0x9E3779B97F4A7C15ull * (uint64_t)(omp_get_thread_num() + 1));
+        auto rng = [&]() { s ^= s << 13; s ^= s >> 7; s ^= s << 17; return s; };
+        auto u2f = [](uint32_t u) { float f; memcpy(&f, &u, 4); return f; };
+        const uint64_t mine = n / (uint64_t)omp_get_num_threads();
+        for (uint64_t it = 0; it < mine; it++) {
+            const uint64_t r1 = rng(), r2 = rng();
+            uint32_t mb = (uint32_t)(r1 & 0x7FFFFF);
+            if ((r1 >> 40) % 16 == 0) mb = 0x7FFFFF - (uint32_t)((r1 >> 23) & 7);
+            if ((r1 >> 40) % 16 == 1) mb = (uint32_t)((r1 >> 23) & 7);
+            const uint32_t eb = 127 - 60 + (uint32_t)((r1 >> 44) % 61);  // 2^-60 .. 2^0 (x mantissa < 2)
+            const float b = u2f(((uint32_t)(r1 >> 63) << 31) | (eb << 23) | mb);
+            uint32_t ma = (uint32_t)(r2 & 0x7FFFFF);
+            if ((r2 >> 40) % 16 == 0) ma = 0x7FFFFF - (uint32_t)((r2 >> 23) & 7);
+            if ((r2 >> 40) % 16 == 1) ma = (uint32_t)((r2 >> 23) & 7);
+            const uint32_t ea = 127 - 24 + (uint32_t)((r2 >> 44) % 84);  // 2^-24 .. 2^59
+            const float a = u2f(((uint32_t)(r2 >> 63) << 31) | (ea << 23) | ma);
+            const float y = 1.0f / b;
+            const float q0 = a * y;
+            const float rem = fmaf(-q0, b, a);
+            const float q = fmaf(rem, y, q0);
+            const float ref = a / b;
+            if (memcmp(&q, &ref, 4) != 0) bad++;
+        }
+    }
+    return bad;
+}
+
 }  // extern "C"

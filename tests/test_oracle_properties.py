@@ -120,3 +120,17 @@ def test_rays_into_the_sky_end_out_of_bounds():
     # around voxel 160 reaches 7 voxels past the edge before MAT_OOB is seen (7.5 + 2 x 7.999)
     assert np.allclose(np.sort(r["ldist"][:, 0]), [15.5] * 3 + [23.498] * 3, atol=2e-3)
     assert r["total_iterations"] == 3 * 3 + 3 * 4
+
+
+def test_reciprocal_division_is_the_ieee_quotient():
+    """The CUDA DDA divides by a ray component through its rounded reciprocal + one exact-remainder step
+    (vxb_device.cuh: ray_box_axis_rcp). On the guarded operand range that must be the IEEE quotient, bit
+    for bit — otherwise the kernels would leave the oracle's positions. 64 M biased pseudo-random pairs."""
+    import ctypes
+
+    from tests.oracle_lib import load
+
+    lib = load()
+    lib.orc_reciprocal_division_mismatches.restype = ctypes.c_uint64
+    lib.orc_reciprocal_division_mismatches.argtypes = [ctypes.c_uint64, ctypes.c_uint64]
+    assert lib.orc_reciprocal_division_mismatches(64_000_000, 0x1234ABCD) == 0

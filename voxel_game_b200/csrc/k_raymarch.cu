@@ -57,9 +57,10 @@ __device__ __forceinline__ void cube_bounds(f3 floor_pos, uint32_t dist, f3& v_m
     v_min = floor_pos - mk3(d, d, d);
     v_max = floor_pos + mk3(d1, d1, d1);
 }
-__device__ __forceinline__ f3 box_delta(f3 pos, f3 ray, f3 v_min, f3 v_max) {
-    return f3{ray_box_axis(pos.x, ray.x, v_min.x, v_max.x), ray_box_axis(pos.y, ray.y, v_min.y, v_max.y),
-              ray_box_axis(pos.z, ray.z, v_min.z, v_max.z)};
+__device__ __forceinline__ f3 ray_inverse3(f3 ray) { return f3{ray_inverse(ray.x), ray_inverse(ray.y), ray_inverse(ray.z)}; }
+__device__ __forceinline__ f3 box_delta(f3 pos, f3 ray, f3 inv, f3 v_min, f3 v_max) {
+    return f3{ray_box_axis_rcp(pos.x, ray.x, inv.x, v_min.x, v_max.x), ray_box_axis_rcp(pos.y, ray.y, inv.y, v_min.y, v_max.y),
+              ray_box_axis_rcp(pos.z, ray.z, inv.z, v_min.z, v_max.z)};
 }
 
 // The "snap to the exit face" tail shared by single/simple/los DDAs (e.g. frag.glsl:130-151).
@@ -130,6 +131,7 @@ __device__ uint32_t raycast(const World& w, f3 pos, f3 ray, uint32_t max_iterati
         else layers[idx] = L;
     };
     const uint32_t offset = ray_octant(ray);
+    const f3 ray_inv = ray_inverse3(ray);
     f3 ray_pos = pos;
     f3 normal = -ray;
     float depth = 0;
@@ -168,7 +170,7 @@ __device__ uint32_t raycast(const World& w, f3 pos, f3 ray, uint32_t max_iterati
             layer_idx++;
             break;
         }
-        const f3 delta = box_delta(ray_pos, ray, v_min, v_max);
+        const f3 delta = box_delta(ray_pos, ray, ray_inv, v_min, v_max);
         const float dist_diff = gmin(delta.x, gmin(delta.y, delta.z));
         if (depth + dist_diff > raster_depth && raster_depth > 0) {
             depth = raster_depth;
@@ -229,6 +231,7 @@ __device__ uint32_t raycast(const World& w, f3 pos, f3 ray, uint32_t max_iterati
 // frag.glsl:93-159
 __device__ Layer single_raycast(const World& w, f3 pos, f3 ray, uint32_t max_iterations, uint32_t& iters) {
     const uint32_t offset = ray_octant(ray);
+    const f3 ray_inv = ray_inverse3(ray);
     f3 ray_pos = pos;
     f3 normal = mk3(0, 0, 0);
     float depth = 0;
@@ -251,7 +254,7 @@ __device__ Layer single_raycast(const World& w, f3 pos, f3 ray, uint32_t max_ite
             did_hit = true;
             break;
         }
-        const f3 delta = box_delta(ray_pos, ray, v_min, v_max);
+        const f3 delta = box_delta(ray_pos, ray, ray_inv, v_min, v_max);
         const float dist_diff = gmin(delta.x, gmin(delta.y, delta.z));
         depth += dist_diff;
         ray_pos = ray_pos + ray * dist_diff;
@@ -267,6 +270,7 @@ template <bool W_PROJ>
 __device__ Layer simple_raycast(const World& w, f3 pos, f3 ray, uint32_t max_iterations, const vxb_projectile* projectiles,
                                 uint32_t projectile_count, float& light, uint32_t& iters) {
     const uint32_t offset = ray_octant(ray);
+    const f3 ray_inv = ray_inverse3(ray);
     float passthrough_light = 1.0f;
     f3 ray_pos = pos;
     float depth = 0;
@@ -318,7 +322,7 @@ __device__ Layer simple_raycast(const World& w, f3 pos, f3 ray, uint32_t max_ite
             if (mat_in(MASK_DATA_DISTANCE, voxel_material)) dist = (voxel_data >> (offset * 3)) & 7u;
             cube_bounds(floor_pos, dist, v_min, v_max);
         }
-        const f3 delta = box_delta(ray_pos, ray, v_min, v_max);
+        const f3 delta = box_delta(ray_pos, ray, ray_inv, v_min, v_max);
         const float dist_diff = gmin(delta.x, gmin(delta.y, delta.z));
         depth += dist_diff;
         if (prev_voxel_material != voxel_material) passthrough_light *= material_transparency(voxel_material);

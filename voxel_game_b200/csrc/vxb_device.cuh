@@ -136,6 +136,28 @@ __device__ __forceinline__ float ray_box_axis(float pos, float ray, float vmin, 
     return gmax((vmin - pos) / ray, (vmax - pos) / ray);
 }
 
+// The same quotient without a division per DDA step: the divisor is a ray component, constant for
+// the whole march, so its correctly rounded reciprocal `inv` is taken once (ray_inverse) and each
+// quotient is q0 = a * inv refined by one exact-remainder step: rem = fma(-q0, ray, a),
+// q = fma(rem, inv, q0). With inv = RN(1/ray) and no overflow / underflow on the way this IS RN(a / ray)
+// (Markstein's theorem; checked against the divider on 3.2e9 pairs incl. all-ones / all-zeros mantissas,
+// tests/test_oracle_properties.py holds the CPU version of that check). Outside the guarded range —
+// |ray| not in [2^-60, 2], |a| not in [2^-24, 2^60), zero, inf, NaN — the literal form above is used.
+__device__ __forceinline__ float ray_inverse(float ray) {
+    const uint32_t e = __float_as_uint(ray) & 0x7FFFFFFFu;
+    return (e - 0x21800000u) <= (0x40000000u - 0x21800000u) ? 1.0f / ray : 0.0f;  // 0 marks "use the divider"
+}
+__device__ __forceinline__ float ray_box_axis_rcp(float pos, float ray, float inv, float vmin, float vmax) {
+    const float a = (ray > 0.0f ? vmax : vmin) - pos;
+    const uint32_t ea = __float_as_uint(a) & 0x7FFFFFFFu;
+    if (inv != 0.0f && (ea - 0x33800000u) < (0x5D800000u - 0x33800000u)) {
+        const float q0 = a * inv;
+        const float rem = __fmaf_rn(-q0, ray, a);
+        return __fmaf_rn(rem, inv, q0);
+    }
+    return ray_box_axis(pos, ray, vmin, vmax);
+}
+
 // common.glsl:297-311
 __device__ __forceinline__ void pcg3d(uint32_t& x, uint32_t& y, uint32_t& z) {
     x = x * 1664525u + 1013904223u;
