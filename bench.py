@@ -352,11 +352,167 @@ def run_ours(args):
         if rank == 0:
             result["rays"] = rays
 
+    # ---------------- the remaining points of SURVEY 8(d): C3 natural world, C2 on the control map, C1 ----------------
+    if rank == 0 and world_size == 1 and not args.no_extras:
+        result["natural_world"] = bench_natural_world(args, torch, vg)
+        if not args.no_rays:
+            result["rays"]["control_map"] = bench_rays_control(args, torch, vg)
+        if not args.no_cpu:
+            result["c1"] = bench_c1(args, torch, vg)
+
     if world_size > 1:
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
         OUT.emit(result)
+
+
+def _surface_from_gpu(gpu, table, RS, SP, cx, cz, default=1800):
+    """First non-air voxel from the top of the world column (cx, cz): host scan of one column of chunks."""
+    for cy in range(SP[1] + RS[1] - 1, SP[1] - 1, -1):
+        slot = int(table[(cx >> 4) % RS[0], cy % RS[1], (cz >> 4) % RS[2]])
+        if slot < 2:
+            continue
+        ch = gpu.read_pool(slot, 1)[0].reshape(16, 16, 16)[cx & 15, :, cz & 15] >> 24
+        solid = np.nonzero((ch != 0) & (ch != 9))[0]
+        if solid.size:
+            return 16 * cy + int(solid.max())
+    return default
+
+
+def _loaded_list(table, chunks, RS):
+    loaded = chunks[(table.reshape(-1)[((chunks[:, 0] % RS[0]) * RS[1] + chunks[:, 1] % RS[1]) * RS[2] + chunks[:, 2] % RS[2]]) >= 2]
+    return np.concatenate([loaded, np.zeros((len(loaded), 1), np.int64)], 1).astype(np.uint32)
+
+
+def bench_natural_world(args, torch, vg):
+    """SURVEY 8(d) C3, secondary: the same world generated with forced = false, so all-air chunks collapse to table
+    entry 1 and are not in the work list (voxel_sim_manager.rs:1039); one tick over every LOADED chunk."""
+    RS, SP = tuple(args.world), C3_SP
+    n = RS[0] * RS[1] * RS[2]
+    gs = vg.GameSettings(render_size=RS, max_loaded_chunks=2 + n, max_worldgen_rate=8 * 32768, max_update_rate=1024)
+    gpu = vg.VoxelComputePipeline(gs, device=torch.cuda.current_device())
+    gpu.set_stream(torch.cuda.current_stream().cuda_stream)
+    chunks = chunk_grid(0, RS[0], RS, SP)
+    generate_world(gpu, SP, chunks, 2, False, torch)
+    lst = _loaded_list(gpu.read_table(), chunks, RS)
+    gpu.update_list_upload(lst)
+    gpu.set_update_kernel(args.variant)
+    for i in range(args.settle + 3):
+        gpu.update_list_run(SP, PHASES[i % 8])
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        gpu.update_list_run(SP, PHASES[(3 + i) % 8])
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    gpu.close()
+    return {"metric": "voxel-updates/s", "value": len(lst) * 4096 / (ms / 1e3), "unit": "voxel-updates/s", "ms_per_step": ms,
+            "loaded_chunks": int(len(lst)), "window_chunks": n,
+            "world_rate": {"value": n * 4096 / (ms / 1e3), "unit": "window voxels/s (all-air chunks cost nothing)"},
+            "config": {"workload": "BASELINE configs[2], natural variant: forced = false worldgen, work list = loaded chunks only"}}
+
+
+def bench_rays_control(args, torch, vg):
+    """SURVEY 8(d) C2, second run: the control map (seed 3646) centred on (10000, 1836, 10000), same camera scheme."""
+    from tests import scenes
+
+    RS = C2_RS
+    SP = (10000 // 16 - RS[0] // 2, 1836 // 16 - RS[1] // 2, 10000 // 16 - RS[2] // 2)
+    n = RS[0] * RS[1] * RS[2]
+    gs = vg.GameSettings(render_size=RS, max_loaded_chunks=2 + n, max_worldgen_rate=8 * 32768, max_update_rate=1024,
+                         world_gen=vg.WorldGen.Control, world_gen_seed=3646)
+    gpu = vg.VoxelComputePipeline(gs, device=torch.cuda.current_device())
+    gpu.set_stream(torch.cuda.current_stream().cuda_stream)
+    chunks = chunk_grid(0, RS[0], RS, SP)
+    wg_s, wg_vox = generate_world(gpu, SP, chunks, 2, False, torch)
+    table = gpu.read_table()
+    gpu.update_list_upload(_loaded_list(table, chunks, RS))
+    for t in range(64):
+        gpu.update_list_run(SP, PHASES[t % 8])
+    cx, cz = 10000, 10000
+    col_y = _surface_from_gpu(gpu, table, RS, SP, cx, cz, default=1836)
+    cams = np.concatenate([scenes.camera((cx + 0.5, col_y + 4.5, cz + 0.5), k * np.pi / 4, -0.2) for k in range(8)])
+    W, H = 1920, 1080
+    caps = vg.RayCaps(100, 40, 20, 15, 0)
+    for k in range(3):
+        gpu.raymarch(SP, cams[k:k + 1], W, H, caps)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        gpu.raymarch(SP, cams[i % 8:i % 8 + 1], W, H, caps)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    iters = 0
+    for k in range(8):
+        gpu.raymarch(SP, cams[k:k + 1], W, H, caps)
+        iters += gpu.ray_download()["total_iterations"]
+    gpu.close()
+    return {"metric": "rays/s", "value": W * H / (ms / 1e3), "unit": "rays/s", "ms_per_frame": ms, "mean_iterations_per_ray": iters / 8 / (W * H),
+            "worldgen": {"value": wg_vox / wg_s, "unit": "voxels-generated/s", "map": "control"},
+            "config": {"workload": "BASELINE configs[1], second run: control map seed 3646, 1024x256x1024 voxels, 1920x1080, 8 cameras cycled"}}
+
+
+def bench_c1(args, torch, vg):
+    """BASELINE configs[0] (the reference's own CPU-runnable case): "Practice Range" preset, 8x8x8 chunks =
+    128^3 voxels around (10000, 1820, 10000): worldgen of all 512 chunks, one update tick at phase (1,0,0), one 640x360
+    frame — on the GPU and, beside it, on the oracle with all host threads (the lavapipe run the config asks for is
+    unavailable on this box). The two worlds and frames are compared while at it."""
+    from tests import scenes
+    from tests.oracle_lib import CpuWorld, chunk_loads_for
+
+    RS, SP = (8, 8, 8), (621, 109, 621)
+    n = 512
+    chunks = [(SP[0] + x, SP[1] + y, SP[2] + z) for x in range(8) for y in range(8) for z in range(8)]
+    loads = chunk_loads_for(chunks, range(2, 2 + n))
+    gs = vg.GameSettings(render_size=RS, max_loaded_chunks=2 + n, max_worldgen_rate=8 * n, max_update_rate=n)
+    gpu = vg.VoxelComputePipeline(gs, device=torch.cuda.current_device())
+    gpu.set_stream(torch.cuda.current_stream().cuda_stream)
+    cpu = CpuWorld(RS, SP, 2 + n)
+    W, H = 640, 360
+    caps = vg.RayCaps(100, 40, 20, 15, 0)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
+    gpu.dispatch_worldgen(SP, loads)  # warm-up (module load), then the timed pass on a fresh table
+    gpu.write_table(np.zeros(RS, np.uint32))
+    ev[0].record()
+    gpu.dispatch_worldgen(SP, loads, want_results=False)
+    ev[1].record()
+    torch.cuda.synchronize()
+    table = gpu.read_table()
+    loaded = [c for c in chunks if table[c[0] % 8, c[1] % 8, c[2] % 8] >= 2]
+    lst = scenes.update_list(loaded)
+    gpu.update_list_upload(lst)
+    ev[2].record()
+    gpu.update_list_run(SP, (1, 0, 0))
+    ev[3].record()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    cpu.worldgen(loads, 0)
+    t1 = time.perf_counter()
+    cpu.voxel_update(lst, (1, 0, 0))
+    t2 = time.perf_counter()
+    same_world = bool(np.array_equal(cpu.table, gpu.read_table()) and np.array_equal(cpu.pool, gpu.read_pool(0, 2 + n)))
+    cx, cz = 10000, 10000
+    sy = _surface_from_gpu(gpu, gpu.read_table(), RS, SP, cx, cz, default=1820)
+    cam = scenes.camera((cx + 0.5, sy + 4.5, cz + 0.5), 0.0, -0.2)
+    gpu.raymarch(SP, cam, W, H, caps)
+    ev[4].record()
+    gpu.raymarch(SP, cam, W, H, caps)
+    ev[5].record()
+    torch.cuda.synchronize()
+    g = gpu.ray_download()
+    t3 = time.perf_counter()
+    c = cpu.raycast_image(cam, W, H, 100)
+    t4 = time.perf_counter()
+    same_frame = bool(np.array_equal(g["layer_count"], c["layer_count"]))
+    out = {"config": {"workload": "BASELINE configs[0]: 8x8x8-chunk Practice Range world: worldgen of 512 chunks + one tick at phase (1,0,0) + one 640x360 frame"},
+           "gpu_ms": {"worldgen": ev[0].elapsed_time(ev[1]), "tick": ev[2].elapsed_time(ev[3]), "frame": ev[4].elapsed_time(ev[5])},
+           "cpu_ms": {"worldgen": (t1 - t0) * 1e3, "tick": (t2 - t1) * 1e3, "frame": (t4 - t3) * 1e3, "cores": int(cpu.lib.orc_num_threads()), "kind": "port"},
+           "loaded_chunks": len(loaded), "world_equals_oracle": same_world, "frame_layer_counts_equal_oracle": same_frame}
+    gpu.close()
+    return out
 
 
 def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp, chunks, exchange, main, side):
@@ -776,6 +932,7 @@ def main():
     ap.add_argument("--no-collisions", action="store_true")
     ap.add_argument("--tick", action="store_true", help="also run BASELINE configs[4], the full tick (default on at 8 GPUs)")
     ap.add_argument("--no-tick", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the natural-world, control-map and config-1 measurements")
     ap.add_argument("--projectiles", type=int, default=1 << 20)
     ap.add_argument("--cpu-sample-cols", type=int, default=4)
     args = ap.parse_args()
