@@ -727,10 +727,41 @@ def bench_rays(args, torch, vg, peak, rank=0, world_size=1, dist=None):
     shaded = {"metric": "shaded pixels/s", "value": W * H / (shade_ms / 1e3), "unit": "pixels/s", "ms_per_frame": shade_ms,
               "dda_iterations_per_pixel": shaded_iters / (W * H),
               "config": {"workload": "frag.glsl main (primary DDA + get_color) at 1920x1080 on the config-2 world, caps 100/40/20/15"}}
+    # player-mesh G-buffer pass: 63 instances of a 100-triangle capsule (player.obj has 124) on the 8x8 player grid of
+    # config 4, the camera being player 0; then the max_depth pass and one primary-ray frame that reads the G-buffer
+    mesh_p, mesh_n = scenes.capsule_mesh()
+    rast = vg.RasterizerSystem(gpu, mesh_p, mesh_n)
+    grid = scenes.players_grid(8, (cx, col_y, cz), 48.0, col_y + 4.0, seed=64)
+    cam0 = cams[0:1].copy()
+    grid["pos"][0] = cam0["pos"][0]
+    cam_pos = cam0["pos"][0, :3]
+    view_r = np.linalg.inv((vg.translation(-cam_pos) @ vg.quat_to_mat4((0, 0, 0, 1))).astype(np.float64)).astype(np.float32)
+    s2w = np.linalg.inv((vg.perspective(np.pi / 2, 1.0, 0.1, 200.0) @ np.linalg.inv(vg.translation(cam_pos).astype(np.float64)).astype(np.float32)).astype(np.float64)).astype(np.float32)
+    inst = rast.instances(grid)
+    for k in range(3):
+        gpu.raster_draw(W, H, view_r, inst)
+        gpu.raster_max_depth(s2w, W / H, cam_pos)
+    g0, g1, g2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+    g0.record()
+    for i in range(args.steps):
+        gpu.raster_draw(W, H, view_r, inst)
+        gpu.raster_max_depth(s2w, W / H, cam_pos)
+    g1.record()
+    gpu.raster_bind(True)
+    for i in range(args.steps):
+        gpu.raymarch(SP, cam0, W, H, caps)
+    g2.record()
+    torch.cuda.synchronize()
+    gpu.raster_bind(False)
+    covered = float((gpu.raster_download(want_max_depth=False)["depth"] < 1.0).mean())
+    raster = {"metric": "G-buffer frames/s", "value": 1e3 * args.steps / g0.elapsed_time(g1), "unit": "frames/s",
+              "ms_per_frame": g0.elapsed_time(g1) / args.steps, "primary_rays_with_gbuffer_ms": g1.elapsed_time(g2) / args.steps,
+              "instances": int(inst.size), "triangles_per_instance": int(mesh_p.shape[0] // 3), "covered_fraction": covered,
+              "config": {"workload": "RasterizerSystem::draw + max_depth at 1920x1080 (host instance upload included), then primary rays reading the G-buffer"}}
     collisions = None if args.no_collisions else bench_collisions(args, torch, vg, gpu, SP, RS, (cx, col_y, cz), peak)
     gpu.close()
     achieved = alg_bytes / (ms / args.steps / 1e3) / 1e9
-    return {"batch8": batch8, "collisions": collisions, "shaded_frame": shaded,"metric": "rays/s", "value": W * H * args.steps / (ms / 1e3), "unit": "rays/s", "ms_per_frame": ms / args.steps,
+    return {"batch8": batch8, "collisions": collisions, "shaded_frame": shaded, "raster": raster,"metric": "rays/s", "value": W * H * args.steps / (ms / 1e3), "unit": "rays/s", "ms_per_frame": ms / args.steps,
             "config": {"workload": "BASELINE configs[1]: 1920x1080 primary-ray DDA, 1024x256x1024-voxel open-world map, 8 cameras cycled",
                        "primary_ray_dist": 100},
             "mean_iterations_per_ray": mean_iters / (W * H), "mean_layers_per_ray": mean_layers / (W * H),

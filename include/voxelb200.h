@@ -124,6 +124,13 @@ typedef struct vxb_ray_buffers {
 } vxb_ray_buffers;
 
 /* chunks()/voxels()/projectiles()/players(), src/voxel_sim_manager.rs:537-543,650-656 */
+/* One instance of the player mesh: ProjectileInstanceData (client/src/rasterizer.rs:52-60), 40 bytes. */
+typedef struct vxb_raster_instance {
+    float position[3]; /* player.pos + PLAYER_HITBOX_OFFSET * size (:224-228) */
+    float rotation[4]; /* quaternion (x, y, z, w) about +y by facing[0] (:229-236) */
+    float scale[3];    /* (size, size, size) (:237-238) */
+} vxb_raster_instance;
+
 typedef struct vxb_ptrs {
     uint32_t* chunk_table; /* render_size x*y*z u32, index (x*ry + y)*rz + z; 0 unloaded, 1 all-air, >=2 slot */
     uint32_t* voxel_pool;  /* [slot][4096], in-chunk index x*256 + y*16 + z (common.glsl:247) */
@@ -288,6 +295,32 @@ int vxb_raymarch(vxb_ctx* ctx, const uint32_t start_pos[3], const vxb_player* ca
  * Asynchronous. raster_depth as in vxb_raymarch. */
 int vxb_render(vxb_ctx* ctx, const uint32_t start_pos[3], const vxb_player* cams, uint32_t n_views, uint32_t w, uint32_t h,
                const vxb_ray_caps* caps, float time, const float* raster_depth);
+/* ---- the player-mesh G-buffer pass (client/src/rasterizer.rs, the Deferred pass of main.rs:609-624) ----
+ * Rasterisation written as CUDA kernels; there is no graphics API underneath. The reference leaves
+ * coverage / clipping / interpolation to the Vulkan implementation; the rules used here (pixel centres,
+ * top-left rule, per-pixel clip 0 <= z <= 1, depth as float32, normals through float16, LESS with the
+ * first-drawn primitive winning ties) are written down in DESIGN.md section 4.5.
+ *   vxb_raster_set_mesh   load_obj_to_vecs (:326-361): the triangle list of player.obj, positions and
+ *                         normals per vertex (3 vertices per triangle). The caller loads the file.
+ *   vxb_raster_draw       RasterizerSystem::draw (:196-323): clears the attachments (diffuse 0, normals 0,
+ *                         depth 1.0; multipass_system.rs:372-376) and draws every instance with the vertex /
+ *                         fragment shaders of :363-420, projection cgmath::perspective(pi/2, w/h, 0.1, 200).
+ *                         view_matrix: column-major, as the caller builds it (main.rs:614-617).
+ *   vxb_raster_max_depth  frag.glsl:716-728: turns the depth attachment into the per-pixel ray length limit
+ *                         (screen_to_world = inverse of proj * view as the caller builds it, main.rs:481,604;
+ *                         aspect_ratio and cam_pos as in the push constants / players[0]).
+ *   vxb_raster_bind       enable != 0: vxb_raymarch / vxb_render called with raster_depth == NULL, one view
+ *                         and the G-buffer's size read max_depth, u_normals and u_diffuse from it
+ *                         (frag.glsl:428-437, 725-728).
+ *   vxb_raster_download   host copies of depth [w*h], normals [w*h][3], diffuse.x [w*h], max_depth [w*h]
+ *                         (each nullable). */
+int vxb_raster_set_mesh(vxb_ctx* ctx, const float (*positions)[3], const float (*normals)[3], uint32_t n_vertices);
+int vxb_raster_draw(vxb_ctx* ctx, uint32_t width, uint32_t height, const float view_matrix[16], const vxb_raster_instance* instances,
+                    uint32_t n_instances);
+int vxb_raster_max_depth(vxb_ctx* ctx, const float screen_to_world[16], float aspect_ratio, const float cam_pos[3]);
+int vxb_raster_bind(vxb_ctx* ctx, int enable);
+int vxb_raster_download(vxb_ctx* ctx, float* depth, float* normal, float* diffuse_x, float* max_depth);
+
 /* Synchronises and copies the last vxb_render result to a HOST array of n_pixels * 4 floats. */
 int vxb_color_download(vxb_ctx* ctx, float* rgba_out, uint64_t n_pixels);
 /* Device pointer and pixel count of the colour buffer (borrowed; valid until the next vxb_render that grows it). */

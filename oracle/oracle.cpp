@@ -13,6 +13,7 @@
 #include "common.h"
 #include "compute_voxel.h"
 #include "entities.h"
+#include "raster.h"
 #include "raycast.h"
 #include "shading.h"
 #include "worldgen.h"
@@ -126,10 +127,10 @@ static void store_result(const frag::RaycastResult& r, uint64_t i, float* layer_
 
 // frag.glsl:main ray set-up + raycast() for every pixel of a w x h viewport (row-major, i = py*w + px).
 // raster_depth: null (=> 0 everywhere) or [w*h] max_depth values.
-void orc_raycast_image(uint32_t* chunks, uint32_t* voxels, const SimData* sim, const Player* cam, uint32_t w, uint32_t h,
-                       uint32_t max_iterations, const Projectile* projectiles, const float* raster_depth, float* layer_pos,
-                       float* layer_normal, uint32_t* layer_voxel, float* layer_dist, uint32_t* layer_leaving,
-                       uint32_t* layer_count, float* dist, uint64_t* total_iters) {
+static void raycast_image_impl(uint32_t* chunks, uint32_t* voxels, const SimData* sim, const Player* cam, uint32_t w, uint32_t h,
+                               uint32_t max_iterations, const Projectile* projectiles, const float* raster_depth, const float* raster_normal,
+                               const float* raster_diffuse_x, float* layer_pos, float* layer_normal, uint32_t* layer_voxel, float* layer_dist,
+                               uint32_t* layer_leaving, uint32_t* layer_count, float* dist, uint64_t* total_iters) {
     float aspect_ratio = (float)w / (float)h;  // raytracer.rs:246
     uint64_t iters_sum = 0;
 #pragma omp parallel for schedule(dynamic, 4) reduction(+ : iters_sum)
@@ -141,28 +142,76 @@ void orc_raycast_image(uint32_t* chunks, uint32_t* voxels, const SimData* sim, c
             vec3 ray = frag::primary_ray_dir(*cam, aspect_ratio, px, (uint32_t)py, w, h);
             vec3 pos = cam->pos.xyz();
             float max_depth = raster_depth ? raster_depth[i] : 0.0f;
-            frag::RaycastResult r = frag::raycast(e, pos, ray, max_iterations, true, max_depth, vec3(0.0f, 1.0f, 0.0f), 1.0f);
+            const vec3 rn = raster_normal ? vec3(raster_normal[3 * i], raster_normal[3 * i + 1], raster_normal[3 * i + 2]) : vec3(0.0f, 1.0f, 0.0f);
+            const float rd = raster_diffuse_x ? raster_diffuse_x[i] : 1.0f;
+            frag::RaycastResult r = frag::raycast(e, pos, ray, max_iterations, true, max_depth, rn, rd);
             store_result(r, i, layer_pos, layer_normal, layer_voxel, layer_dist, layer_leaving, layer_count, dist);
         }
         iters_sum += iters;
     }
     if (total_iters) *total_iters = iters_sum;
 }
+void orc_raycast_image(uint32_t* chunks, uint32_t* voxels, const SimData* sim, const Player* cam, uint32_t w, uint32_t h,
+                       uint32_t max_iterations, const Projectile* projectiles, const float* raster_depth, float* layer_pos,
+                       float* layer_normal, uint32_t* layer_voxel, float* layer_dist, uint32_t* layer_leaving,
+                       uint32_t* layer_count, float* dist, uint64_t* total_iters) {
+    raycast_image_impl(chunks, voxels, sim, cam, w, h, max_iterations, projectiles, raster_depth, nullptr, nullptr, layer_pos, layer_normal,
+                       layer_voxel, layer_dist, layer_leaving, layer_count, dist, total_iters);
+}
+// the same with the rasterised G-buffer (u_normals rgb [w*h][3], u_diffuse.x [w*h]) read per pixel (frag.glsl:428-437)
+void orc_raycast_image_gbuffer(uint32_t* chunks, uint32_t* voxels, const SimData* sim, const Player* cam, uint32_t w, uint32_t h,
+                               uint32_t max_iterations, const Projectile* projectiles, const float* raster_depth, const float* raster_normal,
+                               const float* raster_diffuse_x, float* layer_pos, float* layer_normal, uint32_t* layer_voxel, float* layer_dist,
+                               uint32_t* layer_leaving, uint32_t* layer_count, float* dist, uint64_t* total_iters) {
+    raycast_image_impl(chunks, voxels, sim, cam, w, h, max_iterations, projectiles, raster_depth, raster_normal, raster_diffuse_x, layer_pos,
+                       layer_normal, layer_voxel, layer_dist, layer_leaving, layer_count, dist, total_iters);
+}
 
 // frag.glsl:main for every pixel: primary DDA + get_color. out_rgba [w*h][4]. caps = {primary, shadow, reflection, ao}.
-void orc_render_image(uint32_t* chunks, uint32_t* voxels, const SimData* sim, const Player* cam, uint32_t w, uint32_t h, const uint32_t* caps,
-                      float time, const Projectile* projectiles, const float* raster_depth, float* out_rgba) {
+static void render_image_impl(uint32_t* chunks, uint32_t* voxels, const SimData* sim, const Player* cam, uint32_t w, uint32_t h, const uint32_t* caps,
+                              float time, const Projectile* projectiles, const float* raster_depth, const float* raster_normal,
+                              const float* raster_diffuse_x, float* out_rgba) {
     float aspect_ratio = (float)w / (float)h;
 #pragma omp parallel for schedule(dynamic, 2)
     for (int64_t py = 0; py < (int64_t)h; py++) {
         frag::ShadeEnv e{frag::Env{Images{chunks, voxels}, *sim, projectiles, nullptr}, time, caps[0], caps[1], caps[2], caps[3], h};
         for (uint32_t px = 0; px < w; px++) {
             uint64_t i = (uint64_t)py * w + px;
-            vec4 c = frag::shade_pixel(e, *cam, aspect_ratio, px, (uint32_t)py, w, h, raster_depth ? raster_depth[i] : 0.0f);
+            const vec3 rn = raster_normal ? vec3(raster_normal[3 * i], raster_normal[3 * i + 1], raster_normal[3 * i + 2]) : vec3(0.0f, 1.0f, 0.0f);
+            vec4 c = frag::shade_pixel(e, *cam, aspect_ratio, px, (uint32_t)py, w, h, raster_depth ? raster_depth[i] : 0.0f, rn,
+                                       raster_diffuse_x ? raster_diffuse_x[i] : 1.0f);
             out_rgba[4 * i + 0] = c.x; out_rgba[4 * i + 1] = c.y; out_rgba[4 * i + 2] = c.z; out_rgba[4 * i + 3] = c.w;
         }
     }
 }
+void orc_render_image(uint32_t* chunks, uint32_t* voxels, const SimData* sim, const Player* cam, uint32_t w, uint32_t h, const uint32_t* caps,
+                      float time, const Projectile* projectiles, const float* raster_depth, float* out_rgba) {
+    render_image_impl(chunks, voxels, sim, cam, w, h, caps, time, projectiles, raster_depth, nullptr, nullptr, out_rgba);
+}
+void orc_render_image_gbuffer(uint32_t* chunks, uint32_t* voxels, const SimData* sim, const Player* cam, uint32_t w, uint32_t h,
+                              const uint32_t* caps, float time, const Projectile* projectiles, const float* raster_depth,
+                              const float* raster_normal, const float* raster_diffuse_x, float* out_rgba) {
+    render_image_impl(chunks, voxels, sim, cam, w, h, caps, time, projectiles, raster_depth, raster_normal, raster_diffuse_x, out_rgba);
+}
+
+// ---- player-mesh G-buffer pass (rasterizer.rs draw + frag.glsl:716-728), see raster.h ----
+// positions / normals: [n_vertices][3] triangle list; instances: [n_instances] x 10 floats; outputs [w*h], [w*h][3], [w*h]
+void orc_raster_draw(uint32_t w, uint32_t h, const float* view, const float* positions, const float* normals, uint32_t n_vertices,
+                     const float* instances, uint32_t n_instances, float* depth_out, float* normal_out, float* diffuse_x_out) {
+    raster::GBuffer g;
+    raster::draw(g, w, h, view, positions, normals, n_vertices, reinterpret_cast<const raster::Instance*>(instances), n_instances);
+    memcpy(depth_out, g.depth.data(), g.depth.size() * 4);
+    memcpy(normal_out, g.normal.data(), g.normal.size() * 4);
+    memcpy(diffuse_x_out, g.diffuse_x.data(), g.diffuse_x.size() * 4);
+}
+void orc_raster_max_depth(uint32_t w, uint32_t h, const float* depth, const float* screen_to_world, float aspect_ratio, const float* cam_pos,
+                          float* out) {
+    raster::GBuffer g;
+    g.w = w; g.h = h;
+    g.depth.assign(depth, depth + (size_t)w * h);
+    raster::max_depth(g, screen_to_world, aspect_ratio, cam_pos, out);
+}
+void orc_raster_perspective(float fovy, float aspect, float near_, float far_, float* m) { raster::perspective(fovy, aspect, near_, far_, m); }
 
 // Arbitrary ray batch through raycast(): pos/ray are [n][3].
 void orc_raycast_batch(uint32_t* chunks, uint32_t* voxels, const SimData* sim, const float* pos, const float* ray, uint64_t n,

@@ -315,10 +315,11 @@ static inline vec3 get_color(const ShadeEnv& e, vec3 pos, vec3 ray, const Raycas
 }
 
 // frag.glsl:715-741 for one pixel; returns f_color
-static inline vec4 shade_pixel(const ShadeEnv& e, const Player& cam_data, float aspect_ratio, uint px, uint py, uint w, uint h, float max_depth) {
+static inline vec4 shade_pixel(const ShadeEnv& e, const Player& cam_data, float aspect_ratio, uint px, uint py, uint w, uint h, float max_depth,
+                               vec3 raster_normal = vec3(0.0f, 1.0f, 0.0f), float raster_diffuse_x = 1.0f) {
     vec3 ray = primary_ray_dir(cam_data, aspect_ratio, px, py, w, h);
     vec3 pos = cam_data.pos.xyz();
-    RaycastResult primary_ray = raycast(e.dda, pos, ray, e.dda_primary_ray_dist(), true, max_depth, vec3(0.0f, 1.0f, 0.0f), 1.0f);
+    RaycastResult primary_ray = raycast(e.dda, pos, ray, e.dda_primary_ray_dist(), true, max_depth, raster_normal, raster_diffuse_x);
     if (primary_ray.layer_count == 0) {
         return vec4(1.0f, 0.0f, 0.0f, 1.0f);
     }

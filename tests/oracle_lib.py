@@ -127,20 +127,28 @@ class CpuWorld:
                     ldist=np.zeros((n, 5), np.float32), leaving=np.zeros((n, 5), np.uint32), layer_count=np.zeros(n, np.uint32),
                     dist=np.zeros(n, np.float32))
 
-    def raycast_image(self, cam, w, h, max_iterations, projectiles=None, raster_depth=None):
+    def raycast_image(self, cam, w, h, max_iterations, projectiles=None, raster_depth=None, raster_normal=None, raster_diffuse_x=None):
         cam = np.ascontiguousarray(cam, dtype=PLAYER_DTYPE).reshape(-1)[:1]
         pr = None if projectiles is None else np.ascontiguousarray(projectiles, dtype=PROJECTILE_DTYPE)
         s = self.sim(projectile_count=0 if pr is None else pr.size)
         o = self._ray_out(w * h)
         it = u64(0)
         rd = None if raster_depth is None else np.ascontiguousarray(raster_depth, np.float32)
-        self.lib.orc_raycast_image(p(self.table), p(self.pool), ctypes.byref(s), p(cam), u32(w), u32(h), u32(max_iterations), p(pr), p(rd),
-                                   p(o["pos"]), p(o["normal"]), p(o["voxel"]), p(o["ldist"]), p(o["leaving"]), p(o["layer_count"]),
-                                   p(o["dist"]), ctypes.byref(it))
+        if raster_normal is not None:
+            rn = np.ascontiguousarray(raster_normal, np.float32)
+            rx = np.ascontiguousarray(raster_diffuse_x, np.float32)
+            self.lib.orc_raycast_image_gbuffer(p(self.table), p(self.pool), ctypes.byref(s), p(cam), u32(w), u32(h), u32(max_iterations), p(pr),
+                                               p(rd), p(rn), p(rx), p(o["pos"]), p(o["normal"]), p(o["voxel"]), p(o["ldist"]), p(o["leaving"]),
+                                               p(o["layer_count"]), p(o["dist"]), ctypes.byref(it))
+        else:
+            self.lib.orc_raycast_image(p(self.table), p(self.pool), ctypes.byref(s), p(cam), u32(w), u32(h), u32(max_iterations), p(pr), p(rd),
+                                       p(o["pos"]), p(o["normal"]), p(o["voxel"]), p(o["ldist"]), p(o["leaving"]), p(o["layer_count"]),
+                                       p(o["dist"]), ctypes.byref(it))
         o["total_iterations"] = int(it.value)
         return o
 
-    def render_image(self, cam, w, h, caps=(100, 40, 20, 15), time=0.0, projectiles=None, raster_depth=None):
+    def render_image(self, cam, w, h, caps=(100, 40, 20, 15), time=0.0, projectiles=None, raster_depth=None, raster_normal=None,
+                     raster_diffuse_x=None):
         """frag.glsl main for every pixel (primary DDA + get_color) -> float32 [h, w, 4]."""
         cam = np.ascontiguousarray(cam, dtype=PLAYER_DTYPE).reshape(-1)[:1]
         pr = None if projectiles is None else np.ascontiguousarray(projectiles, dtype=PROJECTILE_DTYPE)
@@ -148,7 +156,13 @@ class CpuWorld:
         out = np.zeros((h, w, 4), np.float32)
         capsa = np.asarray(caps, np.uint32)
         rd = None if raster_depth is None else np.ascontiguousarray(raster_depth, np.float32)
-        self.lib.orc_render_image(p(self.table), p(self.pool), ctypes.byref(s), p(cam), u32(w), u32(h), p(capsa), f32(time), p(pr), p(rd), p(out))
+        if raster_normal is not None:
+            rn = np.ascontiguousarray(raster_normal, np.float32)
+            rx = np.ascontiguousarray(raster_diffuse_x, np.float32)
+            self.lib.orc_render_image_gbuffer(p(self.table), p(self.pool), ctypes.byref(s), p(cam), u32(w), u32(h), p(capsa), f32(time), p(pr),
+                                              p(rd), p(rn), p(rx), p(out))
+        else:
+            self.lib.orc_render_image(p(self.table), p(self.pool), ctypes.byref(s), p(cam), u32(w), u32(h), p(capsa), f32(time), p(pr), p(rd), p(out))
         return out
 
     def raycast_batch(self, pos, ray, max_iterations, projectiles=None):
@@ -233,3 +247,27 @@ def chunk_loads_for(chunks, slots, forced=False):
                 for k in range(2):
                     out.append((2 * cx + i, 2 * cy + j, 2 * cz + k, -slot if forced else slot))
     return np.asarray(out, np.int32)
+
+
+def raster_draw(w, h, view_matrix, positions, normals, instances):
+    """oracle/raster.h draw: view_matrix 4x4 in math layout. -> dict(depth [h,w], normal [h,w,3], diffuse_x [h,w])"""
+    lib = load()
+    view = np.ascontiguousarray(np.asarray(view_matrix, np.float32).reshape(4, 4).T)
+    pos = np.ascontiguousarray(np.asarray(positions, np.float32).reshape(-1, 3))
+    nrm = np.ascontiguousarray(np.asarray(normals, np.float32).reshape(-1, 3))
+    inst = np.ascontiguousarray(instances).reshape(-1)
+    out = {"depth": np.zeros((h, w), np.float32), "normal": np.zeros((h, w, 3), np.float32), "diffuse_x": np.zeros((h, w), np.float32)}
+    lib.orc_raster_draw(u32(w), u32(h), p(view), p(pos), p(nrm), u32(pos.shape[0]), p(inst) if inst.size else None, u32(inst.size),
+                        p(out["depth"]), p(out["normal"]), p(out["diffuse_x"]))
+    return out
+
+
+def raster_max_depth(depth, screen_to_world, aspect_ratio, cam_pos):
+    lib = load()
+    d = np.ascontiguousarray(depth, np.float32)
+    h, w = d.shape
+    m = np.ascontiguousarray(np.asarray(screen_to_world, np.float32).reshape(4, 4).T)
+    cp = np.ascontiguousarray(np.asarray(cam_pos, np.float32).reshape(-1)[:3])
+    out = np.zeros((h, w), np.float32)
+    lib.orc_raster_max_depth(u32(w), u32(h), p(d), p(m), f32(aspect_ratio), p(cp), p(out))
+    return out

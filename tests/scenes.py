@@ -149,3 +149,36 @@ def players_grid(n_side, center, spacing, y, seed, size=1.0):
     pl["gravity"][:] = (0, -1, 0)
     pl["has_world_collision"] = 1
     return pl
+
+
+def capsule_mesh(n_seg=10, n_ring=6, radius=0.9, half_height=1.6):
+    """A closed capsule-like triangle list around the origin (stand-in for player.obj, which is an asset of the
+    reference and is not copied): positions and normals per vertex, 3 vertices per triangle."""
+    rings = []
+    for r in range(n_ring + 1):
+        t = np.pi * r / n_ring  # 0 = top pole, pi = bottom pole
+        y = np.cos(t) * radius + (half_height if t < np.pi / 2 else -half_height)
+        rad = np.sin(t) * radius
+        rings.append([(rad * np.cos(2 * np.pi * s / n_seg), y, rad * np.sin(2 * np.pi * s / n_seg)) for s in range(n_seg)])
+    rings = np.asarray(rings, np.float32)
+    pos, nrm = [], []
+
+    def normal_of(v):
+        c = np.array([0.0, half_height if v[1] > 0 else -half_height, 0.0], np.float32)
+        d = v - c
+        if abs(v[1]) < half_height:
+            d = np.array([v[0], 0.0, v[2]], np.float32)
+        n = np.linalg.norm(d)
+        return (d / n if n > 0 else np.array([0, 1, 0])).astype(np.float32)
+
+    for r in range(n_ring):
+        for s in range(n_seg):
+            a, b = rings[r, s], rings[r, (s + 1) % n_seg]
+            c, d = rings[r + 1, s], rings[r + 1, (s + 1) % n_seg]
+            for tri in ((a, c, b), (b, c, d)):
+                if np.allclose(tri[0], tri[1]) or np.allclose(tri[1], tri[2]) or np.allclose(tri[0], tri[2]):
+                    continue
+                for v in tri:
+                    pos.append(v)
+                    nrm.append(normal_of(v))
+    return np.asarray(pos, np.float32), np.asarray(nrm, np.float32)

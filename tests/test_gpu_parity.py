@@ -519,3 +519,105 @@ def test_render_full_fragment_shader(world_gen, seed, yaw, pitch, t):
     assert close.mean() > 0.999, "only %.4f of the pixels agree" % close.mean()
     assert c[..., :3].std() > 0.02  # a real picture, not a constant
     gpu.close()
+
+
+def _raster_scene(w, h, yaw_cam=0.3):
+    """Camera matrices the way main.rs builds them (:473-481, :614-617) and a ring of players around it."""
+    import voxel_game_b200 as vg
+
+    cam_pos = np.array([10000.5, 1830.0, 10000.5], np.float32)
+    half = np.float32(yaw_cam / 2)
+    cam_rot = np.array([0.0, np.sin(half), 0.0, np.cos(half)], np.float32)
+    view_raster = np.linalg.inv((vg.translation(-cam_pos) @ vg.quat_to_mat4(cam_rot)).astype(np.float64)).astype(np.float32)
+    view_frame = np.linalg.inv((vg.translation(cam_pos) @ vg.quat_to_mat4(cam_rot)).astype(np.float64)).astype(np.float32)
+    proj_frame = vg.perspective(np.pi / 2, 1.0, 0.1, 200.0)
+    screen_to_world = np.linalg.inv((proj_frame @ view_frame).astype(np.float64)).astype(np.float32)
+    players = np.zeros(14, vg.PLAYER_DTYPE)
+    players["size"] = 1.0
+    players["pos"][0, :3] = cam_pos
+    rng = np.random.RandomState(8)
+    for i in range(1, 14):
+        ang = 2 * np.pi * i / 13
+        dist = 2.5 + 9.0 * rng.rand()  # some fill a good part of the view, one or two cross the near plane
+        # the rasteriser works in the reference's mirrored space (vertex - instance_position): place instances so
+        # that they land in front of the camera either way
+        players["pos"][i, :3] = cam_pos + np.array([np.sin(ang) * dist, rng.rand() * 4 - 1, np.cos(ang) * dist], np.float32)
+        players["size"][i] = 0.6 + rng.rand()
+    players["pos"][13, :3] = cam_pos + np.array([1.1, 1.2, 0.9], np.float32)  # close: its triangles cross the near plane
+    players["size"][13] = 0.5
+    facing = rng.rand(14).astype(np.float32) * 6.28
+    health = np.ones(14, np.float32)
+    health[5] = 0.0
+    return cam_pos, view_raster, screen_to_world, players, facing, health
+
+
+@pytest.mark.parametrize("w,h", [(160, 90), (97, 131)])
+def test_raster_gbuffer_matches_the_oracle(w, h):
+    """RasterizerSystem::draw as CUDA kernels against oracle/raster.h: depth, normals (through float16), diffuse
+    and the ray pass's max_depth (frag.glsl:716-728), bit for bit, on a capsule mesh instanced around the camera."""
+    import voxel_game_b200 as vg
+    from tests import oracle_lib
+
+    gpu, _ = make_pair((2, 2, 2), (100, 50, 70), 2 + 8)
+    pos, nrm = scenes.capsule_mesh()
+    rs = vg.RasterizerSystem(gpu, pos, nrm)
+    cam_pos, view, s2w, players, facing, health = _raster_scene(w, h)
+    inst = rs.instances(players, facing, health)
+    assert inst.size == 12  # player 0 (the camera) and the dead one are skipped
+    rs.draw((w, h), view, players, facing, health)
+    gpu.raster_max_depth(s2w, w / h, cam_pos)
+    g = gpu.raster_download()
+    c = oracle_lib.raster_draw(w, h, view, pos, nrm, inst)
+    covered = c["depth"] < 1.0
+    assert 0.02 < covered.mean() < 0.9, covered.mean()
+    assert np.array_equal(g["depth"].view(np.uint32), c["depth"].view(np.uint32))
+    assert np.array_equal(g["diffuse_x"], c["diffuse_x"])
+    assert np.array_equal(g["normal"].view(np.uint32), c["normal"].view(np.uint32))
+    cm = oracle_lib.raster_max_depth(c["depth"], s2w, w / h, cam_pos)
+    assert np.array_equal(g["max_depth"].view(np.uint32), cm.view(np.uint32))
+    assert (cm[covered] > 0).all() and (cm[~covered] == 0).all()
+    # an empty draw leaves the clear values
+    rs.draw((w, h), view, players[:1])
+    e = gpu.raster_download(want_max_depth=False)
+    assert (e["depth"] == 1.0).all() and (e["normal"] == 0).all() and (e["diffuse_x"] == 0).all()
+    gpu.close()
+
+
+def test_ray_pass_reads_the_gbuffer():
+    """frag.glsl:428-437, 725-728: with the G-buffer bound, the primary ray stops at the rasterised depth and the
+    extra layer carries the rasterised normal and MAT_PLAYER; layers equal the oracle's fed with the same G-buffer."""
+    import voxel_game_b200 as vg
+    from tests import oracle_lib
+
+    rs_, center = (6, 4, 6), (10000, 1820, 10000)
+    sp = vg.initial_start_pos(center, rs_)
+    gpu, cpu = _generated_world(rs_, sp, 0, 0, update_ticks=8)
+    w, h = 128, 72
+    pos, nrm = scenes.capsule_mesh()
+    rast = vg.RasterizerSystem(gpu, pos, nrm)
+    cam_pos, view, s2w, players, facing, health = _raster_scene(w, h)
+    sy = _surface_y(cpu, center[0], center[2], 16 * (sp[1] + rs_[1]) - 1)
+    shift = np.array([0, sy + 6 - cam_pos[1], 0], np.float32)
+    players["pos"][:, :3] += shift
+    cam_pos = cam_pos + shift
+    cam = scenes.camera(tuple(cam_pos), 0.3, -0.1)
+    view = np.linalg.inv((vg.translation(-cam_pos) @ vg.quat_to_mat4((0, np.sin(0.15), 0, np.cos(0.15)))).astype(np.float64)).astype(np.float32)
+    rast.draw((w, h), view, players, facing, health)
+    gpu.raster_max_depth(s2w, w / h, cam_pos)
+    gpu.raster_bind(True)
+    caps = vg.RayCaps(100, 40, 20, 15, 0)
+    gpu.raymarch(sp, cam, w, h, caps)
+    g = gpu.ray_download()
+    gb = gpu.raster_download()
+    c = cpu.raycast_image(cam, w, h, 100, raster_depth=gb["max_depth"], raster_normal=gb["normal"], raster_diffuse_x=gb["diffuse_x"])
+    _compare_layers(g, c, w * h)
+    player_layers = (c["voxel"] >> 24) == 8
+    assert player_layers.any()
+    # and the shaded frame
+    gpu.render(sp, cam, w, h, caps, time=0.5)
+    col = gpu.color_download().reshape(h, w, 4)
+    ref = cpu.render_image(cam, w, h, (100, 40, 20, 15), 0.5, raster_depth=gb["max_depth"], raster_normal=gb["normal"], raster_diffuse_x=gb["diffuse_x"])
+    close = np.isclose(col, ref, rtol=1e-4, atol=1e-4).all(axis=2)
+    assert close.mean() > 0.999, close.mean()
+    gpu.raster_bind(False)
+    gpu.close()

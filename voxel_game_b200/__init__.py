@@ -3,7 +3,7 @@ reference's compute-pass / ray-pass interface. See DESIGN.md and include/voxelb2
 
 (The package directory is `voxel_game_b200`: a hyphen is not importable in Python.)
 """
-from ._lib import COLLISION_DTYPE, PLAYER_DTYPE, PROJECTILE_DTYPE, RayCaps, VxbError, load  # noqa: F401
+from ._lib import COLLISION_DTYPE, PLAYER_DTYPE, PROJECTILE_DTYPE, RASTER_INSTANCE_DTYPE, RayCaps, VxbError, load  # noqa: F401
 from .pipeline import (  # noqa: F401
     CHUNK_SIZE,
     CHUNK_VOLUME,
@@ -13,7 +13,11 @@ from .pipeline import (  # noqa: F401
     GameState,
     GraphicsSettings,
     PointLightingSystem,
+    RasterizerSystem,
     VoxelComputePipeline,
     WorldGen,
     initial_start_pos,
+    perspective,
+    quat_to_mat4,
+    translation,
 )

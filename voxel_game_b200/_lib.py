@@ -104,6 +104,9 @@ PLAYER_DTYPE = np.dtype(
         ("has_world_collision", "<u4"),
     ]
 )
+# ProjectileInstanceData (client/src/rasterizer.rs:52-60)
+RASTER_INSTANCE_DTYPE = np.dtype([("position", "<f4", 3), ("rotation", "<f4", 4), ("scale", "<f4", 3)])
+assert RASTER_INSTANCE_DTYPE.itemsize == 40
 COLLISION_DTYPE = np.dtype([("id1", "<u4"), ("id2", "<u4"), ("properties", "<u4"), ("when", "<f4")])
 assert PROJECTILE_DTYPE.itemsize == 112 and PLAYER_DTYPE.itemsize == 128 and COLLISION_DTYPE.itemsize == 16
 
@@ -140,6 +143,11 @@ SIGNATURES = {
     "vxb_update_list_run": (ctypes.c_int, [c_vp, c_vp, c_vp]),
     "vxb_update_list_flags": (ctypes.c_int, [c_vp, c_vp, c_u32]),
     "vxb_set_update_kernel": (ctypes.c_int, [c_vp, ctypes.c_int]),
+    "vxb_raster_set_mesh": (ctypes.c_int, [c_vp, c_vp, c_vp, c_u32]),
+    "vxb_raster_draw": (ctypes.c_int, [c_vp, c_u32, c_u32, c_vp, c_vp, c_u32]),
+    "vxb_raster_max_depth": (ctypes.c_int, [c_vp, c_vp, ctypes.c_float, c_vp]),
+    "vxb_raster_bind": (ctypes.c_int, [c_vp, ctypes.c_int]),
+    "vxb_raster_download": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp]),
     "vxb_update_list_run_range": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_uint32, ctypes.c_uint32, ctypes.POINTER(ctypes.c_void_p)]),
     "vxb_update_list_flags_device": (ctypes.c_int, [c_vp, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_uint32)]),
     "vxb_damage_log_enable": (ctypes.c_int, [c_vp, ctypes.c_uint32]),

@@ -125,7 +125,7 @@ __device__ __forceinline__ void store_layer(const RayOut& o, uint64_t i, uint32_
 template <bool DIRECT>
 __device__ uint32_t raycast(const World& w, f3 pos, f3 ray, uint32_t max_iterations, const vxb_projectile* projectiles,
                             uint32_t projectile_count, float raster_depth, Layer (&layers)[5], float& out_depth, uint32_t& iters,
-                            const RayOut& out, uint64_t ray_index) {
+                            const RayOut& out, uint64_t ray_index, f3 raster_normal = f3{0.0f, 1.0f, 0.0f}, float raster_diffuse_x = 1.0f) {
     auto push = [&](uint32_t idx, const Layer& L) {
         if (DIRECT) store_layer(out, ray_index, idx, L);
         else layers[idx] = L;
@@ -192,8 +192,9 @@ __device__ uint32_t raycast(const World& w, f3 pos, f3 ray, uint32_t max_iterati
     }
 
     if (raster_depth > 0.0f && layer_idx < 5) {
-        // headless: no rasterised G-buffer; u_normals = (0,1,0), u_diffuse.x = 1 (MAT_PLAYER)
-        push(layer_idx, Layer{ray_pos, norm3(mk3(0.0f, 1.0f, 0.0f)), MAT_PLAYER << 24, raster_depth, 0u});
+        // frag.glsl:428-437: u_normals / u_diffuse of the G-buffer pass (k_raster.cu), or, without one, (0,1,0) / 1
+        const uint32_t raster_material = raster_diffuse_x == 0.0f ? MAT_PROJECTILE : MAT_PLAYER;
+        push(layer_idx, Layer{ray_pos, norm3(raster_normal), raster_material << 24, raster_depth, 0u});
         layer_idx++;
     }
 
@@ -353,7 +354,7 @@ __device__ __forceinline__ void count_iters(const RayOut& o, uint32_t iters) {
 // One thread per pixel; block = 8x8 pixels = two 8x4 warp tiles; blockIdx.z = view.
 __global__ void __launch_bounds__(64) k_raymarch_primary(World w, const vxb_player* __restrict__ cams, uint32_t width, uint32_t height,
                                                          uint32_t max_iterations, const vxb_projectile* __restrict__ projectiles,
-                                                         uint32_t projectile_count, const float* __restrict__ raster_depth, RayOut out) {
+                                                         uint32_t projectile_count, RasterIn raster, RayOut out) {
     const uint32_t lane_tile = threadIdx.x;  // 0..63: warp = 8 wide x 4 high
     const uint32_t px = blockIdx.x * 8 + (lane_tile & 7), py = blockIdx.y * 8 + (lane_tile >> 3);
     const uint32_t view = blockIdx.z;
@@ -369,16 +370,18 @@ __global__ void __launch_bounds__(64) k_raymarch_primary(World w, const vxb_play
                  up = mk3(cam.up[0], cam.up[1], cam.up[2]);
         const f3 ray = norm3(dir + sx * right - sy * up);
         const f3 pos = mk3(cam.pos[0], cam.pos[1], cam.pos[2]);
-        const float max_depth = raster_depth ? raster_depth[i] : 0.0f;
+        const float max_depth = raster.depth ? raster.depth[i] : 0.0f;
+        const f3 rnormal = raster.normal ? mk3(raster.normal[3 * i], raster.normal[3 * i + 1], raster.normal[3 * i + 2]) : mk3(0.0f, 1.0f, 0.0f);
+        const float rdiffuse = raster.diffuse_x ? raster.diffuse_x[i] : 1.0f;
         Layer layers[5];
         float depth;
         uint32_t count;
         if (projectile_count == 0) {
-            count = raycast<true>(w, pos, ray, max_iterations, projectiles, 0, max_depth, layers, depth, iters, out, i);
+            count = raycast<true>(w, pos, ray, max_iterations, projectiles, 0, max_depth, layers, depth, iters, out, i, rnormal, rdiffuse);
         } else {
 #pragma unroll
             for (int l = 0; l < 5; l++) layers[l] = Layer{mk3(0, 0, 0), mk3(0, 0, 0), 0u, 0.0f, 0u};
-            count = raycast<false>(w, pos, ray, max_iterations, projectiles, projectile_count, max_depth, layers, depth, iters, out, i);
+            count = raycast<false>(w, pos, ray, max_iterations, projectiles, projectile_count, max_depth, layers, depth, iters, out, i, rnormal, rdiffuse);
 #pragma unroll
             for (uint32_t l = 0; l < 5; l++)
                 if (l < count) store_layer(out, i, l, layers[l]);
@@ -391,7 +394,7 @@ __global__ void __launch_bounds__(64) k_raymarch_primary(World w, const vxb_play
 
 // frag.glsl main (:715-741) fused: primary DDA + get_color, one thread per pixel, f_color as float4.
 __global__ void __launch_bounds__(64) k_render(World w, const vxb_player* __restrict__ cams, uint32_t width, uint32_t height,
-                                               uint32_t max_iterations, ShadeParams sp, const float* __restrict__ raster_depth,
+                                               uint32_t max_iterations, ShadeParams sp, RasterIn raster,
                                                float4* __restrict__ color_out, RayOut out) {
     const uint32_t lane_tile = threadIdx.x;
     const uint32_t px = blockIdx.x * 8 + (lane_tile & 7), py = blockIdx.y * 8 + (lane_tile >> 3);
@@ -407,12 +410,14 @@ __global__ void __launch_bounds__(64) k_render(World w, const vxb_player* __rest
                  up = mk3(cam.up[0], cam.up[1], cam.up[2]);
         const f3 ray = norm3(dir + sx * right - sy * up);
         const f3 pos = mk3(cam.pos[0], cam.pos[1], cam.pos[2]);
-        const float max_depth = raster_depth ? raster_depth[i] : 0.0f;
+        const float max_depth = raster.depth ? raster.depth[i] : 0.0f;
+        const f3 rnormal = raster.normal ? mk3(raster.normal[3 * i], raster.normal[3 * i + 1], raster.normal[3 * i + 2]) : mk3(0.0f, 1.0f, 0.0f);
+        const float rdiffuse = raster.diffuse_x ? raster.diffuse_x[i] : 1.0f;
         Layer layers[5];
 #pragma unroll
         for (int l = 0; l < 5; l++) layers[l] = Layer{mk3(0, 0, 0), mk3(0, 0, 0), 0u, 0.0f, 0u};
         float depth;
-        const uint32_t count = raycast<false>(w, pos, ray, max_iterations, sp.projectiles, sp.projectile_count, max_depth, layers, depth, iters, out, i);
+        const uint32_t count = raycast<false>(w, pos, ray, max_iterations, sp.projectiles, sp.projectile_count, max_depth, layers, depth, iters, out, i, rnormal, rdiffuse);
         float4 c;
         if (count == 0) {
             c = make_float4(1.0f, 0.0f, 0.0f, 1.0f);  // :735-738
@@ -466,15 +471,15 @@ __global__ void __launch_bounds__(128) k_raymarch_rays(World w, const float* __r
 
 cudaError_t launch_raymarch_views(const World& w, const vxb_player* cams_dev, uint32_t n_views, uint32_t width, uint32_t height,
                                   uint32_t max_iterations, const vxb_projectile* projectiles, uint32_t projectile_count,
-                                  const float* raster_depth_dev, RayOut out, cudaStream_t st) {
+                                  RasterIn raster, RayOut out, cudaStream_t st) {
     if (n_views == 0 || width == 0 || height == 0) return cudaSuccess;
     dim3 grid((width + 7) / 8, (height + 7) / 8, n_views);
-    k_raymarch_primary<<<grid, 64, 0, st>>>(w, cams_dev, width, height, max_iterations, projectiles, projectile_count, raster_depth_dev, out);
+    k_raymarch_primary<<<grid, 64, 0, st>>>(w, cams_dev, width, height, max_iterations, projectiles, projectile_count, raster, out);
     return cudaGetLastError();
 }
 
 cudaError_t launch_render(const World& w, const vxb_player* cams_dev, uint32_t n_views, uint32_t width, uint32_t height,
-                          const vxb_ray_caps& caps, float time, const vxb_projectile* projectiles, const float* raster_depth_dev,
+                          const vxb_ray_caps& caps, float time, const vxb_projectile* projectiles, RasterIn raster,
                           float* color_out, unsigned long long* total_iters, cudaStream_t st) {
     if (n_views == 0 || width == 0 || height == 0) return cudaSuccess;
     ShadeParams sp;
@@ -488,7 +493,7 @@ cudaError_t launch_render(const World& w, const vxb_player* cams_dev, uint32_t n
     RayOut out{};
     out.total_iters = total_iters;
     dim3 grid((width + 7) / 8, (height + 7) / 8, n_views);
-    k_render<<<grid, 64, 0, st>>>(w, cams_dev, width, height, caps.primary_ray_dist, sp, raster_depth_dev, reinterpret_cast<float4*>(color_out), out);
+    k_render<<<grid, 64, 0, st>>>(w, cams_dev, width, height, caps.primary_ray_dist, sp, raster, reinterpret_cast<float4*>(color_out), out);
     return cudaGetLastError();
 }
 

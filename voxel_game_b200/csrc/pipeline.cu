@@ -96,6 +96,14 @@ struct vxb_ctx {
     DevBuf<uint32_t> ray_voxel, ray_leaving, ray_count;
     DevBuf<vxb_player> cams;
     DevBuf<float> color;  // float4 per pixel of the last vxb_render
+    // player-mesh G-buffer pass (k_raster.cu)
+    DevBuf<float> mesh_pos, mesh_normal;  // triangle list, 3 floats per vertex
+    uint32_t mesh_vertices = 0;
+    DevBuf<vxb_raster_instance> raster_instances;
+    DevBuf<unsigned long long> raster_key;
+    DevBuf<float> gb_depth, gb_normal, gb_diffuse, gb_max_depth;
+    uint32_t gb_w = 0, gb_h = 0;
+    bool gb_max_depth_valid = false, gb_bound = false;
     uint64_t n_color = 0;
     uint64_t n_rays = 0;
 
@@ -191,6 +199,8 @@ static void free_ctx(vxb_ctx* c) {
     c->ray_pos.release(); c->ray_normal.release(); c->ray_ldist.release(); c->ray_dist.release(); c->ray_in_pos.release();
     c->ray_in_dir.release(); c->raster_depth.release(); c->ray_voxel.release(); c->ray_leaving.release(); c->ray_count.release();
     c->cams.release(); c->color.release(); c->dmg_log.release(); c->dmg_count.release();
+    c->mesh_pos.release(); c->mesh_normal.release(); c->raster_instances.release(); c->raster_key.release();
+    c->gb_depth.release(); c->gb_normal.release(); c->gb_diffuse.release(); c->gb_max_depth.release();
     c->h_projectiles.release(); c->h_players.release(); c->h_collisions.release(); c->h_collision_count.release();
     c->h_worldgen_updates.release(); c->h_worldgen_results.release(); c->h_chunk_updates.release(); c->h_update_flags.release();
     c->h_voxel_writes.release();
@@ -958,11 +968,15 @@ int vxb_raymarch(vxb_ctx* c, const uint32_t start_pos[3], const vxb_player* cams
     if (rc) return rc;
     VXB_CUDA(c, c->cams.ensure(n_views));
     VXB_CUDA(c, cudaMemcpyAsync(c->cams.p, cams, (size_t)n_views * sizeof(vxb_player), cudaMemcpyHostToDevice, st));
-    const float* rd = nullptr;
+    RasterIn rd{nullptr, nullptr, nullptr};
     if (raster_depth) {
         VXB_CUDA(c, c->raster_depth.ensure(n));
         VXB_CUDA(c, cudaMemcpyAsync(c->raster_depth.p, raster_depth, n * sizeof(float), cudaMemcpyHostToDevice, st));
-        rd = c->raster_depth.p;
+        rd.depth = c->raster_depth.p;
+    } else if (c->gb_bound) {
+        VXB_REQUIRE(c, n_views == 1 && w == c->gb_w && h == c->gb_h && c->gb_max_depth_valid,
+                    "vxb_raymarch: the bound G-buffer needs one view of its own size and a vxb_raster_max_depth call after the draw");
+        rd = RasterIn{c->gb_max_depth.p, c->gb_normal.p, c->gb_diffuse.p};
     }
     VXB_CUDA(c, cudaMemsetAsync(c->scalars.p, 0, sizeof(unsigned long long), st));
     VXB_CUDA(c, launch_raymarch_views(c->world(start_pos), c->cams.p, n_views, w, h, caps->primary_ray_dist, c->projectiles.p,
@@ -985,14 +999,104 @@ int vxb_render(vxb_ctx* c, const uint32_t start_pos[3], const vxb_player* cams, 
     c->n_color = n;
     VXB_CUDA(c, c->cams.ensure(n_views));
     VXB_CUDA(c, cudaMemcpyAsync(c->cams.p, cams, (size_t)n_views * sizeof(vxb_player), cudaMemcpyHostToDevice, st));
-    const float* rd = nullptr;
+    RasterIn rd{nullptr, nullptr, nullptr};
     if (raster_depth) {
         VXB_CUDA(c, c->raster_depth.ensure(n));
         VXB_CUDA(c, cudaMemcpyAsync(c->raster_depth.p, raster_depth, n * sizeof(float), cudaMemcpyHostToDevice, st));
-        rd = c->raster_depth.p;
+        rd.depth = c->raster_depth.p;
+    } else if (c->gb_bound) {
+        VXB_REQUIRE(c, n_views == 1 && w == c->gb_w && h == c->gb_h && c->gb_max_depth_valid,
+                    "vxb_render: the bound G-buffer needs one view of its own size and a vxb_raster_max_depth call after the draw");
+        rd = RasterIn{c->gb_max_depth.p, c->gb_normal.p, c->gb_diffuse.p};
     }
     VXB_CUDA(c, cudaMemsetAsync(c->scalars.p, 0, sizeof(unsigned long long), st));
     VXB_CUDA(c, launch_render(c->world(start_pos), c->cams.p, n_views, w, h, *caps, time, c->projectiles.p, rd, c->color.p, c->scalars.p, st));
+    return VXB_OK;
+}
+
+// ---- player-mesh G-buffer pass (RasterizerSystem, client/src/rasterizer.rs) ----
+int vxb_raster_set_mesh(vxb_ctx* c, const float (*positions)[3], const float (*normals)[3], uint32_t n_vertices) {
+    if (!c) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, n_vertices % 3 == 0, "vxb_raster_set_mesh: a triangle list has a multiple of 3 vertices");
+    VXB_REQUIRE(c, n_vertices == 0 || (positions && normals), "vxb_raster_set_mesh: positions / normals is NULL");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, c->mesh_pos.ensure((size_t)n_vertices * 3));
+    VXB_CUDA(c, c->mesh_normal.ensure((size_t)n_vertices * 3));
+    if (n_vertices) {
+        VXB_CUDA(c, cudaMemcpyAsync(c->mesh_pos.p, positions, (size_t)n_vertices * 12, cudaMemcpyHostToDevice, c->stream));
+        VXB_CUDA(c, cudaMemcpyAsync(c->mesh_normal.p, normals, (size_t)n_vertices * 12, cudaMemcpyHostToDevice, c->stream));
+        VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    c->mesh_vertices = n_vertices;
+    return VXB_OK;
+}
+
+// cgmath::perspective(Rad(fovy), aspect, near, far), column-major (rasterizer.rs:204-205)
+static void perspective_matrix(float fovy, float aspect, float near_, float far_, float m[16]) {
+    for (int i = 0; i < 16; i++) m[i] = 0.0f;
+    const float f = 1.0f / std::tan(fovy / 2.0f);
+    m[0] = f / aspect;
+    m[5] = f;
+    m[10] = (far_ + near_) / (near_ - far_);
+    m[11] = -1.0f;
+    m[14] = (2.0f * far_ * near_) / (near_ - far_);
+}
+
+int vxb_raster_draw(vxb_ctx* c, uint32_t width, uint32_t height, const float view_matrix[16], const vxb_raster_instance* instances,
+                    uint32_t n_instances) {
+    if (!c || !view_matrix) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, width > 0 && height > 0 && (uint64_t)width * height <= (1ull << 28), "vxb_raster_draw: bad viewport");
+    VXB_REQUIRE(c, n_instances == 0 || instances, "vxb_raster_draw: instances is NULL");
+    VXB_REQUIRE(c, (uint64_t)n_instances * (c->mesh_vertices / 3) < (1ull << 32), "vxb_raster_draw: too many primitives");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    const size_t n = (size_t)width * height;
+    VXB_CUDA(c, c->raster_key.ensure(n));
+    VXB_CUDA(c, c->gb_depth.ensure(n));
+    VXB_CUDA(c, c->gb_normal.ensure(n * 3));
+    VXB_CUDA(c, c->gb_diffuse.ensure(n));
+    VXB_CUDA(c, c->gb_max_depth.ensure(n));
+    VXB_CUDA(c, c->raster_instances.ensure(n_instances));
+    if (n_instances)
+        VXB_CUDA(c, cudaMemcpyAsync(c->raster_instances.p, instances, (size_t)n_instances * sizeof(vxb_raster_instance), cudaMemcpyHostToDevice, st));
+    float proj[16];
+    perspective_matrix(1.57079632679489661923f, (float)width / (float)height, 0.1f, 200.0f, proj);  // FRAC_PI_2, near 0.1, RASTER_FAR_PLANE (main.rs:45)
+    VXB_CUDA(c, launch_raster_draw(c->mesh_pos.p, c->mesh_normal.p, c->mesh_vertices, c->raster_instances.p, n_instances, view_matrix, proj, width, height,
+                                   c->raster_key.p, c->gb_depth.p, c->gb_normal.p, c->gb_diffuse.p, st));
+    if (n_instances) VXB_CUDA(c, cudaStreamSynchronize(st));  // the host instance array may be reused on return
+    c->gb_w = width;
+    c->gb_h = height;
+    c->gb_max_depth_valid = false;
+    return VXB_OK;
+}
+
+int vxb_raster_max_depth(vxb_ctx* c, const float screen_to_world[16], float aspect_ratio, const float cam_pos[3]) {
+    if (!c || !screen_to_world || !cam_pos) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, c->gb_w > 0, "vxb_raster_max_depth: no G-buffer drawn yet");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, launch_raster_max_depth(c->gb_depth.p, screen_to_world, aspect_ratio, cam_pos, c->gb_w, c->gb_h, c->gb_max_depth.p, c->stream));
+    c->gb_max_depth_valid = true;
+    return VXB_OK;
+}
+
+int vxb_raster_bind(vxb_ctx* c, int enable) {
+    if (!c) return VXB_ERR_INVALID;
+    c->gb_bound = enable != 0;
+    return VXB_OK;
+}
+
+int vxb_raster_download(vxb_ctx* c, float* depth, float* normal, float* diffuse_x, float* max_depth) {
+    if (!c) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, c->gb_w > 0, "vxb_raster_download: no G-buffer drawn yet");
+    VXB_REQUIRE(c, !max_depth || c->gb_max_depth_valid, "vxb_raster_download: max_depth has not been computed for this draw");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    const size_t n = (size_t)c->gb_w * c->gb_h;
+    cudaStream_t st = c->stream;
+    if (depth) VXB_CUDA(c, cudaMemcpyAsync(depth, c->gb_depth.p, n * 4, cudaMemcpyDeviceToHost, st));
+    if (normal) VXB_CUDA(c, cudaMemcpyAsync(normal, c->gb_normal.p, n * 12, cudaMemcpyDeviceToHost, st));
+    if (diffuse_x) VXB_CUDA(c, cudaMemcpyAsync(diffuse_x, c->gb_diffuse.p, n * 4, cudaMemcpyDeviceToHost, st));
+    if (max_depth) VXB_CUDA(c, cudaMemcpyAsync(max_depth, c->gb_max_depth.p, n * 4, cudaMemcpyDeviceToHost, st));
+    VXB_CUDA(c, cudaStreamSynchronize(st));
     return VXB_OK;
 }
 

@@ -41,12 +41,18 @@ struct RayOut {
     float* dist;
     unsigned long long* total_iters;
 };
+// per-pixel inputs from the G-buffer pass (all device pointers, each nullable): max_depth (frag.glsl:725-728), u_normals rgb, u_diffuse.x
+struct RasterIn {
+    const float* depth;
+    const float* normal;
+    const float* diffuse_x;
+};
 cudaError_t launch_raymarch_views(const World& w, const vxb_player* cams_dev, uint32_t n_views, uint32_t width, uint32_t height,
                                   uint32_t max_iterations, const vxb_projectile* projectiles, uint32_t projectile_count,
-                                  const float* raster_depth_dev, RayOut out, cudaStream_t st);
+                                  RasterIn raster, RayOut out, cudaStream_t st);
 // frag.glsl main: primary DDA + shading (get_color) -> float4 colour per pixel
 cudaError_t launch_render(const World& w, const vxb_player* cams_dev, uint32_t n_views, uint32_t width, uint32_t height,
-                          const vxb_ray_caps& caps, float time, const vxb_projectile* projectiles, const float* raster_depth_dev,
+                          const vxb_ray_caps& caps, float time, const vxb_projectile* projectiles, RasterIn raster,
                           float* color_out, unsigned long long* total_iters, cudaStream_t st);
 cudaError_t launch_raymarch_rays(const World& w, const float* pos_dev, const float* dir_dev, uint64_t n, int kind,
                                  uint32_t max_iterations, const vxb_projectile* projectiles, uint32_t projectile_count, RayOut out,
@@ -65,5 +71,12 @@ cudaError_t launch_projectiles(const World& w, vxb_projectile* projectiles, uint
                                float dt, DamageLog dlog, cudaStream_t st);
 cudaError_t launch_apply_damage(const World& w, const uint32_t* records, uint32_t n, cudaStream_t st);
 cudaError_t launch_players(const World& w, vxb_player* players, uint32_t n_players, float dt, cudaStream_t st);
+
+// RasterizerSystem::draw (rasterizer.rs:196-323) + frag.glsl:716-728 as kernels (k_raster.cu)
+cudaError_t launch_raster_draw(const float* positions, const float* normals, uint32_t n_vertices, const vxb_raster_instance* instances,
+                               uint32_t n_instances, const float view[16], const float proj[16], uint32_t W, uint32_t H, unsigned long long* key,
+                               float* depth, float* normal, float* diffuse_x, cudaStream_t st);
+cudaError_t launch_raster_max_depth(const float* depth, const float screen_to_world[16], float aspect_ratio, const float cam_pos[3], uint32_t W,
+                                    uint32_t H, float* out, cudaStream_t st);
 
 }  // namespace vxb

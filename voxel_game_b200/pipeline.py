@@ -12,7 +12,7 @@ from enum import IntEnum
 import numpy as np
 
 from . import _lib
-from ._lib import COLLISION_DTYPE, PLAYER_DTYPE, PROJECTILE_DTYPE, RayBuffers, RayCaps, Ptrs, Settings, VxbError, ptr
+from ._lib import COLLISION_DTYPE, PLAYER_DTYPE, PROJECTILE_DTYPE, RASTER_INSTANCE_DTYPE, RayBuffers, RayCaps, Ptrs, Settings, VxbError, ptr
 
 CHUNK_SIZE = 16
 CHUNK_VOLUME = 4096
@@ -403,6 +403,37 @@ class VoxelComputePipeline:
         t = np.ascontiguousarray(np.asarray(table, dtype=np.uint32).reshape(tuple(int(v) for v in self.settings.render_size)))
         self._check(self._lib.vxb_write_table(self._h, ptr(t)))
 
+    # -- the player-mesh G-buffer pass (client/src/rasterizer.rs) ---------------------------------
+    def raster_set_mesh(self, positions, normals):
+        pos = np.ascontiguousarray(np.asarray(positions, np.float32).reshape(-1, 3))
+        nrm = np.ascontiguousarray(np.asarray(normals, np.float32).reshape(-1, 3))
+        if pos.shape != nrm.shape:
+            raise ValueError("positions and normals must have one entry per vertex")
+        self._check(self._lib.vxb_raster_set_mesh(self._h, ptr(pos) if pos.size else None, ptr(nrm) if nrm.size else None, pos.shape[0]))
+
+    def raster_draw(self, width, height, view_matrix, instances):
+        """view_matrix: 4x4 in math layout (row, column); sent column-major as cgmath stores it."""
+        view = np.ascontiguousarray(np.asarray(view_matrix, np.float32).reshape(4, 4).T)
+        inst = np.ascontiguousarray(instances, dtype=RASTER_INSTANCE_DTYPE).reshape(-1)
+        self._raster_size = (int(width), int(height))
+        self._check(self._lib.vxb_raster_draw(self._h, int(width), int(height), ptr(view), ptr(inst) if inst.size else None, inst.size))
+
+    def raster_max_depth(self, screen_to_world, aspect_ratio, cam_pos):
+        m = np.ascontiguousarray(np.asarray(screen_to_world, np.float32).reshape(4, 4).T)
+        cp = np.ascontiguousarray(np.asarray(cam_pos, np.float32).reshape(-1)[:3])
+        self._check(self._lib.vxb_raster_max_depth(self._h, ptr(m), ctypes.c_float(aspect_ratio), ptr(cp)))
+
+    def raster_bind(self, enable=True):
+        self._check(self._lib.vxb_raster_bind(self._h, int(bool(enable))))
+
+    def raster_download(self, want_max_depth=True):
+        w, h = self._raster_size
+        out = {"depth": np.zeros((h, w), np.float32), "normal": np.zeros((h, w, 3), np.float32), "diffuse_x": np.zeros((h, w), np.float32)}
+        if want_max_depth:
+            out["max_depth"] = np.zeros((h, w), np.float32)
+        self._check(self._lib.vxb_raster_download(self._h, ptr(out["depth"]), ptr(out["normal"]), ptr(out["diffuse_x"]), ptr(out.get("max_depth"))))
+        return out
+
     def world_checksum(self, start_pos):
         out = ctypes.c_uint64(0)
         self._check(self._lib.vxb_world_checksum(self._h, ptr(_u32(start_pos, 3)), ctypes.byref(out)))
@@ -416,6 +447,73 @@ class Game:
         self.voxel_compute = voxel_compute
         self.game_state = game_state
         self.players = players  # PLAYER_DTYPE array; players[0] is the camera (frag.glsl:716)
+
+
+PLAYER_HITBOX_OFFSET = (0.0, -2.0, 0.0)  # client/src/main.rs:63
+
+
+def perspective(fovy, aspect, near, far):
+    """cgmath::perspective in float32, math layout (row, column)."""
+    f = np.float32(1.0) / np.tan(np.float32(fovy) / np.float32(2.0), dtype=np.float32)
+    near, far, aspect = np.float32(near), np.float32(far), np.float32(aspect)
+    m = np.zeros((4, 4), np.float32)
+    m[0, 0] = f / aspect
+    m[1, 1] = f
+    m[2, 2] = (far + near) / (near - far)
+    m[3, 2] = -1.0
+    m[2, 3] = (np.float32(2.0) * far * near) / (near - far)
+    return m
+
+
+def quat_to_mat4(q):
+    """cgmath Matrix4::from(Quaternion), q = (x, y, z, w); math layout."""
+    x, y, z, w = (np.float32(v) for v in q)
+    x2, y2, z2 = x + x, y + y, z + z
+    xx2, xy2, xz2 = x2 * x, x2 * y, x2 * z
+    yy2, yz2, zz2 = y2 * y, y2 * z, z2 * z
+    sx2, sy2, sz2 = w * x2, w * y2, w * z2
+    one = np.float32(1.0)
+    return np.array([[one - yy2 - zz2, xy2 - sz2, xz2 + sy2, 0], [xy2 + sz2, one - xx2 - zz2, yz2 - sx2, 0],
+                     [xz2 - sy2, yz2 + sx2, one - xx2 - yy2, 0], [0, 0, 0, 1]], np.float32)
+
+
+def translation(v):
+    m = np.eye(4, dtype=np.float32)
+    m[:3, 3] = np.asarray(v, np.float32)[:3]
+    return m
+
+
+class RasterizerSystem:
+    """Mirror of RasterizerSystem (client/src/rasterizer.rs): `new` loads the mesh (the caller passes the
+    triangle list load_obj_to_vecs produces, :326-361), `draw` fills the instance buffer from the players
+    (:218-243: every player but the first, alive ones only) and draws the G-buffer on the device."""
+
+    def __init__(self, voxel_compute, player_vertices, player_normals):
+        self.voxel_compute = voxel_compute
+        voxel_compute.raster_set_mesh(player_vertices, player_normals)
+
+    @staticmethod
+    def instances(players, facing=None, health=None):
+        """players: PLAYER_DTYPE array (index 0 = the camera's own player, skipped); facing[i] = facing[0] of
+        player i (yaw), health[i] <= 0 skips the player."""
+        pl = np.ascontiguousarray(players, dtype=PLAYER_DTYPE).reshape(-1)
+        out = []
+        for i in range(1, pl.size):
+            if health is not None and health[i] <= 0.0:
+                continue
+            size = np.float32(pl["size"][i])
+            inst = np.zeros(1, RASTER_INSTANCE_DTYPE)
+            inst["position"][0] = pl["pos"][i, :3] + np.asarray(PLAYER_HITBOX_OFFSET, np.float32) * size
+            yaw = np.float32(0.0 if facing is None else facing[i])
+            half = yaw * np.float32(0.5)  # Quaternion::from_axis_angle((0,1,0), Rad(yaw))
+            inst["rotation"][0] = (0.0, np.sin(half, dtype=np.float32), 0.0, np.cos(half, dtype=np.float32))
+            inst["scale"][0] = (size, size, size)
+            out.append(inst)
+        return np.concatenate(out) if out else np.zeros(0, RASTER_INSTANCE_DTYPE)
+
+    def draw(self, viewport_dimensions, view_matrix, players, facing=None, health=None):
+        w, h = int(viewport_dimensions[0]), int(viewport_dimensions[1])
+        self.voxel_compute.raster_draw(w, h, view_matrix, self.instances(players, facing, health))
 
 
 class PointLightingSystem:
