@@ -127,3 +127,148 @@ def test_slab_sharding_with_ghost_columns_matches_single_ctx():
     assert np.array_equal(ctxs[1].read_pool(2, shards[1].n_own), ref[n0:])
     for g in ctxs + [single]:
         g.close()
+
+
+@pytest.mark.timeout(900)
+def test_config3_full_size_three_kernels_agree():
+    """BASELINE configs[2] at its full size (256x16x256 chunks, 4.3 G voxels, 17 GB per world): the default kernel
+    (store elision, runs of list neighbours with the z hand-over picked automatically at this list length), the
+    same kernel with unconditional stores, and the reference-shaped gather kernel walk the same 16 ticks on
+    three copies of the world; change flags and the world checksum must agree after every tick."""
+    import torch
+
+    import bench
+    import voxel_game_b200 as vg
+
+    free, _ = torch.cuda.mem_get_info()
+    if free < 60e9:
+        pytest.skip("needs 3 x 17 GB of device memory")
+    rs, sp = bench.C3_RS, bench.C3_SP
+    n = rs[0] * rs[1] * rs[2]
+    chunks = bench.chunk_grid(0, rs[0], rs, sp)
+    lst = np.concatenate([chunks, np.zeros((n, 1), np.int64)], 1).astype(np.uint32)
+    worlds = []
+    for variant in (2, 0, 1):
+        g = vg.VoxelComputePipeline(vg.GameSettings(render_size=rs, max_loaded_chunks=2 + n, max_worldgen_rate=8 * 32768, max_update_rate=1024))
+        bench.generate_world(g, sp, chunks, 2, True, torch)
+        g.update_list_upload(lst)
+        g.set_update_kernel(variant)
+        worlds.append(g)
+    c0 = [g.world_checksum(sp) for g in worlds]
+    assert c0[0] == c0[1] == c0[2]
+    seen, changed = set(), 0
+    for t in range(16):
+        off = scenes.PHASES[t % 8]
+        flags, cks = [], []
+        for g in worlds:
+            g.update_list_run(sp, off)
+            flags.append(g.update_list_flags())
+            cks.append(g.world_checksum(sp))
+        assert np.array_equal(flags[0], flags[1]) and np.array_equal(flags[0], flags[2]), "flags differ at tick %d" % t
+        assert cks[0] == cks[1] == cks[2], "world differs at tick %d" % t
+        seen.add(cks[0])
+        changed += int((flags[0] & 1).sum())
+    assert len(seen) == 16 and changed > n  # the world really evolves, everywhere
+    for g in worlds:
+        g.close()
+
+
+def _config2_world(torch):
+    """BASELINE configs[1] world as the benchmark builds it: 64x16x64 chunks, non-forced worldgen, 64 ticks."""
+    import bench
+    import voxel_game_b200 as vg
+
+    rs, sp = bench.C2_RS, bench.C2_SP
+    n = rs[0] * rs[1] * rs[2]
+    g = vg.VoxelComputePipeline(vg.GameSettings(render_size=rs, max_loaded_chunks=2 + n, max_worldgen_rate=8 * 32768, max_update_rate=1024,
+                                                max_collisions=1 << 20))
+    chunks = bench.chunk_grid(0, rs[0], rs, sp)
+    bench.generate_world(g, sp, chunks, 2, False, torch)
+    table = g.read_table()
+    g.update_list_upload(bench._loaded_list(table, chunks, rs))
+    for t in range(64):
+        g.update_list_run(sp, scenes.PHASES[t % 8])
+    cx, cz = 16 * sp[0] + 8 * rs[0], 16 * sp[2] + 8 * rs[2]
+    sy = bench._surface_from_gpu(g, table, rs, sp, cx, cz)
+    return g, rs, sp, (cx, sy, cz)
+
+
+@pytest.mark.timeout(900)
+def test_config2_full_size_primary_rays_equal_explicit_rays():
+    """BASELINE configs[1] at full size (1024x256x1024 voxels, 1920x1080): the per-pixel kernel that builds its
+    rays from the camera and writes layers as it goes, and the explicit-ray kernel fed with the same rays built
+    on the host in float32, must return the same layers, depths and iteration total — two code paths, 2 M rays."""
+    import torch
+
+    import voxel_game_b200 as vg
+
+    g, rs, sp, (cx, sy, cz) = _config2_world(torch)
+    w, h = 1920, 1080
+    cam = scenes.camera((cx + 0.5, sy + 4.5, cz + 0.5), 0.7, -0.2)
+    caps = vg.RayCaps(100, 40, 20, 15, 0)
+    g.raymarch(sp, cam, w, h, caps)
+    a = g.ray_download()
+    f = np.float32
+    px, py = np.meshgrid(np.arange(w, dtype=f), np.arange(h, dtype=f))
+    aspect = f(w) / f(h)
+    sx = ((px + f(0.5)) / f(w) * f(2.0) - f(1.0)) * aspect
+    syy = ((py + f(0.5)) / f(h) * f(2.0) - f(1.0)) * f(1.0)
+    d, r, u = (cam[k][0, :3].astype(f) for k in ("dir", "right", "up"))
+    v = (d[None, None, :] + sx[..., None] * r[None, None, :]) - syy[..., None] * u[None, None, :]
+    ln = np.sqrt((v[..., 0] * v[..., 0] + v[..., 1] * v[..., 1]) + v[..., 2] * v[..., 2])
+    rays = (v / ln[..., None]).reshape(-1, 3).astype(f)
+    pos = np.broadcast_to(cam["pos"][0, :3].astype(f), rays.shape)
+    g.raymarch_rays(sp, pos, rays, 0, 100)
+    b = g.ray_download()
+    assert a["total_iterations"] == b["total_iterations"] > 5 * w * h
+    assert np.array_equal(a["layer_count"], b["layer_count"]) and (a["layer_count"] > 0).mean() > 0.5
+    assert np.array_equal(a["dist"].view(np.uint32), b["dist"].view(np.uint32))
+    lc = a["layer_count"]
+    for l in range(5):
+        m = lc > l
+        if not m.any():
+            continue
+        for k in ("voxel", "leaving"):
+            assert np.array_equal(a[k][l][m], b[k][l][m]), (k, l)
+        for k in ("pos", "normal"):
+            assert np.array_equal(a[k][l][:, m].view(np.uint32), b[k][l][:, m].view(np.uint32)), (k, l)
+        assert np.array_equal(a["ldist"][l][m].view(np.uint32), b["ldist"][l][m].view(np.uint32))
+    g.close()
+
+
+@pytest.mark.timeout(900)
+def test_config4_full_size_sharded_batch_equals_single_batch():
+    """BASELINE configs[3] at full size (1 048 576 projectiles + 64 hulls against the config-2 world): the batch split
+    over two replicas with the voxel damage exchanged (the multi-GPU protocol, here two contexts on one GPU) gives the
+    projectiles, the collision set and the world of the unsplit batch."""
+    import torch
+
+    g_s, rs, sp, (cx, sy, cz) = _config2_world(torch)
+    g_a = _config2_world(torch)[0]
+    g_b = _config2_world(torch)[0]
+    assert g_s.world_checksum(sp) == g_a.world_checksum(sp) == g_b.world_checksum(sp)
+    n = 1 << 20
+    lo = (16 * sp[0] + 8, 16 * sp[1] + 8, 16 * sp[2] + 8)
+    hi = (16 * (sp[0] + rs[0]) - 8, 16 * (sp[1] + rs[1]) - 8, 16 * (sp[2] + rs[2]) - 8)
+    pr = scenes.random_projectiles(n, lo, hi, seed=0x5EED0001 & 0x7FFFFFFF)
+    pl = scenes.players_grid(8, (cx, sy, cz), 48.0, sy + 4.0, seed=64)
+    pr["pos"][:4000, :3] = pl["pos"][np.arange(4000) % 64, :3] + np.random.RandomState(3).randn(4000, 3).astype(np.float32) * 1.5 + (0, -1.5, 0)
+    half = n // 2
+    for g in (g_a, g_b):
+        g.damage_log_enable(half)
+    pa, _, ca, na = g_a.dispatch_entities(sp, projectiles=pr[:half], players=pl, run_players=False)
+    pb, _, cb, nb = g_b.dispatch_entities(sp, projectiles=pr[half:], players=pl, run_players=False)
+    ra, rb = g_a.damage_log_read(half), g_b.damage_log_read(half)
+    g_a.damage_apply(sp, records=rb)
+    g_b.damage_apply(sp, records=ra)
+    ps, _, cs, ns = g_s.dispatch_entities(sp, projectiles=pr, players=pl, run_players=False)
+    assert len(ra) + len(rb) > 50000 and ns > 100
+    assert g_s.world_checksum(sp) == g_a.world_checksum(sp) == g_b.world_checksum(sp)
+    assert np.array_equal(np.concatenate([pa, pb]).view(np.uint8), ps.view(np.uint8))
+    cb = cb.copy()
+    cb["id1"] += half
+    merged = np.concatenate([ca, cb])
+    merged = merged[np.lexsort((merged["id2"], merged["id1"]))]
+    assert na + nb == ns and np.array_equal(merged[["id1", "id2", "properties"]], cs[["id1", "id2", "properties"]])
+    for g in (g_s, g_a, g_b):
+        g.close()
