@@ -393,7 +393,7 @@ __global__ void __launch_bounds__(64) k_raymarch_primary(World w, const vxb_play
 }
 
 // frag.glsl main (:715-741) fused: primary DDA + get_color, one thread per pixel, f_color as float4.
-__global__ void __launch_bounds__(64) k_render(World w, const vxb_player* __restrict__ cams, uint32_t width, uint32_t height,
+__global__ void __launch_bounds__(64, 16) k_render(World w, const vxb_player* __restrict__ cams, uint32_t width, uint32_t height,
                                                uint32_t max_iterations, ShadeParams sp, RasterIn raster,
                                                float4* __restrict__ color_out, RayOut out) {
     const uint32_t lane_tile = threadIdx.x;
