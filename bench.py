@@ -851,7 +851,7 @@ def bench_collisions_sharded(args, torch, vg, dist, gpu, SP, RS, centre, rank, w
     players replicated; the voxel damage each rank adds is logged, all-gathered and replayed on the other
     replicas inside the timed region. Ends with a checksum comparison of the replicas."""
     from tests import scenes
-    from voxel_game_b200.replicas import exchange_damage
+    from voxel_game_b200.replicas import exchange_damage_fixed
 
     cx, col_y, cz = centre
     n_proj, n_side = args.projectiles, 8
@@ -873,8 +873,11 @@ def bench_collisions_sharded(args, torch, vg, dist, gpu, SP, RS, centre, rank, w
     steps = max(4, min(args.steps, 16))
     total_ms, foreign = 0.0, 0
 
-    def apply_fn(rows):
-        gpu.damage_apply(SP, n=rows.shape[0], device_ptr=rows.data_ptr())
+    gathered = torch.empty((world_size * cap, 4), dtype=torch.int32, device="cuda")
+    counts = torch.empty(world_size, dtype=torch.int32, device="cuda")
+
+    def apply_fn(rows, count):
+        gpu.damage_apply_counted(SP, rows.data_ptr(), count.data_ptr(), cap)
 
     for i in range(3 + steps):
         proj_t.copy_(proj0)
@@ -884,12 +887,12 @@ def bench_collisions_sharded(args, torch, vg, dist, gpu, SP, RS, centre, rank, w
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         gpu.entities_resident_run(SP, per, n_side * n_side)
-        got = exchange_damage(dist, torch, rec_t, int(cnt_t.item()), rank, world_size, apply_fn)
+        exchange_damage_fixed(dist, torch, rec_t, cnt_t, rank, world_size, apply_fn, gathered, counts)
         e1.record()
         torch.cuda.synchronize()
         if i >= 3:
             total_ms += e0.elapsed_time(e1)
-            foreign += got
+            foreign += int(counts.sum().item()) - int(cnt_t.item())
     ck = torch.tensor([gpu.world_checksum(SP) & 0x7FFFFFFFFFFFFFFF], dtype=torch.int64, device="cuda")
     cks = torch.zeros(world_size, dtype=torch.int64, device="cuda")
     dist.all_gather_into_tensor(cks, ck)
@@ -899,7 +902,7 @@ def bench_collisions_sharded(args, torch, vg, dist, gpu, SP, RS, centre, rank, w
     return {"metric": "projectiles/s", "value": n_proj / (ms / 1e3), "unit": "projectiles/s", "ms_per_tick": ms, "n_gpus": world_size, "scaling": "strong",
             "replicas_identical": bool((cks == cks[0]).all().item()), "foreign_damage_records_per_tick": foreign / steps,
             "config": {"workload": "BASELINE configs[3]: %d projectiles (index ranges per rank) + %d player hulls vs replicas of the config-2 world; "
-                                   "voxel damage all-gathered and replayed inside the timed region" % (n_proj, n_side * n_side)}}
+                                   "voxel damage logs all-gathered (fixed capacity, counts on the device) and replayed inside the timed region" % (n_proj, n_side * n_side)}}
 
 
 # ------------------------------------------------------------------------------------------------

@@ -253,6 +253,11 @@ int vxb_damage_log_enable(vxb_ctx* ctx, uint32_t capacity);
 int vxb_damage_log_device(vxb_ctx* ctx, void** records_dev, void** count_dev, uint32_t* capacity);
 int vxb_damage_log_read(vxb_ctx* ctx, uint32_t (*records_out)[4], uint32_t capacity, uint32_t* n_out);
 int vxb_damage_apply(vxb_ctx* ctx, const uint32_t start_pos[3], const uint32_t (*records)[4], uint32_t n, int records_on_device);
+/* The same for a device array whose record count also lives on the device (min(*count_dev, capacity) records are
+ * replayed): nothing is read back between the exchange of the logs and their replay. An overflowed log cannot be
+ * detected here; check the source's own count with vxb_damage_log_read when in doubt. */
+int vxb_damage_apply_counted(vxb_ctx* ctx, const uint32_t start_pos[3], const uint32_t (*records_dev)[4], const uint32_t* count_dev,
+                             uint32_t capacity);
 
 /* Resident work list for repeated full sweeps (benchmark configs 3 and 5): upload once, then run
  * the update dispatch on it any number of times without host traffic. */

@@ -466,9 +466,9 @@ def test_sharded_collision_batch_damage_log():
     rec_b = gpu_b.damage_log_read(half)
     assert len(rec_a) > 50 and len(rec_b) > 50
     gpu_a.damage_apply(sp, records=rec_b)
-    ptr_a, _, cap = gpu_a.damage_log_device()
+    ptr_a, cnt_a, cap = gpu_a.damage_log_device()
     assert cap == half
-    gpu_b.damage_apply(sp, n=len(rec_a), device_ptr=ptr_a)
+    gpu_b.damage_apply_counted(sp, ptr_a, cnt_a, cap)  # count read on the device, as the multi-GPU exchange does
     gpu_b.synchronize()
     ps, _, cs, ns = gpu_s.dispatch_entities(sp, projectiles=pr, players=players, run_players=False)
     c_pr, c_co, _ = cpu.projectiles(pr, players, capacity=1024)

@@ -62,7 +62,7 @@ def _worker(rank, world_size, port, out_dir):
     import torch
     import torch.distributed as dist
 
-    from voxel_game_b200.replicas import changed_chunk_mask, exchange_damage, exchange_ghost_mask, gather_changed_chunks
+    from voxel_game_b200.replicas import changed_chunk_mask, exchange_damage, exchange_damage_fixed, exchange_ghost_mask, gather_changed_chunks
     from voxel_game_b200.sharding import SlabShard, halo_exchange
 
     os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -120,6 +120,14 @@ def _worker(rank, world_size, port, out_dir):
                 replica.pool[s, k] = np.uint32((int(replica.pool[s, k]) + int(amt)) & 0xFFFFFFFF)
 
         applied = exchange_damage(dist, torch, torch.from_numpy(rec), len(diff), rank, world_size, apply_fn)
+        # the fixed-capacity variant (counts stay "on the device") must replay the same rows: undo, redo, compare
+        after = replica.pool.copy()
+        replica.pool[:] = before
+        for s_, k_, _, amt in rec[:len(diff)]:
+            replica.pool[s_, k_] = np.uint32((int(replica.pool[s_, k_]) + int(amt)) & 0xFFFFFFFF)
+        exchange_damage_fixed(dist, torch, torch.from_numpy(rec), torch.tensor([len(diff)], dtype=torch.int32), rank, world_size,
+                              lambda rows, cnt: apply_fn(rows[:int(cnt[0])]))
+        assert np.array_equal(replica.pool, after)
         np.savez(os.path.join(out_dir, "rank%d.npz" % rank), states=np.stack(states), moved=moved, final=replica.pool, applied=applied,
                  n_rec=len(diff), health=out_pr["health"])
         dist.barrier()

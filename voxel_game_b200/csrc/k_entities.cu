@@ -616,6 +616,21 @@ __global__ void k_apply_damage(World w, const uint4* __restrict__ records, uint3
     atomicAdd(&w.pool[voxel_index(w, r.x, r.y, r.z)], r.w);
 }
 
+// the same with the record count read on the device (no host round trip between the exchange and the replay)
+__global__ void k_apply_damage_counted(World w, const uint4* __restrict__ records, const uint32_t* __restrict__ count, uint32_t capacity) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t n = min(*count, capacity);
+    if (i >= n) return;
+    const uint4 r = records[i];
+    atomicAdd(&w.pool[voxel_index(w, r.x, r.y, r.z)], r.w);
+}
+
+cudaError_t launch_apply_damage_counted(const World& w, const uint32_t* records, const uint32_t* count_dev, uint32_t capacity, cudaStream_t st) {
+    if (capacity == 0) return cudaSuccess;
+    k_apply_damage_counted<<<(capacity + 255) / 256, 256, 0, st>>>(w, reinterpret_cast<const uint4*>(records), count_dev, capacity);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_apply_damage(const World& w, const uint32_t* records, uint32_t n, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
     k_apply_damage<<<(n + 255) / 256, 256, 0, st>>>(w, reinterpret_cast<const uint4*>(records), n);

@@ -922,6 +922,16 @@ int vxb_damage_apply(vxb_ctx* c, const uint32_t start_pos[3], const uint32_t (*r
     return VXB_OK;
 }
 
+int vxb_damage_apply_counted(vxb_ctx* c, const uint32_t start_pos[3], const uint32_t (*records_dev)[4], const uint32_t* count_dev,
+                             uint32_t capacity) {
+    if (!c || !start_pos) return VXB_ERR_INVALID;
+    VXB_WINDOW(c, start_pos);
+    VXB_REQUIRE(c, capacity == 0 || (records_dev && count_dev), "vxb_damage_apply_counted: records_dev / count_dev is NULL");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, launch_apply_damage_counted(c->world(start_pos), reinterpret_cast<const uint32_t*>(records_dev), count_dev, capacity, c->stream));
+    return VXB_OK;
+}
+
 int vxb_set_update_kernel(vxb_ctx* c, int variant) {
     if (!c) return VXB_ERR_INVALID;
     VXB_REQUIRE(c, (variant & 0xFF) <= 2 && (variant >> 8) >= 0 && (variant >> 8) <= 9,

@@ -70,6 +70,7 @@ cudaError_t launch_projectiles(const World& w, vxb_projectile* projectiles, uint
                                uint32_t n_players, vxb_collision* collisions, uint32_t collision_capacity, uint32_t* collision_count,
                                float dt, DamageLog dlog, cudaStream_t st);
 cudaError_t launch_apply_damage(const World& w, const uint32_t* records, uint32_t n, cudaStream_t st);
+cudaError_t launch_apply_damage_counted(const World& w, const uint32_t* records, const uint32_t* count_dev, uint32_t capacity, cudaStream_t st);
 cudaError_t launch_players(const World& w, vxb_player* players, uint32_t n_players, float dt, cudaStream_t st);
 
 // RasterizerSystem::draw (rasterizer.rs:196-323) + frag.glsl:716-728 as kernels (k_raster.cu)

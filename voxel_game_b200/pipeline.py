@@ -310,6 +310,11 @@ class VoxelComputePipeline:
         rec = np.ascontiguousarray(np.asarray(records, dtype=np.uint32).reshape(-1, 4))
         self._check(self._lib.vxb_damage_apply(self._h, ptr(_u32(start_pos, 3)), ptr(rec) if rec.size else None, rec.shape[0], 0))
 
+    def damage_apply_counted(self, start_pos, records_ptr, count_ptr, capacity):
+        """Replays min(*count_ptr, capacity) records at a device address; the count is read on the device."""
+        self._check(self._lib.vxb_damage_apply_counted(self._h, ptr(_u32(start_pos, 3)), ctypes.c_void_p(int(records_ptr)),
+                                                       ctypes.c_void_p(int(count_ptr)), int(capacity)))
+
     def set_update_kernel(self, variant):
         self._check(self._lib.vxb_set_update_kernel(self._h, int(variant)))
 

@@ -97,6 +97,28 @@ def exchange_ghost_mask(dist, torch, ghost_mask, rank, world_size, plane_chunks,
     return None if recv is None else recv.bool()
 
 
+def exchange_damage_fixed(dist, torch, records, count, rank, world_size, apply_counted_fn, gathered=None, counts=None):
+    """The same exchange without any host round trip: every rank contributes its whole fixed-capacity log
+    ([capacity, 4] int32) and its count ([1] int32, device), both are all-gathered as they are, and
+    apply_counted_fn(rows [capacity, 4], count [1]) replays min(count, capacity) rows of every other rank with the
+    count read on the device. Costs capacity x 16 B per rank on the wire instead of count x 16 B — a few MB over
+    NVLink — and saves the count read-back and the second, length-dependent all-gather. `gathered` / `counts`:
+    optional preallocated [world_size * capacity, 4] / [world_size] buffers."""
+    if world_size == 1:
+        return
+    cap = records.shape[0]
+    if gathered is None:
+        gathered = torch.empty((world_size * cap, 4), dtype=records.dtype, device=records.device)
+    if counts is None:
+        counts = torch.empty(world_size, dtype=count.dtype, device=count.device)
+    dist.all_gather_into_tensor(counts, count)
+    dist.all_gather_into_tensor(gathered, records)
+    g = gathered.view(world_size, cap, 4)
+    for r in range(world_size):
+        if r != rank:
+            apply_counted_fn(g[r], counts[r:r + 1])
+
+
 def gather_changed_chunks(dist, torch, mask, own_pool, own_first_global, replica_pool, idx_buf, chunk_buf, rank, world_size):
     """mask: [n_own] bool, the chunks of this rank's slab whose payload changed (changed_chunk_mask, plus what
     the caller knows: regenerated chunks, the neighbour's ghost mask). own_pool: [n_own, 4096] view of this
