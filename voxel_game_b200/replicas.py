@@ -16,13 +16,15 @@ gloo on CPU tensors (tests):
 """
 
 
-def _all_gather_var(dist, torch, payload, count, world_size):
+def _all_gather_var(dist, torch, payload, count, world_size, counts=None):
     """All-gather `count` leading rows of `payload` ([cap, ...]) from every rank.
-    Returns (list of per-rank row counts, gathered tensor [world_size, max_count, ...])."""
-    counts_t = torch.zeros(world_size, dtype=torch.int64, device=payload.device)
-    mine = torch.tensor([int(count)], dtype=torch.int64, device=payload.device)
-    dist.all_gather_into_tensor(counts_t, mine)
-    counts = [int(c) for c in counts_t.tolist()]
+    Returns (list of per-rank row counts, gathered tensor [world_size, max_count, ...]). `counts`: the per-rank counts
+    if a previous call already exchanged them (saves the small all-gather and its read-back)."""
+    if counts is None:
+        counts_t = torch.zeros(world_size, dtype=torch.int64, device=payload.device)
+        mine = torch.tensor([int(count)], dtype=torch.int64, device=payload.device)
+        dist.all_gather_into_tensor(counts_t, mine)
+        counts = [int(c) for c in counts_t.tolist()]
     m = max(counts)
     if m == 0:
         return counts, None
@@ -140,7 +142,7 @@ def gather_changed_chunks(dist, torch, mask, own_pool, own_first_global, replica
     counts, all_idx = _all_gather_var(dist, torch, idx_buf, n, world_size)
     if all_idx is None:
         return 0
-    _, all_chunks = _all_gather_var(dist, torch, chunk_buf, n, world_size)
+    _, all_chunks = _all_gather_var(dist, torch, chunk_buf, n, world_size, counts)
     total = 0
     for r in range(world_size):
         if counts[r]:
