@@ -245,6 +245,8 @@ def run_ours(args):
     value = n_total_vox * args.steps / (total_ms / 1e3)
     # dominant kernel: this rank's k_voxel_update launches (CUDA events on the launching stream)
     per_step_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
+    if rank == 0:
+        print("per-step ms (rank 0, phase = step %% 8 after %d warm-ups): %s" % (args.warmup, " ".join("%.3f" % m for m in per_step_ms)), file=sys.stderr)
     kern_ms = float(np.mean(per_step_ms)) if world_size == 1 else None
 
     # ---------------- same steps with the reference's unconditional stores (variant 0), for comparison ----------------
