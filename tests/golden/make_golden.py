@@ -112,10 +112,27 @@ def ray_and_entity_cases():
             "n_collisions": int(len(c_co)), "counters": [int(x) for x in counters]}
 
 
+def raster_case():
+    """The player-mesh G-buffer pass (oracle/raster.h) on a generated capsule mesh, 12 instances around the camera,
+    97 x 131 pixels: hashes of the attachments and of the max_depth the ray pass derives."""
+    from tests import oracle_lib
+    from tests.raster_scene import raster_scene, instances_of
+
+    w, h = 97, 131
+    cam_pos, view, s2w, players, facing, health = raster_scene()
+    pos, nrm = scenes.capsule_mesh()
+    inst = instances_of(players, facing, health)
+    g = oracle_lib.raster_draw(w, h, view, pos, nrm, inst)
+    md = oracle_lib.raster_max_depth(g["depth"], s2w, w / h, cam_pos)
+    covered = g["depth"] < 1.0
+    return {"instances": int(inst.size), "covered_pixels": int(covered.sum()), "depth_sha256": sha(g["depth"]), "normal_sha256": sha(g["normal"]),
+            "diffuse_sha256": sha(g["diffuse_x"]), "max_depth_sha256": sha(md)}
+
+
 def main():
     lib = load()
     g = {"hash_kats": hash_kats(lib), "noise_kats": noise_kats(lib), "chunks": chunk_hashes(), "update_trace": update_trace(),
-         "rays_entities": ray_and_entity_cases()}
+         "rays_entities": ray_and_entity_cases(), "raster": raster_case()}
     with open(os.path.join(HERE, "golden.json"), "w") as f:
         json.dump(g, f, indent=1)
     print("wrote golden.json, rays.npz")

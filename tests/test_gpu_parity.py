@@ -522,33 +522,11 @@ def test_render_full_fragment_shader(world_gen, seed, yaw, pitch, t):
 
 
 def _raster_scene(w, h, yaw_cam=0.3):
-    """Camera matrices the way main.rs builds them (:473-481, :614-617) and a ring of players around it."""
-    import voxel_game_b200 as vg
+    """Camera matrices the way main.rs builds them (:473-481, :614-617) and a ring of players around it
+    (shared with the CPU golden test: tests/raster_scene.py)."""
+    from tests.raster_scene import raster_scene
 
-    cam_pos = np.array([10000.5, 1830.0, 10000.5], np.float32)
-    half = np.float32(yaw_cam / 2)
-    cam_rot = np.array([0.0, np.sin(half), 0.0, np.cos(half)], np.float32)
-    view_raster = np.linalg.inv((vg.translation(-cam_pos) @ vg.quat_to_mat4(cam_rot)).astype(np.float64)).astype(np.float32)
-    view_frame = np.linalg.inv((vg.translation(cam_pos) @ vg.quat_to_mat4(cam_rot)).astype(np.float64)).astype(np.float32)
-    proj_frame = vg.perspective(np.pi / 2, 1.0, 0.1, 200.0)
-    screen_to_world = np.linalg.inv((proj_frame @ view_frame).astype(np.float64)).astype(np.float32)
-    players = np.zeros(14, vg.PLAYER_DTYPE)
-    players["size"] = 1.0
-    players["pos"][0, :3] = cam_pos
-    rng = np.random.RandomState(8)
-    for i in range(1, 14):
-        ang = 2 * np.pi * i / 13
-        dist = 2.5 + 9.0 * rng.rand()  # some fill a good part of the view, one or two cross the near plane
-        # the rasteriser works in the reference's mirrored space (vertex - instance_position): place instances so
-        # that they land in front of the camera either way
-        players["pos"][i, :3] = cam_pos + np.array([np.sin(ang) * dist, rng.rand() * 4 - 1, np.cos(ang) * dist], np.float32)
-        players["size"][i] = 0.6 + rng.rand()
-    players["pos"][13, :3] = cam_pos + np.array([1.1, 1.2, 0.9], np.float32)  # close: its triangles cross the near plane
-    players["size"][13] = 0.5
-    facing = rng.rand(14).astype(np.float32) * 6.28
-    health = np.ones(14, np.float32)
-    health[5] = 0.0
-    return cam_pos, view_raster, screen_to_world, players, facing, health
+    return raster_scene(yaw_cam)
 
 
 @pytest.mark.parametrize("w,h", [(160, 90), (97, 131)])

@@ -138,3 +138,9 @@ def test_rays_and_entities_golden(tmp_path, monkeypatch):
     co = b["collisions"].view(COLLISION_DTYPE)
     assert len(co) == GOLD["rays_entities"]["n_collisions"] and set(co["properties"]) <= {1, 2}
     assert b["projectiles"].view(PROJECTILE_DTYPE).size == 64 and b["players"].view(PLAYER_DTYPE).size == 4
+
+
+def test_raster_golden():
+    got = make_golden.raster_case()
+    assert got == GOLD["raster"]
+    assert got["instances"] == 12 and 0.2 < got["covered_pixels"] / (97 * 131) < 0.6
