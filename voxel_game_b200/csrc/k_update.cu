@@ -367,7 +367,14 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
     // longer merge in L2 (y/z-shifted phases lose 15-20 %), and even with stores elided the CTA no
     // longer reads one chunk's 16 KiB together, which costs DRAM page locality: 808 -> 731 G/s.
     // A bounded version — mbarrier arrive at the end of iteration t, wait for t-2 at the start of t, so a
-    // warp runs at most one chunk ahead — measured +0.7 % elided / -2 % with stores: not kept.)
+    // warp runs at most one chunk ahead — measured +0.7 % elided / -2 % with stores: not kept.
+    // Third attempt, elided variant only: no barrier AND the warp <-> slab assignment rotating with the item
+    // (slab = (warp + t) % 8) so that every warp is the heavy one once in eight items and the drift stays a
+    // bounded random walk. The barrier stall disappears (issue slots 63 % -> 73 % busy, IPC 2.2 -> 2.56) but
+    // the per-warp slot rings, the rotating row / flag arithmetic and the flag atomics cost 18 % more
+    // instructions: 891 vs 883 G/s, phases with offset.z = 1 and offset.y = 1 slower. Not kept: what bounds
+    // this kernel is the ALU pipe (LOP3 / IADD3 / VIMNMX at one warp instruction per two cycles per
+    // scheduler), not the barrier.)
     const int tzq = tid & 3, tx = (tid >> 2) & 7, ty = tid >> 5;
     // (i,j) column of this thread: in-chunk word offset of its vector, and which neighbour chunk holds it.
     // Only the last thread column / row straddles (x or y == 16), and only for i / j == 1.
