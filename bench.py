@@ -379,6 +379,7 @@ def run_ours(args):
             result["rays"]["control_map"] = bench_rays_control(args, torch, vg)
         if not args.no_cpu:
             result["c1"] = bench_c1(args, torch, vg)
+        result["game_tick"] = bench_game_tick(args, torch, vg)
 
     if world_size > 1:
         dist.barrier()
@@ -533,6 +534,55 @@ def bench_c1(args, torch, vg):
            "loaded_chunks": len(loaded), "world_equals_oracle": same_world, "frame_layer_counts_equal_oracle": same_frame}
     gpu.close()
     return out
+
+
+def bench_game_tick(args, torch, vg):
+    """The compute pass as the game drives it (main.rs:483-596 around VoxelComputePipeline::compute): the "Open World" preset
+    (settings.yaml: 32^3-chunk window, 8192 slots, 128 worldgen workgroups and 128 chunk updates per tick, dt 0.02), one
+    player walking, chunks around it requested every tick, 200 projectiles in flight; wall clock per tick through the
+    C ABI including the host queues, uploads and the read-back of the previous tick. The reference's target is 50 Hz."""
+    from tests import scenes
+
+    rs, center = (32, 32, 32), (10000, 1820, 10000)
+    gs = vg.GameSettings(render_size=rs, max_loaded_chunks=8192, max_worldgen_rate=128, max_update_rate=128, delta_time=0.02)
+    gpu = vg.VoxelComputePipeline(gs, device=torch.cuda.current_device())
+    gpu.set_stream(torch.cuda.current_stream().cuda_stream)
+    state = vg.GameState(start_pos=vg.initial_start_pos(center, rs))
+    players = scenes.players_grid(1, center, 1.0, center[1] + 6.0, seed=1)
+    players["vel"][0, :3] = (4.0, 0.0, 2.5)
+    gpu.queue_update_from_world_pos(center)
+    sp = state.start_pos
+    lo = (16 * sp[0] + 200, center[1] - 10, 16 * sp[2] + 200)
+    hi = (16 * (sp[0] + rs[0]) - 200, center[1] + 10, 16 * (sp[2] + rs[2]) - 200)
+    batches = [scenes.random_projectiles(200, lo, hi, seed=100 + k) for k in range(8)]  # built outside the timed loop
+    n_ticks, warm = 200, 40
+    t_acc, counts = 0.0, np.zeros(3, np.int64)
+    for tick in range(warm + n_ticks):
+        ppos = [tuple(float(v) for v in players["pos"][0, :3])]
+        t0 = time.perf_counter()
+        gpu.push_updates_from_changed(ppos)
+        pc = [int(v) // 16 for v in ppos[0]]
+        for dx in range(-3, 4):
+            for dy in range(-2, 3):
+                for dz in range(-3, 4):
+                    gpu.ensure_chunk_loaded((pc[0] + dx, pc[1] + dy, pc[2] + dz))
+        if tick > 0:
+            _, _, pl = gpu.download_projectiles()
+            if pl.size:
+                players = pl.copy()
+        gpu.compute(state, batches[tick % len(batches)], players)
+        gpu.synchronize()
+        dt = time.perf_counter() - t0
+        if tick >= warm:
+            t_acc += dt
+            counts += np.asarray(gpu.last_dispatch_counts(), np.int64)
+    gpu.close()
+    ms = 1e3 * t_acc / n_ticks
+    return {"metric": "game ticks/s", "value": 1e3 / ms, "unit": "ticks/s", "ms_per_tick": ms, "ticks": n_ticks,
+            "mean_dispatch_counts": {"worldgen_workgroups": counts[0] / n_ticks, "voxel_writes": counts[1] / n_ticks, "chunk_updates": counts[2] / n_ticks},
+            "config": {"workload": "Open World preset: 32^3-chunk window, 128 worldgen workgroups + 128 chunk updates per tick, 1 player, 200 projectiles; "
+                                   "wall clock per tick through vxb_compute incl. host queues, uploads, read-back (Python driver overhead included)",
+                       "reference_target_ticks_per_s": 50}}
 
 
 def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp, chunks, exchange, main, side):
