@@ -352,11 +352,12 @@ __device__ __forceinline__ void count_iters(const RayOut& o, uint32_t iters) {
 }
 
 // One thread per pixel; block = 8x8 pixels = two 8x4 warp tiles; blockIdx.z = view.
-__global__ void __launch_bounds__(64) k_raymarch_primary(World w, const vxb_player* __restrict__ cams, uint32_t width, uint32_t height,
+__global__ void __launch_bounds__(128) k_raymarch_primary(World w, const vxb_player* __restrict__ cams, uint32_t width, uint32_t height,
                                                          uint32_t max_iterations, const vxb_projectile* __restrict__ projectiles,
                                                          uint32_t projectile_count, RasterIn raster, RayOut out) {
-    const uint32_t lane_tile = threadIdx.x;  // 0..63: warp = 8 wide x 4 high
-    const uint32_t px = blockIdx.x * 8 + (lane_tile & 7), py = blockIdx.y * 8 + (lane_tile >> 3);
+    // block = 16 x 8 pixels, four warps of 8 wide x 4 high
+    const uint32_t tl = threadIdx.x;
+    const uint32_t px = blockIdx.x * 16 + ((tl >> 5) & 1u) * 8 + (tl & 7), py = blockIdx.y * 8 + (tl >> 6) * 4 + ((tl >> 3) & 3u);
     const uint32_t view = blockIdx.z;
     uint32_t iters = 0;
     if (px < width && py < height) {
@@ -473,8 +474,8 @@ cudaError_t launch_raymarch_views(const World& w, const vxb_player* cams_dev, ui
                                   uint32_t max_iterations, const vxb_projectile* projectiles, uint32_t projectile_count,
                                   RasterIn raster, RayOut out, cudaStream_t st) {
     if (n_views == 0 || width == 0 || height == 0) return cudaSuccess;
-    dim3 grid((width + 7) / 8, (height + 7) / 8, n_views);
-    k_raymarch_primary<<<grid, 64, 0, st>>>(w, cams_dev, width, height, max_iterations, projectiles, projectile_count, raster, out);
+    dim3 grid((width + 15) / 16, (height + 7) / 8, n_views);
+    k_raymarch_primary<<<grid, 128, 0, st>>>(w, cams_dev, width, height, max_iterations, projectiles, projectile_count, raster, out);
     return cudaGetLastError();
 }
 
