@@ -137,10 +137,24 @@ __device__ uint32_t raycast(const World& w, f3 pos, f3 ray, uint32_t max_iterati
     float depth = 0;
     uint32_t medium = MAT_AIR;
     uint32_t layer_idx = 0;
+    // consecutive steps mostly stay inside one 16^3 chunk: its pool slot is kept, which saves the window test, the
+    // table index arithmetic and — the point — the dependent table load in front of the voxel load
+    uint32_t ccx = 0xFFFFFFFFu, ccy = 0, ccz = 0, cslot = 0;
     for (uint32_t i = 0; i < max_iterations; i++) {
         iters++;
         const f3 floor_pos = floor3(ray_pos);
-        const uint32_t voxel_data = voxel_at(w, floor_pos);
+        uint32_t voxel_data;
+        {
+            const uint32_t x = f2u(floor_pos.x), y = f2u(floor_pos.y), z = f2u(floor_pos.z);
+            const uint32_t kx = x >> 4, ky = y >> 4, kz = z >> 4;
+            bool have = kx == ccx && ky == ccy && kz == ccz;
+            if (!have && in_window(w, x, y, z)) {
+                cslot = table_lookup_in_window(w, kx, ky, kz);
+                ccx = kx; ccy = ky; ccz = kz;
+                have = true;
+            }
+            voxel_data = have ? w.pool[(uint64_t)cslot * CHUNK_VOLUME + ((x & 15u) << 8 | (y & 15u) << 4 | (z & 15u))] : VOX_OOB;
+        }
         const uint32_t voxel_material = voxel_data >> 24;
         f3 v_min, v_max;
         if (voxel_material == MAT_AIR || voxel_material == MAT_AIR_OOB) {
