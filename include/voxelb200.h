@@ -291,6 +291,12 @@ int vxb_set_update_kernel(vxb_ctx* ctx, int variant);
  * Results stay on the device (vxb_ray_results). Asynchronous. */
 int vxb_raymarch(vxb_ctx* ctx, const uint32_t start_pos[3], const vxb_player* cams, uint32_t n_views, uint32_t w, uint32_t h,
                  const vxb_ray_caps* caps, const float* raster_depth);
+/* Resident cameras for repeated frames (benchmark config 2, replicas rendering many views): upload once,
+ * then run the primary-ray pass on views [first_view, first_view + n_views) without host traffic. Any
+ * vxb_raymarch / vxb_render call replaces the uploaded cameras. No raster depth in this form. */
+int vxb_cams_upload(vxb_ctx* ctx, const vxb_player* cams, uint32_t n_views);
+int vxb_raymarch_resident(vxb_ctx* ctx, const uint32_t start_pos[3], uint32_t first_view, uint32_t n_views, uint32_t w, uint32_t h,
+                          const vxb_ray_caps* caps);
 /* The whole fragment shader of the ray pass, frag.glsl main (:715-741): primary DDA (raycast) plus
  * get_color (:650-713) — material noise, neighbour-voxel blending, sun shadow, reflection and two
  * ambient-occlusion rays, Cook-Torrance lighting, depth transparency — for every pixel of n_views

@@ -599,3 +599,32 @@ def test_ray_pass_reads_the_gbuffer():
     assert close.mean() > 0.999, close.mean()
     gpu.raster_bind(False)
     gpu.close()
+
+
+def test_resident_cameras_give_the_same_frames():
+    """vxb_cams_upload + vxb_raymarch_resident (no host traffic per frame) against vxb_raymarch with host cameras."""
+    import voxel_game_b200 as vg
+
+    rs_, center = (6, 4, 6), (10000, 1820, 10000)
+    sp = vg.initial_start_pos(center, rs_)
+    gpu, cpu = _generated_world(rs_, sp, 0, 0, update_ticks=8)
+    sy = _surface_y(cpu, center[0], center[2], 16 * (sp[1] + rs_[1]) - 1)
+    cams = np.concatenate([scenes.camera((center[0] + 0.5, sy + 4.5, center[2] + 0.5), k * 0.9, -0.2) for k in range(4)])
+    caps = vg.RayCaps(100, 40, 20, 15, 0)
+    w, h = 96, 54
+    gpu.raymarch(sp, cams[1:3], w, h, caps)
+    a = gpu.ray_download()
+    gpu.cams_upload(cams)
+    gpu.raymarch_resident(sp, 1, 2, w, h, caps)
+    b = gpu.ray_download()
+    assert a["total_iterations"] == b["total_iterations"]
+    for k in ("layer_count", "voxel", "leaving"):
+        assert np.array_equal(a[k], b[k]), k
+    for k in ("pos", "normal", "ldist", "dist"):
+        assert np.array_equal(a[k].view(np.uint32), b[k].view(np.uint32)), k
+    with pytest.raises(vg.VxbError):
+        gpu.raymarch_resident(sp, 3, 2, w, h, caps)  # beyond the uploaded cameras
+    gpu.raymarch(sp, cams[:1], w, h, caps)           # replaces the resident cameras
+    with pytest.raises(vg.VxbError):
+        gpu.raymarch_resident(sp, 0, 1, w, h, caps)
+    gpu.close()

@@ -95,6 +95,7 @@ struct vxb_ctx {
     DevBuf<float> ray_pos, ray_normal, ray_ldist, ray_dist, ray_in_pos, ray_in_dir, raster_depth;
     DevBuf<uint32_t> ray_voxel, ray_leaving, ray_count;
     DevBuf<vxb_player> cams;
+    uint32_t cams_resident = 0;  // cameras uploaded by vxb_cams_upload (vxb_raymarch / vxb_render overwrite the buffer)
     DevBuf<float> color;  // float4 per pixel of the last vxb_render
     // player-mesh G-buffer pass (k_raster.cu)
     DevBuf<float> mesh_pos, mesh_normal;  // triangle list, 3 floats per vertex
@@ -977,6 +978,7 @@ int vxb_raymarch(vxb_ctx* c, const uint32_t start_pos[3], const vxb_player* cams
     int rc = ensure_ray_buffers(c, n);
     if (rc) return rc;
     VXB_CUDA(c, c->cams.ensure(n_views));
+    c->cams_resident = 0;
     VXB_CUDA(c, cudaMemcpyAsync(c->cams.p, cams, (size_t)n_views * sizeof(vxb_player), cudaMemcpyHostToDevice, st));
     RasterIn rd{nullptr, nullptr, nullptr};
     if (raster_depth) {
@@ -994,6 +996,36 @@ int vxb_raymarch(vxb_ctx* c, const uint32_t start_pos[3], const vxb_player* cams
     return VXB_OK;
 }
 
+int vxb_cams_upload(vxb_ctx* c, const vxb_player* cams, uint32_t n_views) {
+    if (!c) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, n_views > 0 && cams, "vxb_cams_upload: cams is NULL or empty");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, c->cams.ensure(n_views));
+    VXB_CUDA(c, cudaMemcpyAsync(c->cams.p, cams, (size_t)n_views * sizeof(vxb_player), cudaMemcpyHostToDevice, c->stream));
+    VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->cams_resident = n_views;
+    return VXB_OK;
+}
+
+int vxb_raymarch_resident(vxb_ctx* c, const uint32_t start_pos[3], uint32_t first_view, uint32_t n_views, uint32_t w, uint32_t h,
+                          const vxb_ray_caps* caps) {
+    if (!c || !start_pos) return VXB_ERR_INVALID;
+    VXB_WINDOW(c, start_pos);
+    VXB_REQUIRE(c, caps, "vxb_raymarch_resident: caps is NULL");
+    VXB_REQUIRE(c, n_views > 0 && w > 0 && h > 0 && n_views <= 65535, "vxb_raymarch_resident: bad view count or size");
+    VXB_REQUIRE(c, (uint64_t)first_view + n_views <= c->cams_resident, "vxb_raymarch_resident: views exceed the uploaded cameras");
+    VXB_REQUIRE(c, caps->projectile_count <= c->projectiles.n, "vxb_raymarch_resident: projectile_count exceeds the projectile buffer");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    const uint64_t n = (uint64_t)n_views * w * h;
+    int rc = ensure_ray_buffers(c, n);
+    if (rc) return rc;
+    VXB_CUDA(c, cudaMemsetAsync(c->scalars.p, 0, sizeof(unsigned long long), st));
+    VXB_CUDA(c, launch_raymarch_views(c->world(start_pos), c->cams.p + first_view, n_views, w, h, caps->primary_ray_dist, c->projectiles.p,
+                                      caps->projectile_count, RasterIn{nullptr, nullptr, nullptr}, ray_out(c), st));
+    return VXB_OK;
+}
+
 int vxb_render(vxb_ctx* c, const uint32_t start_pos[3], const vxb_player* cams, uint32_t n_views, uint32_t w, uint32_t h,
                const vxb_ray_caps* caps, float time, const float* raster_depth) {
     if (!c || !start_pos) return VXB_ERR_INVALID;
@@ -1008,6 +1040,7 @@ int vxb_render(vxb_ctx* c, const uint32_t start_pos[3], const vxb_player* cams, 
     VXB_CUDA(c, c->color.ensure(n * 4));
     c->n_color = n;
     VXB_CUDA(c, c->cams.ensure(n_views));
+    c->cams_resident = 0;
     VXB_CUDA(c, cudaMemcpyAsync(c->cams.p, cams, (size_t)n_views * sizeof(vxb_player), cudaMemcpyHostToDevice, st));
     RasterIn rd{nullptr, nullptr, nullptr};
     if (raster_depth) {

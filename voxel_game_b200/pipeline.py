@@ -324,6 +324,13 @@ class VoxelComputePipeline:
         rd = None if raster_depth is None else np.ascontiguousarray(raster_depth, dtype=np.float32)
         self._check(self._lib.vxb_raymarch(self._h, ptr(_u32(start_pos, 3)), ptr(cams), cams.size, int(w), int(h), ctypes.byref(caps), ptr(rd)))
 
+    def cams_upload(self, cams):
+        cams = np.ascontiguousarray(cams, dtype=PLAYER_DTYPE).reshape(-1)
+        self._check(self._lib.vxb_cams_upload(self._h, ptr(cams), cams.size))
+
+    def raymarch_resident(self, start_pos, first_view, n_views, w, h, caps: RayCaps):
+        self._check(self._lib.vxb_raymarch_resident(self._h, ptr(_u32(start_pos, 3)), int(first_view), int(n_views), int(w), int(h), ctypes.byref(caps)))
+
     def render(self, start_pos, cams, w, h, caps: RayCaps, time=0.0, raster_depth=None):
         """vxb_render: frag.glsl main (primary DDA + get_color) for every pixel; result stays on the device."""
         cams = np.ascontiguousarray(cams, dtype=PLAYER_DTYPE).reshape(-1)
