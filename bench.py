@@ -631,7 +631,7 @@ def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp,
     regen_t = torch.as_tensor(regen_idx, device="cuda")
     # cameras: the 64 players of config 4 around the world centre, yaw = idx * 2 pi / 64
     cx, cz = 16 * SP[0] + 8 * RS[0], 16 * SP[2] + 8 * RS[2]
-    cam_y = 16 * (SP[1] + RS[1] // 2) + 40.0
+    cam_y = _surface_from_gpu(rep, rep.read_table(), RS, SP, cx, cz) + 4.0  # surface + 4 at the world centre, as config 4 places its players
     grid = scenes.players_grid(8, (cx, cam_y, cz), 48.0, cam_y, seed=64)
     cams = np.concatenate([scenes.camera(tuple(grid["pos"][k, :3]), k * 2 * np.pi / 64, -0.2) for k in range(64)])
     mine = cams[rank * 64 // world_size:(rank + 1) * 64 // world_size]
