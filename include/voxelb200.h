@@ -239,6 +239,27 @@ int vxb_dispatch_entities(vxb_ctx* ctx, const uint32_t start_pos[3], vxb_project
 int vxb_entities_resident_run(vxb_ctx* ctx, const uint32_t start_pos[3], uint32_t n_projectiles, uint32_t n_players,
                               int run_projectiles, int run_players, uint32_t* n_collisions_out);
 
+/* Replicated worlds (no counterpart in the reference): after a sharded update every GPU
+ * owns the new state of its slab and the other GPUs' full copies of the world have to follow. Three device-side
+ * steps, none of which reads anything back to the host (all pointers are device addresses, all work is
+ * stream-ordered):
+ *   vxb_changed_chunk_mask  which chunk PAYLOADS did the last vxb_update_list_run change? The resident list must
+ *                           be the full (x, y, z)-ordered grid of cols x ry x rz chunks. An item's region reaches
+ *                           one voxel plane into its +x/+y/+z neighbours where offset is 1, which set_data
+ *                           (compute_voxel.glsl:55-86) reports through the high-face flag bits; mask_dev gets one
+ *                           byte per list entry, ghost_mask_dev (nullable) one per chunk of the column after the
+ *                           last own one (a neighbouring GPU's first column).
+ *   vxb_update_list_pack    entries whose mask byte is set append (x, y, z, 0) to coords_dev and their 16 KiB to
+ *                           payload_dev (capacity records); coords_dev has capacity + 1 rows of 4 words and word 0
+ *                           of the last row is the record count — larger than capacity means overflow.
+ *   vxb_chunks_unpack       writes the first min(count, capacity) records of such a buffer into the chunks they
+ *                           name in THIS ctx's world (records naming chunks without a slot here are skipped). */
+int vxb_changed_chunk_mask(vxb_ctx* ctx, uint32_t cols, uint32_t ry, uint32_t rz, const uint32_t offset[3], uint8_t* mask_dev,
+                           uint8_t* ghost_mask_dev);
+int vxb_update_list_pack(vxb_ctx* ctx, const uint32_t start_pos[3], const uint8_t* mask_dev, uint32_t* coords_dev, uint32_t* payload_dev,
+                         uint32_t capacity);
+int vxb_chunks_unpack(vxb_ctx* ctx, const uint32_t start_pos[3], const uint32_t* coords_dev, const uint32_t* payload_dev, uint32_t capacity);
+
 /* Sharded collision batches (no counterpart in the reference, which runs on one GPU): the
  * world is replicated, every GPU runs compute_projectile.glsl on its own range of the projectile array,
  * and the voxel damage it adds (imageAtomicAdd, compute_projectile.glsl:230-233) is logged as

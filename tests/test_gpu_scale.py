@@ -272,3 +272,90 @@ def test_config4_full_size_sharded_batch_equals_single_batch():
     assert na + nb == ns and np.array_equal(merged[["id1", "id2", "properties"]], cs[["id1", "id2", "properties"]])
     for g in (g_s, g_a, g_b):
         g.close()
+
+
+def test_device_replica_refresh_follows_the_world():
+    """replicas.DeviceReplicaRefresh (mask, pack, unpack kernels; nothing read back) keeps a second copy of a world
+    equal to the first through 24 ticks of sparse activity; its mask kernel equals the tensor version of the same
+    rule, with and without a ghost column; an undersized buffer reports its overflow through the record count."""
+    import torch
+
+    import voxel_game_b200 as vg
+    from voxel_game_b200.replicas import DeviceReplicaRefresh, changed_chunk_mask
+    from voxel_game_b200.sharding import SlabShard
+
+    rs, sp = (6, 4, 5), (300, 40, 70)
+    n = rs[0] * rs[1] * rs[2]
+
+    # world A (updated) and replica B: saturated air with a few stones / water cells near chunk corners and faces
+    grid = np.full((rs[0], rs[1], rs[2], 16, 16, 16), 0x00FFFFFF, np.uint32)
+    stone, water = np.uint32(1 << 24), np.uint32(7 << 24)
+    grid[1, 0, 1, 15, 15, 15] = stone
+    grid[2, 1, 0, 0, 0, 0] = stone
+    grid[0, 0, 2, 8, 15, 0] = stone
+    grid[3, 1, 2, 15, 3, 15] = stone
+    grid[5, 3, 4, 15, 15, 15] = stone
+    grid[1, 1, 1, 15, 8, 7] = water
+    grid[2, 1, 1, 0, 9, 7] = water
+    grid[0, 1, 0, 5, 0, 5] = water
+    chunks = _grid(rs, sp)
+    table = np.zeros(rs, np.uint32)
+    for i, c in enumerate(chunks):
+        table[c[0] % rs[0], c[1] % rs[1], c[2] % rs[2]] = 2 + i
+    worlds = []
+    for _ in range(2):
+        g = vg.VoxelComputePipeline(vg.GameSettings(render_size=rs, max_loaded_chunks=2 + n, max_update_rate=n))
+        g.write_table(table)
+        g.write_pool(2, grid.reshape(n, 4096))
+        worlds.append(g)
+    a, b = worlds
+    st = torch.cuda.Stream()
+    for g in worlds:
+        g.set_stream(st.cuda_stream)
+    lst = scenes.update_list(chunks)
+    a.update_list_upload(lst)
+    shard = SlabShard(rs, sp, 0, 1)
+    with torch.cuda.stream(st):
+        ref = DeviceReplicaRefresh(torch, None, a, b, shard, sp, sp, capacity=n)
+        small = DeviceReplicaRefresh(torch, None, a, b, shard, sp, sp, capacity=2)
+        moved = 0
+        for t in range(24):
+            off = scenes.PHASES[t % 8]
+            a.update_list_run(sp, off)
+            if t == 0:  # an undersized buffer: the record count tells the caller that it overflowed
+                small.refresh(off)
+                st.synchronize()
+                assert int(small.counts()[0].item()) > 2
+            ref.refresh(off)
+            st.synchronize()
+            flags = torch.from_numpy(a.update_list_flags().astype(np.int32)).cuda()
+            want, _ = changed_chunk_mask(torch, flags, rs[0], rs[1], rs[2], off, False)
+            assert torch.equal(ref.mask.bool(), want), "mask differs at tick %d" % t
+            moved += int(ref.counts()[0].item())
+            assert np.array_equal(b.read_pool(0, 2 + n), a.read_pool(0, 2 + n)), "replica differs after tick %d" % t
+        assert 0 < moved < 24 * n
+    for g in worlds:
+        g.close()
+
+    # ghost column: a slab of 3 own columns + 1 ghost, x-shifted phase; kernel mask / ghost mask against the tensor rule
+    shard2 = SlabShard(rs, sp, 0, 2)
+    lrs, lsp = shard2.local_render_size, shard2.local_start_pos
+    nl = lrs[0] * lrs[1] * lrs[2]
+    s = vg.VoxelComputePipeline(vg.GameSettings(render_size=lrs, max_loaded_chunks=2 + nl, max_update_rate=nl))
+    lchunks = _grid(lrs, lsp)
+    ltable = np.zeros(lrs, np.uint32)
+    for i, c in enumerate(lchunks):
+        ltable[c[0] % lrs[0], c[1] % lrs[1], c[2] % lrs[2]] = 2 + i
+    s.write_table(ltable)
+    s.write_pool(2, scenes.random_pool(2 + nl, 5, water=0.1, air=0.7))
+    s.update_list_upload(scenes.update_list(lchunks[:shard2.n_own]))
+    mask = torch.zeros(shard2.n_own, dtype=torch.uint8, device="cuda")
+    ghost = torch.zeros(shard2.plane_chunks, dtype=torch.uint8, device="cuda")
+    for off in scenes.PHASES:
+        s.update_list_run(lsp, off)
+        s.changed_chunk_mask(shard2.cols, rs[1], rs[2], off, mask.data_ptr(), ghost.data_ptr())
+        s.synchronize()
+        flags = torch.from_numpy(s.update_list_flags().astype(np.int32)).cuda()
+        want, want_ghost = changed_chunk_mask(torch, flags, shard2.cols, rs[1], rs[2], off, True)
+        assert torch.equal(mask.bool(), want) and torch.equal(ghost.bool(), want_ghost), off
+    s.close()

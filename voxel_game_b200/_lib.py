@@ -152,6 +152,9 @@ SIGNATURES = {
     "vxb_raster_download": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp]),
     "vxb_update_list_run_range": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_uint32, ctypes.c_uint32, ctypes.POINTER(ctypes.c_void_p)]),
     "vxb_update_list_flags_device": (ctypes.c_int, [c_vp, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_uint32)]),
+    "vxb_changed_chunk_mask": (ctypes.c_int, [c_vp, c_u32, c_u32, c_u32, c_vp, c_vp, c_vp]),
+    "vxb_update_list_pack": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_u32]),
+    "vxb_chunks_unpack": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_u32]),
     "vxb_damage_log_enable": (ctypes.c_int, [c_vp, ctypes.c_uint32]),
     "vxb_damage_log_device": (ctypes.c_int, [c_vp, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_uint32)]),
     "vxb_damage_log_read": (ctypes.c_int, [c_vp, c_vp, ctypes.c_uint32, ctypes.POINTER(ctypes.c_uint32)]),

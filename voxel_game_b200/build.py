@@ -12,7 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libvoxelb200.so")
-SOURCES = ["k_update.cu", "k_worldgen.cu", "k_raymarch.cu", "k_entities.cu", "pipeline.cu", "noalloc.cu", "k_raster.cu"]
+SOURCES = ["k_update.cu", "k_worldgen.cu", "k_raymarch.cu", "k_entities.cu", "pipeline.cu", "noalloc.cu", "k_raster.cu", "k_replicas.cu"]
 HEADERS = ["vxb_device.cuh", "vxb_kernels.h", "host_queues.h", os.path.join("..", "..", "include", "voxelb200.h")]
 
 # -fmad=false: no FMA contraction — float parity with the oracle (DESIGN.md "Float semantics").

@@ -1,0 +1,97 @@
+// k_replicas — device-side pieces of "sharded update + replicated world" (SURVEY 8(e), config 5): which chunk
+// payloads did an update dispatch change, pack them, and unpack them into another copy of the world by chunk
+// coordinates. No counterpart in the reference (it runs on one GPU); everything stays on the device so that
+// a tick needs no host read-back between the update and the refresh of the replicas.
+#include "vxb_device.cuh"
+#include "vxb_kernels.h"
+
+namespace vxb {
+
+// An item's region is the 16^3 box at `offset` inside its chunk: with offset components of 1 it reaches one
+// voxel plane into the +x / +y / +z neighbours (and the edge / corner neighbours). set_data (compute_voxel.glsl:
+// 55-86) reports that through the high-face bits 0x10 / 0x20 / 0x40 next to bit 0. A chunk's payload changed iff
+// for some d in {0,1}^3 (d_a = 1 only where offset_a = 1) the item at (chunk - d) has bit 0 and the high-face bit of
+// every axis with d_a = 1 (conservative: local coordinate 15 sets those bits too).
+// flags: the work list is the full (x, y, z)-ordered grid of cols x ry x rz own chunks. mask: one byte per own
+// chunk; ghost: one byte per chunk of the column after the last own one (nullable).
+__global__ void k_changed_chunk_mask(const uint32_t* __restrict__ flags, uint32_t cols, uint32_t ry, uint32_t rz, uint32_t ox, uint32_t oy,
+                                     uint32_t oz, uint8_t* __restrict__ mask, uint8_t* __restrict__ ghost) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t plane = ry * rz, n = (cols + (ghost ? 1u : 0u)) * plane;
+    if (i >= n) return;
+    const uint32_t x = i / plane, y = (i / rz) % ry, z = i % rz;
+    uint32_t changed = 0;
+    for (uint32_t d = 0; d < 8; d++) {
+        const uint32_t dx = d >> 2, dy = (d >> 1) & 1u, dz = d & 1u;
+        if ((dx && !ox) || (dy && !oy) || (dz && !oz)) continue;
+        if (dx > x || dy > y || dz > z) continue;
+        const uint32_t sx = x - dx;
+        if (sx >= cols) continue;  // the ghost column has no item of its own
+        const uint32_t f = flags[(sx * ry + (y - dy)) * rz + (z - dz)];
+        const uint32_t need = 1u | (dx ? 0x10u : 0u) | (dy ? 0x20u : 0u) | (dz ? 0x40u : 0u);
+        if ((f & need) == need) changed = 1;
+    }
+    if (x < cols) mask[i] = (uint8_t)changed;
+    else ghost[i - cols * plane] = (uint8_t)changed;
+}
+
+// One CTA per resident-list entry: entries whose mask byte is set append (x, y, z, 0) and their 16 KiB payload.
+// coords has capacity + 1 rows: row `capacity` word 0 is the running count (may exceed capacity: overflow).
+__global__ void __launch_bounds__(256) k_pack_chunks(World w, const uint4* __restrict__ list, const uint8_t* __restrict__ mask, uint32_t n,
+                                                     uint4* __restrict__ coords, uint4* __restrict__ payload, uint32_t capacity) {
+    const uint32_t i = blockIdx.x;
+    if (i >= n || mask[i] == 0) return;
+    __shared__ uint32_t s_at, s_slot;
+    if (threadIdx.x == 0) {
+        const uint4 e = list[i];
+        s_at = atomicAdd(reinterpret_cast<uint32_t*>(&coords[capacity]), 1u);
+        s_slot = resolve_chunk_slot(w, e.x, e.y, e.z);
+        if (s_at < capacity) coords[s_at] = make_uint4(e.x, e.y, e.z, 0u);
+    }
+    __syncthreads();
+    if (s_at >= capacity) return;
+    const uint4* src = reinterpret_cast<const uint4*>(w.pool + ((size_t)s_slot << 12));
+    uint4* dst = payload + (size_t)s_at * 1024;
+#pragma unroll
+    for (int k = 0; k < 4; k++) dst[threadIdx.x + 256 * k] = src[threadIdx.x + 256 * k];
+}
+
+// One CTA per received record: the first min(count, capacity) records are written into the chunks they name
+// (records naming chunks that hold no slot here — unloaded, all-air, outside the window — are skipped).
+__global__ void __launch_bounds__(256) k_unpack_chunks(World w, const uint4* __restrict__ coords, const uint4* __restrict__ payload, uint32_t capacity) {
+    const uint32_t i = blockIdx.x;
+    const uint32_t count = min(reinterpret_cast<const uint32_t*>(&coords[capacity])[0], capacity);
+    if (i >= count) return;
+    const uint4 e = coords[i];
+    const uint32_t slot = resolve_chunk_slot(w, e.x, e.y, e.z);
+    if (slot < 2) return;
+    uint4* dst = reinterpret_cast<uint4*>(w.pool + ((size_t)slot << 12));
+    const uint4* src = payload + (size_t)i * 1024;
+#pragma unroll
+    for (int k = 0; k < 4; k++) dst[threadIdx.x + 256 * k] = src[threadIdx.x + 256 * k];
+}
+
+cudaError_t launch_changed_chunk_mask(const uint32_t* flags, uint32_t cols, uint32_t ry, uint32_t rz, const uint32_t offset[3], uint8_t* mask,
+                                      uint8_t* ghost, cudaStream_t st) {
+    const uint32_t n = (cols + (ghost ? 1u : 0u)) * ry * rz;
+    if (n == 0) return cudaSuccess;
+    k_changed_chunk_mask<<<(n + 255) / 256, 256, 0, st>>>(flags, cols, ry, rz, offset[0] & 1u, offset[1] & 1u, offset[2] & 1u, mask, ghost);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pack_chunks(const World& w, const uint32_t* list, const uint8_t* mask, uint32_t n, uint32_t* coords, uint32_t* payload,
+                               uint32_t capacity, cudaStream_t st) {
+    cudaError_t e = cudaMemsetAsync(coords + (size_t)capacity * 4, 0, 16, st);
+    if (e != cudaSuccess || n == 0) return e;
+    k_pack_chunks<<<n, 256, 0, st>>>(w, reinterpret_cast<const uint4*>(list), mask, n, reinterpret_cast<uint4*>(coords), reinterpret_cast<uint4*>(payload),
+                                     capacity);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_unpack_chunks(const World& w, const uint32_t* coords, const uint32_t* payload, uint32_t capacity, cudaStream_t st) {
+    if (capacity == 0) return cudaSuccess;
+    k_unpack_chunks<<<capacity, 256, 0, st>>>(w, reinterpret_cast<const uint4*>(coords), reinterpret_cast<const uint4*>(payload), capacity);
+    return cudaGetLastError();
+}
+
+}  // namespace vxb

@@ -866,6 +866,36 @@ int vxb_update_list_flags_device(vxb_ctx* c, void** flags_dev, uint32_t* n) {
     return VXB_OK;
 }
 
+// ---- replicated worlds: which chunk payloads changed, pack them, unpack them elsewhere (k_replicas.cu) ----
+int vxb_changed_chunk_mask(vxb_ctx* c, uint32_t cols, uint32_t ry, uint32_t rz, const uint32_t offset[3], uint8_t* mask_dev, uint8_t* ghost_mask_dev) {
+    if (!c || !offset) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, mask_dev != nullptr, "vxb_changed_chunk_mask: mask_dev is NULL");
+    VXB_REQUIRE(c, (uint64_t)cols * ry * rz == c->res_n, "vxb_changed_chunk_mask: cols x ry x rz must be the resident list (a full grid in x, y, z order)");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, launch_changed_chunk_mask(c->res_flags.p, cols, ry, rz, offset, mask_dev, ghost_mask_dev, c->stream));
+    return VXB_OK;
+}
+
+int vxb_update_list_pack(vxb_ctx* c, const uint32_t start_pos[3], const uint8_t* mask_dev, uint32_t* coords_dev, uint32_t* payload_dev,
+                         uint32_t capacity) {
+    if (!c || !start_pos) return VXB_ERR_INVALID;
+    VXB_WINDOW(c, start_pos);
+    VXB_REQUIRE(c, mask_dev && coords_dev && payload_dev && capacity > 0, "vxb_update_list_pack: NULL buffer or zero capacity");
+    VXB_REQUIRE(c, c->res_n > 0, "vxb_update_list_pack: no resident list uploaded");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, launch_pack_chunks(c->world(start_pos), c->res_list.p, mask_dev, c->res_n, coords_dev, payload_dev, capacity, c->stream));
+    return VXB_OK;
+}
+
+int vxb_chunks_unpack(vxb_ctx* c, const uint32_t start_pos[3], const uint32_t* coords_dev, const uint32_t* payload_dev, uint32_t capacity) {
+    if (!c || !start_pos) return VXB_ERR_INVALID;
+    VXB_WINDOW(c, start_pos);
+    VXB_REQUIRE(c, coords_dev && payload_dev && capacity > 0, "vxb_chunks_unpack: NULL buffer or zero capacity");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, launch_unpack_chunks(c->world(start_pos), coords_dev, payload_dev, capacity, c->stream));
+    return VXB_OK;
+}
+
 // ---- sharded collision batches: log of voxel damage adds, replayed on the other replicas ----
 int vxb_damage_log_enable(vxb_ctx* c, uint32_t capacity) {
     if (!c) return VXB_ERR_INVALID;

@@ -74,6 +74,11 @@ __device__ __forceinline__ uint32_t table_lookup_in_window(const World& w, uint3
                    tz = wrap_in_window(cz, w.sp[2], w.spm[2], w.rs[2]);
     return __ldg(&w.table[((uint64_t)tx * w.rs[1] + ty) * w.rs[2] + tz]);
 }
+// pool slot of chunk (cx, cy, cz): 0 outside the window (and for unloaded chunks), 1 for all-air chunks
+__device__ __forceinline__ uint32_t resolve_chunk_slot(const World& w, uint32_t cx, uint32_t cy, uint32_t cz) {
+    if (!(cx >= w.sp[0] && cy >= w.sp[1] && cz >= w.sp[2] && cx - w.sp[0] < w.rs[0] && cy - w.sp[1] < w.rs[1] && cz - w.sp[2] < w.rs[2])) return 0;
+    return table_lookup_in_window(w, cx, cy, cz);
+}
 __device__ __forceinline__ uint32_t get_data(const World& w, uint32_t x, uint32_t y, uint32_t z) {
     if (!in_window(w, x, y, z)) return VOX_OOB;
     const uint32_t slot = table_lookup_in_window(w, x >> 4, y >> 4, z >> 4);

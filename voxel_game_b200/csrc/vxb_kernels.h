@@ -73,6 +73,13 @@ cudaError_t launch_apply_damage(const World& w, const uint32_t* records, uint32_
 cudaError_t launch_apply_damage_counted(const World& w, const uint32_t* records, const uint32_t* count_dev, uint32_t capacity, cudaStream_t st);
 cudaError_t launch_players(const World& w, vxb_player* players, uint32_t n_players, float dt, cudaStream_t st);
 
+// replicated worlds (k_replicas.cu): changed-payload mask from the change flags, pack by list entry, unpack by chunk coordinates
+cudaError_t launch_changed_chunk_mask(const uint32_t* flags, uint32_t cols, uint32_t ry, uint32_t rz, const uint32_t offset[3], uint8_t* mask,
+                                      uint8_t* ghost, cudaStream_t st);
+cudaError_t launch_pack_chunks(const World& w, const uint32_t* list, const uint8_t* mask, uint32_t n, uint32_t* coords, uint32_t* payload,
+                               uint32_t capacity, cudaStream_t st);
+cudaError_t launch_unpack_chunks(const World& w, const uint32_t* coords, const uint32_t* payload, uint32_t capacity, cudaStream_t st);
+
 // RasterizerSystem::draw (rasterizer.rs:196-323) + frag.glsl:716-728 as kernels (k_raster.cu)
 cudaError_t launch_raster_draw(const float* positions, const float* normals, uint32_t n_vertices, const vxb_raster_instance* instances,
                                uint32_t n_instances, const float view[16], const float proj[16], uint32_t W, uint32_t H, unsigned long long* key,

@@ -286,6 +286,19 @@ class VoxelComputePipeline:
         self._check(self._lib.vxb_update_list_flags_device(self._h, ctypes.byref(a), ctypes.byref(n)))
         return a.value, n.value
 
+    # -- replicated worlds: changed-payload mask, pack, unpack (device pointers throughout) --------
+    def changed_chunk_mask(self, cols, ry, rz, offset, mask_ptr, ghost_mask_ptr=None):
+        g = None if ghost_mask_ptr is None else ctypes.c_void_p(int(ghost_mask_ptr))
+        self._check(self._lib.vxb_changed_chunk_mask(self._h, int(cols), int(ry), int(rz), ptr(_u32(offset, 3)), ctypes.c_void_p(int(mask_ptr)), g))
+
+    def update_list_pack(self, start_pos, mask_ptr, coords_ptr, payload_ptr, capacity):
+        self._check(self._lib.vxb_update_list_pack(self._h, ptr(_u32(start_pos, 3)), ctypes.c_void_p(int(mask_ptr)), ctypes.c_void_p(int(coords_ptr)),
+                                                   ctypes.c_void_p(int(payload_ptr)), int(capacity)))
+
+    def chunks_unpack(self, start_pos, coords_ptr, payload_ptr, capacity):
+        self._check(self._lib.vxb_chunks_unpack(self._h, ptr(_u32(start_pos, 3)), ctypes.c_void_p(int(coords_ptr)), ctypes.c_void_p(int(payload_ptr)),
+                                                int(capacity)))
+
     # -- sharded collision batches (voxel damage log, see include/voxelb200.h) ----------------
     def damage_log_enable(self, capacity):
         self._check(self._lib.vxb_damage_log_enable(self._h, int(capacity)))

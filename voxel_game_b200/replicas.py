@@ -149,3 +149,66 @@ def gather_changed_chunks(dist, torch, mask, own_pool, own_first_global, replica
             replica_pool.index_copy_(0, all_idx[r, :counts[r]], all_chunks[r, :counts[r]])
             total += counts[r]
     return total
+
+
+class DeviceReplicaRefresh:
+    """The changed-chunk refresh of `gather_changed_chunks` with every step on the device (CUDA only): the mask
+    comes from one kernel (vxb_changed_chunk_mask), the marked chunks are packed by another into a fixed-capacity
+    (coords, payload) buffer whose record count lives in the buffer itself (vxb_update_list_pack), the buffers are
+    all-gathered as they are, and one kernel per source rank writes the records into the replica by chunk
+    coordinates (vxb_chunks_unpack). Nothing is read back between the update and the refreshed replica, so the
+    host never waits inside a tick; `counts()` exposes the gathered record counts for a deferred overflow check.
+
+    slab / replica: VoxelComputePipeline objects on the same CUDA stream; the slab's resident list must be the
+    full (x, y, z) grid of its own columns (shard.cols x ry x rz)."""
+
+    def __init__(self, torch, dist, slab, replica, shard, slab_start_pos, replica_start_pos, capacity):
+        self.torch, self.dist, self.slab, self.replica, self.shard = torch, dist, slab, replica, shard
+        self.lsp, self.rsp, self.cap = tuple(slab_start_pos), tuple(replica_start_pos), int(capacity)
+        self.rank, self.ws = shard.rank, shard.world_size
+        self.ry, self.rz = int(shard.render_size[1]), int(shard.render_size[2])
+        dev = torch.device("cuda", torch.cuda.current_device())
+        self.mask = torch.zeros(shard.n_own, dtype=torch.uint8, device=dev)
+        self.ghost = torch.zeros(shard.plane_chunks, dtype=torch.uint8, device=dev) if shard.ghost else None
+        self.recv = torch.zeros(shard.plane_chunks, dtype=torch.uint8, device=dev) if shard.rank > 0 else None
+        self.coords = torch.zeros((self.cap + 1, 4), dtype=torch.int32, device=dev)
+        self.payload = torch.empty((self.cap, 4096), dtype=torch.int32, device=dev)
+        if self.ws > 1:
+            self.g_coords = torch.zeros((self.ws * (self.cap + 1), 4), dtype=torch.int32, device=dev)
+            self.g_payload = torch.empty((self.ws * self.cap, 4096), dtype=torch.int32, device=dev)
+
+    def refresh(self, offset, also=None):
+        """offset: the phase of the update dispatch that just ran; also: optional int64 tensor of own chunk
+        indices to refresh regardless (e.g. chunks regenerated this tick)."""
+        torch, dist, sh = self.torch, self.dist, self.shard
+        self.slab.changed_chunk_mask(sh.cols, self.ry, self.rz, offset, self.mask.data_ptr(), None if self.ghost is None else self.ghost.data_ptr())
+        if also is not None:
+            self.mask[also] = 1
+        if self.ws > 1 and offset[0] == 1:
+            ops = []
+            if self.ghost is not None:
+                ops.append(dist.P2POp(dist.isend, self.ghost, self.rank + 1))
+            if self.recv is not None:
+                ops.append(dist.P2POp(dist.irecv, self.recv, self.rank - 1))
+            if ops:
+                for req in dist.batch_isend_irecv(ops):
+                    req.wait()
+            if self.recv is not None:
+                self.mask[:sh.plane_chunks] |= self.recv
+        self.slab.update_list_pack(self.lsp, self.mask.data_ptr(), self.coords.data_ptr(), self.payload.data_ptr(), self.cap)
+        if self.ws == 1:
+            self.replica.chunks_unpack(self.rsp, self.coords.data_ptr(), self.payload.data_ptr(), self.cap)
+            return
+        dist.all_gather_into_tensor(self.g_coords, self.coords)
+        dist.all_gather_into_tensor(self.g_payload, self.payload)
+        gc = self.g_coords.view(self.ws, self.cap + 1, 4)
+        gp = self.g_payload.view(self.ws, self.cap, 4096)
+        for r in range(self.ws):
+            self.replica.chunks_unpack(self.rsp, gc[r].data_ptr(), gp[r].data_ptr(), self.cap)
+
+    def counts(self):
+        """Record counts of the last refresh, one per source rank (device tensor; > capacity means that rank's
+        buffer overflowed and its replica rows are incomplete)."""
+        if self.ws == 1:
+            return self.coords[self.cap, :1]
+        return self.g_coords.view(self.ws, self.cap + 1, 4)[:, self.cap, 0]
