@@ -590,12 +590,13 @@ def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp,
       1. worldgen: 512 chunks regenerated in place (512 / N per rank, in its own slab; forced, so that slots
          and the table stay put and only chunk payloads travel to the replicas),
       2. the update step over all chunks (x-slab sharded, halo exchange on offset.x == 1 phases),
-      3. replica refresh: chunks whose change flag is set (plus the regenerated ones) are all-gathered into
-         every rank's full replica of the world (replicas.gather_changed_chunks),
+      3. replica refresh: chunks whose payload changed (from the change flags, plus the regenerated ones) are packed,
+         all-gathered and unpacked into every rank's full replica of the world, all on the device
+         (replicas.DeviceReplicaRefresh),
       4. 64 camera views x 1920x1080 primary rays against the replica, 64 / N views per rank.
     Device time per phase (CUDA events on the one stream everything runs on), max over ranks."""
     from tests import scenes
-    from voxel_game_b200.replicas import changed_chunk_mask, exchange_ghost_mask, gather_changed_chunks
+    from voxel_game_b200.replicas import DeviceReplicaRefresh, gather_changed_chunks
     from voxel_game_b200.sharding import sharded_update
 
     RS, SP = tuple(args.world), C3_SP
@@ -622,7 +623,11 @@ def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp,
         mark[b:b + cap] = False
     del mark
     same0 = bool(torch.equal(rep_pool[first_global:first_global + n_own], own_pool))
-    flags_t = torch.as_tensor(DevView(gpu.update_list_flags_device()[0], n_own), device="cuda")
+    del idx_buf, chunk_buf
+    # per-tick refresh: mask, pack and unpack kernels with fixed-capacity buffers, nothing read back inside the tick
+    refresh_cap = max(512, 4096 // world_size)
+    refresher = DeviceReplicaRefresh(torch, dist, gpu, rep, shard, lsp, SP, refresh_cap)
+    tick_counts = []
     # regenerated chunks: first column of the slab, all y, the first 32/N z  (512 / N chunks)
     per_rank = max(1, 512 // world_size)
     nz = max(1, per_rank // RS[1])
@@ -651,20 +656,15 @@ def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp,
         ev[1].record()
         sharded_update(torch, gpu, shard, lsp, off, exchange, main, side)
         ev[2].record()
-        mask, ghost_mask = changed_chunk_mask(torch, flags_t, shard.cols, RS[1], RS[2], off, bool(shard.ghost))
-        mask[regen_t] = True
-        if off[0] == 1:
-            got = exchange_ghost_mask(dist, torch, ghost_mask, rank, world_size, pc, flags_t.device)
-            if got is not None:
-                mask[:pc] |= got
-        m = gather_changed_chunks(dist, torch, mask, own_pool, first_global, rep_pool, idx_buf, chunk_buf, rank, world_size)
+        refresher.refresh(off, also=regen_t)
         ev[3].record()
+        if timed:
+            tick_counts.append(refresher.counts().clone())  # device tensor; looked at after the run
         for b in range(0, len(mine), 8):
             rep.raymarch(SP, mine[b:b + 8], W, H, caps)
         ev[4].record()
         torch.cuda.synchronize()
         if timed:
-            moved += m
             for k in range(4):
                 acc[names[k]] += ev[k].elapsed_time(ev[k + 1])
 
@@ -677,14 +677,17 @@ def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp,
     if world_size > 1:
         dist.barrier()
     same1 = bool(torch.equal(rep_pool[first_global:first_global + n_own], own_pool))
+    counts = torch.stack(tick_counts).to(torch.int64)
+    moved = int(counts.sum().item())
+    overflowed = bool((counts > refresh_cap).any().item())
     t = torch.tensor([acc[k] / n_ticks for k in names] + [sum(acc.values()) / n_ticks, 0.0 if (same0 and same1) else 1.0], dtype=torch.float64, device="cuda")
     if world_size > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     t = t.tolist()
     rep.close()
     return {"metric": "ticks/s", "value": 1e3 / t[4], "unit": "ticks/s", "ms_per_tick": t[4], "n_gpus": world_size, "ticks": n_ticks,
-            "phases_ms": {names[k]: t[k] for k in range(4)}, "replica_matches_slab": t[5] == 0.0,
-            "chunks_refreshed_per_tick": moved / n_ticks,
+            "phases_ms": {names[k]: t[k] for k in range(4)}, "replica_matches_slab": t[5] == 0.0 and not overflowed,
+            "chunks_refreshed_per_tick": moved / n_ticks, "refresh_buffer_chunks_per_rank": refresh_cap,
             "config": {"workload": "BASELINE configs[4]: %d chunks regenerated + update over all %d chunks + 64 views x 1920x1080 primary rays per tick"
                                    % (per_rank * world_size, n_total),
                        "note": "regeneration is forced (slots keep their place) instead of forced = false; per-phase times are the max over ranks, "

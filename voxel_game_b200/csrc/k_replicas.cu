@@ -35,23 +35,35 @@ __global__ void k_changed_chunk_mask(const uint32_t* __restrict__ flags, uint32_
     else ghost[i - cols * plane] = (uint8_t)changed;
 }
 
-// One CTA per resident-list entry: entries whose mask byte is set append (x, y, z, 0) and their 16 KiB payload.
-// coords has capacity + 1 rows: row `capacity` word 0 is the running count (may exceed capacity: overflow).
-__global__ void __launch_bounds__(256) k_pack_chunks(World w, const uint4* __restrict__ list, const uint8_t* __restrict__ mask, uint32_t n,
-                                                     uint4* __restrict__ coords, uint4* __restrict__ payload, uint32_t capacity) {
-    const uint32_t i = blockIdx.x;
-    if (i >= n || mask[i] == 0) return;
-    __shared__ uint32_t s_at, s_slot;
-    if (threadIdx.x == 0) {
-        const uint4 e = list[i];
-        s_at = atomicAdd(reinterpret_cast<uint32_t*>(&coords[capacity]), 1u);
-        s_slot = resolve_chunk_slot(w, e.x, e.y, e.z);
-        if (s_at < capacity) coords[s_at] = make_uint4(e.x, e.y, e.z, 0u);
+// Pack in two steps. Select: one thread per resident-list entry, entries whose mask byte is set append their list
+// index (warp-aggregated atomic) — coords has capacity + 1 rows and word 0 of row `capacity` is the running count,
+// which may exceed capacity (overflow, visible to the caller). Copy: one CTA per selected record fills in the chunk
+// coordinates and copies the 16 KiB payload.
+__global__ void __launch_bounds__(256) k_pack_select(const uint8_t* __restrict__ mask, uint32_t n, uint4* __restrict__ coords, uint32_t capacity) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool take = i < n && mask[i] != 0;
+    const uint32_t ballot = __ballot_sync(0xFFFFFFFFu, take);
+    if (ballot == 0) return;
+    const uint32_t lane = threadIdx.x & 31u, leader = __ffs(ballot) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(reinterpret_cast<uint32_t*>(&coords[capacity]), __popc(ballot));
+    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    if (take) {
+        const uint32_t at = base + __popc(ballot & ((1u << lane) - 1u));
+        if (at < capacity) coords[at].w = i;
     }
-    __syncthreads();
-    if (s_at >= capacity) return;
-    const uint4* src = reinterpret_cast<const uint4*>(w.pool + ((size_t)s_slot << 12));
-    uint4* dst = payload + (size_t)s_at * 1024;
+}
+__global__ void __launch_bounds__(256) k_pack_copy(World w, const uint4* __restrict__ list, uint4* __restrict__ coords, uint4* __restrict__ payload,
+                                                   uint32_t capacity) {
+    const uint32_t at = blockIdx.x;
+    const uint32_t count = min(reinterpret_cast<const uint32_t*>(&coords[capacity])[0], capacity);
+    if (at >= count) return;
+    const uint4 e = list[coords[at].w];
+    const uint32_t slot = resolve_chunk_slot(w, e.x, e.y, e.z);
+    __syncthreads();  // every thread has read coords[at].w before thread 0 rewrites the row
+    if (threadIdx.x == 0) coords[at] = make_uint4(e.x, e.y, e.z, 0u);
+    const uint4* src = reinterpret_cast<const uint4*>(w.pool + ((size_t)slot << 12));
+    uint4* dst = payload + (size_t)at * 1024;
 #pragma unroll
     for (int k = 0; k < 4; k++) dst[threadIdx.x + 256 * k] = src[threadIdx.x + 256 * k];
 }
@@ -83,8 +95,9 @@ cudaError_t launch_pack_chunks(const World& w, const uint32_t* list, const uint8
                                uint32_t capacity, cudaStream_t st) {
     cudaError_t e = cudaMemsetAsync(coords + (size_t)capacity * 4, 0, 16, st);
     if (e != cudaSuccess || n == 0) return e;
-    k_pack_chunks<<<n, 256, 0, st>>>(w, reinterpret_cast<const uint4*>(list), mask, n, reinterpret_cast<uint4*>(coords), reinterpret_cast<uint4*>(payload),
-                                     capacity);
+    k_pack_select<<<(n + 255) / 256, 256, 0, st>>>(mask, n, reinterpret_cast<uint4*>(coords), capacity);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    k_pack_copy<<<capacity, 256, 0, st>>>(w, reinterpret_cast<const uint4*>(list), reinterpret_cast<uint4*>(coords), reinterpret_cast<uint4*>(payload), capacity);
     return cudaGetLastError();
 }
 
