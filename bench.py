@@ -639,7 +639,7 @@ def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp,
     cam_y = _surface_from_gpu(rep, rep.read_table(), RS, SP, cx, cz) + 4.0  # surface + 4 at the world centre, as config 4 places its players
     grid = scenes.players_grid(8, (cx, cam_y, cz), 48.0, cam_y, seed=64)
     cams = np.concatenate([scenes.camera(tuple(grid["pos"][k, :3]), k * 2 * np.pi / 64, -0.2) for k in range(64)])
-    mine = cams[rank * 64 // world_size:(rank + 1) * 64 // world_size]
+    mine = cams[rank::world_size]  # interleaved: neighbouring yaw angles see similar scenes, so contiguous ranges would load the ranks unevenly
     W, H = 1920, 1080
     caps = vg.RayCaps(100, 40, 20, 15, 0)
     names = ("worldgen", "update", "replica_refresh", "rays")
