@@ -216,9 +216,15 @@ def run_ours(args):
     # clocks are sampled from here on: the settle ticks are the same kernel on the same world as the timed steps, and
     # the timed region alone (16 steps x 5 ms) is shorter than one nvidia-smi sampling period
     sampler = ClockSampler(local_rank) if rank == 0 else None
+    unsettled = [torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)]
     for i in range(args.settle):
+        if i == 0:
+            unsettled[0].record()
+        if i == 8:
+            unsettled[1].record()
         settle_step(i)
     torch.cuda.synchronize()
+    unsettled_ms = unsettled[0].elapsed_time(unsettled[1]) / 8 if args.settle > 8 else None
 
     def step(i):
         launches[0] += sharded_update(torch, gpu, shard, lsp, PHASES[i % 8], exchange, stream, side)
@@ -322,6 +328,10 @@ def run_ours(args):
         }
         if alt is not None:
             result["unconditional_store_variant"] = alt
+        if unsettled_ms is not None and world_size == 1:
+            result["first_ticks_after_worldgen"] = {"ms_per_step": unsettled_ms, "value": n_total_vox / (unsettled_ms / 1e3), "unit": "voxel-updates/s",
+                                                    "note": "the 8 ticks right after worldgen (one per phase), when distance fields are still being built and most "
+                                                            "vectors change: the store-eliding kernel with little to elide"}
         if achieved is not None:
             result["roofline"] = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                                   "traffic": traffic_from_profiles("k_voxel_update_elide_dram_bytes_per_chunk" if (args.variant & 0xFF) == 2
