@@ -118,7 +118,19 @@ __device__ __forceinline__ yw voronoise_staged(const FieldStage& fs, const Field
         const float dx = ((float)kx - fx) + o.x, dy = ((float)ky - fy) + o.y, dz = ((float)kz - fz) + o.z;
         const float dsq = dx * dx + dy * dy + dz * dz;
         if (dsq < 2.0f) {
-            float t = gclamp(sqrtf(dsq) / 1.414f, 0.0f, 1.0f);
+            // smoothstep's (x - 0) / (1.414 - 0): the divisor is a constant, so the quotient is its rounded reciprocal
+            // times x plus one exact-remainder step — the IEEE quotient for every float in [2^-24, 2) (checked
+            // exhaustively on the CPU, 2.1e8 values); smaller x takes the divider
+            const float len = sqrtf(dsq);
+            constexpr float kDiv = 1.414f, kInv = 1.0f / 1.414f;
+            float quot;
+            if (len >= 5.9604645e-8f) {
+                const float q0 = len * kInv;
+                quot = __fmaf_rn(__fmaf_rn(-q0, kDiv, len), kInv, q0);
+            } else {
+                quot = len / kDiv;
+            }
+            float t = gclamp(quot, 0.0f, 1.0f);
             const float w = 1.0f - t * t * (3.0f - 2.0f * t);
             ax += o.w * w;
             ay += w;
