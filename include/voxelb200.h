@@ -303,6 +303,77 @@ int vxb_update_list_flags_device(vxb_ctx* ctx, void** flags_dev, uint32_t* n);
  * results do not depend on it. */
 int vxb_set_update_kernel(vxb_ctx* ctx, int variant);
 
+/* ---- the update step over several GPUs ------------------------------------------------
+ * No counterpart in the reference, which drives one GPU through one queue (client/src/app.rs:126-138,
+ * :206). The world window is cut into x-slabs of whole chunk columns, one slab ctx per GPU. The only
+ * coupling between slabs is the Margolus straddle (compute_voxel.glsl:91): with offset.x == 1 the last
+ * column of slab g reads and writes the x == 0 voxel plane of slab g+1's first column. There is no halo
+ * copy and no collective: a slab's voxel pool is CUDA virtual-memory-management memory, its first
+ * column a separate physical allocation that the left neighbour maps into its own pool as the slots of
+ * a ghost column, so the unchanged update kernel reaches it over NVLink. Neighbours are kept in order by
+ * tick counters in a mailbox each slab shares with its neighbours (see csrc/slab.cu).
+ *
+ * A slab ctx is a vxb_ctx: every other entry point works on it, with the slab's LOCAL window
+ * (vxb_slab_info.local_start_pos / local_render_size; the ghost column is the window's last column).
+ * Its pool slots are assigned by position (vxb_slab_info.slot_*), not by the free list, so the host
+ * queue entry points that allocate slots (vxb_compute's worldgen) are not for slab ctxs.
+ *
+ *   vxb_slab_create        slab `rank` of `world_size` of the window world_settings->render_size at
+ *                          start_pos (max_loaded_chunks is ignored: computed). col_splits: NULL = equal
+ *                          slabs (render_size.x divisible by world_size), else world_size + 1 rising
+ *                          column indices from 0 to render_size.x.
+ *   vxb_slab_export_fds    POSIX file descriptors of this slab's first column (for the LEFT neighbour)
+ *                          and mailbox (for both neighbours). The caller carries them to the neighbouring
+ *                          process (SCM_RIGHTS) and closes them afterwards; either pointer may be NULL.
+ *   vxb_slab_import_fds    maps the right neighbour's first column as the ghost column and both
+ *                          neighbours' mailboxes; -1 where there is no such neighbour. The descriptors
+ *                          stay the caller's to close.
+ *   vxb_slab_populate      worldgen of every own chunk into its positional slot (forced != 0: all-air
+ *                          chunks keep their slot), host mirror refreshed, resident update list = the
+ *                          loaded own chunks in (x, y, z) order. Synchronises.
+ *   vxb_slab_publish_column / vxb_slab_sync_ghost_table   after the table of the first column changed:
+ *                          publish its entries, then (once every slab has published AND synchronised —
+ *                          the caller's barrier) the left neighbour copies them into its ghost column.
+ *   vxb_slab_update        one update dispatch over the resident list: wait for the neighbour this
+ *                          offset depends on, run the kernel, report the tick to both neighbours; all
+ *                          stream-ordered, nothing blocks the host. Every slab must issue the same
+ *                          sequence of offsets. Before the first update and before reading a neighbour-
+ *                          written plane back, synchronise all slabs (the caller's barrier).
+ *   vxb_slab_status        synchronises and fails with VXB_ERR_STATE if a wait ran into its time limit.
+ *
+ * One process driving several devices uses vxb_group_*: the same slabs, linked directly. */
+typedef struct vxb_slab_info {
+    uint32_t rank, world_size;
+    uint32_t own_cols, ghost_cols, chunks_per_column;
+    uint32_t local_render_size[3], local_start_pos[3];
+    uint32_t slot_first; /* slot of local chunk (0, y, z) = slot_first + y*rz + z */
+    uint32_t slot_rest;  /* slot of local chunk (x, y, z), 0 < x < own_cols = slot_rest + ((x-1)*ry + y)*rz + z */
+    uint32_t slot_ghost; /* slot of ghost chunk (own_cols, y, z) = slot_ghost + y*rz + z (the right neighbour's memory) */
+    uint32_t max_loaded_chunks;
+} vxb_slab_info;
+int vxb_slab_create(const vxb_settings* world_settings, const uint32_t start_pos[3], int device, int rank, int world_size,
+                    const uint32_t* col_splits, vxb_ctx** out);
+int vxb_slab_get_info(const vxb_ctx* ctx, vxb_slab_info* out);
+int vxb_slab_export_fds(vxb_ctx* ctx, int* first_column_fd, int* mailbox_fd);
+int vxb_slab_import_fds(vxb_ctx* ctx, int right_first_column_fd, int right_mailbox_fd, int left_mailbox_fd);
+int vxb_slab_populate(vxb_ctx* ctx, int forced);
+int vxb_slab_publish_column(vxb_ctx* ctx);
+int vxb_slab_sync_ghost_table(vxb_ctx* ctx);
+int vxb_slab_update(vxb_ctx* ctx, const uint32_t offset[3]);
+int vxb_slab_status(vxb_ctx* ctx);
+
+typedef struct vxb_group vxb_group;
+/* devices[r] = CUDA device of slab r (a device may appear more than once). The ctxs are owned by the group. */
+int vxb_group_create(const vxb_settings* world_settings, const uint32_t start_pos[3], const int* devices, int n_devices,
+                     const uint32_t* col_splits, vxb_group** out);
+void vxb_group_destroy(vxb_group* group);
+int vxb_group_size(const vxb_group* group);
+vxb_ctx* vxb_group_ctx(vxb_group* group, int rank); /* borrowed */
+const char* vxb_group_last_error(const vxb_group* group);
+int vxb_group_populate(vxb_group* group, int forced);              /* populate + ghost tables of every slab */
+int vxb_group_update(vxb_group* group, const uint32_t offset[3]);  /* vxb_slab_update on every slab; asynchronous */
+int vxb_group_synchronize(vxb_group* group);                       /* vxb_slab_status on every slab */
+
 /* ---- the ray pass (src/raytracer.rs, shaders/frag.glsl) --------------------------------------- */
 
 /* PointLightingSystem::draw (src/raytracer.rs:234-305) without the graphics pipeline: one primary

@@ -14,6 +14,8 @@ from .pipeline import (  # noqa: F401
     GraphicsSettings,
     PointLightingSystem,
     RasterizerSystem,
+    SlabGroup,
+    SlabPipeline,
     VoxelComputePipeline,
     WorldGen,
     initial_start_pos,

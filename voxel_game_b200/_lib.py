@@ -71,6 +71,18 @@ class RayBuffers(ctypes.Structure):
     ]
 
 
+class SlabInfo(ctypes.Structure):
+    """vxb_slab_info"""
+
+    _fields_ = [
+        ("rank", c_u32), ("world_size", c_u32),
+        ("own_cols", c_u32), ("ghost_cols", c_u32), ("chunks_per_column", c_u32),
+        ("local_render_size", c_u32 * 3), ("local_start_pos", c_u32 * 3),
+        ("slot_first", c_u32), ("slot_rest", c_u32), ("slot_ghost", c_u32),
+        ("max_loaded_chunks", c_u32),
+    ]
+
+
 # numpy views of the 112 / 128 / 16-byte entity structs (common.glsl:8-45)
 PROJECTILE_DTYPE = np.dtype(
     [
@@ -168,6 +180,23 @@ SIGNATURES = {
     "vxb_ray_results": (ctypes.c_int, [c_vp, ctypes.POINTER(RayBuffers)]),
     "vxb_ray_download": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "vxb_raymarch_rays_noalloc": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_u32, ctypes.c_int, c_u32, c_u32, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "vxb_slab_create": (ctypes.c_int, [ctypes.POINTER(Settings), c_vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_vp, ctypes.POINTER(c_vp)]),
+    "vxb_slab_get_info": (ctypes.c_int, [c_vp, ctypes.POINTER(SlabInfo)]),
+    "vxb_slab_export_fds": (ctypes.c_int, [c_vp, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int)]),
+    "vxb_slab_import_fds": (ctypes.c_int, [c_vp, ctypes.c_int, ctypes.c_int, ctypes.c_int]),
+    "vxb_slab_populate": (ctypes.c_int, [c_vp, ctypes.c_int]),
+    "vxb_slab_publish_column": (ctypes.c_int, [c_vp]),
+    "vxb_slab_sync_ghost_table": (ctypes.c_int, [c_vp]),
+    "vxb_slab_update": (ctypes.c_int, [c_vp, c_vp]),
+    "vxb_slab_status": (ctypes.c_int, [c_vp]),
+    "vxb_group_create": (ctypes.c_int, [ctypes.POINTER(Settings), c_vp, c_vp, ctypes.c_int, c_vp, ctypes.POINTER(c_vp)]),
+    "vxb_group_destroy": (None, [c_vp]),
+    "vxb_group_size": (ctypes.c_int, [c_vp]),
+    "vxb_group_ctx": (c_vp, [c_vp, ctypes.c_int]),
+    "vxb_group_last_error": (ctypes.c_char_p, [c_vp]),
+    "vxb_group_populate": (ctypes.c_int, [c_vp, ctypes.c_int]),
+    "vxb_group_update": (ctypes.c_int, [c_vp, c_vp]),
+    "vxb_group_synchronize": (ctypes.c_int, [c_vp]),
     "vxb_read_pool": (ctypes.c_int, [c_vp, c_u64, c_u64, c_vp]),
     "vxb_write_pool": (ctypes.c_int, [c_vp, c_u64, c_u64, c_vp]),
     "vxb_read_table": (ctypes.c_int, [c_vp, c_vp]),

@@ -12,8 +12,15 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libvoxelb200.so")
-SOURCES = ["k_update.cu", "k_worldgen.cu", "k_raymarch.cu", "k_entities.cu", "pipeline.cu", "noalloc.cu", "k_raster.cu", "k_replicas.cu"]
-HEADERS = ["vxb_device.cuh", "vxb_kernels.h", "host_queues.h", os.path.join("..", "..", "include", "voxelb200.h")]
+import glob
+
+SOURCES = ["k_update.cu", "k_worldgen.cu", "k_raymarch.cu", "k_entities.cu", "pipeline.cu", "noalloc.cu", "k_raster.cu", "k_replicas.cu", "slab.cu"]
+
+
+def headers():
+    """Every header a source may include: a change to any of them rebuilds the library."""
+    return sorted(glob.glob(os.path.join(CSRC, "*.cuh")) + glob.glob(os.path.join(CSRC, "*.h"))) + [
+        os.path.join(HERE, "..", "include", "voxelb200.h")]
 
 # -fmad=false: no FMA contraction — float parity with the oracle (DESIGN.md "Float semantics").
 # -lineinfo: ncu source pages map back to these files.
@@ -36,7 +43,7 @@ def needs_build():
     if not os.path.exists(LIB):
         return True
     t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, f) for f in SOURCES + HEADERS] + [os.path.abspath(__file__)]
+    deps = [os.path.join(CSRC, f) for f in SOURCES] + headers() + [os.path.abspath(__file__)]
     return any(os.path.getmtime(d) > t for d in deps)
 
 

@@ -26,6 +26,8 @@
 //  * the reference re-reads every voxel in set_data; here the original stays in registers.
 //  * the shader's straight-line block logic (~200 instructions per voxel) would make the kernel
 //    issue-bound 5x over; margolus_block() classifies the block first (exact, see there).
+#include <mutex>
+
 #include "vxb_device.cuh"
 #include "vxb_kernels.h"
 
@@ -666,24 +668,36 @@ __global__ void __launch_bounds__(512) k_voxel_update_gather(World w, const uint
 
 template <int PHASE, bool ELIDE>
 static cudaError_t launch_one(const World& w, const uint4* list, uint32_t n, uint32_t* flags, int run_code, cudaStream_t st) {
-    static int grid_cap = 0;  // per instantiation: SMs x resident CTAs (one device model per process)
+    // Per instantiation AND per device: the opt-in to > 48 KB of dynamic shared memory is a per-device function
+    // attribute, and SMs x resident CTAs is a property of the device the launch goes to (the current one).
+    constexpr int MAX_DEVICES = 64;
+    static int grid_cap[MAX_DEVICES] = {0};
+    static std::mutex setup_mutex;
     auto kern = k_voxel_update_tiled<PHASE, ELIDE>;
-    if (grid_cap == 0) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UpdSmem));
-        if (e != cudaSuccess) return e;
-        int dev = 0, sms = 0, per_sm = 0;
-        if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
-        if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
-        if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, UPD_THREADS, sizeof(UpdSmem))) != cudaSuccess) return e;
-        if (per_sm < 1) return cudaErrorLaunchOutOfResources;
-        grid_cap = sms * per_sm;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= MAX_DEVICES) return cudaErrorInvalidDevice;
+    int cap;
+    {
+        std::lock_guard<std::mutex> lock(setup_mutex);
+        if (grid_cap[dev] == 0) {
+            if ((e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UpdSmem))) != cudaSuccess) return e;
+            int sms = 0, per_sm = 0;
+            if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+            if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, UPD_THREADS, sizeof(UpdSmem))) != cudaSuccess) return e;
+            if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+            grid_cap[dev] = sms * per_sm;
+        }
+        cap = grid_cap[dev];
     }
+    const int grid_cap_dev = cap;
     // runs of 8 list neighbours per CTA visit once the list is long enough to keep every CTA busy with them.
     // (config 3, G voxel-updates/s, all stores / elided: R=1 424/888, R=4 530/881, R=8 547/885, R=16 554/869, R=32 557/857)
     // (run_code != 0 forces 2^(run_code-1): tests use it to drive the hand-over path with small worlds)
-    const uint32_t run_log2 = run_code ? (uint32_t)(run_code - 1) : (n >= 8u * 8u * (uint32_t)grid_cap ? 3u : 0u);
+    const uint32_t run_log2 = run_code ? (uint32_t)(run_code - 1) : (n >= 8u * 8u * (uint32_t)grid_cap_dev ? 3u : 0u);
     const uint32_t n_runs = (n + (1u << run_log2) - 1) >> run_log2;
-    const uint32_t grid = n_runs < (uint32_t)grid_cap ? n_runs : (uint32_t)grid_cap;
+    const uint32_t grid = n_runs < (uint32_t)grid_cap_dev ? n_runs : (uint32_t)grid_cap_dev;
     kern<<<grid, UPD_THREADS, sizeof(UpdSmem), st>>>(w, list, n, flags, run_log2);
     return cudaGetLastError();
 }

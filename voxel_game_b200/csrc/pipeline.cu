@@ -10,159 +10,11 @@
 #include <string>
 #include <vector>
 
-#include "host_queues.h"
-#include "vxb_device.cuh"
-#include "vxb_kernels.h"
-
-namespace vxb {
+#include "vxb_ctx.h"
 
 static thread_local std::string g_create_error;
 
-static_assert(sizeof(vxb_projectile) == 112, "Projectile is 112 bytes (common.glsl:8-25)");
-static_assert(sizeof(vxb_player) == 128, "Player is 128 bytes (common.glsl:27-38)");
-static_assert(sizeof(vxb_collision) == 16, "Collision is 16 bytes (common.glsl:40-45)");
-
-template <typename T>
-struct DevBuf {
-    T* p = nullptr;
-    size_t n = 0;
-    cudaError_t alloc(size_t count) {
-        n = count;
-        return cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T));
-    }
-    cudaError_t ensure(size_t count) {
-        if (count <= n && p) return cudaSuccess;
-        if (p) cudaFree(p);
-        p = nullptr;
-        return alloc(count);
-    }
-    void release() {
-        if (p) cudaFree(p);
-        p = nullptr;
-        n = 0;
-    }
-};
-template <typename T>
-struct PinBuf {
-    T* p = nullptr;
-    size_t n = 0;
-    cudaError_t alloc(size_t count) {
-        n = count;
-        return cudaMallocHost(&p, std::max<size_t>(count, 1) * sizeof(T));
-    }
-    cudaError_t ensure(size_t count) {
-        if (count <= n && p) return cudaSuccess;
-        if (p) cudaFreeHost(p);
-        p = nullptr;
-        return alloc(count);
-    }
-    void release() {
-        if (p) cudaFreeHost(p);
-        p = nullptr;
-        n = 0;
-    }
-};
-
-}  // namespace vxb
-
-using namespace vxb;
-
-struct vxb_ctx {
-    vxb_settings s;
-    int device = 0;
-    cudaStream_t own_stream = nullptr;
-    cudaStream_t stream = nullptr;
-    std::string error;
-
-    // device state (D1, D2 of SURVEY §8a)
-    DevBuf<uint32_t> table, pool;
-    DevBuf<vxb_projectile> projectiles;
-    DevBuf<vxb_player> players;
-    DevBuf<vxb_collision> collisions;
-    DevBuf<uint32_t> collision_count;
-    DevBuf<uint32_t> dmg_log, dmg_count;  // voxel damage adds of the last projectile dispatch (vxb_damage_log_enable)
-    uint32_t dmg_cap = 0;
-    DevBuf<int32_t> worldgen_updates;   // ivec4 per 8^3 workgroup
-    DevBuf<uint32_t> worldgen_results;  // one per chunk
-    DevBuf<uint32_t> chunk_updates;     // uvec4 per chunk
-    DevBuf<uint32_t> update_flags;      // chunk_updates[].w, kept separately (4 B instead of 16 B read-back)
-    DevBuf<uint32_t> voxel_writes;      // uvec4
-    DevBuf<unsigned long long> scalars;  // [0] ray iteration total, [1] checksum
-    // resident update list
-    DevBuf<uint32_t> res_list, res_flags;
-    uint32_t res_n = 0;
-    // rays
-    DevBuf<float> ray_pos, ray_normal, ray_ldist, ray_dist, ray_in_pos, ray_in_dir, raster_depth;
-    DevBuf<uint32_t> ray_voxel, ray_leaving, ray_count;
-    DevBuf<vxb_player> cams;
-    uint32_t cams_resident = 0;  // cameras uploaded by vxb_cams_upload (vxb_raymarch / vxb_render overwrite the buffer)
-    DevBuf<float> color;  // float4 per pixel of the last vxb_render
-    // player-mesh G-buffer pass (k_raster.cu)
-    DevBuf<float> mesh_pos, mesh_normal;  // triangle list, 3 floats per vertex
-    uint32_t mesh_vertices = 0;
-    DevBuf<vxb_raster_instance> raster_instances;
-    DevBuf<unsigned long long> raster_key;
-    DevBuf<float> gb_depth, gb_normal, gb_diffuse, gb_max_depth;
-    uint32_t gb_w = 0, gb_h = 0;
-    bool gb_max_depth_valid = false, gb_bound = false;
-    uint64_t n_color = 0;
-    uint64_t n_rays = 0;
-
-    // pinned staging
-    PinBuf<vxb_projectile> h_projectiles;
-    PinBuf<vxb_player> h_players;
-    PinBuf<vxb_collision> h_collisions;
-    PinBuf<uint32_t> h_collision_count;
-    PinBuf<int32_t> h_worldgen_updates;
-    PinBuf<uint32_t> h_worldgen_results;
-    PinBuf<uint32_t> h_chunk_updates;
-    PinBuf<uint32_t> h_update_flags;
-    PinBuf<uint32_t> h_voxel_writes;
-
-    // host bookkeeping (voxel_sim_manager.rs:105-126)
-    std::vector<uint32_t> cpu_chunks_copy;  // (x*ry + y)*rz + z
-    std::vector<uint32_t> available_chunks;
-    int slice_to_unload = -1;  // Direction or -1
-    QueueMapForced worldgen_update_queue;
-    std::unordered_set<Key3, Key3Hash> oob_worldgens;
-    size_t last_worldgen_count = 0;
-    QueueSet4 voxel_write_queue;
-    VoxelUpdateQueue chunk_update_queue;
-    std::vector<int32_t> last_update_priorities;
-    size_t last_update_count = 0;
-    uint32_t upload_projectile_count = 0, upload_player_count = 0;
-    uint32_t last_counts[3] = {0, 0, 0};
-    uint32_t last_start_pos[3] = {0, 0, 0};
-    bool results_pending = false;  // flags / worldgen_results D2H enqueued by the last compute
-    int update_variant = 2;  // tiled kernel with unchanged-store elision (identical results, fewer bytes)
-
-    DamageLog dlog() const { return DamageLog{dmg_cap ? reinterpret_cast<uint4*>(dmg_log.p) : nullptr, dmg_cap, dmg_count.p}; }
-
-    World world(const uint32_t start_pos[3]) const {
-        World w;
-        w.table = table.p;
-        w.pool = pool.p;
-        for (int i = 0; i < 3; i++) {
-            w.rs[i] = s.render_size[i];
-            w.sp[i] = start_pos[i];
-        }
-        world_derive(w);
-        return w;
-    }
-    size_t table_index(const uint32_t pos[3]) const {
-        return ((size_t)(pos[0] % s.render_size[0]) * s.render_size[1] + (pos[1] % s.render_size[1])) * s.render_size[2] +
-               (pos[2] % s.render_size[2]);
-    }
-    uint32_t get_chunk(const uint32_t pos[3]) const { return cpu_chunks_copy[table_index(pos)]; }  // :686-689
-    void set_chunk(const uint32_t pos[3], uint32_t v) { cpu_chunks_copy[table_index(pos)] = v; }    // :691-695
-    bool is_inbounds(const uint32_t loc[3], const uint32_t start_pos[3]) const {                     // :242-251
-        for (int i = 0; i < 3; i++)
-            if (!(loc[i] >= start_pos[i] && loc[i] < start_pos[i] + s.render_size[i])) return false;
-        return true;
-    }
-};
-
-static int fail(vxb_ctx* ctx, int code, const char* fmt, ...) {
+int vxb::fail(vxb_ctx* ctx, int code, const char* fmt, ...) {
     char buf[512];
     va_list ap;
     va_start(ap, fmt);
@@ -171,30 +23,11 @@ static int fail(vxb_ctx* ctx, int code, const char* fmt, ...) {
     if (ctx) ctx->error = buf; else g_create_error = buf;
     return code;
 }
-#define VXB_CUDA(ctx, expr)                                                                        \
-    do {                                                                                           \
-        cudaError_t _e = (expr);                                                                   \
-        if (_e != cudaSuccess) return fail(ctx, VXB_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(_e)); \
-    } while (0)
-// the kernels' one-compare window test needs 16 * (start_pos + render_size) to fit in u32
-static bool window_ok(const vxb_ctx* c, const uint32_t start_pos[3]) {
-    for (int a = 0; a < 3; a++)
-        if ((uint64_t)start_pos[a] + c->s.render_size[a] > (1ull << 28) - 1) return false;
-    return true;
-}
-#define VXB_WINDOW(ctx, sp)                                                                                              \
-    do {                                                                                                                 \
-        if (!window_ok(ctx, sp)) return fail(ctx, VXB_ERR_INVALID, "start_pos + render_size exceeds 2^28 chunks");        \
-    } while (0)
-#define VXB_REQUIRE(ctx, cond, msg)                                  \
-    do {                                                             \
-        if (!(cond)) return fail(ctx, VXB_ERR_INVALID, "%s", msg);   \
-    } while (0)
-
 static void free_ctx(vxb_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
-    c->table.release(); c->pool.release(); c->projectiles.release(); c->players.release(); c->collisions.release();
+    if (c->slab) slab_release(c); else c->pool.release();
+    c->table.release(); c->projectiles.release(); c->players.release(); c->collisions.release();
     c->collision_count.release(); c->worldgen_updates.release(); c->worldgen_results.release(); c->chunk_updates.release();
     c->update_flags.release(); c->voxel_writes.release(); c->scalars.release(); c->res_list.release(); c->res_flags.release();
     c->ray_pos.release(); c->ray_normal.release(); c->ray_ldist.release(); c->ray_dist.release(); c->ray_in_pos.release();
@@ -209,12 +42,7 @@ static void free_ctx(vxb_ctx* c) {
     delete c;
 }
 
-#pragma GCC visibility push(default)
-extern "C" {
-
-const char* vxb_last_error(const vxb_ctx* ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
-
-int vxb_create(const vxb_settings* settings, int device, vxb_ctx** out) {
+int vxb::create_ctx(const vxb_settings* settings, int device, cudaError_t (*pool_alloc)(vxb_ctx*, void*), void* user, vxb_ctx** out) {
     if (!settings || !out) return fail(nullptr, VXB_ERR_INVALID, "vxb_create: null argument");
     *out = nullptr;
     vxb_settings s = *settings;
@@ -252,7 +80,11 @@ int vxb_create(const vxb_settings* settings, int device, vxb_ctx** out) {
     TRY(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
     c->stream = c->own_stream;
     TRY(c->table.alloc(n_table));
-    TRY(c->pool.alloc((size_t)s.max_loaded_chunks * CHUNK_VOLUME));
+    if (pool_alloc) {
+        TRY(pool_alloc(c, user));
+    } else {
+        TRY(c->pool.alloc((size_t)s.max_loaded_chunks * CHUNK_VOLUME));
+    }
     TRY(c->projectiles.alloc(s.max_projectiles));
     TRY(c->players.alloc(s.max_players));
     TRY(c->collisions.alloc(s.max_collisions));
@@ -288,6 +120,13 @@ int vxb_create(const vxb_settings* settings, int device, vxb_ctx** out) {
     *out = c;
     return VXB_OK;
 }
+
+#pragma GCC visibility push(default)
+extern "C" {
+
+const char* vxb_last_error(const vxb_ctx* ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
+
+int vxb_create(const vxb_settings* settings, int device, vxb_ctx** out) { return create_ctx(settings, device, nullptr, nullptr, out); }
 
 void vxb_destroy(vxb_ctx* ctx) {
     if (!ctx) return;

@@ -108,6 +108,7 @@ class VoxelComputePipeline:
         self._lib = _lib.load()
         self.settings = game_settings
         self._h = ctypes.c_void_p()
+        self._owned = True
         cs = game_settings.to_c()
         rc = self._lib.vxb_create(ctypes.byref(cs), int(device), ctypes.byref(self._h))
         if rc != 0:
@@ -121,7 +122,8 @@ class VoxelComputePipeline:
 
     def close(self):
         if getattr(self, "_h", None) is not None and self._h.value:
-            self._lib.vxb_destroy(self._h)
+            if getattr(self, "_owned", True):
+                self._lib.vxb_destroy(self._h)
             self._h = ctypes.c_void_p()
 
     def __del__(self):
@@ -463,6 +465,120 @@ class VoxelComputePipeline:
         out = ctypes.c_uint64(0)
         self._check(self._lib.vxb_world_checksum(self._h, ptr(_u32(start_pos, 3)), ctypes.byref(out)))
         return int(out.value)
+
+
+class SlabPipeline(VoxelComputePipeline):
+    """One x-slab of a world window sharded over several GPUs (vxb_slab_*, include/voxelb200.h): a
+    VoxelComputePipeline over the slab's local window whose ghost column is the right neighbour's first
+    column, mapped over NVLink. No counterpart in the reference (single GPU)."""
+
+    def __init__(self, world_settings: GameSettings, start_pos, device, rank, world_size, col_splits=None, _handle=None):
+        self._lib = _lib.load()
+        self._h = ctypes.c_void_p()
+        self._owned = _handle is None
+        if _handle is None:
+            cs = world_settings.to_c()
+            splits = None if col_splits is None else _u32(col_splits, world_size + 1)
+            rc = self._lib.vxb_slab_create(ctypes.byref(cs), ptr(_u32(start_pos, 3)), int(device), int(rank), int(world_size), ptr(splits),
+                                           ctypes.byref(self._h))
+            if rc != 0:
+                raise VxbError("vxb_slab_create failed (%d): %s" % (rc, self._lib.vxb_last_error(None).decode()))
+        else:
+            self._h = ctypes.c_void_p(_handle)
+        self.device = device
+        info = _lib.SlabInfo()
+        self._check(self._lib.vxb_slab_get_info(self._h, ctypes.byref(info)))
+        self.info = info
+        self.rank, self.world_size = int(info.rank), int(info.world_size)
+        self.cols, self.ghost, self.plane_chunks = int(info.own_cols), int(info.ghost_cols), int(info.chunks_per_column)
+        self.local_render_size = tuple(int(v) for v in info.local_render_size)
+        self.local_start_pos = tuple(int(v) for v in info.local_start_pos)
+        self.n_own = self.cols * self.plane_chunks
+        import copy
+
+        self.settings = copy.copy(world_settings)
+        self.settings.render_size = self.local_render_size
+        self.settings.max_loaded_chunks = int(info.max_loaded_chunks)
+
+    def slot(self, lx, y, z):
+        """Pool slot of the chunk at local window coordinates (lx, y, z); lx == cols is the ghost column."""
+        i = y * self.local_render_size[2] + z
+        if lx == 0:
+            return int(self.info.slot_first) + i
+        if lx < self.cols:
+            return int(self.info.slot_rest) + (lx - 1) * self.plane_chunks + i
+        return int(self.info.slot_ghost) + i
+
+    def own_slots(self):
+        """Slots of the own chunks in (x, y, z) order."""
+        pc = self.plane_chunks
+        return np.concatenate([int(self.info.slot_first) + np.arange(pc, dtype=np.int64),
+                               int(self.info.slot_rest) + np.arange((self.cols - 1) * pc, dtype=np.int64)])
+
+    def export_fds(self):
+        a, b = ctypes.c_int(-1), ctypes.c_int(-1)
+        self._check(self._lib.vxb_slab_export_fds(self._h, ctypes.byref(a), ctypes.byref(b)))
+        return a.value, b.value
+
+    def import_fds(self, right_first_column_fd=-1, right_mailbox_fd=-1, left_mailbox_fd=-1):
+        self._check(self._lib.vxb_slab_import_fds(self._h, int(right_first_column_fd), int(right_mailbox_fd), int(left_mailbox_fd)))
+
+    def populate(self, forced=True):
+        self._check(self._lib.vxb_slab_populate(self._h, int(bool(forced))))
+
+    def publish_column(self):
+        self._check(self._lib.vxb_slab_publish_column(self._h))
+
+    def sync_ghost_table(self):
+        self._check(self._lib.vxb_slab_sync_ghost_table(self._h))
+
+    def update(self, offset):
+        self._check(self._lib.vxb_slab_update(self._h, ptr(_u32(offset, 3))))
+
+    def status(self):
+        self._check(self._lib.vxb_slab_status(self._h))
+
+
+class SlabGroup:
+    """vxb_group: every slab of a window in ONE process, one per entry of `devices` (a device may repeat)."""
+
+    def __init__(self, world_settings: GameSettings, start_pos, devices, col_splits=None):
+        self._lib = _lib.load()
+        self._g = ctypes.c_void_p()
+        cs = world_settings.to_c()
+        dev = np.ascontiguousarray(np.asarray(devices, dtype=np.int32))
+        splits = None if col_splits is None else _u32(col_splits, len(devices) + 1)
+        rc = self._lib.vxb_group_create(ctypes.byref(cs), ptr(_u32(start_pos, 3)), ptr(dev), len(devices), ptr(splits), ctypes.byref(self._g))
+        if rc != 0:
+            raise VxbError("vxb_group_create failed (%d): %s" % (rc, self._lib.vxb_last_error(None).decode()))
+        self.slabs = [SlabPipeline(world_settings, start_pos, int(devices[r]), r, len(devices), _handle=self._lib.vxb_group_ctx(self._g, r))
+                      for r in range(len(devices))]
+
+    def _check(self, rc):
+        if rc != 0:
+            raise VxbError("libvoxelb200 error %d: %s" % (rc, self._lib.vxb_group_last_error(self._g).decode()))
+
+    def populate(self, forced=True):
+        self._check(self._lib.vxb_group_populate(self._g, int(bool(forced))))
+
+    def update(self, offset):
+        self._check(self._lib.vxb_group_update(self._g, ptr(_u32(offset, 3))))
+
+    def synchronize(self):
+        self._check(self._lib.vxb_group_synchronize(self._g))
+
+    def close(self):
+        if self._g is not None and self._g.value:
+            for s in self.slabs:
+                s.close()  # borrowed handles: only forgotten
+            self._lib.vxb_group_destroy(self._g)
+            self._g = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 class Game:

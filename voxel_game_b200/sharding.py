@@ -107,3 +107,80 @@ def sharded_update(torch, gpu, shard, local_start_pos, offset, exchange, main, s
         exchange(False)
     main.wait_stream(side)
     return 2 if n_int else 1
+
+
+# ------------------------------------------------------------------------------------------------
+# Peer-mapped ghost column (vxb_slab_*, csrc/slab.cu): one process per GPU. The halo exchange above is
+# replaced by mapping the right neighbour's first chunk column into the own voxel pool; what travels
+# between the processes, once, are POSIX file descriptors of CUDA VMM allocations. File descriptors
+# cross process boundaries as SCM_RIGHTS ancillary data on a unix socket.
+
+def _sock_name(tag, rank):
+    return "\0vxb-slab-%s-%d" % (tag, rank)  # abstract namespace: no file to clean up
+
+
+def exchange_slab_fds(slab, tag, timeout=120.0):
+    """Hands this slab's first-column / mailbox descriptors to its neighbours and maps theirs
+    (vxb_slab_export_fds -> SCM_RIGHTS -> vxb_slab_import_fds). `tag` must be the same string on every
+    rank of one job and unique on the machine (e.g. MASTER_PORT). Every rank calls this once; the caller
+    still owes a barrier between this and the first vxb_slab_update."""
+    import os
+    import socket
+    import time
+
+    rank, n = slab.rank, slab.world_size
+    if n == 1:
+        return
+    first_fd, mbox_fd = slab.export_fds()
+    srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+    srv.bind(_sock_name(tag, rank))
+    srv.listen(2)
+    srv.settimeout(timeout)
+
+    def send_to(peer, kind, fds):
+        deadline = time.time() + timeout
+        while True:
+            c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            try:
+                c.connect(_sock_name(tag, peer))
+                break
+            except (ConnectionRefusedError, FileNotFoundError):
+                c.close()
+                if time.time() > deadline:
+                    raise TimeoutError("slab %d: neighbour %d never opened its socket" % (rank, peer))
+                time.sleep(0.05)
+        socket.send_fds(c, [kind], fds)
+        c.recv(1)  # the peer has the descriptors: ours may be closed
+        c.close()
+
+    got = {}
+    expect = (1 if rank > 0 else 0) + (1 if rank + 1 < n else 0)
+    import threading
+
+    def serve():
+        for _ in range(expect):
+            conn, _ = srv.accept()
+            msg, fds, _, _ = socket.recv_fds(conn, 16, 4)
+            got[msg.decode()] = list(fds)
+            conn.send(b"k")
+            conn.close()
+
+    th = threading.Thread(target=serve)
+    th.start()
+    # to the LEFT neighbour I am its right neighbour: first column + mailbox; to the RIGHT one: mailbox only
+    if rank > 0:
+        send_to(rank - 1, b"R", [first_fd, mbox_fd])
+    if rank + 1 < n:
+        send_to(rank + 1, b"L", [mbox_fd])
+    th.join(timeout)
+    srv.close()
+    if len(got) != expect:
+        raise TimeoutError("slab %d: descriptors of a neighbour did not arrive" % rank)
+    rf, rm = got.get("R", [-1, -1])
+    (lm,) = got.get("L", [-1])
+    try:
+        slab.import_fds(rf, rm, lm)
+    finally:
+        for fd in [first_fd, mbox_fd, rf, rm, lm]:
+            if fd >= 0:
+                os.close(fd)
