@@ -51,6 +51,20 @@ def traffic_from_profiles(key, scale=1.0):
     return None
 
 
+def oracle_all_threads():
+    """The CPU arms use every host thread this process may run on, whatever OMP_NUM_THREADS says (torch.distributed.run
+    exports OMP_NUM_THREADS=1 to its workers, which made round 1's N > 1 reference arm single-threaded)."""
+    from tests.oracle_lib import load as load_oracle
+
+    lib = load_oracle()
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    lib.orc_set_num_threads(int(n))
+    return lib, int(lib.orc_num_threads())
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
 
@@ -114,13 +128,13 @@ def loads_for(chunks, slots, forced):
     return np.concatenate([xyz, w[:, None]], 1).astype(np.int32)
 
 
-def generate_world(gpu, sp, chunks, first_slot, forced, torch, batch=32768):
-    """Worldgen every chunk of `chunks` (slot = first_slot + i). Returns (seconds on device, voxels)."""
+def generate_world(gpu, sp, chunks, first_slot, forced, torch, batch=32768, slots=None):
+    """Worldgen every chunk of `chunks` (slot = first_slot + i, or slots[i]). Returns (seconds on device, voxels)."""
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     for b in range(0, len(chunks), batch):
         c = chunks[b:b + batch]
-        loads = loads_for(c, np.arange(first_slot + b, first_slot + b + len(c)), forced)
+        loads = loads_for(c, np.arange(first_slot + b, first_slot + b + len(c)) if slots is None else slots[b:b + len(c)], forced)
         gpu.dispatch_worldgen(sp, loads, complete=True, want_results=False)
     ev1.record()
     torch.cuda.synchronize()
@@ -186,12 +200,48 @@ def run_ours(args):
     RS, SP = tuple(args.world), C3_SP
     shard = SlabShard(RS, SP, rank, world_size)
     cols, ghost, lrs, lsp, n_local, n_own = shard.cols, shard.ghost, shard.local_render_size, shard.local_start_pos, shard.n_local, shard.n_own
-    gs = vg.GameSettings(render_size=lrs, max_loaded_chunks=2 + n_local, max_worldgen_rate=8 * 32768, max_update_rate=1024)
-    gpu = vg.VoxelComputePipeline(gs, device=local_rank)
-    gpu.set_stream(stream.cuda_stream)
     chunks = chunk_grid(0, lrs[0], lrs, lsp)
-    wg_s, wg_vox = generate_world(gpu, lsp, chunks, 2, True, torch)
     own_list = np.concatenate([chunks[:n_own], np.zeros((n_own, 1), np.int64)], 1).astype(np.uint32)
+    # Halo between slabs. "peer" (default): vxb_slab_* — the ghost column IS the right neighbour's first column,
+    # mapped into this rank's pool (CUDA VMM over NVLink); no copy, no collective, ordering by mailbox counters.
+    # "nccl": round 1's exchange of the x == 0 planes with torch.distributed P2P (kept as the fallback).
+    halo, halo_note = ("peer" if world_size > 1 else "none"), None
+    gpu = None
+    if world_size > 1 and args.halo == "peer":
+        ok = 1
+        try:
+            from voxel_game_b200.sharding import exchange_slab_fds
+
+            wsets = vg.GameSettings(render_size=RS, max_worldgen_rate=8 * 32768, max_update_rate=1024)
+            gpu = vg.SlabPipeline(wsets, SP, local_rank, rank, world_size)
+            assert gpu.local_start_pos == tuple(lsp) and gpu.local_render_size == tuple(lrs)
+            exchange_slab_fds(gpu, os.environ.get("MASTER_PORT", "0"))
+        except Exception as e:  # no VMM / no peer access on this box: every rank falls back together
+            ok, halo_note = 0, "peer mapping failed (%s)" % (str(e)[:200],)
+        t_ok = torch.tensor([ok], dtype=torch.int32, device="cuda")
+        dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
+        if int(t_ok.item()) == 0:
+            if gpu is not None:
+                gpu.close()
+            gpu, halo = None, "nccl"
+            halo_note = halo_note or "peer mapping failed on another rank"
+    elif world_size > 1:
+        halo = "nccl"
+    if gpu is None:
+        gs = vg.GameSettings(render_size=lrs, max_loaded_chunks=2 + n_local, max_worldgen_rate=8 * 32768, max_update_rate=1024)
+        gpu = vg.VoxelComputePipeline(gs, device=local_rank)
+    gpu.set_stream(stream.cuda_stream)
+    if halo == "peer":
+        own_slots = gpu.own_slots()
+        assert np.array_equal(own_slots, np.arange(2, 2 + n_own)) and int(gpu.info.slot_ghost) == 2 + n_own, \
+            "bench.py addresses the pool as [2 + local chunk index]: columns must fill whole VMM granules (ry * rz % 128 == 0)"
+        wg_s, wg_vox = generate_world(gpu, lsp, chunks[:n_own], 2, True, torch)
+        gpu.publish_column()
+        barrier()
+        gpu.sync_ghost_table()
+        barrier()
+    else:
+        wg_s, wg_vox = generate_world(gpu, lsp, chunks, 2, True, torch)
     gpu.update_list_upload(own_list)
     gpu.set_update_kernel(args.variant)
 
@@ -199,20 +249,30 @@ def run_ours(args):
     ptrs = gpu.device_ptrs()
     pool_t = torch.as_tensor(DevView(ptrs.voxel_pool, (2 + n_local) * 4096), device="cuda").view(2 + n_local, 4096)
     first_col, ghost_col = shard.views(pool_t)
-    sendbuf = torch.empty((shard.plane_chunks, 256), dtype=torch.int32, device="cuda")
-    recvbuf = torch.empty((shard.plane_chunks, 256), dtype=torch.int32, device="cuda")
     launches = [0]
+    side = torch.cuda.Stream()  # nccl halo: exchange + boundary column, hidden behind the slab's interior
+    if halo == "nccl":
+        sendbuf = torch.empty((shard.plane_chunks, 256), dtype=torch.int32, device="cuda")
+        recvbuf = torch.empty((shard.plane_chunks, 256), dtype=torch.int32, device="cuda")
 
     def exchange(pre):
         launches[0] += halo_exchange(dist, shard, first_col, ghost_col, sendbuf, recvbuf, pre)
 
+    seen_x = [False, False]
+
+    def do_update(off):
+        """One sharded update dispatch; returns the number of our kernels it launched."""
+        if halo == "peer":
+            gpu.update(off)
+            # update kernel + tick signal + (if a neighbour's earlier tick of the other x parity has to be awaited) the wait
+            waits = 1 if ((off[0] == 1 and ghost and seen_x[0]) or (off[0] == 0 and rank > 0 and seen_x[1])) else 0
+            seen_x[off[0]] = True
+            return 2 + waits
+        return sharded_update(torch, gpu, shard, lsp, off, exchange, stream, side)
+
     # settle: run the automaton until the distance fields have propagated (<= 7 per 8 phases) so the
     # timed steps see the steady state of a running game, not the first ticks after worldgen
-    side = torch.cuda.Stream()  # halo exchange + boundary column, hidden behind the slab's interior
-
-    def settle_step(i):
-        sharded_update(torch, gpu, shard, lsp, PHASES[i % 8], exchange, stream, side)
-
+    barrier()
     # clocks are sampled from here on: the settle ticks are the same kernel on the same world as the timed steps, and
     # the timed region alone (16 steps x 5 ms) is shorter than one nvidia-smi sampling period
     sampler = ClockSampler(local_rank) if rank == 0 else None
@@ -222,12 +282,12 @@ def run_ours(args):
             unsettled[0].record()
         if i == 8:
             unsettled[1].record()
-        settle_step(i)
+        do_update(PHASES[i % 8])
     torch.cuda.synchronize()
     unsettled_ms = unsettled[0].elapsed_time(unsettled[1]) / 8 if args.settle > 8 else None
 
     def step(i):
-        launches[0] += sharded_update(torch, gpu, shard, lsp, PHASES[i % 8], exchange, stream, side)
+        launches[0] += do_update(PHASES[i % 8])
 
     for i in range(args.warmup):
         step(i)
@@ -251,6 +311,15 @@ def run_ours(args):
     value = n_total_vox * args.steps / (total_ms / 1e3)
     # dominant kernel: this rank's k_voxel_update launches (CUDA events on the launching stream)
     per_step_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
+    # mean device time per Margolus phase on this rank, and the same for every rank (slab content imbalance vs enqueue
+    # overhead: profiles/r02_scaling.md reads this table)
+    phase_ms = [float(np.mean([per_step_ms[i] for i in range(args.steps) if (args.warmup + i) % 8 == ph] or [float("nan")])) for ph in range(8)]
+    rank_phase_ms = None
+    if world_size > 1:
+        tp = torch.tensor(phase_ms, dtype=torch.float64, device="cuda")
+        allp = torch.empty(world_size * 8, dtype=torch.float64, device="cuda")
+        dist.all_gather_into_tensor(allp, tp)
+        rank_phase_ms = [[round(v, 4) for v in row] for row in allp.view(world_size, 8).tolist()]
     if rank == 0:
         print("per-step ms (rank 0, phase = step %% 8 after %d warm-ups): %s" % (args.warmup, " ".join("%.3f" % m for m in per_step_ms)), file=sys.stderr)
     kern_ms = float(np.mean(per_step_ms)) if world_size == 1 else None
@@ -287,6 +356,12 @@ def run_ours(args):
 
         def e2e_step(i):
             off = PHASES[i % 8]
+            if halo == "peer":
+                # host list in, sharded dispatch, flags out: the three C-ABI calls a multi-GPU host makes per tick
+                assert lib.vxb_update_list_upload(h, ptr(lnp), n_own) == 0
+                assert lib.vxb_slab_update(h, ptr(offs[i % 8])) == 0
+                assert lib.vxb_update_list_flags(h, ptr(fnp), n_own) == 0  # syncs: flags are host-visible
+                return
             if world_size > 1 and off[0] == 1:
                 exchange(True)
             rc = lib.vxb_dispatch_voxel_update(h, ptr(spc), ptr(lnp), n_own, ptr(offs[i % 8]), ptr(fnp))  # syncs: flags are host-visible
@@ -307,7 +382,8 @@ def run_ours(args):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e = {"value": n_total_vox * args.steps / float(t.item()), "unit": "voxel-updates/s",
                "h2d_bytes_per_step": int(n_own * 16 * world_size), "d2h_bytes_per_step": int(n_own * 4 * world_size),
-               "api": "vxb_dispatch_voxel_update (host chunk_updates list in, chunk_updates[].w flags out)"}
+               "api": ("vxb_update_list_upload + vxb_slab_update + vxb_update_list_flags" if halo == "peer" else "vxb_dispatch_voxel_update")
+                      + " (host chunk_updates list in, chunk_updates[].w flags out)"}
 
     result = None
     if rank == 0:
@@ -319,9 +395,16 @@ def run_ours(args):
             "config": {"workload": "BASELINE configs[2]: voxel update step, %dx%dx%d-voxel world, all %d chunks per step, phase cycled"
                                    % (RS[0] * 16, RS[1] * 16, RS[2] * 16, RS[0] * RS[1] * RS[2]),
                        "sharding": "x-slab x%d, halo = one voxel plane per boundary on offset.x==1 phases" % world_size,
+                       "halo": {"none": "single GPU", "peer": "ghost column = the right neighbour's first column mapped into the pool (CUDA VMM over NVLink), "
+                                "ordering by mailbox tick counters; no copy, no collective (vxb_slab_*)",
+                                "nccl": "x == 0 planes exchanged with torch.distributed P2P (NCCL) around the boundary column"}[halo],
+                       "halo_note": halo_note,
                        "l2": "inputs larger than L2 (%.2f GB of voxel state per GPU vs 126 MB)" % (n_local * 16384 / 1e9),
                        "update_kernel_variant": args.variant, "settle_ticks_before_timing": args.settle},
             "gpu_launches": launches[0],
+            "phase_mean_ms": [round(v, 4) for v in phase_ms],
+            "ms_per_step_phase_balanced": float(np.nanmean(phase_ms)),
+            "rank_phase_ms": rank_phase_ms,
             "clocks": clocks,
             "e2e": e2e,
             "worldgen": worldgen_result(torch, wg_vox, wg_s),
@@ -348,8 +431,9 @@ def run_ours(args):
 
     # ---------------- cpu_baseline (rank 0, N == 1): oracle on a bounded sample of the same world ----
     if rank == 0 and world_size == 1 and not args.no_cpu:
-        from tests.oracle_lib import CpuWorld, load as load_oracle
+        from tests.oracle_lib import CpuWorld
 
+        _, cpu_threads = oracle_all_threads()
         sx = min(args.cpu_sample_cols, RS[0])
         n_s = sx * RS[1] * RS[2]
         cw = CpuWorld((sx, RS[1], RS[2]), SP, 2 + n_s)
@@ -363,16 +447,17 @@ def run_ours(args):
             cw.voxel_update(lst, PHASES[(reps + 1) % 8])
             reps += 1
         cs = time.perf_counter() - t0
-        result["cpu_baseline"] = {"value": n_s * 4096 * reps / cs, "unit": "voxel-updates/s", "cores": load_oracle().orc_num_threads(),
+        result["cpu_baseline"] = {"value": n_s * 4096 * reps / cs, "unit": "voxel-updates/s", "cores": cpu_threads,
                                   "kind": "port",
                                   "sample": "%d ticks over the first %d x-columns of the same world (%d chunks, %d voxels), OpenMP over chunks"
                                             % (reps, sx, n_s, n_s * 4096)}
     # ---------------- C5: full tick (worldgen stream + sharded update + replica refresh + 64 views) ----------------
     tick = None
     if args.tick or (world_size == 8 and not args.no_tick):
-        tick = bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp, chunks, exchange, stream, side)
+        tick = bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp, chunks, do_update)
         if rank == 0:
             result["tick"] = tick
+    barrier()  # a slab's first column and mailbox are mapped by its neighbours until they are done
     gpu.close()
     del pool_t, first_col, ghost_col
 
@@ -494,6 +579,7 @@ def bench_c1(args, torch, vg):
     from tests import scenes
     from tests.oracle_lib import CpuWorld, chunk_loads_for
 
+    oracle_all_threads()
     RS, SP = (8, 8, 8), (621, 109, 621)
     n = 512
     chunks = [(SP[0] + x, SP[1] + y, SP[2] + z) for x in range(8) for y in range(8) for z in range(8)]
@@ -595,7 +681,7 @@ def bench_game_tick(args, torch, vg):
                        "reference_target_ticks_per_s": 50}}
 
 
-def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp, chunks, exchange, main, side):
+def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp, chunks, do_update):
     """BASELINE configs[4]: one game tick on the config-3 world —
       1. worldgen: 512 chunks regenerated in place (512 / N per rank, in its own slab; forced, so that slots
          and the table stay put and only chunk payloads travel to the replicas),
@@ -607,7 +693,6 @@ def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp,
     Device time per phase (CUDA events on the one stream everything runs on), max over ranks."""
     from tests import scenes
     from voxel_game_b200.replicas import DeviceReplicaRefresh, gather_changed_chunks
-    from voxel_game_b200.sharding import sharded_update
 
     RS, SP = tuple(args.world), C3_SP
     n_total = RS[0] * RS[1] * RS[2]
@@ -664,7 +749,7 @@ def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp,
         ev[0].record()
         gpu.dispatch_worldgen(lsp, regen_loads, complete=True, want_results=False)
         ev[1].record()
-        sharded_update(torch, gpu, shard, lsp, off, exchange, main, side)
+        do_update(off)
         ev[2].record()
         refresher.refresh(off, also=regen_t)
         ev[3].record()
@@ -896,6 +981,7 @@ def bench_collisions(args, torch, vg, gpu, SP, RS, centre, peak):
                       "note": "device time of k_projectiles + k_players; entity arrays restored by a device copy between steps (untimed)"}}
     if not args.no_cpu:
         # oracle on a bounded sample of the same batch, same world (downloaded); counters from a sequential pass
+        oracle_all_threads()
         n_s = min(65536, n_proj)
         n = RS[0] * RS[1] * RS[2]
         cw = CpuWorld(RS, SP, 2 + n)
@@ -984,10 +1070,9 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from tests.oracle_lib import CpuWorld, chunk_loads_for, load as load_oracle
+    from tests.oracle_lib import CpuWorld, chunk_loads_for
 
-    lib = load_oracle()
-    cores = lib.orc_num_threads()
+    lib, cores = oracle_all_threads()
     # sample: an 8x8x8-chunk open-world block generated by the oracle itself around the spawn, tiled 4x1x4
     base_rs, tile = (8, 8, 8), (4, 1, 4)
     sp = (621, 109, 621)
@@ -1050,6 +1135,7 @@ def main():
     ap.add_argument("--world", type=int, nargs=3, default=list(C3_RS), help="update-step world size in chunks (default BASELINE configs[2])")
     ap.add_argument("--variant", type=int, default=2, help="update kernel variant: 2 = tiled + unchanged-store elision (product default), 0 = tiled with the reference's unconditional stores, 1 = reference-shaped gather")
     ap.add_argument("--settle", type=int, default=96, help="untimed update ticks after worldgen (world preparation)")
+    ap.add_argument("--halo", default="peer", choices=["peer", "nccl"], help="N > 1: peer-mapped ghost column (vxb_slab_*, default) or round 1's NCCL plane exchange")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-rays", action="store_true")
     ap.add_argument("--no-collisions", action="store_true")

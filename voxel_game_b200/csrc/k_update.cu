@@ -26,6 +26,7 @@
 //  * the reference re-reads every voxel in set_data; here the original stays in registers.
 //  * the shader's straight-line block logic (~200 instructions per voxel) would make the kernel
 //    issue-bound 5x over; margolus_block() classifies the block first (exact, see there).
+#include <atomic>
 #include <mutex>
 
 #include "vxb_device.cuh"
@@ -326,6 +327,7 @@ struct UpdSmem {
     uint32_t flags[2];
     uint32_t cz[4][UPD_THREADS / 4];        // z-run carry: updated voxel z == 16 of column (i,j), kept for the next item
     uint32_t cc[UPD_THREADS / 4];           // ... and whether it changed (bit i*2+j), for ELIDE
+    uint32_t run_ring[8];                   // list runs this CTA has claimed, by claim order (mod 8); >= n_runs: none left
 };
 
 // The 2x2x2 neighbour slots of one work item, picked apart for one thread: s[i*2+j] is the slot of
@@ -343,24 +345,31 @@ struct ThreadSlots {
 // exactly set_data's guard for those two materials.
 template <int PHASE, bool ELIDE>
 __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, const uint4* __restrict__ chunk_updates, uint32_t n_items,
-                                                                       uint32_t* __restrict__ flags_out, uint32_t run_log2) {
+                                                                       uint32_t* __restrict__ flags_out, uint32_t run_log2,
+                                                                       uint32_t* __restrict__ sched) {
     constexpr int OX = PHASE & 1, OY = (PHASE >> 1) & 1, OZ = (PHASE >> 2) & 1;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     UpdSmem& sm = *reinterpret_cast<UpdSmem*>(smem_raw);
 
     const uint32_t tid = threadIdx.x;
-    const uint32_t G = gridDim.x;
-    // Work distribution: the list is cut into runs of R = 2^run_log2 consecutive entries and the runs are
-    // dealt round-robin to the CTAs, so a CTA walks R list neighbours back to back (in a z-fastest list:
-    // R chunks along z, which is what the z-run carry below feeds on) while heavy regions of the list
-    // still spread over all CTAs. The launcher picks R = 1 for short lists.
+    // Work distribution: the list is cut into runs of R = 2^run_log2 consecutive entries (in a z-fastest list: R
+    // chunks along z, which is what the z-run carry below feeds on) and the CTAs CLAIM runs in list order from a
+    // global counter (sched[0]), one run ahead of need. Chunk cost varies several-fold (a uniform chunk against one
+    // holding terrain surface or water), so a static deal leaves a tail: measured on a 131 072-chunk slab, 27 runs per
+    // CTA dealt round-robin took 11 % longer per chunk than the 1 M-chunk list (profiles/r02_scaling.md). With claims
+    // the CTAs still sweep the list as one front (DRAM page locality) and finish within one run of each other.
+    // The launcher picks R = 1 for short lists. sched[1] counts finished CTAs; the last one re-arms both counters.
     const uint32_t R = 1u << run_log2;
     const uint32_t n_runs = (n_items + R - 1) >> run_log2;
-    if (blockIdx.x >= n_runs) return;
-    const uint32_t runs_mine = (n_runs - blockIdx.x + G - 1) / G;
-    const uint32_t last_start = (blockIdx.x + (runs_mine - 1) * G) << run_log2;
-    const uint32_t T = ((runs_mine - 1) << run_log2) + min(R, n_items - last_start);  // only the list's last run is short
-    auto item = [&](uint32_t t) { return ((blockIdx.x + (t >> run_log2) * G) << run_log2) + (t & (R - 1)); };
+    constexpr uint32_t NONE = 0xFFFFFFFFu;
+    // global list index of this CTA's t-th item, NONE past its end (items are valid up to some t, then never again)
+    auto item = [&](uint32_t t) -> uint32_t {
+        const uint32_t run = sm.run_ring[(t >> run_log2) & 7];
+        if (run >= n_runs) return NONE;
+        const uint32_t i = (run << run_log2) + (t & (R - 1));
+        return i < n_items ? i : NONE;  // only the list's last run is short
+    };
+    constexpr uint32_t AHEAD = UPD_STAGES + 2;  // iteration t reads items up to t + STAGES + 1 (slot + link prefetch)
 
     // warp = one ty: a 16 x 2 x 16-voxel horizontal slab. Terrain and water surfaces are mostly
     // horizontal, so few warps of a chunk contain them and leave the block fast paths.
@@ -411,21 +420,24 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
 
     // resolve the 2x2x2 slot neighbourhood of work item t (lane n of 8): list entry -> table lookup
     auto resolve = [&](uint32_t t, uint32_t n) -> uint32_t {
-        if (t >= T) return 0;
-        const uint4 e = chunk_updates[item(t)];
+        const uint32_t it = item(t);
+        if (it == NONE) return 0;
+        const uint4 e = chunk_updates[it];
         return resolve_chunk(w, e.x + ((n >> 2) & 1), e.y + ((n >> 1) & 1), e.z + (n & 1));
     };
     // offset.z == 1: is item t+1 of this CTA the +z neighbour of item t? Then item t does not store its
     // z == 16 voxels (first word of each row of the +z chunk, a 4-byte store into a sector that item t+1
     // writes the rest of) but hands them over, and item t+1 stores full aligned vectors.
     auto resolve_link = [&](uint32_t t) -> uint32_t {
-        if (OZ == 0 || t + 1 >= T) return 0;
-        const uint4 a = chunk_updates[item(t)], b = chunk_updates[item(t + 1)];
+        if (OZ == 0) return 0;
+        const uint32_t ia = item(t), ib = item(t + 1);
+        if (ia == NONE || ib == NONE) return 0;
+        const uint4 a = chunk_updates[ia], b = chunk_updates[ib];
         return (a.x == b.x && a.y == b.y && a.z + 1 == b.z) ? 1u : 0u;
     };
     // issue this thread's copies of work item t into its ring stage (always commits one group)
     auto issue = [&](uint32_t t) {
-        if (t < T) {
+        if (item(t) != NONE) {
             UpdStage& st = sm.stage[t % UPD_STAGES];
             const ThreadSlots ts = thread_slots(sm.slot[t % UPD_NSLOT]);
 #pragma unroll
@@ -442,7 +454,14 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
         cp_async_commit();
     };
 
-    // ---- prologue: slot tables of the first STAGES items, copies of the first STAGES-1 ----
+    // ---- prologue: the runs holding the first AHEAD items, then slot tables of the first STAGES items, copies of
+    // the first STAGES-1 ----
+    uint32_t claimed = 0;  // thread 64 only: runs claimed so far
+    if (tid == 64) {
+        claimed = ((AHEAD - 1) >> run_log2) + 1;
+        for (uint32_t k = 0; k < claimed; k++) sm.run_ring[k] = atomicAdd(&sched[0], 1u);
+    }
+    __syncthreads();
     if (tid < 8 * UPD_STAGES) sm.slot[tid >> 3][tid & 7] = resolve(tid >> 3, tid & 7);
     if (tid >= 32 && tid < 32 + UPD_STAGES) sm.link[tid - 32] = resolve_link(tid - 32);
     if (tid < 2) sm.flags[tid] = 0;
@@ -451,7 +470,16 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
 #pragma unroll
     for (int t = 0; t < UPD_STAGES - 1; t++) issue(t);
 
-    for (uint32_t t = 0; t < T; t++) {
+    for (uint32_t t = 0;; t++) {
+        const uint32_t cur = item(t);
+        if (cur == NONE) break;  // CTA-uniform: the ring is only written ahead of a barrier
+        if (tid == 64) {         // the run holding item t + AHEAD, read from the next iteration on
+            const uint32_t k = (t + AHEAD) >> run_log2;
+            if (k >= claimed) {
+                sm.run_ring[k & 7] = atomicAdd(&sched[0], 1u);
+                claimed = k + 1;
+            }
+        }
         // slots of item t+STAGES (consumed by issue() one iteration later): loads start now, the
         // result is only touched at the end of the iteration
         uint32_t pend = 0;
@@ -571,11 +599,16 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
         else if (OZ == 1 && tid == 32) sm.link[(t + UPD_STAGES) % UPD_NSLOT] = pend;
         __syncthreads();
         if (tid == 0) {
-            flags_out[item(t)] = sm.flags[t & 1];
+            flags_out[cur] = sm.flags[t & 1];
             sm.flags[t & 1] = 0;  // next written in iteration t+2, after the barrier of t+1
         }
     }
     cp_async_wait<0>();
+    // every claim of this CTA happened before the barrier it left the loop through; the last CTA out re-arms the counters
+    if (tid == 0 && atomicAdd(&sched[1], 1u) == gridDim.x - 1) {
+        sched[0] = 0;
+        sched[1] = 0;
+    }
 }
 
 // Reference-shaped variant: one thread per 2x2x2 block, every voxel through get_data (window test
@@ -666,6 +699,27 @@ __global__ void __launch_bounds__(512) k_voxel_update_gather(World w, const uint
     if (tid == 0) flags_out[blockIdx.x] = s_flags;
 }
 
+// Run-claim counters of k_voxel_update_tiled: SCHED_SLOTS pairs per device, allocated and zeroed at the first launch
+// on that device; a launch takes the next pair round-robin and the kernel's last CTA re-arms it, so launches that
+// overlap on different streams do not share one (launches on one stream run one after the other anyway).
+static cudaError_t sched_counters(int dev, uint32_t** out) {
+    constexpr int MAX_DEVICES = 64;
+    constexpr uint32_t SCHED_SLOTS = 64;
+    static uint32_t* base[MAX_DEVICES] = {nullptr};
+    static std::mutex mutex;
+    static std::atomic<uint32_t> next{0};
+    {
+        std::lock_guard<std::mutex> lock(mutex);
+        if (!base[dev]) {
+            cudaError_t e = cudaMalloc(&base[dev], SCHED_SLOTS * 2 * sizeof(uint32_t));
+            if (e != cudaSuccess) return e;
+            if ((e = cudaMemset(base[dev], 0, SCHED_SLOTS * 2 * sizeof(uint32_t))) != cudaSuccess) return e;
+        }
+    }
+    *out = base[dev] + 2 * (next.fetch_add(1) % SCHED_SLOTS);
+    return cudaSuccess;
+}
+
 template <int PHASE, bool ELIDE>
 static cudaError_t launch_one(const World& w, const uint4* list, uint32_t n, uint32_t* flags, int run_code, cudaStream_t st) {
     // Per instantiation AND per device: the opt-in to > 48 KB of dynamic shared memory is a per-device function
@@ -673,6 +727,7 @@ static cudaError_t launch_one(const World& w, const uint4* list, uint32_t n, uin
     constexpr int MAX_DEVICES = 64;
     static int grid_cap[MAX_DEVICES] = {0};
     static std::mutex setup_mutex;
+
     auto kern = k_voxel_update_tiled<PHASE, ELIDE>;
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
@@ -691,14 +746,19 @@ static cudaError_t launch_one(const World& w, const uint4* list, uint32_t n, uin
         }
         cap = grid_cap[dev];
     }
+    uint32_t* sched = nullptr;
+    if ((e = sched_counters(dev, &sched)) != cudaSuccess) return e;
     const int grid_cap_dev = cap;
-    // runs of 8 list neighbours per CTA visit once the list is long enough to keep every CTA busy with them.
-    // (config 3, G voxel-updates/s, all stores / elided: R=1 424/888, R=4 530/881, R=8 547/885, R=16 554/869, R=32 557/857)
+    // Run length. With all stores (the reference's behaviour) runs of 8 list neighbours pay once the list is long:
+    // the z-run hand-over turns the 4-byte row-end stores of offset.z == 1 into full vectors. With unchanged-store
+    // elision few vectors are stored at all and single-entry runs win: the finer the claims, the shorter the tail.
+    // (config 3 settled, elided, ms per step by run length, claimed runs: R=1 4.30, 2 4.30, 4 4.36, 8 4.41, 16 4.45;
+    //  a 1/8 slab: 0.565, 0.567, 0.578, 0.594, 0.620. Round 1, statically dealt runs: R=1 5.00, R=8 4.85 / 0.633, 0.673.)
     // (run_code != 0 forces 2^(run_code-1): tests use it to drive the hand-over path with small worlds)
-    const uint32_t run_log2 = run_code ? (uint32_t)(run_code - 1) : (n >= 8u * 8u * (uint32_t)grid_cap_dev ? 3u : 0u);
+    const uint32_t run_log2 = run_code ? (uint32_t)(run_code - 1) : ((!ELIDE && n >= 8u * 8u * (uint32_t)grid_cap_dev) ? 3u : 0u);
     const uint32_t n_runs = (n + (1u << run_log2) - 1) >> run_log2;
     const uint32_t grid = n_runs < (uint32_t)grid_cap_dev ? n_runs : (uint32_t)grid_cap_dev;
-    kern<<<grid, UPD_THREADS, sizeof(UpdSmem), st>>>(w, list, n, flags, run_log2);
+    kern<<<grid, UPD_THREADS, sizeof(UpdSmem), st>>>(w, list, n, flags, run_log2, sched);
     return cudaGetLastError();
 }
 
