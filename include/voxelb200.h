@@ -443,17 +443,18 @@ int vxb_ray_download(vxb_ctx* ctx, float* pos, float* normal, uint32_t* voxel, f
 
 /* Has no counterpart in the reference. Same single-hit ray queries as vxb_raymarch_rays with kind
  * 1, 2 or 3, for callers that must not allocate when they ask: a fixed-rate simulation thread (a
- * cudaMalloc there stalls every stream of the device), a host that gave all device memory to its own
- * pool at start-up, or code that runs while a stream is being captured. This entry point calls no
- * cudaMalloc / cudaFree and no allocating library routine. Its device staging is a fixed array inside
+ * cudaMalloc there stalls every stream of the device) or a host that gave all device memory to its own
+ * pool at start-up. This entry point calls no cudaMalloc / cudaFree and no allocating library routine. Its device staging is a fixed array inside
  * the library image (about 1.1 MB, held by every GPU that loads the library until the process
  * exits), so one call takes at most VXB_NOALLOC_MAX_RAYS rays; more is rejected with VXB_ERR_INVALID.
  *  - pos, dir: HOST arrays [n][3]. Outputs are HOST arrays and may each be NULL: out_pos and
  *    out_normal are component-major ([c*n + i], c = 0..2; normal is only meaningful for kind 1),
  *    out_voxel / out_ldist per ray, out_light = passthrough_light (kinds 2, 3).
- *  - Synchronises the ctx stream before returning.
- *  - The first call on a device looks up that device's address of the array; make that first call
- *    before any stream capture begins.
+ *  - Copies the inputs from and the outputs to the caller's host arrays on the ctx stream and
+ *    synchronises that stream before returning.
+ *  - The first call on a device looks up that device's address of the array (the driver loads the
+ *    module holding it then); make that first call per device at start-up, before any stream capture
+ *    begins.
  *  - All calls share the one array per GPU and it keeps the previous call's contents (the call
  *    clears the one counter that must start at zero). Two calls that overlap on the same GPU, from
  *    different ctxs or streams, race on it: issue them one after the other. */

@@ -613,7 +613,8 @@ __global__ void k_apply_damage(World w, const uint4* __restrict__ records, uint3
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint4 r = records[i];
-    atomicAdd(&w.pool[voxel_index(w, r.x, r.y, r.z)], r.w);
+    const uint64_t idx = voxel_index(w, r.x, r.y, r.z);
+    if (idx >= 2ull * CHUNK_VOLUME) atomicAdd(&w.pool[idx], r.w);  // never into the sentinel slots 0 / 1
 }
 
 // the same with the record count read on the device (no host round trip between the exchange and the replay)
@@ -622,7 +623,8 @@ __global__ void k_apply_damage_counted(World w, const uint4* __restrict__ record
     const uint32_t n = min(*count, capacity);
     if (i >= n) return;
     const uint4 r = records[i];
-    atomicAdd(&w.pool[voxel_index(w, r.x, r.y, r.z)], r.w);
+    const uint64_t idx = voxel_index(w, r.x, r.y, r.z);
+    if (idx >= 2ull * CHUNK_VOLUME) atomicAdd(&w.pool[idx], r.w);
 }
 
 cudaError_t launch_apply_damage_counted(const World& w, const uint32_t* records, const uint32_t* count_dev, uint32_t capacity, cudaStream_t st) {

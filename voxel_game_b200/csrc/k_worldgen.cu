@@ -483,7 +483,11 @@ __global__ void k_write_voxels(World w, const uint4* __restrict__ writes, uint32
     const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
     if (gid >= n) return;
     const uint4 wr = writes[gid];
-    w.pool[voxel_index(w, wr.x, wr.y, wr.z)] = wr.w;
+    // The shader stores through whatever the table says (write_voxels.glsl:36-39); its host only forwards writes into
+    // loaded chunks (voxel_sim_manager.rs:1066-1075). Here slots 0 / 1 are constants every kernel relies on, so a
+    // write into an unloaded or all-air chunk is dropped instead.
+    const uint64_t idx = voxel_index(w, wr.x, wr.y, wr.z);
+    if (idx >= 2ull * CHUNK_VOLUME) w.pool[idx] = wr.w;
 }
 
 // unload_chunks.glsl:19-26; the reference launches floor(rs/16) 16x16 workgroups per axis.

@@ -3,14 +3,16 @@
 // Who needs this: code that must not call cudaMalloc at the point where it asks its line-of-sight /
 // visibility questions. Typical cases are a game's fixed-rate simulation thread (cudaMalloc and
 // cudaFree serialise against the whole device, so one allocation in the tick stalls every stream,
-// including the renderer's), hosts that hand all device memory to their own pool at start-up and
-// leave none for later, and code running while a stream is being captured into a CUDA graph, where
-// allocating calls are not permitted. vxb_raymarch_rays grows the ctx's ray buffers with cudaMalloc
+// including the renderer's) and hosts that hand all device memory to their own pool at start-up and
+// leave none for later. vxb_raymarch_rays grows the ctx's ray buffers with cudaMalloc
 // when a batch is larger than any before; this variant instead keeps its device staging in a
 // fixed array that is part of the library image.
 //
 // Cost and limits: the array below (about 1.1 MB) is held by every GPU that loads the library
-// until the process exits, and a batch is limited to VXB_NOALLOC_MAX_RAYS rays.
+// until the process exits, and a batch is limited to VXB_NOALLOC_MAX_RAYS rays. The first call on a
+// device looks the array's address up (cudaGetSymbolAddress, which makes the driver load this module
+// on that device): make one warm-up call per device at start-up, before any stream capture begins.
+// The call copies from / to the caller's host arrays and synchronises the ctx stream before returning.
 #include <mutex>
 
 #include "vxb_device.cuh"
@@ -21,6 +23,7 @@ namespace vxb {
 void ctx_view(const vxb_ctx* c, const uint32_t start_pos[3], World* w, cudaStream_t* st, const vxb_projectile** projectiles,
               size_t* projectile_capacity, int* device);
 int ctx_fail(vxb_ctx* c, int code, const char* msg);
+bool ctx_window_ok(const vxb_ctx* c, const uint32_t start_pos[3]);
 }  // namespace vxb
 
 namespace {
@@ -63,8 +66,8 @@ extern "C" int vxb_raymarch_rays_noalloc(vxb_ctx* ctx, const uint32_t start_pos[
     if (kind < 1 || kind > 3) return ctx_fail(ctx, VXB_ERR_INVALID, "vxb_raymarch_rays_noalloc: kind must be 1, 2 or 3 (single-hit queries)");
     if (n == 0) return VXB_OK;
     if (!pos || !dir) return ctx_fail(ctx, VXB_ERR_INVALID, "vxb_raymarch_rays_noalloc: pos / dir is NULL");
-    for (int a = 0; a < 3; a++)
-        if (start_pos[a] > (1u << 27)) return ctx_fail(ctx, VXB_ERR_INVALID, "vxb_raymarch_rays_noalloc: start_pos out of range");
+    if (!ctx_window_ok(ctx, start_pos))  // the same window rule as vxb_raymarch_rays
+        return ctx_fail(ctx, VXB_ERR_INVALID, "vxb_raymarch_rays_noalloc: start_pos + render_size exceeds 2^28 chunks");
 
     World w;
     cudaStream_t st;

@@ -107,6 +107,9 @@ int vxb::create_ctx(const vxb_settings* settings, int device, cudaError_t (*pool
     // empty_chunk_grid (:129-155): host mirror all 0; the device image is zeroed too (the reference
     // leaves it undefined). empty_voxels (:157-240): slot 0 = Unloaded, slot 1 = UnloadedAir.
     TRY(cudaMemsetAsync(c->table.p, 0, n_table * sizeof(uint32_t), c->stream));
+    // slots >= 2 start as zeros (all MAT_AIR, no data): the reference leaves the image undefined; a defined start makes
+    // whole-pool comparisons and checksums reproducible. A slab ctx zeroes its own segments itself.
+    if (!pool_alloc) TRY(cudaMemsetAsync(c->pool.p + 2 * CHUNK_VOLUME, 0, ((size_t)s.max_loaded_chunks - 2) * CHUNK_VOLUME * sizeof(uint32_t), c->stream));
     TRY(launch_fill(c->pool.p, VOX_OOB, CHUNK_VOLUME, c->stream));
     TRY(launch_fill(c->pool.p + CHUNK_VOLUME, VOX_AIR_OOB, CHUNK_VOLUME, c->stream));
     TRY(cudaMemsetAsync(c->scalars.p, 0, 2 * sizeof(unsigned long long), c->stream));
@@ -537,8 +540,11 @@ int vxb_dispatch_worldgen(vxb_ctx* c, const uint32_t start_pos[3], const int32_t
     VXB_REQUIRE(c, chunk_loads, "vxb_dispatch_worldgen: chunk_loads is NULL");
     VXB_REQUIRE(c, n_workgroups % 8 == 0, "vxb_dispatch_worldgen: n_workgroups must be a multiple of 8 (8 workgroups per chunk)");
     for (uint32_t i = 0; i < n_workgroups; i++) {
-        const uint32_t slot = (uint32_t)std::abs(chunk_loads[i][3]);
-        if (slot >= c->s.max_loaded_chunks) return fail(c, VXB_ERR_INVALID, "vxb_dispatch_worldgen: slot %u beyond max_loaded_chunks", slot);
+        const int64_t w64 = chunk_loads[i][3];
+        const uint64_t slot = (uint64_t)(w64 < 0 ? -w64 : w64);  // abs() of INT_MIN is undefined in 32 bits
+        if (slot < 2 || slot >= c->s.max_loaded_chunks)
+            return fail(c, VXB_ERR_INVALID, "vxb_dispatch_worldgen: slot %llu is not a pool slot (2 .. max_loaded_chunks - 1; 0 and 1 are the sentinels)",
+                        (unsigned long long)slot);
     }
     VXB_CUDA(c, cudaSetDevice(c->device));
     cudaStream_t st = c->stream;
@@ -593,6 +599,7 @@ int vxb_dispatch_write_voxels(vxb_ctx* c, const uint32_t start_pos[3], const uin
 int vxb_dispatch_unload(vxb_ctx* c, int32_t unload_index, uint32_t unload_component) {
     if (!c) return VXB_ERR_INVALID;
     VXB_REQUIRE(c, unload_component < 3, "vxb_dispatch_unload: unload_component must be 0..2");
+    VXB_REQUIRE(c, unload_index >= 0, "vxb_dispatch_unload: unload_index must be >= 0 (it is a chunk coordinate, voxel_sim_manager.rs:917-923)");
     VXB_CUDA(c, cudaSetDevice(c->device));
     const uint32_t zero[3] = {0, 0, 0};
     VXB_CUDA(c, launch_unload(c->world(zero), c->table.p, unload_index, unload_component, c->stream));
@@ -1148,4 +1155,5 @@ void ctx_view(const vxb_ctx* c, const uint32_t start_pos[3], World* w, cudaStrea
     *device = c->device;
 }
 int ctx_fail(vxb_ctx* c, int code, const char* msg) { return fail(c, code, "%s", msg); }
+bool ctx_window_ok(const vxb_ctx* c, const uint32_t start_pos[3]) { return window_ok(c, start_pos); }
 }  // namespace vxb

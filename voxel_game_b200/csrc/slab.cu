@@ -89,6 +89,7 @@ static std::string cu_err(CUresult r) {
 constexpr size_t SLOT_BYTES = (size_t)CHUNK_VOLUME * 4;  // 16 KiB
 constexpr uint32_t MBOX_FROM_LEFT = 0, MBOX_FROM_RIGHT = 32, MBOX_ERROR = 64;  // word indices, 128 bytes apart
 constexpr long long SLAB_WAIT_CYCLES = 6000000000ll;                           // ~3 s at 1.965 GHz
+constexpr uint32_t MBOX_COLUMN_WORDS = 1024;  // word offset of the published first-column table inside the head granule
 
 // One mapped range of the pool's address reservation.
 struct Segment {
@@ -217,7 +218,9 @@ static cudaError_t slab_pool_alloc(vxb_ctx* c, void* user) {
     }
     c->pool.p = reinterpret_cast<uint32_t*>(s->va + s->gran - 2 * SLOT_BYTES);
     c->pool.n = (size_t)c->s.max_loaded_chunks * CHUNK_VOLUME;
-    return cudaMemsetAsync(reinterpret_cast<void*>(s->va), 0, 512, c->stream);  // the mailbox starts at zero
+    cudaError_t e = cudaMemsetAsync(reinterpret_cast<void*>(s->va + s->first.offset), 0, s->first.bytes + s->rest.bytes, c->stream);  // own slots
+    if (e != cudaSuccess) return e;
+    return cudaMemsetAsync(reinterpret_cast<void*>(s->va), 0, (MBOX_COLUMN_WORDS + (size_t)s->pc) * 4, c->stream);  // the mailbox starts at zero
 }
 
 }  // namespace vxb
@@ -258,7 +261,6 @@ __global__ void k_slab_signal(uint32_t* left_mbox, uint32_t* right_mbox, uint32_
 
 // Table entries of the own first column, in slab-independent form (0 unloaded, 1 all air, 2 + index in the column),
 // written behind the mailbox for the left neighbour; and the reverse on the reading side.
-constexpr uint32_t MBOX_COLUMN_WORDS = 1024;  // word offset of the published column inside the head granule
 __global__ void k_slab_publish_column(const uint32_t* table, uint32_t tx, uint32_t pc, uint32_t slot_first, uint32_t* mbox) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= pc) return;

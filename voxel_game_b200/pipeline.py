@@ -368,7 +368,7 @@ class VoxelComputePipeline:
 
     def raymarch_rays_noalloc(self, start_pos, pos, dirs, kind, max_iterations, projectile_count=0):
         """vxb_raymarch_rays_noalloc: single-hit queries (kind 1..3) for callers that must not allocate
-        on the device when they ask (simulation tick, pooled-memory hosts, during stream capture).
+        on the device when they ask (simulation tick, pooled-memory hosts); warm it up once per device at start-up.
         At most 16384 rays per call. Returns a dict of host arrays: pos/normal [3, n], voxel, ldist, light [n]."""
         p = np.ascontiguousarray(np.asarray(pos, dtype=np.float32).reshape(-1, 3))
         d = np.ascontiguousarray(np.asarray(dirs, dtype=np.float32).reshape(-1, 3))
