@@ -327,7 +327,7 @@ struct UpdSmem {
     uint32_t flags[2];
     uint32_t cz[4][UPD_THREADS / 4];        // z-run carry: updated voxel z == 16 of column (i,j), kept for the next item
     uint32_t cc[UPD_THREADS / 4];           // ... and whether it changed (bit i*2+j), for ELIDE
-    uint32_t run_ring[8];                   // list runs this CTA has claimed, by claim order (mod 8); >= n_runs: none left
+    uint32_t item_ring[16];                 // list index of the CTA's t-th item at [t % 16], NONE past its last one
 };
 
 // The 2x2x2 neighbour slots of one work item, picked apart for one thread: s[i*2+j] is the slot of
@@ -362,14 +362,20 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
     const uint32_t R = 1u << run_log2;
     const uint32_t n_runs = (n_items + R - 1) >> run_log2;
     constexpr uint32_t NONE = 0xFFFFFFFFu;
-    // global list index of this CTA's t-th item, NONE past its end (items are valid up to some t, then never again)
-    auto item = [&](uint32_t t) -> uint32_t {
-        const uint32_t run = sm.run_ring[(t >> run_log2) & 7];
-        if (run >= n_runs) return NONE;
-        const uint32_t i = (run << run_log2) + (t & (R - 1));
-        return i < n_items ? i : NONE;  // only the list's last run is short
-    };
+    // global list index of this CTA's t-th item, NONE past its end (items are valid up to some t, then never again).
+    // One thread (64) claims the runs and publishes the indices AHEAD items early; everybody else pays one LDS.
+    auto item = [&](uint32_t t) -> uint32_t { return sm.item_ring[t & 15]; };
     constexpr uint32_t AHEAD = UPD_STAGES + 2;  // iteration t reads items up to t + STAGES + 1 (slot + link prefetch)
+    uint32_t run_id = 0;                        // thread 64 only: the run being handed out
+    auto publish = [&](uint32_t t) {
+        if ((t & (R - 1)) == 0) run_id = atomicAdd(&sched[0], 1u);
+        uint32_t i = NONE;
+        if (run_id < n_runs) {
+            i = (run_id << run_log2) + (t & (R - 1));
+            if (i >= n_items) i = NONE;  // only the list's last run is short
+        }
+        sm.item_ring[t & 15] = i;
+    };
 
     // warp = one ty: a 16 x 2 x 16-voxel horizontal slab. Terrain and water surfaces are mostly
     // horizontal, so few warps of a chunk contain them and leave the block fast paths.
@@ -437,7 +443,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
     };
     // issue this thread's copies of work item t into its ring stage (always commits one group)
     auto issue = [&](uint32_t t) {
-        if (item(t) != NONE) {
+        {   // past the CTA's last item the slot table holds zeros: the copies read the sentinel chunk (L2 hits), unused
             UpdStage& st = sm.stage[t % UPD_STAGES];
             const ThreadSlots ts = thread_slots(sm.slot[t % UPD_NSLOT]);
 #pragma unroll
@@ -456,11 +462,8 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
 
     // ---- prologue: the runs holding the first AHEAD items, then slot tables of the first STAGES items, copies of
     // the first STAGES-1 ----
-    uint32_t claimed = 0;  // thread 64 only: runs claimed so far
-    if (tid == 64) {
-        claimed = ((AHEAD - 1) >> run_log2) + 1;
-        for (uint32_t k = 0; k < claimed; k++) sm.run_ring[k] = atomicAdd(&sched[0], 1u);
-    }
+    if (tid == 64)
+        for (uint32_t k = 0; k < AHEAD; k++) publish(k);
     __syncthreads();
     if (tid < 8 * UPD_STAGES) sm.slot[tid >> 3][tid & 7] = resolve(tid >> 3, tid & 7);
     if (tid >= 32 && tid < 32 + UPD_STAGES) sm.link[tid - 32] = resolve_link(tid - 32);
@@ -473,13 +476,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
     for (uint32_t t = 0;; t++) {
         const uint32_t cur = item(t);
         if (cur == NONE) break;  // CTA-uniform: the ring is only written ahead of a barrier
-        if (tid == 64) {         // the run holding item t + AHEAD, read from the next iteration on
-            const uint32_t k = (t + AHEAD) >> run_log2;
-            if (k >= claimed) {
-                sm.run_ring[k & 7] = atomicAdd(&sched[0], 1u);
-                claimed = k + 1;
-            }
-        }
+        if (tid == 64) publish(t + AHEAD);  // read from the next iteration on
         // slots of item t+STAGES (consumed by issue() one iteration later): loads start now, the
         // result is only touched at the end of the iteration
         uint32_t pend = 0;
@@ -491,7 +488,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
 
         const UpdStage& st = sm.stage[t % UPD_STAGES];
         const ThreadSlots ts = thread_slots(sm.slot[t % UPD_NSLOT]);
-        uint32_t v[2][2][4];  // originals
+        uint32_t v[2][2][4];  // the thread's 16 voxels, updated in place
 #pragma unroll
         for (int i = 0; i < 2; i++) {
 #pragma unroll
@@ -507,21 +504,42 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
             }
         }
 
-        // two Margolus blocks per thread: z pairs (0,1) and (2,3); change flags of set_data (:55-86)
-        uint32_t r[2][2][4];
+        // two Margolus blocks per thread: z pairs (0,1) and (2,3), updated in place; change flags of set_data (:55-86).
+        // First the commonest case on the raw words: all 16 identical and that word a fixed point (margolus_block's F0
+        // for both blocks at once; deep stone and open sky are most of any world).
+        uint32_t (&r)[2][2][4] = v;
+        uint32_t chg2 = 0;  // bits 0-7: change mask of block 0 (bit = i*4 + j*2 + k), bits 8-15: block 1
+        {
+            const uint32_t W = v[0][0][0];
+            uint32_t diff = 0;
+#pragma unroll
+            for (int q = 0; q < 4; q++)
+#pragma unroll
+                for (int z = 0; z < 4; z++) diff |= v[q >> 1][q & 1][z] ^ W;
+            bool inert = false;
+            if (diff == 0) {
+                const uint32_t m0 = W >> 24, d0 = W & 0xFFFFFFu;
+                inert = W == 0x00FFFFFFu || W == (MAT_STONE << 24) ||
+                        (mat_in(MASK_DATA_DISTANCE, m0) ? (d0 == 0xFFFFFFu) : !(mat_in(MASK_DATA_DAMAGE, m0) && d0 >= (m0 == MAT_STONE ? 10u : 5u)));
+            }
+            if (!inert) {
+#pragma unroll
+                for (int b = 0; b < 2; b++) {
+                    uint32_t blk[8];
+#pragma unroll
+                    for (int c = 0; c < 8; c++) blk[c] = v[c >> 2][(c >> 1) & 1][2 * b + (c & 1)];
+                    chg2 |= margolus_block<OY>(blk) << (8 * b);
+#pragma unroll
+                    for (int c = 0; c < 8; c++) v[c >> 2][(c >> 1) & 1][2 * b + (c & 1)] = blk[c];
+                }
+            }
+        }
         uint32_t flags = 0;
         uint32_t chg16 = 0;  // bit (i*2+j)*4 + z: voxel changed
+        if (chg2) {          // rare on a settled world: a real branch, not fourteen always-executed selects
 #pragma unroll
-        for (int b = 0; b < 2; b++) {
-            uint32_t blk[8];
-#pragma unroll
-            for (int c = 0; c < 8; c++) blk[c] = v[c >> 2][(c >> 1) & 1][2 * b + (c & 1)];
-            const uint32_t chg = margolus_block<OY>(blk);
-#pragma unroll
-            for (int c = 0; c < 8; c++) r[c >> 2][(c >> 1) & 1][2 * b + (c & 1)] = blk[c];
-            if (chg) {
-                // chg bit c = i*4 + j*2 + k
-                flags |= 1u;
+            for (int b = 0; b < 2; b++) {
+                const uint32_t chg = (chg2 >> (8 * b)) & 0xFFu;
                 if (chg & 0x0Fu) flags |= fx[0];
                 if (chg & 0xF0u) flags |= fx[1];
                 if (chg & 0x33u) flags |= fy[0];
@@ -534,6 +552,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
                         if (chg & (1u << c)) chg16 |= 1u << (((c >> 2) * 2 + ((c >> 1) & 1)) * 4 + 2 * b + (c & 1));
                 }
             }
+            flags |= 1u;
         }
 
         // write-back (imageStore :87 is unconditional; sentinel slots are never stored). Under ELIDE a
