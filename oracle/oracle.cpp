@@ -305,4 +305,31 @@ uint64_t orc_reciprocal_division_mismatches(uint64_t n, uint64_t seed) {
     return bad;
 }
 
+// The worldgen kernel divides smoothstep's argument by the constant 1.414 the same way (k_worldgen.cu, voronoise_staged):
+// q0 = x * RN(1 / 1.414), q = fma(fma(-q0, 1.414, x), RN(1 / 1.414), q0), for every x in [2^-24, sqrt(2)). This walks ALL
+// float32 values of that range (2.05e8) and counts the ones whose result is not the IEEE quotient x / 1.414. Expected: 0.
+uint64_t orc_div1414_mismatches(void) {
+    const uint32_t lo = 0x33800000u;  // 2^-24
+    uint32_t hi;
+    {
+        const float two = 2.0f;
+        const float r = sqrtf(two);
+        memcpy(&hi, &r, 4);
+        hi += 1;  // a little past the largest x with x * x < 2
+    }
+    const float kDiv = 1.414f, kInv = 1.0f / 1.414f;
+    uint64_t bad = 0;
+#pragma omp parallel for reduction(+ : bad) schedule(static)
+    for (int64_t u = (int64_t)lo; u <= (int64_t)hi; u++) {
+        const uint32_t bits = (uint32_t)u;
+        float x;
+        memcpy(&x, &bits, 4);
+        const float q0 = x * kInv;
+        const float q = fmaf(fmaf(-q0, kDiv, x), kInv, q0);
+        const float ref = x / kDiv;
+        if (memcmp(&q, &ref, 4) != 0) bad++;
+    }
+    return bad;
+}
+
 }  // extern "C"

@@ -134,3 +134,16 @@ def test_reciprocal_division_is_the_ieee_quotient():
     lib.orc_reciprocal_division_mismatches.restype = ctypes.c_uint64
     lib.orc_reciprocal_division_mismatches.argtypes = [ctypes.c_uint64, ctypes.c_uint64]
     assert lib.orc_reciprocal_division_mismatches(64_000_000, 0x1234ABCD) == 0
+
+
+def test_division_by_1414_through_the_reciprocal_is_the_ieee_quotient():
+    """k_worldgen_open replaces smoothstep's `x / 1.414` (common.glsl:349) by x * RN(1/1.414) plus one exact-remainder
+    step for x in [2^-24, sqrt 2). Exhaustive: every float32 of that range (2.05e8 values) must give the IEEE quotient."""
+    import ctypes
+
+    from tests.oracle_lib import load
+
+    lib = load()
+    lib.orc_div1414_mismatches.restype = ctypes.c_uint64
+    lib.orc_div1414_mismatches.argtypes = []
+    assert lib.orc_div1414_mismatches() == 0
