@@ -4,9 +4,8 @@ TEST INFRASTRUCTURE (the oracle for vxb_compute & friends). Follows, line by lin
       load_voxel_writes :1055-1138, load_chunk_updates :1010-1053, push_updates_from_changed :741-816,
       move_start_pos :697-737, download_projectiles :545-648 (read-back part), queue_* :658-684, :1201
   client/src/utils.rs  QueueMap :58-149, QueueSet :151-219, VoxelUpdateQueue :221-304
-Tie order among equal priorities: the reference's (priority-queue + ahash iteration order) is
-UNPINNED; like the product this uses "priority desc, then the order in which priorities were set"."""
-import heapq
+Tie order among equal priorities: the reference's is whatever priority-queue 2.0.3 produces; the crate is not in the
+reference tree, so IncreasePQ below restates its published heap mechanics (PARITY UNPINNED)."""
 import math
 from collections import OrderedDict, deque
 
@@ -16,31 +15,97 @@ from tests.oracle_lib import CpuWorld
 
 
 class IncreasePQ:
+    """`priority-queue` 2.0.3 (client/Cargo.lock:3029-3036), the PriorityQueue<[u32; 3], i32> behind VoxelUpdateQueue
+    (utils.rs:222). The crate's source is absent from the reference tree: this restates its published store — an IndexMap of
+    (item, priority) in insertion order, `heap` = map indices in binary-heap order, `qp` = map index -> heap position — and its
+    push / push_increase / pop. PARITY UNPINNED (no reference test holds a pop order). The product's IncreasePQ
+    (csrc/host_queues.h) is a smaller model of the same mechanics; test_host_queues.py checks them against each other."""
+
     def __init__(self):
-        self.prio = {}
+        self.items = []   # IndexMap: entries in index order ...
+        self.index = {}   # ... and item -> index (what the hasher is for; never consulted for order)
         self.heap = []
-        self.seq = 0
+        self.qp = []
+
+    def _prio_at(self, position):
+        return self.items[self.heap[position]][1]
+
+    def _bubble_up(self, position, map_index):
+        priority = self.items[map_index][1]
+        while position > 0:
+            parent = (position - 1) // 2
+            if not self._prio_at(parent) < priority:
+                break
+            self.heap[position] = self.heap[parent]
+            self.qp[self.heap[position]] = position
+            position = parent
+        self.heap[position] = map_index
+        self.qp[map_index] = position
+        return position
+
+    def _heapify(self, i):
+        n = len(self.heap)
+        if n <= 1:
+            return
+        while True:
+            l, r, largest = 2 * i + 1, 2 * i + 2, i
+            lp = self._prio_at(i)
+            if l < n:
+                if self._prio_at(l) > lp:
+                    largest, lp = l, self._prio_at(l)
+                if r < n and self._prio_at(r) > lp:
+                    largest = r
+            if largest == i:
+                return
+            a, b = self.heap[i], self.heap[largest]
+            self.heap[i], self.heap[largest] = b, a
+            self.qp[a], self.qp[b] = largest, i
+            i = largest
+
+    def push(self, item, priority):
+        if item in self.index:
+            mi = self.index[item]
+            self.items[mi] = (item, priority)
+            self._heapify(self._bubble_up(self.qp[mi], mi))
+            return
+        mi = len(self.items)
+        self.items.append((item, priority))
+        self.index[item] = mi
+        self.qp.append(mi)
+        self.heap.append(mi)
+        self._bubble_up(mi, mi)
 
     def push_increase(self, item, priority):
-        if item not in self.prio:
-            self.prio[item] = priority
-            heapq.heappush(self.heap, (-priority, self.seq, item))
-            self.seq += 1
-        elif priority > self.prio[item]:
-            self.prio[item] = priority
-            heapq.heappush(self.heap, (-priority, self.seq, item))
-            self.seq += 1
+        if item not in self.index or priority > self.items[self.index[item]][1]:
+            self.push(item, priority)
 
     def pop(self):
-        while self.heap:
-            negp, _, item = heapq.heappop(self.heap)
-            if item in self.prio and self.prio[item] == -negp:
-                del self.prio[item]
-                return item, -negp
-        return None
+        if not self.heap:
+            return None
+        # Store::swap_remove(Position(0)): Vec::swap_remove on heap, on qp and on the map
+        head = self.heap[0]
+        last_pos = len(self.heap) - 1
+        self.heap[0] = self.heap[last_pos]
+        self.heap.pop()
+        size = len(self.heap)
+        if size > 0:
+            self.qp[self.heap[0]] = 0
+        self.qp[head] = self.qp[size]
+        self.qp.pop()
+        if head < size:
+            self.heap[self.qp[head]] = head
+        item, priority = self.items[head]
+        moved = self.items[size]
+        self.items[head] = moved
+        self.items.pop()
+        del self.index[item]
+        if head < size:
+            self.index[moved[0]] = head
+        self._heapify(0)
+        return item, priority
 
     def __len__(self):
-        return len(self.prio)
+        return len(self.heap)
 
 
 class VoxelUpdateQueue:

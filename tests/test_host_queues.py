@@ -121,15 +121,87 @@ def test_update_queue_pops_by_priority_and_never_lowers_it(q):
     q.uq_del(u)
 
 
-def test_update_queue_ties_pop_in_insertion_order(q):
-    # the reference's tie order (ahash iteration order) is unpinned; ours is FIFO and deterministic
+def _drain(q, u):
+    out, pr = k(0, 0, 0), ctypes.c_int32(0)
+    got = []
+    while q.uq_pop(u, ptr(out), ctypes.byref(pr)):
+        got.append((int(out[0]), pr.value))
+    return got
+
+
+def test_update_queue_ties_pop_in_the_crates_heap_order(q):
+    # priority-queue 2.0.3: equal priorities never bubble (strict <), so four pushes sit at heap positions 0..3 in push
+    # order; each pop moves the LAST position to the root, where it stays (no child is strictly greater).
+    # [9 3 7 1] -> pop 9, [1 3 7] -> pop 1, [7 3] -> pop 7, [3] -> pop 3. Worked by hand from the crate's algorithm.
     u = q.uq_new()
     for x in (9, 3, 7, 1):
         q.uq_push_all(u, ptr(k(x, 0, 0)))
     q.uq_swap(u)
+    assert [g[0] for g in _drain(q, u)] == [9, 1, 7, 3]
+    q.uq_del(u)
+
+
+def test_update_queue_raise_then_pop_by_hand(q):
+    # heap after pushes a0 b0 c0 d0 e0: [a b c d e]. raise d to 2: bubbles past b (pos 1) and a (pos 0): [d a c b e].
+    # raise e to 2: parent a(0) < 2 -> swap, parent d(2) not < 2 -> stop: [d e c b a].
+    # pop d: a to the root; children e(2), c(0): left strictly greater -> [e a c b]; a's child b(0) not greater.
+    # pop e: b to the root: [b a c]; pop b: c to the root: [c a]; pop c; pop a.
+    u = q.uq_new()
+    for x in (1, 2, 3, 4, 5):
+        q.uq_push_all(u, ptr(k(x, 0, 0)))
+    q.uq_push_prio(u, ptr(k(4, 0, 0)), 2)
+    q.uq_push_prio(u, ptr(k(5, 0, 0)), 2)
+    q.uq_swap(u)
+    assert _drain(q, u) == [(4, 2), (5, 2), (2, 0), (3, 0), (1, 0)]
+    q.uq_del(u)
+
+
+def test_update_queue_repush_after_pop_is_a_fresh_entry(q):
+    # round 1's lazy-deletion heap let a re-pushed item inherit the place of its stale entry; an indexed heap cannot
+    u = q.uq_new()
+    q.uq_push_all(u, ptr(k(1, 0, 0)))
+    q.uq_push_prio(u, ptr(k(1, 0, 0)), 5)
+    q.uq_swap(u)                                      # phase (1,0,0)
     out, pr = k(0, 0, 0), ctypes.c_int32(0)
-    got = []
-    while q.uq_pop(u, ptr(out), ctypes.byref(pr)):
-        got.append(int(out[0]))
-    assert got == [9, 3, 7, 1]
+    assert q.uq_pop(u, ptr(out), ctypes.byref(pr)) == 1 and pr.value == 5
+    for x in (7, 8, 1):
+        q.uq_push_all(u, ptr(k(x, 0, 0)))             # 1 is new in phase (1,0,0) only; elsewhere push_increase(0) is a no-op
+    assert [g[0] for g in _drain(q, u)] == [7, 1, 8]  # [7 8 1] -> pop 7, [1 8] -> pop 1, pop 8
+    q.uq_del(u)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_update_queue_follows_the_full_store_restatement_on_random_traffic(q, seed):
+    """The product keeps a heap of items (csrc/host_queues.h); tests/host_oracle.py keeps the crate's three arrays (IndexMap,
+    heap of indices, qp) with their swap_removes. Same pops, tick after tick, under a binding cap with most priorities equal
+    (load_chunk_updates, voxel_sim_manager.rs:1010-1053, pops at most max_update_rate per tick and leaves the rest queued)."""
+    from tests.host_oracle import VoxelUpdateQueue
+
+    rng = np.random.RandomState(seed)
+    u, ref = q.uq_new(), VoxelUpdateQueue()
+    out, pr, idx = k(0, 0, 0), ctypes.c_int32(0), k(0, 0, 0)
+    for tick in range(120):
+        for _ in range(rng.randint(0, 40)):
+            item = tuple(int(v) for v in rng.randint(0, 6, 3))
+            prio = int(rng.choice([0, 0, 0, 0, 1, 1, 2, 5, -3]))  # push_updates_from_changed priorities are small ints
+            if rng.rand() < 0.5:
+                q.uq_push_all(u, ptr(k(*item)))
+                ref.push_all(item)
+            else:
+                q.uq_push_prio(u, ptr(k(*item)), prio)
+                ref.push_with_priority(item, prio)
+        assert q.uq_len(u) == len(ref)
+        if len(ref) == 0:
+            continue
+        q.uq_swap(u)
+        ref.swap_queue_set()
+        q.uq_idx(u, ptr(idx))
+        assert list(idx) == ref.active
+        for _ in range(rng.randint(1, 14)):               # the cap
+            r = ref.pop()
+            g = q.uq_pop(u, ptr(out), ctypes.byref(pr))
+            if r is None:
+                assert g == 0
+                break
+            assert g == 1 and (tuple(int(v) for v in out), pr.value) == r, "tick %d" % tick
     q.uq_del(u)

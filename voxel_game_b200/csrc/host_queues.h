@@ -1,16 +1,15 @@
 // Host work queues of the compute pass, re-expressed in C++.
 // Mirrors src/utils.rs: QueueMap (:58-149), QueueSet (:151-219), VoxelUpdateQueue (:221-304).
 //
-// Tie order inside VoxelUpdateQueue: the reference pops equal-priority chunks in the iteration
-// order of `priority_queue 2.0.3` over `ahash 0.8.11` (seed 0); neither crate is vendored in the
-// reference tree and no reference test pins the order, so it is UNPINNED. This implementation is
-// deterministic instead: among equal priorities the entry whose priority was set first pops first.
-// The order only decides WHICH chunks run in a tick when max_update_rate binds; the result of
-// updating a given list is order-independent.
+// Tie order inside VoxelUpdateQueue: the reference pops equal-priority chunks in the order that
+// `priority-queue 2.0.3` produces. That crate is not vendored in the reference tree and no reference
+// test pins the order (PARITY UNPINNED); IncreasePQ below restates the crate's heap mechanics, which
+// fix the order without reference to hash values. The order only decides WHICH chunks run in a tick
+// when max_update_rate binds; the result of updating a given list is order-independent.
 #pragma once
 #include <cstdint>
 #include <deque>
-#include <queue>
+#include <utility>
 #include <unordered_map>
 #include <unordered_set>
 #include <vector>
@@ -94,50 +93,91 @@ class QueueSet4 {
     std::unordered_set<Key4, Key4Hash> set_;
 };
 
-// One PriorityQueue<[u32;3], i32> with push_increase / pop (priority-queue crate semantics):
-// push_increase inserts, or raises the priority of an existing item, never lowers it.
+// One PriorityQueue<[u32;3], i32, RandomState> as VoxelUpdateQueue uses it (utils.rs:222, :240, :250, :285):
+// push_increase and pop with the pop ORDER of the `priority-queue` crate, version 2.0.3 (client/Cargo.lock:3029-3036).
+//
+// The crate's source is not under /root/reference, so this restates its published algorithm (PARITY UNPINNED, no
+// reference test holds the order). The crate keeps the items in an insertion-ordered IndexMap and a binary max-heap of
+// map indices beside it. The hasher (ahash, seed 0) only serves look-ups; the pop order among equal priorities follows
+// from the heap mechanics alone:
+//   push of a new item   : appended as the last heap position, then bubbled up while parent < new (strict)
+//   push of a known item : priority replaced, bubbled up from where it stands, then sifted down from where it lands
+//   push_increase        : a push when the item is new or the priority is strictly greater; otherwise nothing
+//   pop                  : the root leaves, the LAST heap position takes its place and is sifted down; a child takes the
+//                          place only when strictly greater, the left child wins a tie between the children
+// The IndexMap's swap_remove relabels map indices on a pop but never moves a heap position, so a heap of items with a
+// position look-up gives the same order as the crate's heap of indices (tests/host_oracle.py keeps the crate's full
+// three-array store and tests/test_host_queues.py checks the two against each other on random traffic).
 class IncreasePQ {
    public:
     void push_increase(const Key3& item, int32_t priority) {
-        auto it = prio_.find(item);
-        if (it == prio_.end()) {
-            prio_.emplace(item, priority);
-            heap_.push(Entry{priority, seq_++, item});
-        } else if (priority > it->second) {
-            it->second = priority;
-            heap_.push(Entry{priority, seq_++, item});  // the stale lower entry is skipped on pop
+        auto it = pos_.find(item);
+        if (it == pos_.end()) {
+            heap_.push_back(Node{item, priority});
+            bubble_up(heap_.size() - 1);
+        } else if (priority > heap_[it->second].priority) {
+            heap_[it->second].priority = priority;
+            heapify(bubble_up(it->second));
         }
     }
     bool pop(Key3& item, int32_t& priority) {
-        while (!heap_.empty()) {
-            Entry e = heap_.top();
-            heap_.pop();
-            auto it = prio_.find(e.item);
-            if (it != prio_.end() && it->second == e.priority) {
-                item = e.item;
-                priority = e.priority;
-                prio_.erase(it);
-                return true;
-            }
+        if (heap_.empty()) return false;
+        item = heap_[0].item;
+        priority = heap_[0].priority;
+        pos_.erase(item);
+        Node last = heap_.back();
+        heap_.pop_back();
+        if (!heap_.empty()) {
+            heap_[0] = last;
+            pos_[last.item] = 0;
+            heapify(0);
         }
-        return false;
+        return true;
     }
-    size_t len() const { return prio_.size(); }
-    bool is_empty() const { return prio_.empty(); }
+    size_t len() const { return heap_.size(); }
+    bool is_empty() const { return heap_.empty(); }
 
    private:
-    struct Entry {
-        int32_t priority;
-        uint64_t seq;
+    struct Node {
         Key3 item;
-        bool operator<(const Entry& o) const {  // max-heap on priority, then FIFO
-            if (priority != o.priority) return priority < o.priority;
-            return seq > o.seq;
-        }
+        int32_t priority;
     };
-    std::unordered_map<Key3, int32_t, Key3Hash> prio_;
-    std::priority_queue<Entry> heap_;
-    uint64_t seq_ = 0;
+    // moves the node at position i towards the root past every strictly smaller parent; returns where it lands
+    size_t bubble_up(size_t i) {
+        Node n = heap_[i];
+        while (i > 0) {
+            size_t parent = (i - 1) / 2;
+            if (!(heap_[parent].priority < n.priority)) break;
+            heap_[i] = heap_[parent];
+            pos_[heap_[i].item] = (uint32_t)i;
+            i = parent;
+        }
+        heap_[i] = n;
+        pos_[n.item] = (uint32_t)i;
+        return i;
+    }
+    void heapify(size_t i) {
+        const size_t n = heap_.size();
+        if (n <= 1) return;
+        for (;;) {
+            size_t l = 2 * i + 1, r = l + 1, largest = i;
+            int32_t lp = heap_[i].priority;
+            if (l < n) {
+                if (heap_[l].priority > lp) {
+                    largest = l;
+                    lp = heap_[l].priority;
+                }
+                if (r < n && heap_[r].priority > lp) largest = r;
+            }
+            if (largest == i) return;
+            std::swap(heap_[i], heap_[largest]);
+            pos_[heap_[i].item] = (uint32_t)i;
+            pos_[heap_[largest].item] = (uint32_t)largest;
+            i = largest;
+        }
+    }
+    std::vector<Node> heap_;
+    std::unordered_map<Key3, uint32_t, Key3Hash> pos_;
 };
 
 // src/utils.rs:221-304
