@@ -447,10 +447,42 @@ def run_ours(args):
             cw.voxel_update(lst, PHASES[(reps + 1) % 8])
             reps += 1
         cs = time.perf_counter() - t0
+        # the same sample walked by the GPU (its own sx-column window, fed the same downloaded voxels, same phases) must end
+        # in the same world: the checker and the product agree on the benchmark's own data, not only on the test scenes
+        chk = vg.VoxelComputePipeline(vg.GameSettings(render_size=(sx, RS[1], RS[2]), max_loaded_chunks=2 + n_s, max_update_rate=1024), device=local_rank)
+        chk.write_table(cw.table)
+        chk.write_pool(2, gpu.read_pool(2, n_s))
+        chk.update_list_upload(lst)
+        for ph in [0] + [(r + 1) % 8 for r in range(reps)]:
+            chk.update_list_run(SP, PHASES[ph])
+        cpu_equal = bool(np.array_equal(chk.read_pool(0, 2 + n_s), cw.pool))
+        chk.close()
         result["cpu_baseline"] = {"value": n_s * 4096 * reps / cs, "unit": "voxel-updates/s", "cores": cpu_threads,
-                                  "kind": "port",
-                                  "sample": "%d ticks over the first %d x-columns of the same world (%d chunks, %d voxels), OpenMP over chunks"
-                                            % (reps, sx, n_s, n_s * 4096)}
+                                  "kind": "port", "equal": cpu_equal,
+                                  "sample": "%d ticks over the first %d x-columns of the same world (%d chunks, %d voxels), OpenMP over chunks; "
+                                            "`equal`: the GPU, given the same %d columns as a window of their own, ends in the same world"
+                                            % (reps, sx, n_s, n_s * 4096, sx)}
+        assert cpu_equal, "GPU and oracle disagree on the benchmark's own world"
+        # worldgen beside it: the oracle generates one 1x16x8-chunk column block of the same world (every height of the
+        # map, 524 288 voxels); the GPU generates the same chunks in a window of their own and must produce the same voxels
+        from tests.oracle_lib import chunk_loads_for
+
+        wrs = (1, RS[1], min(8, RS[2]))
+        n_w = wrs[0] * wrs[1] * wrs[2]
+        ww = CpuWorld(wrs, SP, 2 + n_w)
+        wloads = chunk_loads_for(ww.load_all_chunks(), range(2, 2 + n_w), forced=True)
+        ww.table[:] = 0
+        t0 = time.perf_counter()
+        ww.worldgen(wloads, 0)
+        ws = time.perf_counter() - t0
+        wchk = vg.VoxelComputePipeline(vg.GameSettings(render_size=wrs, max_loaded_chunks=2 + n_w, max_worldgen_rate=8 * n_w), device=local_rank)
+        wchk.dispatch_worldgen(SP, wloads, complete=True, want_results=False)
+        wg_equal = bool(np.array_equal(wchk.read_pool(0, 2 + n_w), ww.pool) and np.array_equal(wchk.read_table(), ww.table))
+        wchk.close()
+        result["worldgen"]["cpu_baseline"] = {"value": n_w * 4096 / ws, "unit": "voxels-generated/s", "cores": cpu_threads, "kind": "port", "equal": wg_equal,
+                                              "sample": "%d chunks (one 1x%dx%d-chunk block at the window origin, forced), OpenMP over 8^3 blocks; `equal`: "
+                                                        "the GPU's voxels and table for the same chunks are identical" % (n_w, wrs[1], wrs[2])}
+        assert wg_equal, "GPU and oracle worldgen disagree on the benchmark's own chunks"
     # ---------------- C5: full tick (worldgen stream + sharded update + replica refresh + 64 views) ----------------
     tick = None
     if args.tick or (world_size == 8 and not args.no_tick):
@@ -783,8 +815,8 @@ def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp,
     return {"metric": "ticks/s", "value": 1e3 / t[4], "unit": "ticks/s", "ms_per_tick": t[4], "n_gpus": world_size, "ticks": n_ticks,
             "phases_ms": {names[k]: t[k] for k in range(4)}, "replica_matches_slab": t[5] == 0.0 and not overflowed,
             "chunks_refreshed_per_tick": moved / n_ticks, "refresh_buffer_chunks_per_rank": refresh_cap,
-            "config": {"workload": "BASELINE configs[4]: %d chunks regenerated + update over all %d chunks + 64 views x 1920x1080 primary rays per tick"
-                                   % (per_rank * world_size, n_total),
+            "config": {"workload": "BASELINE configs[4]: %d chunks regenerated IN PLACE with forced = true (not a new slab face streamed with forced = false) "
+                                               "+ update over all %d chunks + 64 views x 1920x1080 primary rays per tick" % (per_rank * world_size, n_total),
                        "note": "regeneration is forced (slots keep their place) instead of forced = false; per-phase times are the max over ranks, "
                                "their sum is the max over ranks of the per-rank sum"}}
 
@@ -878,14 +910,28 @@ def bench_rays(args, torch, vg, peak, rank=0, world_size=1, dist=None):
     # e2e: camera in from host, layer_count + depth + first layer voxel out to host
     from voxel_game_b200._lib import ptr
 
-    lc_t, out_lc = pinned_u32(torch, (W * H,))  # results land in pinned host memory
+    # results land in pinned host memory: layer_count, depth and the first layer's hit voxel + distance (16 B per ray) — what a
+    # host-side consumer of one hit per pixel reads; the deeper layers stay on the device as in the reference, whose ray
+    # results never leave the GPU (raytracer.rs:234-331 writes the swapchain image)
+    lc_t, out_lc = pinned_u32(torch, (W * H,))
     d_t, out_d = pinned_u32(torch, (W * H,))
-    gpu.raymarch(SP, cams[0:1], W, H, caps)
-    assert gpu._lib.vxb_ray_download(gpu._h, None, None, None, None, None, ptr(out_lc), ptr(out_d), None) == 0
+    v0_t, _ = pinned_u32(torch, (W * H,))
+    l0_t, _ = pinned_u32(torch, (W * H,))
+
+    def e2e_frame(i):
+        gpu.raymarch(SP, cams[i % 8:i % 8 + 1], W, H, caps)
+        rb = gpu.ray_results()
+        assert int(rb.n_rays) == W * H
+        vox0 = torch.as_tensor(DevView(int(rb.voxel), W * H), device="cuda")  # layer 0 = the first n_rays words
+        ld0 = torch.as_tensor(DevView(int(rb.ldist), W * H), device="cuda")
+        v0_t.copy_(vox0, non_blocking=True)
+        l0_t.copy_(ld0, non_blocking=True)
+        assert gpu._lib.vxb_ray_download(gpu._h, None, None, None, None, None, ptr(out_lc), ptr(out_d), None) == 0  # synchronises the stream
+
+    e2e_frame(0)
     t0 = time.perf_counter()
     for i in range(args.steps):
-        gpu.raymarch(SP, cams[i % 8:i % 8 + 1], W, H, caps)
-        assert gpu._lib.vxb_ray_download(gpu._h, None, None, None, None, None, ptr(out_lc), ptr(out_d), None) == 0
+        e2e_frame(i)
     e2e_s = time.perf_counter() - t0
     # full fragment shader (primary DDA + get_color: shadow, reflection, 2 AO rays, PBR) at 1080p
     for k in range(3):
@@ -932,6 +978,34 @@ def bench_rays(args, torch, vg, peak, rank=0, world_size=1, dist=None):
               "ms_per_frame": g0.elapsed_time(g1) / args.steps, "primary_rays_with_gbuffer_ms": g1.elapsed_time(g2) / args.steps,
               "instances": int(inst.size), "triangles_per_instance": int(mesh_p.shape[0] // 3), "covered_fraction": covered,
               "config": {"workload": "RasterizerSystem::draw + max_depth at 1920x1080 (host instance upload included), then primary rays reading the G-buffer"}}
+    # cpu_baseline: the oracle's raycast over whole 1080p frames of the same (downloaded) world, rows in parallel; camera 0's
+    # frame is compared with the GPU's while at it
+    cpu_rays = None
+    if not args.no_cpu:
+        from tests.oracle_lib import CpuWorld
+
+        _, cpu_threads = oracle_all_threads()
+        cw = CpuWorld(RS, SP, 2 + n)
+        cw.table[:] = table
+        cw.pool[:] = gpu.read_pool(0, 2 + n)
+        gpu.raymarch(SP, cams[0:1], W, H, caps)
+        gref = gpu.ray_download()
+        c0 = cw.raycast_image(cams[0:1], W, H, 100)  # also the warm-up
+        m0 = c0["layer_count"] > 0
+        same = bool(np.array_equal(gref["layer_count"], c0["layer_count"]) and gref["total_iterations"] == c0["total_iterations"]
+                    and np.array_equal(gref["voxel"][0][m0], c0["voxel"][m0, 0])
+                    and np.allclose(gref["ldist"][0][m0], c0["ldist"][m0, 0], rtol=1e-4, atol=0))
+        t0 = time.perf_counter()
+        frames = 0
+        while frames < 16 and (time.perf_counter() - t0 < 10 or frames < 2):
+            cw.raycast_image(cams[frames % 8:frames % 8 + 1], W, H, 100)
+            frames += 1
+        cs = time.perf_counter() - t0
+        cpu_rays = {"value": W * H * frames / cs, "unit": "rays/s", "cores": cpu_threads, "kind": "port", "equal": same,
+                    "sample": "%d whole 1920x1080 frames (the same 8 cameras cycled) on the same world, OpenMP over image rows; `equal`: camera 0's "
+                              "layer counts, iteration total and first-layer voxels equal the GPU's, distances within 1e-4" % frames}
+        assert same, "GPU and oracle disagree on the benchmark's own frame"
+        del cw
     collisions = None if args.no_collisions else bench_collisions(args, torch, vg, gpu, SP, RS, (cx, col_y, cz), peak)
     gpu.close()
     achieved = alg_bytes / (ms / args.steps / 1e3) / 1e9
@@ -941,7 +1015,10 @@ def bench_rays(args, torch, vg, peak, rank=0, world_size=1, dist=None):
             "mean_iterations_per_ray": mean_iters / (W * H), "mean_layers_per_ray": mean_layers / (W * H),
             "roofline": {"bound": "hbm", "model": "gather: 8 B per DDA iteration + 16 B + 24 B x layers per ray", "achieved": achieved,
                          "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic_from_profiles("k_raymarch_primary_bytes_per_launch")},
-            "e2e": {"value": W * H * args.steps / e2e_s, "unit": "rays/s", "h2d_bytes_per_step": 128, "d2h_bytes_per_step": W * H * 8}}
+            "cpu_baseline": cpu_rays,
+            "e2e": {"value": W * H * args.steps / e2e_s, "unit": "rays/s", "h2d_bytes_per_step": 128, "d2h_bytes_per_step": W * H * 16,
+                    "api": "vxb_raymarch (host camera in) + vxb_ray_results / vxb_ray_download: layer_count, depth, layer-0 voxel and layer-0 "
+                           "distance to pinned host memory (16 B per ray); layers 1-4, positions and normals stay on the device"}}
 
 
 def bench_collisions(args, torch, vg, gpu, SP, RS, centre, peak):
@@ -977,7 +1054,8 @@ def bench_collisions(args, torch, vg, gpu, SP, RS, centre, peak):
     n_coll = gpu.entities_resident_run(SP, n_proj, n_side * n_side, want_count=True)
     ms = total_ms / steps
     out = {"metric": "projectiles/s", "value": n_proj / (ms / 1e3), "unit": "projectiles/s", "ms_per_tick": ms, "collisions_found": n_coll,
-           "config": {"workload": "BASELINE configs[3]: %d projectiles + %d player hulls vs the config-2 world, one tick (dt 0.02)" % (n_proj, n_side * n_side),
+           "config": {"workload": "BASELINE configs[3]: %d projectiles + %d player hulls vs the config-2 world, one tick (dt 0.02); batch drawn from "
+                                   "numpy RandomState(0x5EED0001) with the distributions of SURVEY 8(d) C4 (not its xorshift64* stream)" % (n_proj, n_side * n_side),
                       "note": "device time of k_projectiles + k_players; entity arrays restored by a device copy between steps (untimed)"}}
     if not args.no_cpu:
         # oracle on a bounded sample of the same batch, same world (downloaded); counters from a sequential pass
