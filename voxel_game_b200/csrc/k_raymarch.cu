@@ -106,26 +106,42 @@ __device__ __forceinline__ SlabHit projectile_slabs(const vxb_projectile& p, f3 
 }
 
 __device__ __forceinline__ void store_layer(const RayOut& o, uint64_t i, uint32_t l, const Layer& L) {
-    const uint64_t n = o.n_rays;
-    o.pos[(l * 3 + 0) * n + i] = L.pos.x;
-    o.pos[(l * 3 + 1) * n + i] = L.pos.y;
-    o.pos[(l * 3 + 2) * n + i] = L.pos.z;
-    o.normal[(l * 3 + 0) * n + i] = L.normal.x;
-    o.normal[(l * 3 + 1) * n + i] = L.normal.y;
-    o.normal[(l * 3 + 2) * n + i] = L.normal.z;
-    o.voxel[l * n + i] = L.voxel;
-    o.ldist[l * n + i] = L.dist;
-    o.leaving[l * n + i] = L.leaving;
+    // pos / normal: [(l*3 + c) * n + i]; voxel / ldist / leaving: [l * n + i]. One 64-bit product, the rest are pointer steps.
+    const uint64_t n = o.n_rays, at = (uint64_t)l * n + i;
+    float* p = o.pos + (at + 2 * (uint64_t)l * n);
+    float* q = o.normal + (at + 2 * (uint64_t)l * n);
+    p[0] = L.pos.x; p[n] = L.pos.y; p[2 * n] = L.pos.z;
+    q[0] = L.normal.x; q[n] = L.normal.y; q[2 * n] = L.normal.z;
+    o.voxel[at] = L.voxel;
+    o.ldist[at] = L.dist;
+    o.leaving[at] = L.leaving;
 }
 
 // frag.glsl:348-486. layers[] must be zero-initialised by the caller (GLSL leaves them undefined;
 // the oracle zeroes them too: the reference's insertion quirk at layer_idx 0 -> 1 exposes layer 0).
 // DIRECT (no projectiles to insert): layers go straight to the output arrays as they are produced and
 // the local layers[] array is never touched (it would live in local memory: dynamic indexing).
+//
+// The DDA loop exists twice with identical results. march_fast serves rays whose three components all have a usable
+// reciprocal and whose origin is below 2^40 (every camera ray in practice); march_generic is the literal form for
+// the rest (a zero / tiny / huge component, NaNs). What march_fast does differently, none of it visible in the bits:
+//  * only the box face a ray can leave through is built per axis (v_max where ray > 0, v_min where ray < 0: the other
+//    one is never read), as floor_pos + s with s = dist + 1 or -dist made by an integer-to-float bit trick instead of
+//    two conversions (x - d == x + (-d) exactly);
+//  * the quotient guard's upper half (|a| < 2^60) holds for the whole march when the origin is below 2^40 (a step
+//    moves a ray by at most the box size), so only |a| >= 2^-24 is tested, once for the three axes;
+//  * the chunk cache holds a pointer to the chunk's 4096 words and the chunk's base coordinates: a step that stays
+//    inside the chunk costs three XORs; outside the window the cache points at sentinel slot 0 (all MAT_OOB);
+//  * the face normal is kept as an axis number and only built when a layer is written.
+struct MarchState {
+    f3 ray_pos, normal;
+    float depth;
+    uint32_t layer_idx;
+};
+
 template <bool DIRECT>
-__device__ uint32_t raycast(const World& w, f3 pos, f3 ray, uint32_t max_iterations, const vxb_projectile* projectiles,
-                            uint32_t projectile_count, float raster_depth, Layer (&layers)[5], float& out_depth, uint32_t& iters,
-                            const RayOut& out, uint64_t ray_index, f3 raster_normal = f3{0.0f, 1.0f, 0.0f}, float raster_diffuse_x = 1.0f) {
+__device__ __forceinline__ MarchState march_generic(const World& w, f3 pos, f3 ray, uint32_t max_iterations, float raster_depth, Layer (&layers)[5],
+                                                    uint32_t& iters, const RayOut& out, uint64_t ray_index) {
     auto push = [&](uint32_t idx, const Layer& L) {
         if (DIRECT) store_layer(out, ray_index, idx, L);
         else layers[idx] = L;
@@ -137,24 +153,10 @@ __device__ uint32_t raycast(const World& w, f3 pos, f3 ray, uint32_t max_iterati
     float depth = 0;
     uint32_t medium = MAT_AIR;
     uint32_t layer_idx = 0;
-    // consecutive steps mostly stay inside one 16^3 chunk: its pool slot is kept, which saves the window test, the
-    // table index arithmetic and — the point — the dependent table load in front of the voxel load
-    uint32_t ccx = 0xFFFFFFFFu, ccy = 0, ccz = 0, cslot = 0;
     for (uint32_t i = 0; i < max_iterations; i++) {
         iters++;
         const f3 floor_pos = floor3(ray_pos);
-        uint32_t voxel_data;
-        {
-            const uint32_t x = f2u(floor_pos.x), y = f2u(floor_pos.y), z = f2u(floor_pos.z);
-            const uint32_t kx = x >> 4, ky = y >> 4, kz = z >> 4;
-            bool have = kx == ccx && ky == ccy && kz == ccz;
-            if (!have && in_window(w, x, y, z)) {
-                cslot = table_lookup_in_window(w, kx, ky, kz);
-                ccx = kx; ccy = ky; ccz = kz;
-                have = true;
-            }
-            voxel_data = have ? w.pool[(uint64_t)cslot * CHUNK_VOLUME + ((x & 15u) << 8 | (y & 15u) << 4 | (z & 15u))] : VOX_OOB;
-        }
+        const uint32_t voxel_data = voxel_at(w, floor_pos);
         const uint32_t voxel_material = voxel_data >> 24;
         f3 v_min, v_max;
         if (voxel_material == MAT_AIR || voxel_material == MAT_AIR_OOB) {
@@ -204,6 +206,156 @@ __device__ uint32_t raycast(const World& w, f3 pos, f3 ray, uint32_t max_iterati
             if (ray.z < 0 && ray_pos.z >= v_min.z) ray_pos.z = v_min.z - 0.001f;
         }
     }
+    return MarchState{ray_pos, normal, depth, layer_idx};
+}
+
+// RN(a / ray) from the correctly rounded reciprocal (see ray_box_axis_rcp); the caller has checked the ranges
+__device__ __forceinline__ float quotient_rcp(float a, float ray, float inv) {
+    const float q0 = a * inv;
+    return __fmaf_rn(__fmaf_rn(-q0, ray, a), inv, q0);
+}
+
+template <bool DIRECT>
+__device__ __forceinline__ MarchState march_fast(const World& w, f3 pos, f3 ray, f3 inv, uint32_t max_iterations, float raster_depth,
+                                                 Layer (&layers)[5], uint32_t& iters, const RayOut& out, uint64_t ray_index) {
+    auto push = [&](uint32_t idx, const Layer& L) {
+        if (DIRECT) store_layer(out, ray_index, idx, L);
+        else layers[idx] = L;
+    };
+    // every component is non-zero here, so "not positive" is "negative". Per axis: sg = +-1, one = 1 or -0:
+    //   far face of a cube of reach d   floor_pos + (d * sg + one)        (d + 1 or -d; exact, so an FMA is the same bits)
+    //   far face of the chunk box       chunk_floor + 16 * one            (x + (-0) == x for every x)
+    const bool pdx = ray.x > 0.0f, pdy = ray.y > 0.0f, pdz = ray.z > 0.0f;
+    const float sgx = pdx ? 1.0f : -1.0f, sgy = pdy ? 1.0f : -1.0f, sgz = pdz ? 1.0f : -1.0f;
+    const float onex = pdx ? 1.0f : -0.0f, oney = pdy ? 1.0f : -0.0f, onez = pdz ? 1.0f : -0.0f;
+    const uint32_t field_shift = 3u * ((pdx ? 0u : 1u) + (pdy ? 0u : 2u) + (pdz ? 0u : 4u));  // ray_octant * 3
+    // the depth clip only exists for raster_depth > 0: otherwise it compares against +inf
+    const float clip = raster_depth > 0.0f ? raster_depth : __uint_as_float(0x7F800000u);
+    uint32_t axis = 3;  // face the ray entered the current voxel through: 0 / 1 / 2, 3 = none yet (normal = -ray)
+    auto face_normal = [&]() -> f3 {
+        if (axis == 0) return mk3(-sgx, 0, 0);
+        if (axis == 1) return mk3(0, -sgy, 0);
+        if (axis == 2) return mk3(0, 0, -sgz);
+        return -ray;
+    };
+    f3 ray_pos = pos;
+    float depth = 0;
+    uint32_t medium = MAT_AIR, layer_idx = 0;
+    // chunk cache: base voxel coordinates of the cached chunk and a pointer to its words; primed so that the first
+    // voxel cannot match
+    uint32_t cbx = __float2uint_rd(pos.x) ^ 0x80000000u, cby = 0, cbz = 0;
+    const uint32_t* cptr = w.pool;
+    uint32_t i = 0;
+    if (max_iterations != 0) {
+        do {
+            i++;
+            const f3 floor_pos = floor3(ray_pos);
+            const uint32_t x = __float2uint_rd(ray_pos.x), y = __float2uint_rd(ray_pos.y), z = __float2uint_rd(ray_pos.z);
+            if (((x ^ cbx) | (y ^ cby) | (z ^ cbz)) >= 16u) {
+                const uint32_t dx = (x >> 4) - w.sp[0], dy = (y >> 4) - w.sp[1], dz = (z >> 4) - w.sp[2];
+                uint32_t slot = 0;  // outside the window: the all-MAT_OOB sentinel chunk
+                if (dx < w.rs[0] && dy < w.rs[1] && dz < w.rs[2]) {
+                    uint32_t tx = dx + w.spm[0], ty = dy + w.spm[1], tz = dz + w.spm[2];
+                    tx -= tx >= w.rs[0] ? w.rs[0] : 0u;
+                    ty -= ty >= w.rs[1] ? w.rs[1] : 0u;
+                    tz -= tz >= w.rs[2] ? w.rs[2] : 0u;
+                    slot = __ldg(&w.table[(size_t)((tx * w.rs[1] + ty) * w.rs[2] + tz)]);  // the table has < 2^32 entries
+                }
+                cptr = w.pool + (size_t)slot * CHUNK_VOLUME;
+                cbx = x & ~15u; cby = y & ~15u; cbz = z & ~15u;
+            }
+            const uint32_t voxel_data = cptr[(x & 15u) << 8 | (y & 15u) << 4 | (z & 15u)];
+            const uint32_t voxel_material = voxel_data >> 24;
+            float bx, by, bz;  // the face of the empty box around the voxel that the ray leaves through, per axis
+            if ((voxel_material | medium) == MAT_AIR) {  // air seen from air: most steps
+                const float d = __uint_as_float(0x4B000000u | ((voxel_data >> field_shift) & 7u)) - 8388608.0f;  // (float)field, from the bits of 2^23 + field
+                bx = floor_pos.x + __fmaf_rn(d, sgx, onex);
+                by = floor_pos.y + __fmaf_rn(d, sgy, oney);
+                bz = floor_pos.z + __fmaf_rn(d, sgz, onez);
+            } else if (voxel_material == MAT_AIR_OOB) {
+                if (medium != MAT_AIR) {
+                    push(layer_idx, Layer{ray_pos, face_normal(), medium << 24, depth, 1u});
+                    layer_idx++;
+                    if (layer_idx >= 5) break;
+                }
+                medium = MAT_AIR;
+                const f3 c = floor3(ray_pos / 16.0f) * 16.0f;  // chunk_bounds
+                bx = __fmaf_rn(onex, 16.0f, c.x); by = __fmaf_rn(oney, 16.0f, c.y); bz = __fmaf_rn(onez, 16.0f, c.z);
+            } else {
+                float d = 0.0f;  // transparent voxels: the unit cube, i.e. reach 0
+                if (voxel_material == MAT_AIR) {
+                    push(layer_idx, Layer{ray_pos, face_normal(), medium << 24, depth, 1u});  // medium != MAT_AIR here
+                    layer_idx++;
+                    if (layer_idx >= 5) break;
+                    medium = MAT_AIR;
+                    d = __uint_as_float(0x4B000000u | ((voxel_data >> field_shift) & 7u)) - 8388608.0f;
+                } else if (mat_in(MASK_TRANSPARENT, voxel_material)) {
+                    if (medium != voxel_material) {
+                        push(layer_idx, Layer{ray_pos, face_normal(), voxel_data, depth, 0u});
+                        layer_idx++;
+                        if (layer_idx >= 5) break;
+                    }
+                    medium = voxel_material;
+                } else {
+                    push(layer_idx, Layer{ray_pos, face_normal(), voxel_data, depth, 0u});
+                    layer_idx++;
+                    break;
+                }
+                bx = floor_pos.x + __fmaf_rn(d, sgx, onex);
+                by = floor_pos.y + __fmaf_rn(d, sgy, oney);
+                bz = floor_pos.z + __fmaf_rn(d, sgz, onez);
+            }
+            const float ax = bx - ray_pos.x, ay = by - ray_pos.y, az = bz - ray_pos.z;
+            float qx = quotient_rcp(ax, ray.x, inv.x), qy = quotient_rcp(ay, ray.y, inv.y), qz = quotient_rcp(az, ray.z, inv.z);
+            const float QMIN = 5.9604644775390625e-08f;  // 2^-24, the lower end of the range the reciprocal form is exact on
+            if (!(fminf(fminf(fabsf(ax), fabsf(ay)), fabsf(az)) >= QMIN)) {  // (a NaN operand makes fminf return the other one: NaNs cannot
+                if (!(fabsf(ax) >= QMIN)) qx = ax / ray.x;                      //  occur here, and the divider would reproduce them anyway)
+                if (!(fabsf(ay) >= QMIN)) qy = ay / ray.y;
+                if (!(fabsf(az) >= QMIN)) qz = az / ray.z;
+            }
+            const float qyz = gmin(qy, qz);
+            const float dist_diff = gmin(qx, qyz);
+            if (depth + dist_diff > clip) {
+                depth = raster_depth;
+                ray_pos = pos + depth * ray;
+                break;
+            }
+            depth += dist_diff;
+            ray_pos = ray_pos + ray * dist_diff;
+            // snap onto the far side of the face just crossed; only rays travelling down an axis need it (:412-424)
+            if (qx < qy && qx < qz) {
+                axis = 0;
+                if (!pdx && ray_pos.x >= bx) ray_pos.x = bx - 0.001f;
+            } else if (qy < qz) {
+                axis = 1;
+                if (!pdy && ray_pos.y >= by) ray_pos.y = by - 0.001f;
+            } else {
+                axis = 2;
+                if (!pdz && ray_pos.z >= bz) ray_pos.z = bz - 0.001f;
+            }
+        } while (i < max_iterations);
+    }
+    iters += i;
+    return MarchState{ray_pos, face_normal(), depth, layer_idx};
+}
+
+template <bool DIRECT>
+__device__ uint32_t raycast(const World& w, f3 pos, f3 ray, uint32_t max_iterations, const vxb_projectile* projectiles,
+                            uint32_t projectile_count, float raster_depth, Layer (&layers)[5], float& out_depth, uint32_t& iters,
+                            const RayOut& out, uint64_t ray_index, f3 raster_normal = f3{0.0f, 1.0f, 0.0f}, float raster_diffuse_x = 1.0f) {
+    auto push = [&](uint32_t idx, const Layer& L) {
+        if (DIRECT) store_layer(out, ray_index, idx, L);
+        else layers[idx] = L;
+    };
+    const f3 ray_inv = ray_inverse3(ray);
+    const float POS_MAX = 1099511627776.0f;  // 2^40
+    const bool fast = ray_inv.x != 0.0f && ray_inv.y != 0.0f && ray_inv.z != 0.0f && fabsf(pos.x) < POS_MAX && fabsf(pos.y) < POS_MAX &&
+                      fabsf(pos.z) < POS_MAX;
+    const MarchState ms = fast ? march_fast<DIRECT>(w, pos, ray, ray_inv, max_iterations, raster_depth, layers, iters, out, ray_index)
+                               : march_generic<DIRECT>(w, pos, ray, max_iterations, raster_depth, layers, iters, out, ray_index);
+    const f3 ray_pos = ms.ray_pos;
+    float depth = ms.depth;
+    uint32_t layer_idx = ms.layer_idx;
 
     if (raster_depth > 0.0f && layer_idx < 5) {
         // frag.glsl:428-437: u_normals / u_diffuse of the G-buffer pass (k_raster.cu), or, without one, (0,1,0) / 1
@@ -243,8 +395,127 @@ __device__ uint32_t raycast(const World& w, f3 pos, f3 ray, uint32_t max_iterati
     return layer_idx;
 }
 
+// State shared by the fast forms of the secondary DDAs (single_raycast, simple_raycast): the same devices as march_fast
+// above (one face per axis, chunk pointer cache, 2^-24 guard only), with the two-sided snap of frag.glsl:130-151.
+struct FastDda {
+    f3 ray, inv;
+    float sgx, sgy, sgz, onex, oney, onez;  // +-1 and 1 / -0 per axis (see march_fast)
+    bool pdx, pdy, pdz;
+    uint32_t field_shift;
+    uint32_t cbx, cby, cbz;
+    const uint32_t* cptr;
+
+    __device__ __forceinline__ void init(const World& w, f3 pos, f3 ray_, f3 inv_) {
+        ray = ray_; inv = inv_;
+        pdx = ray.x > 0.0f; pdy = ray.y > 0.0f; pdz = ray.z > 0.0f;
+        sgx = pdx ? 1.0f : -1.0f; sgy = pdy ? 1.0f : -1.0f; sgz = pdz ? 1.0f : -1.0f;
+        onex = pdx ? 1.0f : -0.0f; oney = pdy ? 1.0f : -0.0f; onez = pdz ? 1.0f : -0.0f;
+        field_shift = 3u * ((pdx ? 0u : 1u) + (pdy ? 0u : 2u) + (pdz ? 0u : 4u));
+        cbx = __float2uint_rd(pos.x) ^ 0x80000000u; cby = 0; cbz = 0;
+        cptr = w.pool;
+    }
+    // get_data(uvec3(floor(ray_pos)))
+    __device__ __forceinline__ uint32_t fetch(const World& w, f3 ray_pos) {
+        const uint32_t x = __float2uint_rd(ray_pos.x), y = __float2uint_rd(ray_pos.y), z = __float2uint_rd(ray_pos.z);
+        if (((x ^ cbx) | (y ^ cby) | (z ^ cbz)) >= 16u) {
+            const uint32_t dx = (x >> 4) - w.sp[0], dy = (y >> 4) - w.sp[1], dz = (z >> 4) - w.sp[2];
+            uint32_t slot = 0;
+            if (dx < w.rs[0] && dy < w.rs[1] && dz < w.rs[2]) {
+                uint32_t tx = dx + w.spm[0], ty = dy + w.spm[1], tz = dz + w.spm[2];
+                tx -= tx >= w.rs[0] ? w.rs[0] : 0u;
+                ty -= ty >= w.rs[1] ? w.rs[1] : 0u;
+                tz -= tz >= w.rs[2] ? w.rs[2] : 0u;
+                slot = __ldg(&w.table[(size_t)((tx * w.rs[1] + ty) * w.rs[2] + tz)]);
+            }
+            cptr = w.pool + (size_t)slot * CHUNK_VOLUME;
+            cbx = x & ~15u; cby = y & ~15u; cbz = z & ~15u;
+        }
+        return cptr[(x & 15u) << 8 | (y & 15u) << 4 | (z & 15u)];
+    }
+    // far faces of the cube of reach `field` around floor_pos (cube_bounds) / of the chunk box (chunk_bounds)
+    __device__ __forceinline__ void cube_faces(f3 floor_pos, uint32_t field, float& bx, float& by, float& bz) const {
+        const float d = __uint_as_float(0x4B000000u | field) - 8388608.0f;
+        bx = floor_pos.x + __fmaf_rn(d, sgx, onex);
+        by = floor_pos.y + __fmaf_rn(d, sgy, oney);
+        bz = floor_pos.z + __fmaf_rn(d, sgz, onez);
+    }
+    __device__ __forceinline__ void chunk_faces(f3 ray_pos, float& bx, float& by, float& bz) const {
+        const f3 c = floor3(ray_pos / 16.0f) * 16.0f;
+        bx = __fmaf_rn(onex, 16.0f, c.x); by = __fmaf_rn(oney, 16.0f, c.y); bz = __fmaf_rn(onez, 16.0f, c.z);
+    }
+    // box_delta for the three faces
+    __device__ __forceinline__ f3 quotients(f3 ray_pos, float bx, float by, float bz) const {
+        const float ax = bx - ray_pos.x, ay = by - ray_pos.y, az = bz - ray_pos.z;
+        float qx = quotient_rcp(ax, ray.x, inv.x), qy = quotient_rcp(ay, ray.y, inv.y), qz = quotient_rcp(az, ray.z, inv.z);
+        const float QMIN = 5.9604644775390625e-08f;
+        if (!(fminf(fminf(fabsf(ax), fabsf(ay)), fabsf(az)) >= QMIN)) {
+            if (!(fabsf(ax) >= QMIN)) qx = ax / ray.x;
+            if (!(fabsf(ay) >= QMIN)) qy = ay / ray.y;
+            if (!(fabsf(az) >= QMIN)) qz = az / ray.z;
+        }
+        return f3{qx, qy, qz};
+    }
+    // snap_both on the face crossed; returns its axis
+    __device__ __forceinline__ uint32_t snap(f3& ray_pos, f3 q, float bx, float by, float bz) const {
+        if (q.x < q.y && q.x < q.z) {
+            if (pdx) { if (ray_pos.x < bx) ray_pos.x = bx; } else if (ray_pos.x >= bx) ray_pos.x = bx - 0.001f;
+            return 0;
+        } else if (q.y < q.z) {
+            if (pdy) { if (ray_pos.y < by) ray_pos.y = by; } else if (ray_pos.y >= by) ray_pos.y = by - 0.001f;
+            return 1;
+        }
+        if (pdz) { if (ray_pos.z < bz) ray_pos.z = bz; } else if (ray_pos.z >= bz) ray_pos.z = bz - 0.001f;
+        return 2;
+    }
+    __device__ __forceinline__ f3 face_normal(uint32_t axis) const {
+        if (axis == 0) return mk3(-sgx, 0, 0);
+        if (axis == 1) return mk3(0, -sgy, 0);
+        if (axis == 2) return mk3(0, 0, -sgz);
+        return mk3(0, 0, 0);
+    }
+};
+__device__ __forceinline__ bool fast_ray(f3 pos, f3 inv) {
+    const float POS_MAX = 1099511627776.0f;  // 2^40
+    return inv.x != 0.0f && inv.y != 0.0f && inv.z != 0.0f && fabsf(pos.x) < POS_MAX && fabsf(pos.y) < POS_MAX && fabsf(pos.z) < POS_MAX;
+}
+
+__device__ Layer single_raycast_fast(const World& w, f3 pos, f3 ray, f3 ray_inv, uint32_t max_iterations, uint32_t& iters) {
+    FastDda d;
+    d.init(w, pos, ray, ray_inv);
+    f3 ray_pos = pos;
+    uint32_t axis = 3;
+    float depth = 0;
+    uint32_t voxel_data = VOX_OOB;
+    const uint32_t medium = d.fetch(w, ray_pos) >> 24;
+    const bool medium_has_field = mat_in(MASK_DATA_DISTANCE, medium);
+    bool did_hit = false;
+    uint32_t i = 0;
+    while (i < max_iterations) {
+        i++;
+        voxel_data = d.fetch(w, ray_pos);
+        const uint32_t voxel_material = voxel_data >> 24;
+        float bx, by, bz;
+        if (voxel_material == MAT_AIR_OOB) {
+            d.chunk_faces(ray_pos, bx, by, bz);
+        } else if (voxel_material == medium) {
+            d.cube_faces(floor3(ray_pos), medium_has_field ? (voxel_data >> d.field_shift) & 7u : 0u, bx, by, bz);
+        } else {
+            did_hit = true;
+            break;
+        }
+        const f3 q = d.quotients(ray_pos, bx, by, bz);
+        const float dist_diff = gmin(q.x, gmin(q.y, q.z));
+        depth += dist_diff;
+        ray_pos = ray_pos + ray * dist_diff;
+        axis = d.snap(ray_pos, q, bx, by, bz);
+    }
+    iters += i;
+    if (!did_hit) return Layer{pos, mk3(0.0f, 0.0f, 0.0f), VOX_OOB, 0.0f, 0u};
+    return Layer{ray_pos, d.face_normal(axis), voxel_data, depth, 0u};
+}
+
 // frag.glsl:93-159
-__device__ Layer single_raycast(const World& w, f3 pos, f3 ray, uint32_t max_iterations, uint32_t& iters) {
+__device__ Layer single_raycast_generic(const World& w, f3 pos, f3 ray, uint32_t max_iterations, uint32_t& iters) {
     const uint32_t offset = ray_octant(ray);
     const f3 ray_inv = ray_inverse3(ray);
     f3 ray_pos = pos;
@@ -279,13 +550,18 @@ __device__ Layer single_raycast(const World& w, f3 pos, f3 ray, uint32_t max_ite
     return Layer{ray_pos, normal, voxel_data, depth, 0u};
 }
 
+__device__ __noinline__ Layer single_raycast(const World& w, f3 pos, f3 ray, uint32_t max_iterations, uint32_t& iters) {
+    const f3 ray_inv = ray_inverse3(ray);
+    if (fast_ray(pos, ray_inv)) return single_raycast_fast(w, pos, ray, ray_inv, max_iterations, iters);
+    return single_raycast_generic(w, pos, ray, max_iterations, iters);
+}
+
 // frag.glsl:275-345 (W_PROJ = false) and :161-273 (W_PROJ = true). Returns layer-shaped result;
 // passthrough_light through `light`.
-template <bool W_PROJ>
-__device__ Layer simple_raycast(const World& w, f3 pos, f3 ray, uint32_t max_iterations, const vxb_projectile* projectiles,
-                                uint32_t projectile_count, float& light, uint32_t& iters) {
+template <bool W_PROJ, bool FAST>
+__device__ __forceinline__ Layer simple_raycast_impl(const World& w, f3 pos, f3 ray, f3 ray_inv, uint32_t max_iterations,
+                                                     const vxb_projectile* projectiles, uint32_t projectile_count, float& light, uint32_t& iters) {
     const uint32_t offset = ray_octant(ray);
-    const f3 ray_inv = ray_inverse3(ray);
     float passthrough_light = 1.0f;
     f3 ray_pos = pos;
     float depth = 0;
@@ -317,41 +593,78 @@ __device__ Layer simple_raycast(const World& w, f3 pos, f3 ray, uint32_t max_ite
         }
     }
 
-    for (uint32_t i = 0; i < max_iterations; i++) {
-        iters++;
-        const f3 floor_pos = floor3(ray_pos);
-        voxel_data = voxel_at(w, floor_pos);
-        f3 v_min, v_max;
-        const uint32_t voxel_material = voxel_data >> 24;
-        if (!mat_in(MASK_TRANSPARENT, voxel_material)) {
-            did_hit = true;
-            end_ray_pos = ray_pos;
-            end_voxel_data = voxel_data;
-            end_depth = depth;
-            break;
+    if (FAST) {
+        FastDda d;
+        d.init(w, pos, ray, ray_inv);
+        uint32_t i = 0;
+        while (i < max_iterations) {
+            i++;
+            voxel_data = d.fetch(w, ray_pos);
+            const uint32_t voxel_material = voxel_data >> 24;
+            if (!mat_in(MASK_TRANSPARENT, voxel_material)) {
+                did_hit = true;
+                end_ray_pos = ray_pos;
+                end_voxel_data = voxel_data;
+                end_depth = depth;
+                break;
+            }
+            float bx, by, bz;
+            if (voxel_material == MAT_AIR_OOB) d.chunk_faces(ray_pos, bx, by, bz);
+            else d.cube_faces(floor3(ray_pos), mat_in(MASK_DATA_DISTANCE, voxel_material) ? (voxel_data >> d.field_shift) & 7u : 0u, bx, by, bz);
+            const f3 q = d.quotients(ray_pos, bx, by, bz);
+            const float dist_diff = gmin(q.x, gmin(q.y, q.z));
+            depth += dist_diff;
+            if (prev_voxel_material != voxel_material) passthrough_light *= material_transparency(voxel_material);
+            prev_voxel_material = voxel_material;
+            if (W_PROJ && depth > max_dist) break;
+            ray_pos = ray_pos + ray * dist_diff;
+            d.snap(ray_pos, q, bx, by, bz);
         }
-        if (voxel_material == MAT_AIR_OOB) {
-            chunk_bounds(ray_pos, v_min, v_max);
-        } else {
-            uint32_t dist = 0;
-            if (mat_in(MASK_DATA_DISTANCE, voxel_material)) dist = (voxel_data >> (offset * 3)) & 7u;
-            cube_bounds(floor_pos, dist, v_min, v_max);
+        iters += i;
+    } else {
+        for (uint32_t i = 0; i < max_iterations; i++) {
+            iters++;
+            const f3 floor_pos = floor3(ray_pos);
+            voxel_data = voxel_at(w, floor_pos);
+            f3 v_min, v_max;
+            const uint32_t voxel_material = voxel_data >> 24;
+            if (!mat_in(MASK_TRANSPARENT, voxel_material)) {
+                did_hit = true;
+                end_ray_pos = ray_pos;
+                end_voxel_data = voxel_data;
+                end_depth = depth;
+                break;
+            }
+            if (voxel_material == MAT_AIR_OOB) {
+                chunk_bounds(ray_pos, v_min, v_max);
+            } else {
+                uint32_t dist = 0;
+                if (mat_in(MASK_DATA_DISTANCE, voxel_material)) dist = (voxel_data >> (offset * 3)) & 7u;
+                cube_bounds(floor_pos, dist, v_min, v_max);
+            }
+            const f3 delta = box_delta(ray_pos, ray, ray_inv, v_min, v_max);
+            const float dist_diff = gmin(delta.x, gmin(delta.y, delta.z));
+            depth += dist_diff;
+            if (prev_voxel_material != voxel_material) passthrough_light *= material_transparency(voxel_material);
+            prev_voxel_material = voxel_material;
+            if (W_PROJ && depth > max_dist) break;
+            ray_pos = ray_pos + ray * dist_diff;
+            f3 unused;
+            snap_both<false>(ray_pos, ray, delta, v_min, v_max, unused);
         }
-        const f3 delta = box_delta(ray_pos, ray, ray_inv, v_min, v_max);
-        const float dist_diff = gmin(delta.x, gmin(delta.y, delta.z));
-        depth += dist_diff;
-        if (prev_voxel_material != voxel_material) passthrough_light *= material_transparency(voxel_material);
-        prev_voxel_material = voxel_material;
-        if (W_PROJ && depth > max_dist) break;
-        ray_pos = ray_pos + ray * dist_diff;
-        f3 unused;
-        snap_both<false>(ray_pos, ray, delta, v_min, v_max, unused);
     }
     light = passthrough_light;
     if (!did_hit) return Layer{pos, mk3(0, 0, 0), VOX_OOB, 0.0f, 0u};
     if (W_PROJ) return Layer{end_ray_pos, mk3(0, 0, 0), end_voxel_data, end_depth, 0u};
     // simple_raycast returns the loop's own state (identical to end_* when did_hit)
     return Layer{ray_pos, mk3(0, 0, 0), voxel_data, depth, 0u};
+}
+template <bool W_PROJ>
+__device__ __noinline__ Layer simple_raycast(const World& w, f3 pos, f3 ray, uint32_t max_iterations, const vxb_projectile* projectiles,
+                                             uint32_t projectile_count, float& light, uint32_t& iters) {
+    const f3 ray_inv = ray_inverse3(ray);
+    if (fast_ray(pos, ray_inv)) return simple_raycast_impl<W_PROJ, true>(w, pos, ray, ray_inv, max_iterations, projectiles, projectile_count, light, iters);
+    return simple_raycast_impl<W_PROJ, false>(w, pos, ray, ray_inv, max_iterations, projectiles, projectile_count, light, iters);
 }
 
 }  // namespace vxb
@@ -366,7 +679,10 @@ __device__ __forceinline__ void count_iters(const RayOut& o, uint32_t iters) {
 }
 
 // One thread per pixel; block = 8x8 pixels = two 8x4 warp tiles; blockIdx.z = view.
-__global__ void __launch_bounds__(128) k_raymarch_primary(World w, const vxb_player* __restrict__ cams, uint32_t width, uint32_t height,
+#ifndef VXB_PRIMARY_MIN_BLOCKS
+#define VXB_PRIMARY_MIN_BLOCKS 8
+#endif
+__global__ void __launch_bounds__(128, VXB_PRIMARY_MIN_BLOCKS) k_raymarch_primary(World w, const vxb_player* __restrict__ cams, uint32_t width, uint32_t height,
                                                          uint32_t max_iterations, const vxb_projectile* __restrict__ projectiles,
                                                          uint32_t projectile_count, RasterIn raster, RayOut out) {
     // block = 16 x 8 pixels, four warps of 8 wide x 4 high

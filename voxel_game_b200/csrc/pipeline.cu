@@ -55,6 +55,8 @@ int vxb::create_ctx(const vxb_settings* settings, int device, cudaError_t (*pool
     for (int i = 0; i < 3; i++)
         if (s.render_size[i] == 0) return fail(nullptr, VXB_ERR_INVALID, "vxb_create: render_size must be > 0 on every axis");
     if (s.max_loaded_chunks < 2) return fail(nullptr, VXB_ERR_INVALID, "vxb_create: max_loaded_chunks must be >= 2 (sentinel slots)");
+    if ((uint64_t)s.render_size[0] * s.render_size[1] >= (1ull << 32) || (uint64_t)s.render_size[0] * s.render_size[1] * s.render_size[2] >= (1ull << 32))
+        return fail(nullptr, VXB_ERR_INVALID, "vxb_create: the chunk table must have fewer than 2^32 entries (the ray kernels index it in 32 bits)");
     if (s.world_gen > 1) return fail(nullptr, VXB_ERR_INVALID, "vxb_create: world_gen must be 0 (Normal) or 1 (Control)");
     if ((uint64_t)s.max_loaded_chunks * CHUNK_VOLUME >= (1ull << 40))
         return fail(nullptr, VXB_ERR_INVALID, "vxb_create: voxel pool too large");
