@@ -398,6 +398,12 @@ int vxb_raymarch_resident(vxb_ctx* ctx, const uint32_t start_pos[3], uint32_t fi
  * Asynchronous. raster_depth as in vxb_raymarch. */
 int vxb_render(vxb_ctx* ctx, const uint32_t start_pos[3], const vxb_player* cams, uint32_t n_views, uint32_t w, uint32_t h,
                const vxb_ray_caps* caps, float time, const float* raster_depth);
+/* Selects how vxb_render runs the shader: 0 = default, a wavefront of small kernels (primary layers into the ray
+ * buffers — vxb_ray_results / vxb_ray_download then return the primary layers of the last group of views — followed by
+ * per-layer rounds of material / shadow / reflection / ambient / lighting kernels over compacted pixel lists), 1 = one
+ * fused kernel per pixel, the shape of the fragment shader. Same arithmetic in the same order: identical colours.
+ * No counterpart in the reference (the fragment shader is one draw, src/raytracer.rs:286-303). */
+int vxb_set_render_kernel(vxb_ctx* ctx, int variant);
 /* ---- the player-mesh G-buffer pass (client/src/rasterizer.rs, the Deferred pass of main.rs:609-624) ----
  * Rasterisation written as CUDA kernels; there is no graphics API underneath. The reference leaves
  * coverage / clipping / interpolation to the Vulkan implementation; the rules used here (pixel centres,

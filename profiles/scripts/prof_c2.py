@@ -39,7 +39,12 @@ if what in ("rays", "all"):
     print("primary: %.4f ms/frame  %.2f G rays/s  (last frame %.2f iterations/ray)" % (ms, W * H / ms / 1e6, it / (W * H)))
 if what in ("render", "all"):
     ms = timed(lambda k: g.render(SP, cams[k % 8:k % 8 + 1], W, H, caps, time=1.0), 16)
-    print("shaded: %.4f ms/frame" % ms)
+    print("shaded (wavefront): %.4f ms/frame" % ms)
+    a = g.color_download()[0].copy()
+    g.set_render_kernel(1)
+    ms = timed(lambda k: g.render(SP, cams[k % 8:k % 8 + 1], W, H, caps, time=1.0), 16)
+    print("shaded (fused): %.4f ms/frame; same bits: %s" % (ms, np.array_equal(a.view(np.uint32), g.color_download()[0].view(np.uint32))))
+    g.set_render_kernel(0)
 if what in ("proj", "all"):
     n_proj, n_side = 1 << 20, 8
     lo = (16 * SP[0] + 8, 16 * SP[1] + 8, 16 * SP[2] + 8)

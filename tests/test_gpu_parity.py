@@ -512,6 +512,14 @@ def test_render_full_fragment_shader(world_gen, seed, yaw, pitch, t):
     game = vg.Game(gpu, vg.GameState(start_pos=list(sp)), cam)
     vg.PointLightingSystem().draw((w, h), None, None, None, None, game, vg.GraphicsSettings(), rendered_projectile_count=4, time=t)
     g = gpu.color_download()[0]
+    it_wave = gpu.ray_download()["total_iterations"]
+    # the default is a wavefront of small kernels (shade_wave.cuh); the fused per-pixel kernel must give the same bits and
+    # walk the same number of DDA iterations (primary + secondary)
+    gpu.set_render_kernel(1)
+    vg.PointLightingSystem().draw((w, h), None, None, None, None, game, vg.GraphicsSettings(), rendered_projectile_count=4, time=t)
+    fused = gpu.color_download()[0]
+    assert np.array_equal(g.view(np.uint32), fused.view(np.uint32)) and it_wave == gpu.ray_download()["total_iterations"] > 20 * w * h
+    gpu.set_render_kernel(0)
     c = cpu.render_image(cam, w, h, caps=(100, 40, 20, 15), time=t, projectiles=projectiles)
     assert np.isfinite(c).all() and g.shape == c.shape
     close = np.isclose(g, c, rtol=RTOL, atol=1e-5).all(axis=2)

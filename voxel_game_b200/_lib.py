@@ -155,6 +155,7 @@ SIGNATURES = {
     "vxb_update_list_run": (ctypes.c_int, [c_vp, c_vp, c_vp]),
     "vxb_update_list_flags": (ctypes.c_int, [c_vp, c_vp, c_u32]),
     "vxb_set_update_kernel": (ctypes.c_int, [c_vp, ctypes.c_int]),
+    "vxb_set_render_kernel": (ctypes.c_int, [c_vp, ctypes.c_int]),
     "vxb_cams_upload": (ctypes.c_int, [c_vp, c_vp, c_u32]),
     "vxb_raymarch_resident": (ctypes.c_int, [c_vp, c_vp, c_u32, c_u32, c_u32, c_u32, c_vp]),
     "vxb_raster_set_mesh": (ctypes.c_int, [c_vp, c_vp, c_vp, c_u32]),

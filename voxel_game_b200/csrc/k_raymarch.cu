@@ -669,6 +669,7 @@ __device__ __noinline__ Layer simple_raycast(const World& w, f3 pos, f3 ray, uin
 
 }  // namespace vxb
 #include "shade.cuh"
+#include "shade_wave.cuh"
 namespace vxb {
 
 __device__ __forceinline__ void count_iters(const RayOut& o, uint32_t iters) {
@@ -825,6 +826,56 @@ cudaError_t launch_render(const World& w, const vxb_player* cams_dev, uint32_t n
     out.total_iters = total_iters;
     dim3 grid((width + 7) / 8, (height + 7) / 8, n_views);
     k_render<<<grid, 64, 0, st>>>(w, cams_dev, width, height, caps.primary_ray_dist, sp, raster, reinterpret_cast<float4*>(color_out), out);
+    return cudaGetLastError();
+}
+
+uint64_t render_wave_scratch_words(uint32_t n_views, uint32_t width, uint32_t height) {
+    const uint64_t cap = (uint64_t)((width + 15) / 16) * ((height + 7) / 8) * n_views * WAVE_BLOCK;
+    return cap * (18 + 8 + 1 + 2) + 8;
+}
+
+// frag.glsl main as a wavefront (shade_wave.cuh): primary layers -> five rounds of setup / trace / combine.
+// `layers` must hold n_views * width * height rays; `scratch` render_wave_scratch_words() words.
+cudaError_t launch_render_wave(const World& w, const vxb_player* cams_dev, uint32_t n_views, uint32_t width, uint32_t height,
+                               const vxb_ray_caps& caps, float time, const vxb_projectile* projectiles, RasterIn raster, RayOut layers,
+                               uint32_t* scratch, float* color_out, cudaStream_t st) {
+    if (n_views == 0 || width == 0 || height == 0) return cudaSuccess;
+    ShadeParams sp;
+    sp.time = time;
+    sp.shadow_ray_dist = caps.shadow_ray_dist;
+    sp.reflection_ray_dist = caps.reflection_ray_dist;
+    sp.ao_ray_dist = caps.ao_ray_dist;
+    sp.vertical_resolution = height;  // raytracer.rs:252
+    sp.projectiles = projectiles;
+    sp.projectile_count = caps.projectile_count;
+    const uint64_t cap64 = (uint64_t)((width + 15) / 16) * ((height + 7) / 8) * n_views * WAVE_BLOCK;
+    if (cap64 >= (1ull << 32)) return cudaErrorInvalidValue;  // pixel lists are 32-bit: the caller splits the views
+    const uint32_t cap = (uint32_t)cap64;
+    WaveScratch ws;
+    ws.cap = cap;
+    ws.job = reinterpret_cast<float*>(scratch);
+    ws.res = scratch + (size_t)18 * cap;
+    ws.state = scratch + (size_t)26 * cap;
+    ws.list[0] = scratch + (size_t)27 * cap;
+    ws.list[1] = scratch + (size_t)28 * cap;
+    ws.count = scratch + (size_t)29 * cap;
+    cudaError_t e = cudaMemsetAsync(ws.count, 0, 8 * sizeof(uint32_t), st);
+    if (e != cudaSuccess) return e;
+    dim3 pgrid((width + 15) / 16, (height + 7) / 8, n_views);
+    k_raymarch_primary<<<pgrid, 128, 0, st>>>(w, cams_dev, width, height, caps.primary_ray_dist, projectiles, caps.projectile_count, raster, layers);
+    float4* color = reinterpret_cast<float4*>(color_out);
+    const uint32_t full = cap / WAVE_BLOCK;
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
+    for (uint32_t round = 0; round < 5; round++) {
+        // round 0 walks every slot; later rounds walk a list whose length only the device knows (grid-stride over it)
+        const uint32_t g = round == 0 ? full : (full < (uint32_t)sms * 8u ? full : (uint32_t)sms * 8u);
+        k_shade_setup<<<g, WAVE_BLOCK, 0, st>>>(w, cams_dev, width, height, sp, layers, ws, cap, round, color);
+        k_trace_shadow<<<g, WAVE_BLOCK, 0, st>>>(w, sp, ws, cap, round, layers.total_iters);
+        k_trace_reflect<<<g, WAVE_BLOCK, 0, st>>>(w, sp, ws, cap, round, layers.total_iters);
+        k_trace_ao<<<dim3(g, 2), WAVE_BLOCK, 0, st>>>(w, sp, ws, cap, round, layers.total_iters);
+        k_shade_combine<<<g, WAVE_BLOCK, 0, st>>>(cams_dev, width, height, layers, ws, cap, round, color);
+    }
     return cudaGetLastError();
 }
 

@@ -32,7 +32,7 @@ static void free_ctx(vxb_ctx* c) {
     c->update_flags.release(); c->voxel_writes.release(); c->scalars.release(); c->res_list.release(); c->res_flags.release();
     c->ray_pos.release(); c->ray_normal.release(); c->ray_ldist.release(); c->ray_dist.release(); c->ray_in_pos.release();
     c->ray_in_dir.release(); c->raster_depth.release(); c->ray_voxel.release(); c->ray_leaving.release(); c->ray_count.release();
-    c->cams.release(); c->color.release(); c->dmg_log.release(); c->dmg_count.release();
+    c->cams.release(); c->color.release(); c->wave_scratch.release(); c->dmg_log.release(); c->dmg_count.release();
     c->mesh_pos.release(); c->mesh_normal.release(); c->raster_instances.release(); c->raster_key.release();
     c->gb_depth.release(); c->gb_normal.release(); c->gb_diffuse.release(); c->gb_max_depth.release();
     c->h_projectiles.release(); c->h_players.release(); c->h_collisions.release(); c->h_collision_count.release();
@@ -931,7 +931,33 @@ int vxb_render(vxb_ctx* c, const uint32_t start_pos[3], const vxb_player* cams, 
         rd = RasterIn{c->gb_max_depth.p, c->gb_normal.p, c->gb_diffuse.p};
     }
     VXB_CUDA(c, cudaMemsetAsync(c->scalars.p, 0, sizeof(unsigned long long), st));
-    VXB_CUDA(c, launch_render(c->world(start_pos), c->cams.p, n_views, w, h, *caps, time, c->projectiles.p, rd, c->color.p, c->scalars.p, st));
+    if (c->render_variant == 1) {
+        VXB_CUDA(c, launch_render(c->world(start_pos), c->cams.p, n_views, w, h, *caps, time, c->projectiles.p, rd, c->color.p, c->scalars.p, st));
+        return VXB_OK;
+    }
+    // wavefront: the primary layers of a group of views go to the ray buffers, then the shading rounds run over them.
+    // Views are taken in groups so that the scratch stays below ~2 GB (2^24 tile slots)
+    const uint64_t slots_per_view = (uint64_t)((w + 15) / 16) * ((h + 7) / 8) * 128;
+    VXB_REQUIRE(c, slots_per_view < (1ull << 31), "vxb_render: view too large");
+    const uint32_t group = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(n_views, (1ull << 24) / slots_per_view));
+    int rc = ensure_ray_buffers(c, (uint64_t)group * w * h);
+    if (rc) return rc;
+    VXB_CUDA(c, c->wave_scratch.ensure(render_wave_scratch_words(group, w, h)));
+    for (uint32_t v0 = 0; v0 < n_views; v0 += group) {
+        const uint32_t nv = std::min(group, n_views - v0);
+        c->n_rays = (uint64_t)nv * w * h;  // the ray buffers hold the layers of the last group
+        const uint64_t off = (uint64_t)v0 * w * h;
+        RasterIn rdv{rd.depth ? rd.depth + off : nullptr, rd.normal ? rd.normal + 3 * off : nullptr, rd.diffuse_x ? rd.diffuse_x + off : nullptr};
+        VXB_CUDA(c, launch_render_wave(c->world(start_pos), c->cams.p + v0, nv, w, h, *caps, time, c->projectiles.p, rdv, ray_out(c),
+                                       c->wave_scratch.p, c->color.p + 4 * off, st));
+    }
+    return VXB_OK;
+}
+
+int vxb_set_render_kernel(vxb_ctx* c, int variant) {
+    if (!c) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, variant == 0 || variant == 1, "vxb_set_render_kernel: 0 (wavefront) or 1 (fused)");
+    c->render_variant = variant;
     return VXB_OK;
 }
 

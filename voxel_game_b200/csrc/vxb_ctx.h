@@ -99,6 +99,8 @@ struct vxb_ctx {
     DevBuf<vxb_player> cams;
     uint32_t cams_resident = 0;  // cameras uploaded by vxb_cams_upload (vxb_raymarch / vxb_render overwrite the buffer)
     DevBuf<float> color;  // float4 per pixel of the last vxb_render
+    DevBuf<uint32_t> wave_scratch;  // job / result / list arrays of the wavefront render (shade_wave.cuh)
+    int render_variant = 0;  // 0: wavefront of small kernels (default), 1: the fused k_render
     // player-mesh G-buffer pass (k_raster.cu)
     DevBuf<float> mesh_pos, mesh_normal;  // triangle list, 3 floats per vertex
     uint32_t mesh_vertices = 0;

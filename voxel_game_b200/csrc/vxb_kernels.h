@@ -54,6 +54,11 @@ cudaError_t launch_raymarch_views(const World& w, const vxb_player* cams_dev, ui
 cudaError_t launch_render(const World& w, const vxb_player* cams_dev, uint32_t n_views, uint32_t width, uint32_t height,
                           const vxb_ray_caps& caps, float time, const vxb_projectile* projectiles, RasterIn raster,
                           float* color_out, unsigned long long* total_iters, cudaStream_t st);
+// the same frame as a wavefront of small kernels (shade_wave.cuh); colours identical to launch_render's
+uint64_t render_wave_scratch_words(uint32_t n_views, uint32_t width, uint32_t height);
+cudaError_t launch_render_wave(const World& w, const vxb_player* cams_dev, uint32_t n_views, uint32_t width, uint32_t height,
+                               const vxb_ray_caps& caps, float time, const vxb_projectile* projectiles, RasterIn raster, RayOut layers,
+                               uint32_t* scratch, float* color_out, cudaStream_t st);
 cudaError_t launch_raymarch_rays(const World& w, const float* pos_dev, const float* dir_dev, uint64_t n, int kind,
                                  uint32_t max_iterations, const vxb_projectile* projectiles, uint32_t projectile_count, RayOut out,
                                  cudaStream_t st);

@@ -333,6 +333,10 @@ class VoxelComputePipeline:
     def set_update_kernel(self, variant):
         self._check(self._lib.vxb_set_update_kernel(self._h, int(variant)))
 
+    def set_render_kernel(self, variant):
+        """0 = wavefront of small kernels (default), 1 = the fused per-pixel kernel; identical colours."""
+        self._check(self._lib.vxb_set_render_kernel(self._h, int(variant)))
+
     # -- rays ---------------------------------------------------------------------------------
     def raymarch(self, start_pos, cams, w, h, caps: RayCaps, raster_depth=None):
         cams = np.ascontiguousarray(cams, dtype=PLAYER_DTYPE).reshape(-1)
