@@ -871,9 +871,7 @@ cudaError_t launch_render_wave(const World& w, const vxb_player* cams_dev, uint3
         // round 0 walks every slot; later rounds walk a list whose length only the device knows (grid-stride over it)
         const uint32_t g = round == 0 ? full : (full < (uint32_t)sms * 8u ? full : (uint32_t)sms * 8u);
         k_shade_setup<<<g, WAVE_BLOCK, 0, st>>>(w, cams_dev, width, height, sp, layers, ws, cap, round, color);
-        k_trace_shadow<<<g, WAVE_BLOCK, 0, st>>>(w, sp, ws, cap, round, layers.total_iters);
-        k_trace_reflect<<<g, WAVE_BLOCK, 0, st>>>(w, sp, ws, cap, round, layers.total_iters);
-        k_trace_ao<<<dim3(g, 2), WAVE_BLOCK, 0, st>>>(w, sp, ws, cap, round, layers.total_iters);
+        k_trace<<<dim3(g, 4), WAVE_BLOCK, 0, st>>>(w, sp, ws, cap, round, layers.total_iters);
         k_shade_combine<<<g, WAVE_BLOCK, 0, st>>>(cams_dev, width, height, layers, ws, cap, round, color);
     }
     return cudaGetLastError();

@@ -1,9 +1,8 @@
 // frag.glsl main (:715-741) as a sequence of small kernels instead of one: the primary DDA writes its layers
 // (k_raymarch_primary), then get_color (:650-713) runs layer by layer, each round as
 //     k_shade_setup    material of the layer (position_material), sky, emission; origins and directions of its rays
-//     k_trace_shadow   simple_raycast_w_projectiles towards the light
-//     k_trace_reflect  single_raycast along the reflection, then simple_raycast from its hit towards the light
-//     k_trace_ao       the two ambient rays (one launch, y = 0 / 1)
+//     k_trace          the rays, blockIdx.y = kind: simple_raycast_w_projectiles towards the light | single_raycast along the
+//                      reflection, then simple_raycast from its hit towards the light | the two ambient rays
 //     k_shade_combine  the Cook-Torrance terms in the shader's order, depth transparency, the multiplier
 // Round 0 covers every pixel in 16x8 tiles; a pixel whose multiplier stays above 0.05 with layers left is appended
 // (warp ballot + one atomic per warp) to the list the next round walks. Every kernel runs ONE loop over coherent work, so
@@ -150,57 +149,36 @@ __device__ __forceinline__ void wave_count_iters(unsigned long long* total, uint
     if ((threadIdx.x & 31) == 0 && total && s) atomicAdd(total, (unsigned long long)s);
 }
 
-// :270-273
-__global__ void __launch_bounds__(WAVE_BLOCK) k_trace_shadow(World w, ShadeParams sp, WaveScratch ws, uint32_t n_slots, uint32_t round,
-                                                             unsigned long long* total_iters) {
-    const uint32_t cap = ws.cap;
+// The rays of a round, one launch: blockIdx.y picks the kind so that the four kinds overlap (on the sparse later rounds a
+// kernel lasts as long as its longest single ray, a chain of dependent loads).
+//   0  :270-273  simple_raycast_w_projectiles towards the light
+//   1  :275-288  single_raycast along the reflection, then simple_raycast from its hit towards the light
+//   2, 3  :291-301  the two ambient rays
+__global__ void __launch_bounds__(WAVE_BLOCK) k_trace(World w, ShadeParams sp, WaveScratch ws, uint32_t n_slots, uint32_t round,
+                                                      unsigned long long* total_iters) {
+    const uint32_t cap = ws.cap, kind = blockIdx.y;
     uint32_t iters = 0;
     const uint32_t n = round == 0 ? n_slots : ws.count[round];
     for (uint32_t base = blockIdx.x * WAVE_BLOCK; base < n; base += gridDim.x * WAVE_BLOCK) {
         const uint32_t t = base + threadIdx.x;
-        if (t < n && ws.state[t] == 1) {
-            float light = 0.0f;
-            const Layer hit = simple_raycast<true>(w, job_f3(ws, t, 12), -wave_light_dir(), sp.shadow_ray_dist, sp.projectiles, sp.projectile_count, light, iters);
+        if (t >= n || ws.state[t] != 1) continue;
+        const f3 origin = job_f3(ws, t, 12);
+        float light = 0.0f;
+        if (kind == 0) {
+            const Layer hit = simple_raycast<true>(w, origin, -wave_light_dir(), sp.shadow_ray_dist, sp.projectiles, sp.projectile_count, light, iters);
             ws.res[t] = (hit.voxel >> 24) == MAT_OOB ? 1u : 0u;
             ws.res[(size_t)cap + t] = __float_as_uint(light);
-        }
-    }
-    wave_count_iters(total_iters, iters);
-}
-
-// :275-288
-__global__ void __launch_bounds__(WAVE_BLOCK) k_trace_reflect(World w, ShadeParams sp, WaveScratch ws, uint32_t n_slots, uint32_t round,
-                                                              unsigned long long* total_iters) {
-    const uint32_t cap = ws.cap;
-    uint32_t iters = 0;
-    const uint32_t n = round == 0 ? n_slots : ws.count[round];
-    for (uint32_t base = blockIdx.x * WAVE_BLOCK; base < n; base += gridDim.x * WAVE_BLOCK) {
-        const uint32_t t = base + threadIdx.x;
-        if (t < n && ws.state[t] == 1) {
+        } else if (kind == 1) {
             const f3 reflection = job_f3(ws, t, 15);
-            const Layer rc = single_raycast(w, job_f3(ws, t, 12), reflection, sp.reflection_ray_dist, iters);
-            float light = 0.0f;
+            const Layer rc = single_raycast(w, origin, reflection, sp.reflection_ray_dist, iters);
             const Layer rl = simple_raycast<false>(w, rc.pos - 0.001f * reflection, -wave_light_dir(), sp.ao_ray_dist, sp.projectiles, 0, light, iters);
             ws.res[(size_t)2 * cap + t] = (rc.voxel >> 24) | (((rl.voxel >> 24) == MAT_OOB ? 1u : 0u) << 8);
             ws.res[(size_t)3 * cap + t] = __float_as_uint(light);
-        }
-    }
-    wave_count_iters(total_iters, iters);
-}
-
-// :291-301, blockIdx.y = which of the two ambient rays
-__global__ void __launch_bounds__(WAVE_BLOCK) k_trace_ao(World w, ShadeParams sp, WaveScratch ws, uint32_t n_slots, uint32_t round,
-                                                         unsigned long long* total_iters) {
-    const uint32_t cap = ws.cap, k = blockIdx.y;
-    uint32_t iters = 0;
-    const uint32_t n = round == 0 ? n_slots : ws.count[round];
-    for (uint32_t base = blockIdx.x * WAVE_BLOCK; base < n; base += gridDim.x * WAVE_BLOCK) {
-        const uint32_t t = base + threadIdx.x;
-        if (t < n && ws.state[t] == 1) {
+        } else {
+            const uint32_t k = kind - 2;
             const f3 normal = job_f3(ws, t, 3);
             const f3 ao_dir = k == 0 ? normal : norm3(2.0f * normal - wave_light_dir());
-            float light = 0.0f;
-            const Layer hit = simple_raycast<false>(w, job_f3(ws, t, 12), ao_dir, sp.ao_ray_dist, sp.projectiles, 0, light, iters);
+            const Layer hit = simple_raycast<false>(w, origin, ao_dir, sp.ao_ray_dist, sp.projectiles, 0, light, iters);
             ws.res[(size_t)(4 + 2 * k) * cap + t] = (hit.voxel >> 24) == MAT_OOB ? 1u : 0u;
             ws.res[(size_t)(5 + 2 * k) * cap + t] = __float_as_uint(light);
         }
