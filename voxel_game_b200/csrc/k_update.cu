@@ -343,7 +343,9 @@ struct ThreadSlots {
 // MAT_OOB<<24 / MAT_AIR_OOB<<24 and no kernel ever writes them, so LOADS need no special case (they
 // read the sentinel chunk, which stays in L1/L2); only STORES are predicated on slot >= 2, which is
 // exactly set_data's guard for those two materials.
-template <int PHASE, bool ELIDE>
+// LINK: the z hand-over between consecutive items of a CTA (offset.z == 1 only). Runs of one list entry have next to
+// nothing to hand over, and the bookkeeping costs ~290 warp instructions per chunk: the launcher turns it off for them.
+template <int PHASE, bool ELIDE, bool LINK>
 __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, const uint4* __restrict__ chunk_updates, uint32_t n_items,
                                                                        uint32_t* __restrict__ flags_out, uint32_t run_log2,
                                                                        uint32_t* __restrict__ sched) {
@@ -435,7 +437,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
     // z == 16 voxels (first word of each row of the +z chunk, a 4-byte store into a sector that item t+1
     // writes the rest of) but hands them over, and item t+1 stores full aligned vectors.
     auto resolve_link = [&](uint32_t t) -> uint32_t {
-        if (OZ == 0) return 0;
+        if (OZ == 0 || !LINK) return 0;
         const uint32_t ia = item(t), ib = item(t + 1);
         if (ia == NONE || ib == NONE) return 0;
         const uint4 a = chunk_updates[ia], b = chunk_updates[ib];
@@ -466,7 +468,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
         for (uint32_t k = 0; k < AHEAD; k++) publish(k);
     __syncthreads();
     if (tid < 8 * UPD_STAGES) sm.slot[tid >> 3][tid & 7] = resolve(tid >> 3, tid & 7);
-    if (tid >= 32 && tid < 32 + UPD_STAGES) sm.link[tid - 32] = resolve_link(tid - 32);
+    if (OZ == 1 && LINK && tid >= 32 && tid < 32 + UPD_STAGES) sm.link[tid - 32] = resolve_link(tid - 32);
     if (tid < 2) sm.flags[tid] = 0;
     __syncthreads();
     uint32_t link_prev = 0;  // CTA-uniform: the previous item handed its z == 16 voxels over
@@ -481,8 +483,8 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
         // result is only touched at the end of the iteration
         uint32_t pend = 0;
         if (tid < 8) pend = resolve(t + UPD_STAGES, tid);
-        else if (OZ == 1 && tid == 32) pend = resolve_link(t + UPD_STAGES);
-        const uint32_t link_out = OZ == 1 ? sm.link[t % UPD_NSLOT] : 0u;
+        else if (OZ == 1 && LINK && tid == 32) pend = resolve_link(t + UPD_STAGES);
+        const uint32_t link_out = (OZ == 1 && LINK) ? sm.link[t % UPD_NSLOT] : 0u;
         issue(t + UPD_STAGES - 1);
         cp_async_wait<UPD_STAGES - 1>();  // this thread's copies of item t have landed
 
@@ -558,7 +560,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
         // write-back (imageStore :87 is unconditional; sentinel slots are never stored). Under ELIDE a
         // warp in which no voxel changed has nothing to store and skips the whole section.
         uint32_t cin_chg = 0;  // ELIDE: change bits of the handed-over z == 0 voxels (lanes tzq == 0)
-        if (OZ == 1 && ELIDE && link_prev && tzq == 0) cin_chg = sm.cc[tid >> 2];
+        if (OZ == 1 && LINK && ELIDE && link_prev && tzq == 0) cin_chg = sm.cc[tid >> 2];
         if (!ELIDE || __any_sync(0xFFFFFFFFu, (chg16 | cin_chg) != 0)) {
 #pragma unroll
         for (int i = 0; i < 2; i++) {
@@ -602,7 +604,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
         }
         }
 
-        if (OZ == 1) {
+        if (OZ == 1 && LINK) {
             __syncwarp();  // the hand-over words of the previous item have been read by lanes tzq == 0
             if (link_out && tzq == 3) {
 #pragma unroll
@@ -615,7 +617,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
         flags = __reduce_or_sync(0xFFFFFFFFu, flags);
         if ((tid & 31) == 0 && flags) atomicOr(&sm.flags[t & 1], flags);
         if (tid < 8) sm.slot[(t + UPD_STAGES) % UPD_NSLOT][tid] = pend;
-        else if (OZ == 1 && tid == 32) sm.link[(t + UPD_STAGES) % UPD_NSLOT] = pend;
+        else if (OZ == 1 && LINK && tid == 32) sm.link[(t + UPD_STAGES) % UPD_NSLOT] = pend;
         __syncthreads();
         if (tid == 0) {
             flags_out[cur] = sm.flags[t & 1];
@@ -739,15 +741,15 @@ static cudaError_t sched_counters(int dev, uint32_t** out) {
     return cudaSuccess;
 }
 
-template <int PHASE, bool ELIDE>
-static cudaError_t launch_one(const World& w, const uint4* list, uint32_t n, uint32_t* flags, int run_code, cudaStream_t st) {
+template <int PHASE, bool ELIDE, bool LINK>
+static cudaError_t launch_one(const World& w, const uint4* list, uint32_t n, uint32_t* flags, uint32_t run_log2, cudaStream_t st) {
     // Per instantiation AND per device: the opt-in to > 48 KB of dynamic shared memory is a per-device function
     // attribute, and SMs x resident CTAs is a property of the device the launch goes to (the current one).
     constexpr int MAX_DEVICES = 64;
     static int grid_cap[MAX_DEVICES] = {0};
     static std::mutex setup_mutex;
 
-    auto kern = k_voxel_update_tiled<PHASE, ELIDE>;
+    auto kern = k_voxel_update_tiled<PHASE, ELIDE, LINK>;
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
@@ -767,31 +769,37 @@ static cudaError_t launch_one(const World& w, const uint4* list, uint32_t n, uin
     }
     uint32_t* sched = nullptr;
     if ((e = sched_counters(dev, &sched)) != cudaSuccess) return e;
-    const int grid_cap_dev = cap;
-    // Run length. With all stores (the reference's behaviour) runs of 8 list neighbours pay once the list is long:
-    // the z-run hand-over turns the 4-byte row-end stores of offset.z == 1 into full vectors. With unchanged-store
-    // elision few vectors are stored at all and single-entry runs win: the finer the claims, the shorter the tail.
-    // (config 3 settled, elided, ms per step by run length, claimed runs: R=1 4.30, 2 4.30, 4 4.36, 8 4.41, 16 4.45;
-    //  a 1/8 slab: 0.565, 0.567, 0.578, 0.594, 0.620. Round 1, statically dealt runs: R=1 5.00, R=8 4.85 / 0.633, 0.673.)
-    // (run_code != 0 forces 2^(run_code-1): tests use it to drive the hand-over path with small worlds)
-    const uint32_t run_log2 = run_code ? (uint32_t)(run_code - 1) : ((!ELIDE && n >= 8u * 8u * (uint32_t)grid_cap_dev) ? 3u : 0u);
     const uint32_t n_runs = (n + (1u << run_log2) - 1) >> run_log2;
-    const uint32_t grid = n_runs < (uint32_t)grid_cap_dev ? n_runs : (uint32_t)grid_cap_dev;
+    const uint32_t grid = n_runs < (uint32_t)cap ? n_runs : (uint32_t)cap;
     kern<<<grid, UPD_THREADS, sizeof(UpdSmem), st>>>(w, list, n, flags, run_log2, sched);
     return cudaGetLastError();
 }
 
+// Run length. With all stores (the reference's behaviour) runs of 8 list neighbours pay once the list is long: the z-run
+// hand-over turns the 4-byte row-end stores of offset.z == 1 into full vectors. With unchanged-store elision few vectors
+// are stored at all and single-entry runs win: the finer the claims, the shorter the tail.
+// (config 3 settled, elided, ms per step by run length, claimed runs: R=1 4.30, 2 4.30, 4 4.36, 8 4.41, 16 4.45;
+//  a 1/8 slab: 0.565, 0.567, 0.578, 0.594, 0.620. Round 1, statically dealt runs: R=1 5.00, R=8 4.85 / 0.633, 0.673.)
+// (run_code != 0 forces 2^(run_code-1): tests use it to drive the hand-over path with small worlds)
+template <bool ELIDE>
+static uint32_t pick_run_log2(uint32_t n, int run_code) {
+    if (run_code) return (uint32_t)(run_code - 1);
+    return (!ELIDE && n >= 8u * 8u * 592u) ? 3u : 0u;  // 592 = 148 SMs x 4 resident CTAs
+}
+
 template <bool ELIDE>
 static cudaError_t launch_tiled(int phase, const World& w, const uint4* list, uint32_t n, uint32_t* flags, int run_code, cudaStream_t st) {
+    const uint32_t r = pick_run_log2<ELIDE>(n, run_code);
+    const bool link = r > 0;  // only phases with offset.z == 1 have a hand-over at all
     switch (phase) {
-        case 0: return launch_one<0, ELIDE>(w, list, n, flags, run_code, st);
-        case 1: return launch_one<1, ELIDE>(w, list, n, flags, run_code, st);
-        case 2: return launch_one<2, ELIDE>(w, list, n, flags, run_code, st);
-        case 3: return launch_one<3, ELIDE>(w, list, n, flags, run_code, st);
-        case 4: return launch_one<4, ELIDE>(w, list, n, flags, run_code, st);
-        case 5: return launch_one<5, ELIDE>(w, list, n, flags, run_code, st);
-        case 6: return launch_one<6, ELIDE>(w, list, n, flags, run_code, st);
-        default: return launch_one<7, ELIDE>(w, list, n, flags, run_code, st);
+        case 0: return launch_one<0, ELIDE, false>(w, list, n, flags, r, st);
+        case 1: return launch_one<1, ELIDE, false>(w, list, n, flags, r, st);
+        case 2: return launch_one<2, ELIDE, false>(w, list, n, flags, r, st);
+        case 3: return launch_one<3, ELIDE, false>(w, list, n, flags, r, st);
+        case 4: return link ? launch_one<4, ELIDE, true>(w, list, n, flags, r, st) : launch_one<4, ELIDE, false>(w, list, n, flags, r, st);
+        case 5: return link ? launch_one<5, ELIDE, true>(w, list, n, flags, r, st) : launch_one<5, ELIDE, false>(w, list, n, flags, r, st);
+        case 6: return link ? launch_one<6, ELIDE, true>(w, list, n, flags, r, st) : launch_one<6, ELIDE, false>(w, list, n, flags, r, st);
+        default: return link ? launch_one<7, ELIDE, true>(w, list, n, flags, r, st) : launch_one<7, ELIDE, false>(w, list, n, flags, r, st);
     }
 }
 
