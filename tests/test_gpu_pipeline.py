@@ -99,3 +99,32 @@ def test_compute_pass_tick_by_tick(world_gen, seed, center, moves, rs, n_slots):
     # the run exercised every dispatch kind
     assert ho.worldgen_capacity() < n_slots - 2
     gpu.close()
+
+
+def test_replay_file_drives_the_gpu_like_the_oracle():
+    """A replay in the reference's file format (tests/replay_fixture.py) played through voxel_game_b200.replay.ReplayGame twice: on
+    the GPU pipeline and on the host oracle. Same window scrolls at the same ticks, same players bit for bit after every
+    tick's entity pass, same world and queues (the Explorer window follows the walking players: streaming + unload + slot reuse)."""
+    import voxel_game_b200 as vg
+    from tests.replay_fixture import replay_text
+    from tests.test_replay_cpu import OracleAsPipeline
+    from voxel_game_b200 import replay as rp
+
+    text = replay_text(n_ticks=48, render_size=(16, 16, 16), max_loaded_chunks=2 + 700, max_worldgen_rate=512,
+                       game_mode="Explorer(spawn_location:(x:10040.0,y:1850.0,z:10020.0))")
+    g = rp.ReplayGame(rp.read_replay(text.split("\n")), lambda gs: vg.VoxelComputePipeline(gs), sim=rp.WalkSim(speed=60.0))
+    o = rp.ReplayGame(rp.read_replay(text.split("\n")), OracleAsPipeline, sim=rp.WalkSim(speed=60.0))
+    assert g.game_state.start_pos == o.game_state.start_pos
+    tick = 0
+    while True:
+        a, b = g.step(), o.step()
+        assert a == b
+        if not a:
+            break
+        g.voxel_compute.synchronize()
+        assert g.game_state.start_pos == o.game_state.start_pos and g.moves == o.moves, "tick %d window" % tick
+        assert np.array_equal(g.players.view(np.uint8), o.players.view(np.uint8)), "tick %d players" % tick
+        _compare(g.voxel_compute, o.voxel_compute.ho, tick)
+        tick += 1
+    assert tick == 48 and len(g.moves) >= 2
+    g.voxel_compute.close()

@@ -23,3 +23,4 @@ from .pipeline import (  # noqa: F401
     quat_to_mat4,
     translation,
 )
+from .replay import ReplayGame, read_replay  # noqa: F401
