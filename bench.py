@@ -1083,8 +1083,8 @@ def bench_collisions(args, torch, vg, gpu, SP, RS, centre, peak):
 
 def bench_collisions_sharded(args, torch, vg, dist, gpu, SP, RS, centre, rank, world_size):
     """BASELINE configs[3] on N GPUs: replicated config-2 world, projectile index ranges per rank,
-    players replicated; the voxel damage each rank adds is logged, all-gathered and replayed on the other
-    replicas inside the timed region. Ends with a checksum comparison of the replicas."""
+    players replicated; the voxel damage each rank adds reaches the other replicas inside the timed region (added by the
+    projectile kernel itself through peer memory, or logged, all-gathered and replayed). Ends with a checksum comparison."""
     from tests import scenes
     from voxel_game_b200.replicas import exchange_damage_fixed
 
@@ -1096,23 +1096,45 @@ def bench_collisions_sharded(args, torch, vg, dist, gpu, SP, RS, centre, rank, w
     pl = scenes.players_grid(n_side, (cx, col_y, cz), 48.0, col_y + 4.0, seed=64)
     per = n_proj // world_size
     mine = pr[rank * per:(rank + 1) * per]
-    gpu.damage_log_enable(per)
+    # How the voxel damage reaches the other replicas. "peer" (default): every rank opens the other replicas' table and
+    # pool (CUDA IPC) and k_projectiles adds its damage to all of them itself (system-scope atomics over NVLink); the
+    # only thing left after the kernel is a barrier. "log": round 1's damage logs, all-gathered and replayed.
+    mode, mode_note = "peer", None
+    ok = 1
+    try:
+        mine_h = torch.from_numpy(gpu.replica_export()).cuda()
+    except Exception as e:
+        ok, mode_note, mine_h = 0, "replica export failed (%s)" % (str(e)[:160],), torch.zeros(128, dtype=torch.uint8, device="cuda")
+    all_h = torch.empty(world_size * 128, dtype=torch.uint8, device="cuda")
+    dist.all_gather_into_tensor(all_h, mine_h)
+    if ok:
+        try:
+            gpu.replica_peers_open(all_h.view(world_size, 128)[[r for r in range(world_size) if r != rank]].cpu().numpy())
+        except Exception as e:
+            ok, mode_note = 0, "opening the peer replicas failed (%s)" % (str(e)[:160],)
+    t_ok = torch.tensor([ok], dtype=torch.int32, device="cuda")
+    dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
+    if int(t_ok.item()) == 0:
+        mode, mode_note = "log", mode_note or "peer replicas unavailable on another rank"
+        gpu.replica_peers_open(np.zeros((0, 128), np.uint8))
+        gpu.damage_log_enable(per)
     gpu.dispatch_entities(SP, projectiles=mine, players=pl, run_projectiles=False, run_players=False)  # upload only
     ptrs = gpu.device_ptrs()
     proj_t = torch.as_tensor(DevView(ptrs.projectiles, per * 28), device="cuda")
     play_t = torch.as_tensor(DevView(ptrs.players, n_side * n_side * 32), device="cuda")
     proj0, play0 = proj_t.clone(), play_t.clone()
-    rec_ptr, cnt_ptr, cap = gpu.damage_log_device()
-    rec_t = torch.as_tensor(DevView(rec_ptr, cap * 4), device="cuda").view(cap, 4)
-    cnt_t = torch.as_tensor(DevView(cnt_ptr, 1), device="cuda")
     steps = max(4, min(args.steps, 16))
     total_ms, foreign = 0.0, 0
+    one = torch.ones(1, dtype=torch.int32, device="cuda")
+    if mode == "log":
+        rec_ptr, cnt_ptr, cap = gpu.damage_log_device()
+        rec_t = torch.as_tensor(DevView(rec_ptr, cap * 4), device="cuda").view(cap, 4)
+        cnt_t = torch.as_tensor(DevView(cnt_ptr, 1), device="cuda")
+        gathered = torch.empty((world_size * cap, 4), dtype=torch.int32, device="cuda")
+        counts = torch.empty(world_size, dtype=torch.int32, device="cuda")
 
-    gathered = torch.empty((world_size * cap, 4), dtype=torch.int32, device="cuda")
-    counts = torch.empty(world_size, dtype=torch.int32, device="cuda")
-
-    def apply_fn(rows, count):
-        gpu.damage_apply_counted(SP, rows.data_ptr(), count.data_ptr(), cap)
+        def apply_fn(rows, count):
+            gpu.damage_apply_counted(SP, rows.data_ptr(), count.data_ptr(), cap)
 
     for i in range(3 + steps):
         proj_t.copy_(proj0)
@@ -1122,12 +1144,16 @@ def bench_collisions_sharded(args, torch, vg, dist, gpu, SP, RS, centre, rank, w
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         gpu.entities_resident_run(SP, per, n_side * n_side)
-        exchange_damage_fixed(dist, torch, rec_t, cnt_t, rank, world_size, apply_fn, gathered, counts)
+        if mode == "peer":
+            dist.all_reduce(one, op=dist.ReduceOp.MAX)  # on the stream: every rank's adds have landed before anything later runs
+        else:
+            exchange_damage_fixed(dist, torch, rec_t, cnt_t, rank, world_size, apply_fn, gathered, counts)
         e1.record()
         torch.cuda.synchronize()
         if i >= 3:
             total_ms += e0.elapsed_time(e1)
-            foreign += int(counts.sum().item()) - int(cnt_t.item())
+            if mode == "log":
+                foreign += int(counts.sum().item()) - int(cnt_t.item())
     ck = torch.tensor([gpu.world_checksum(SP) & 0x7FFFFFFFFFFFFFFF], dtype=torch.int64, device="cuda")
     cks = torch.zeros(world_size, dtype=torch.int64, device="cuda")
     dist.all_gather_into_tensor(cks, ck)
@@ -1135,9 +1161,11 @@ def bench_collisions_sharded(args, torch, vg, dist, gpu, SP, RS, centre, rank, w
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
     return {"metric": "projectiles/s", "value": n_proj / (ms / 1e3), "unit": "projectiles/s", "ms_per_tick": ms, "n_gpus": world_size, "scaling": "strong",
-            "replicas_identical": bool((cks == cks[0]).all().item()), "foreign_damage_records_per_tick": foreign / steps,
-            "config": {"workload": "BASELINE configs[3]: %d projectiles (index ranges per rank) + %d player hulls vs replicas of the config-2 world; "
-                                   "voxel damage logs all-gathered (fixed capacity, counts on the device) and replayed inside the timed region" % (n_proj, n_side * n_side)}}
+            "replicas_identical": bool((cks == cks[0]).all().item()), "damage_sharing": mode, "damage_sharing_note": mode_note,
+            "foreign_damage_records_per_tick": (foreign / steps) if mode == "log" else None,
+            "config": {"workload": "BASELINE configs[3]: %d projectiles (index ranges per rank) + %d player hulls vs replicas of the config-2 world; " % (n_proj, n_side * n_side)
+                                   + ("voxel damage added to every replica by the projectile kernel itself (peer memory), one barrier inside the timed region" if mode == "peer" else
+                                      "voxel damage logs all-gathered (fixed capacity, counts on the device) and replayed inside the timed region")}}
 
 
 # ------------------------------------------------------------------------------------------------

@@ -280,6 +280,19 @@ int vxb_damage_apply(vxb_ctx* ctx, const uint32_t start_pos[3], const uint32_t (
 int vxb_damage_apply_counted(vxb_ctx* ctx, const uint32_t start_pos[3], const uint32_t (*records_dev)[4], const uint32_t* count_dev,
                              uint32_t capacity);
 
+/* The same sharing without any exchange step: a ctx that knows its peer replicas adds the voxel damage of its projectile
+ * dispatches straight into their pools (system-scope atomics over NVLink / peer memory, each through the peer's own
+ * chunk table) in the kernel that adds it to its own. Afterwards every replica holds the sum of all ranks' damage as
+ * soon as all ranks' dispatches have finished — the caller orders that (a barrier on the streams, e.g. a one-word
+ * all-reduce). All replicas must share render_size and be dispatched with the same start_pos. No counterpart in the
+ * reference (one GPU).
+ *   vxb_replica_export      two cudaIpcMemHandle_t (chunk table, voxel pool) of this ctx for other PROCESSES
+ *   vxb_replica_peers_open  opens up to 15 exported replicas and makes them this ctx's peers (replaces earlier peers)
+ *   vxb_replica_peers_set   the same for ctxs of THIS process, on this or on a peer-accessible device; n_peers = 0 clears */
+int vxb_replica_export(vxb_ctx* ctx, unsigned char handles[128]);
+int vxb_replica_peers_open(vxb_ctx* ctx, const unsigned char (*handles)[128], uint32_t n_peers);
+int vxb_replica_peers_set(vxb_ctx* ctx, vxb_ctx* const* peers, uint32_t n_peers);
+
 /* Resident work list for repeated full sweeps (benchmark configs 3 and 5): upload once, then run
  * the update dispatch on it any number of times without host traffic. */
 int vxb_update_list_upload(vxb_ctx* ctx, const uint32_t (*chunk_updates)[4], uint32_t n);

@@ -107,7 +107,8 @@ __device__ __forceinline__ int lattice_map(int g, int i) {
 __global__ void __launch_bounds__(PROJ_BLOCK, 6) k_projectiles(World w, vxb_projectile* __restrict__ projectiles, uint32_t n_projectiles,
                                                      const vxb_player* __restrict__ players, uint32_t n_players,
                                                      vxb_collision* __restrict__ collisions, uint32_t collision_capacity,
-                                                     uint32_t* __restrict__ collision_count, float dt, DamageLog dlog) {
+                                                     uint32_t* __restrict__ collision_count, float dt, DamageLog dlog,
+                                                     PeerReplicas peers) {
     __shared__ float4 s_players[PLAYER_TILE];  // (pos.xyz, size) is all the hit test reads
     __shared__ float2 s_cull[PLAYER_TILE];     // (y of the hitsphere column's midpoint, its reach)
     const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -394,7 +395,16 @@ __global__ void __launch_bounds__(PROJ_BLOCK, 6) k_projectiles(World w, vxb_proj
         if (damage > 0) {
             // imageAtomicAdd(voxels, get_index(voxel_pos), int(projectile.damage)) (:230-233)
             atomicAdd(&w.pool[voxel_index(w, (uint32_t)vx, (uint32_t)vy, (uint32_t)vz)], (uint32_t)f2i(damage));
-            if (dlog.records) {  // sharded batches: the other replicas of the world replay this add
+            // sharded batches: the same add on the other replicas of the world, over NVLink, each through its own table
+            // (integer adds commute: every replica ends with the sum of all ranks' damage)
+            for (uint32_t p = 0; p < peers.n; p++) {
+                World pw = w;
+                pw.table = peers.table[p];
+                pw.pool = peers.pool[p];
+                const uint64_t at = voxel_index(pw, (uint32_t)vx, (uint32_t)vy, (uint32_t)vz);
+                if (at >= 2ull * CHUNK_VOLUME) atomicAdd_system(&pw.pool[at], (uint32_t)f2i(damage));  // never into a sentinel slot
+            }
+            if (dlog.records) {  // ... or logged, for replicas this GPU cannot reach: they replay the records
                 const uint32_t at = atomicAdd(dlog.count, 1u);
                 if (at < dlog.capacity) dlog.records[at] = make_uint4((uint32_t)vx, (uint32_t)vy, (uint32_t)vz, (uint32_t)f2i(damage));
             }
@@ -602,10 +612,10 @@ __global__ void __launch_bounds__(128) k_players(World w, vxb_player* __restrict
 
 cudaError_t launch_projectiles(const World& w, vxb_projectile* projectiles, uint32_t n_projectiles, const vxb_player* players,
                                uint32_t n_players, vxb_collision* collisions, uint32_t collision_capacity, uint32_t* collision_count,
-                               float dt, DamageLog dlog, cudaStream_t st) {
+                               float dt, DamageLog dlog, const PeerReplicas& peers, cudaStream_t st) {
     if (n_projectiles == 0) return cudaSuccess;
     k_projectiles<<<(n_projectiles + PROJ_BLOCK - 1) / PROJ_BLOCK, PROJ_BLOCK, 0, st>>>(w, projectiles, n_projectiles, players, n_players, collisions,
-                                                               collision_capacity, collision_count, dt, dlog);
+                                                               collision_capacity, collision_count, dt, dlog, peers);
     return cudaGetLastError();
 }
 // replays logged voxel damage (x, y, z, amount) on this replica: the same add k_projectiles made on its own

@@ -23,9 +23,16 @@ int vxb::fail(vxb_ctx* ctx, int code, const char* fmt, ...) {
     if (ctx) ctx->error = buf; else g_create_error = buf;
     return code;
 }
+// closes IPC-opened peer replicas and forgets the peers (vxb_replica_peers_*)
+static void peers_close(vxb_ctx* c) {
+    for (void* p : c->peer_ipc) cudaIpcCloseMemHandle(p);
+    c->peer_ipc.clear();
+    c->peers = PeerReplicas{};
+}
 static void free_ctx(vxb_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
+    peers_close(c);
     if (c->slab) slab_release(c); else c->pool.release();
     c->table.release(); c->projectiles.release(); c->players.release(); c->collisions.release();
     c->collision_count.release(); c->worldgen_updates.release(); c->worldgen_results.release(); c->chunk_updates.release();
@@ -391,7 +398,7 @@ int vxb_compute(vxb_ctx* c, const uint32_t start_pos[3], const vxb_projectile* p
     // dispatch order of :944-1000
     if (c->upload_projectile_count > 0)
         VXB_CUDA(c, launch_projectiles(w, c->projectiles.p, c->upload_projectile_count, c->players.p, c->upload_player_count,
-                                       c->collisions.p, c->s.max_collisions, c->collision_count.p, c->s.delta_time, c->dlog(), st));
+                                       c->collisions.p, c->s.max_collisions, c->collision_count.p, c->s.delta_time, c->dlog(), c->peers, st));
     if (c->upload_player_count > 0) VXB_CUDA(c, launch_players(w, c->players.p, c->upload_player_count, c->s.delta_time, st));
     if (c->slice_to_unload >= 0) {
         const int comp = c->slice_to_unload / 2;
@@ -626,7 +633,7 @@ int vxb_dispatch_entities(vxb_ctx* c, const uint32_t start_pos[3], vxb_projectil
     const World w = c->world(start_pos);
     if (run_projectiles && n_projectiles)
         VXB_CUDA(c, launch_projectiles(w, c->projectiles.p, n_projectiles, c->players.p, n_players, c->collisions.p, c->s.max_collisions,
-                                       c->collision_count.p, c->s.delta_time, c->dlog(), st));
+                                       c->collision_count.p, c->s.delta_time, c->dlog(), c->peers, st));
     if (run_players && n_players) VXB_CUDA(c, launch_players(w, c->players.p, n_players, c->s.delta_time, st));
     if (n_projectiles) VXB_CUDA(c, cudaMemcpyAsync(projectiles, c->projectiles.p, (size_t)n_projectiles * sizeof(vxb_projectile), cudaMemcpyDeviceToHost, st));
     if (n_players) VXB_CUDA(c, cudaMemcpyAsync(players, c->players.p, (size_t)n_players * sizeof(vxb_player), cudaMemcpyDeviceToHost, st));
@@ -656,7 +663,7 @@ int vxb_entities_resident_run(vxb_ctx* c, const uint32_t start_pos[3], uint32_t 
     const World w = c->world(start_pos);
     if (run_projectiles && n_projectiles)
         VXB_CUDA(c, launch_projectiles(w, c->projectiles.p, n_projectiles, c->players.p, n_players, c->collisions.p, c->s.max_collisions,
-                                       c->collision_count.p, c->s.delta_time, c->dlog(), st));
+                                       c->collision_count.p, c->s.delta_time, c->dlog(), c->peers, st));
     if (run_players && n_players) VXB_CUDA(c, launch_players(w, c->players.p, n_players, c->s.delta_time, st));
     if (n_collisions_out) {
         VXB_CUDA(c, cudaMemcpyAsync(n_collisions_out, c->collision_count.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
@@ -745,6 +752,66 @@ int vxb_chunks_unpack(vxb_ctx* c, const uint32_t start_pos[3], const uint32_t* c
 }
 
 // ---- sharded collision batches: log of voxel damage adds, replayed on the other replicas ----
+// ---- peer replicas: voxel damage added straight into the other replicas of the world ----
+int vxb_replica_export(vxb_ctx* c, unsigned char handles[128]) {
+    if (!c || !handles) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, !c->slab, "vxb_replica_export: a slab ctx's pool is VMM memory (no IPC handle); replicas are plain contexts");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "two 64-byte handles");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h[2];
+    VXB_CUDA(c, cudaIpcGetMemHandle(&h[0], c->table.p));
+    VXB_CUDA(c, cudaIpcGetMemHandle(&h[1], c->pool.p));
+    memcpy(handles, h, 128);
+    return VXB_OK;
+}
+
+int vxb_replica_peers_open(vxb_ctx* c, const unsigned char (*handles)[128], uint32_t n_peers) {
+    if (!c) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, n_peers <= MAX_PEER_REPLICAS && (n_peers == 0 || handles), "vxb_replica_peers_open: at most 15 peers");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    peers_close(c);
+    for (uint32_t p = 0; p < n_peers; p++) {
+        cudaIpcMemHandle_t h[2];
+        memcpy(h, handles[p], 128);
+        void *table = nullptr, *pool = nullptr;
+        VXB_CUDA(c, cudaIpcOpenMemHandle(&table, h[0], cudaIpcMemLazyEnablePeerAccess));
+        c->peer_ipc.push_back(table);
+        VXB_CUDA(c, cudaIpcOpenMemHandle(&pool, h[1], cudaIpcMemLazyEnablePeerAccess));
+        c->peer_ipc.push_back(pool);
+        c->peers.table[p] = static_cast<const uint32_t*>(table);
+        c->peers.pool[p] = static_cast<uint32_t*>(pool);
+        c->peers.n = p + 1;
+    }
+    return VXB_OK;
+}
+
+int vxb_replica_peers_set(vxb_ctx* c, vxb_ctx* const* peers, uint32_t n_peers) {
+    if (!c) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, n_peers <= MAX_PEER_REPLICAS && (n_peers == 0 || peers), "vxb_replica_peers_set: at most 15 peers");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    peers_close(c);
+    for (uint32_t p = 0; p < n_peers; p++) {
+        vxb_ctx* o = peers[p];
+        VXB_REQUIRE(c, o && o != c, "vxb_replica_peers_set: a peer is NULL or the ctx itself");
+        for (int a = 0; a < 3; a++)
+            VXB_REQUIRE(c, o->s.render_size[a] == c->s.render_size[a], "vxb_replica_peers_set: a peer has another render_size");
+        if (o->device != c->device) {
+            int can = 0;
+            VXB_CUDA(c, cudaDeviceCanAccessPeer(&can, c->device, o->device));
+            VXB_REQUIRE(c, can, "vxb_replica_peers_set: no peer access to a peer's device");
+            cudaError_t e = cudaDeviceEnablePeerAccess(o->device, 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+            else if (e != cudaSuccess) return fail(c, VXB_ERR_CUDA, "cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e));
+        }
+        c->peers.table[p] = o->table.p;
+        c->peers.pool[p] = o->pool.p;
+        c->peers.n = p + 1;
+    }
+    return VXB_OK;
+}
+
 int vxb_damage_log_enable(vxb_ctx* c, uint32_t capacity) {
     if (!c) return VXB_ERR_INVALID;
     VXB_CUDA(c, cudaSetDevice(c->device));

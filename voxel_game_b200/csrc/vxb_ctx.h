@@ -84,6 +84,8 @@ struct vxb_ctx {
     DevBuf<uint32_t> collision_count;
     DevBuf<uint32_t> dmg_log, dmg_count;  // voxel damage adds of the last projectile dispatch (vxb_damage_log_enable)
     uint32_t dmg_cap = 0;
+    vxb::PeerReplicas peers{};               // other replicas the projectile pass adds its voxel damage to (vxb_replica_peers_*)
+    std::vector<void*> peer_ipc;             // what cudaIpcOpenMemHandle returned, closed on clear / destroy
     DevBuf<int32_t> worldgen_updates;   // ivec4 per 8^3 workgroup
     DevBuf<uint32_t> worldgen_results;  // one per chunk
     DevBuf<uint32_t> chunk_updates;     // uvec4 per chunk

@@ -71,9 +71,17 @@ struct DamageLog {
     uint32_t capacity;
     uint32_t* count;
 };
+// Other replicas of the same world (same window, their own table and pool; peer-mapped or IPC-opened memory of other GPUs,
+// or plain pointers on this one): k_projectiles adds its voxel damage to them as it adds it to its own world.
+constexpr uint32_t MAX_PEER_REPLICAS = 15;
+struct PeerReplicas {
+    uint32_t n;
+    const uint32_t* table[MAX_PEER_REPLICAS];
+    uint32_t* pool[MAX_PEER_REPLICAS];
+};
 cudaError_t launch_projectiles(const World& w, vxb_projectile* projectiles, uint32_t n_projectiles, const vxb_player* players,
                                uint32_t n_players, vxb_collision* collisions, uint32_t collision_capacity, uint32_t* collision_count,
-                               float dt, DamageLog dlog, cudaStream_t st);
+                               float dt, DamageLog dlog, const PeerReplicas& peers, cudaStream_t st);
 cudaError_t launch_apply_damage(const World& w, const uint32_t* records, uint32_t n, cudaStream_t st);
 cudaError_t launch_apply_damage_counted(const World& w, const uint32_t* records, const uint32_t* count_dev, uint32_t capacity, cudaStream_t st);
 cudaError_t launch_players(const World& w, vxb_player* players, uint32_t n_players, float dt, cudaStream_t st);

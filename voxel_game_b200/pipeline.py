@@ -330,6 +330,21 @@ class VoxelComputePipeline:
         self._check(self._lib.vxb_damage_apply_counted(self._h, ptr(_u32(start_pos, 3)), ctypes.c_void_p(int(records_ptr)),
                                                        ctypes.c_void_p(int(count_ptr)), int(capacity)))
 
+    # -- peer replicas: voxel damage added straight into the other replicas of the world ------------
+    def replica_export(self):
+        """-> 128 bytes (two CUDA IPC handles) another process passes to replica_peers_open."""
+        out = np.zeros(128, np.uint8)
+        self._check(self._lib.vxb_replica_export(self._h, ptr(out)))
+        return out
+
+    def replica_peers_open(self, handles):
+        h = np.ascontiguousarray(np.asarray(handles, np.uint8).reshape(-1, 128))
+        self._check(self._lib.vxb_replica_peers_open(self._h, ptr(h) if h.size else None, h.shape[0]))
+
+    def replica_peers_set(self, peers):
+        arr = (ctypes.c_void_p * max(1, len(peers)))(*[p._h for p in peers])
+        self._check(self._lib.vxb_replica_peers_set(self._h, arr, len(peers)))
+
     def set_update_kernel(self, variant):
         self._check(self._lib.vxb_set_update_kernel(self._h, int(variant)))
 
