@@ -753,7 +753,33 @@ def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp,
     del idx_buf, chunk_buf
     # per-tick refresh: mask, pack and unpack kernels with fixed-capacity buffers, nothing read back inside the tick
     refresh_cap = max(512, 4096 // world_size)
-    refresher = DeviceReplicaRefresh(torch, dist, gpu, rep, shard, lsp, SP, refresh_cap)
+    # Replica refresh by push when the slab ctx can reach every replica (its own process's directly, the others' through
+    # CUDA IPC): changed chunks are copied straight into all replicas by one kernel, no staging, no all-gather.
+    push, push_note = True, None
+    ok = 1
+    try:
+        mine_h = torch.from_numpy(rep.replica_export()).cuda()
+    except Exception as e:
+        ok, push_note, mine_h = 0, "replica export failed (%s)" % (str(e)[:160],), torch.zeros(144, dtype=torch.uint8, device="cuda")
+    if world_size > 1:
+        all_h = torch.empty(world_size * 144, dtype=torch.uint8, device="cuda")
+        dist.all_gather_into_tensor(all_h, mine_h)
+    if ok:
+        try:
+            gpu.replica_peers_clear()
+            gpu.replica_peers_add([rep])
+            if world_size > 1:
+                gpu.replica_peers_add_ipc(all_h.view(world_size, 144)[[r for r in range(world_size) if r != rank]].cpu().numpy())
+        except Exception as e:
+            ok, push_note = 0, "opening the peer replicas failed (%s)" % (str(e)[:160],)
+    if world_size > 1:
+        t_ok = torch.tensor([ok], dtype=torch.int32, device="cuda")
+        dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
+        ok = int(t_ok.item())
+    if not ok:
+        push, push_note = False, push_note or "peer replicas unavailable on another rank"
+        gpu.replica_peers_clear()
+    refresher = DeviceReplicaRefresh(torch, dist, gpu, rep, shard, lsp, SP, refresh_cap, push=push)
     tick_counts = []
     # regenerated chunks: first column of the slab, all y, the first 32/N z  (512 / N chunks)
     per_rank = max(1, 512 // world_size)
@@ -804,9 +830,13 @@ def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp,
     if world_size > 1:
         dist.barrier()
     same1 = bool(torch.equal(rep_pool[first_global:first_global + n_own], own_pool))
-    counts = torch.stack(tick_counts).to(torch.int64)
-    moved = int(counts.sum().item())
-    overflowed = bool((counts > refresh_cap).any().item())
+    counts = torch.stack(tick_counts).to(torch.int64)  # push: this rank's own counts; else every rank's, gathered
+    moved_t = counts.sum().reshape(1).clone()
+    over_t = (counts > refresh_cap).any().to(torch.int64).reshape(1).clone()
+    if push and world_size > 1:
+        dist.all_reduce(moved_t)
+        dist.all_reduce(over_t, op=dist.ReduceOp.MAX)
+    moved, overflowed = int(moved_t.item()), bool(over_t.item())
     t = torch.tensor([acc[k] / n_ticks for k in names] + [sum(acc.values()) / n_ticks, 0.0 if (same0 and same1) else 1.0], dtype=torch.float64, device="cuda")
     if world_size > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -815,6 +845,8 @@ def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp,
     return {"metric": "ticks/s", "value": 1e3 / t[4], "unit": "ticks/s", "ms_per_tick": t[4], "n_gpus": world_size, "ticks": n_ticks,
             "phases_ms": {names[k]: t[k] for k in range(4)}, "replica_matches_slab": t[5] == 0.0 and not overflowed,
             "chunks_refreshed_per_tick": moved / n_ticks, "refresh_buffer_chunks_per_rank": refresh_cap,
+            "replica_refresh": ("push: changed chunks copied into every replica over peer memory by one kernel (vxb_update_list_push) + one barrier" if push
+                                else "pack + all-gather of fixed-capacity buffers + unpack"), "replica_refresh_note": push_note,
             "config": {"workload": "BASELINE configs[4]: %d chunks regenerated IN PLACE with forced = true (not a new slab face streamed with forced = false) "
                                                "+ update over all %d chunks + 64 views x 1920x1080 primary rays per tick" % (per_rank * world_size, n_total),
                        "note": "regeneration is forced (slots keep their place) instead of forced = false; per-phase times are the max over ranks, "
@@ -1104,19 +1136,19 @@ def bench_collisions_sharded(args, torch, vg, dist, gpu, SP, RS, centre, rank, w
     try:
         mine_h = torch.from_numpy(gpu.replica_export()).cuda()
     except Exception as e:
-        ok, mode_note, mine_h = 0, "replica export failed (%s)" % (str(e)[:160],), torch.zeros(128, dtype=torch.uint8, device="cuda")
-    all_h = torch.empty(world_size * 128, dtype=torch.uint8, device="cuda")
+        ok, mode_note, mine_h = 0, "replica export failed (%s)" % (str(e)[:160],), torch.zeros(144, dtype=torch.uint8, device="cuda")
+    all_h = torch.empty(world_size * 144, dtype=torch.uint8, device="cuda")
     dist.all_gather_into_tensor(all_h, mine_h)
     if ok:
         try:
-            gpu.replica_peers_open(all_h.view(world_size, 128)[[r for r in range(world_size) if r != rank]].cpu().numpy())
+            gpu.replica_peers_add_ipc(all_h.view(world_size, 144)[[r for r in range(world_size) if r != rank]].cpu().numpy())
         except Exception as e:
             ok, mode_note = 0, "opening the peer replicas failed (%s)" % (str(e)[:160],)
     t_ok = torch.tensor([ok], dtype=torch.int32, device="cuda")
     dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
     if int(t_ok.item()) == 0:
         mode, mode_note = "log", mode_note or "peer replicas unavailable on another rank"
-        gpu.replica_peers_open(np.zeros((0, 128), np.uint8))
+        gpu.replica_peers_clear()
         gpu.damage_log_enable(per)
     gpu.dispatch_entities(SP, projectiles=mine, players=pl, run_projectiles=False, run_players=False)  # upload only
     ptrs = gpu.device_ptrs()

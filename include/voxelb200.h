@@ -280,18 +280,36 @@ int vxb_damage_apply(vxb_ctx* ctx, const uint32_t start_pos[3], const uint32_t (
 int vxb_damage_apply_counted(vxb_ctx* ctx, const uint32_t start_pos[3], const uint32_t (*records_dev)[4], const uint32_t* count_dev,
                              uint32_t capacity);
 
-/* The same sharing without any exchange step: a ctx that knows its peer replicas adds the voxel damage of its projectile
- * dispatches straight into their pools (system-scope atomics over NVLink / peer memory, each through the peer's own
- * chunk table) in the kernel that adds it to its own. Afterwards every replica holds the sum of all ranks' damage as
- * soon as all ranks' dispatches have finished — the caller orders that (a barrier on the streams, e.g. a one-word
- * all-reduce). All replicas must share render_size and be dispatched with the same start_pos. No counterpart in the
- * reference (one GPU).
- *   vxb_replica_export      two cudaIpcMemHandle_t (chunk table, voxel pool) of this ctx for other PROCESSES
- *   vxb_replica_peers_open  opens up to 15 exported replicas and makes them this ctx's peers (replaces earlier peers)
- *   vxb_replica_peers_set   the same for ctxs of THIS process, on this or on a peer-accessible device; n_peers = 0 clears */
-int vxb_replica_export(vxb_ctx* ctx, unsigned char handles[128]);
-int vxb_replica_peers_open(vxb_ctx* ctx, const unsigned char (*handles)[128], uint32_t n_peers);
-int vxb_replica_peers_set(vxb_ctx* ctx, vxb_ctx* const* peers, uint32_t n_peers);
+/* Peer replicas — the same sharing without any exchange step (no counterpart in the reference, one GPU). A ctx that
+ * knows other copies of the world as its peers writes to them itself, over NVLink / peer memory, each through the
+ * peer's own chunk table:
+ *   - its projectile dispatches add their voxel damage to every peer's pool (system-scope atomics) in the kernel that
+ *     adds it to its own; the peers must then share this ctx's render_size and be dispatched with the same start_pos;
+ *   - vxb_update_list_push copies the chunks an update changed straight into every peer (below).
+ * When every rank's kernels have finished, every replica is complete — the caller orders that (a barrier on the
+ * streams, e.g. a one-word all-reduce).
+ *   vxb_replica_export         this ctx's chunk table and voxel pool as CUDA IPC handles + its render_size, for other
+ *                              PROCESSES (plain contexts only: a slab ctx's pool is VMM memory)
+ *   vxb_replica_peers_add_ipc  opens exported replicas and appends them to this ctx's peers
+ *   vxb_replica_peers_add      appends ctxs of THIS process, on this or on a peer-accessible device
+ *   vxb_replica_peers_clear    forgets all peers (and closes what add_ipc opened); at most 15 peers */
+typedef struct vxb_replica_handle {
+    unsigned char ipc[128]; /* two cudaIpcMemHandle_t: chunk table, voxel pool */
+    uint32_t render_size[3];
+    uint32_t reserved;
+} vxb_replica_handle;
+int vxb_replica_export(vxb_ctx* ctx, vxb_replica_handle* out);
+int vxb_replica_peers_add_ipc(vxb_ctx* ctx, const vxb_replica_handle* handles, uint32_t n_peers);
+int vxb_replica_peers_add(vxb_ctx* ctx, vxb_ctx* const* peers, uint32_t n_peers);
+int vxb_replica_peers_clear(vxb_ctx* ctx);
+/* Replica refresh by push (config 5): the entries of the resident list whose mask byte is set (vxb_changed_chunk_mask)
+ * are selected on the device and their 16 KiB payloads are written into the chunk of the same coordinates of every
+ * peer, whose window starts at peer_start_pos (peers without a slot for a chunk are skipped). Replaces
+ * pack + all-gather + unpack: nothing is staged, nothing is read back. coords_dev: scratch of (capacity + 1) x 4 words;
+ * word 0 of its last row is the number of selected entries, larger than capacity means overflow (the surplus is not
+ * pushed). */
+int vxb_update_list_push(vxb_ctx* ctx, const uint32_t start_pos[3], const uint8_t* mask_dev, const uint32_t peer_start_pos[3],
+                         uint32_t* coords_dev, uint32_t capacity);
 
 /* Resident work list for repeated full sweeps (benchmark configs 3 and 5): upload once, then run
  * the update dispatch on it any number of times without host traffic. */

@@ -516,7 +516,7 @@ def test_sharded_collision_batch_peer_replicas(devices):
         g.write_pool(0, cpu.pool)
         reps.append(g)
     for g in reps:
-        g.replica_peers_set([o for o in reps if o is not g])
+        g.replica_peers_add([o for o in reps if o is not g])
     sy = _surface_y(cpu, center[0], center[2], 16 * (sp[1] + rs[1]) - 1)
     players = scenes.players_grid(2, center, 9.0, sy + 5.0, seed=2)
     lo = (16 * sp[0] + 8, sy - 8, 16 * sp[2] + 8)
@@ -538,7 +538,7 @@ def test_sharded_collision_batch_peer_replicas(devices):
     assert np.array_equal(both.view(np.uint8), ps.view(np.uint8))
     assert sum(o[3] for o in outs) == ns == len(c_co)
     # peers can be dropped again: a dispatch then only touches its own world
-    reps[0].replica_peers_set([])
+    reps[0].replica_peers_clear()
     reps[0].dispatch_entities(sp, projectiles=pr[:third], players=players, run_players=False)
     assert np.array_equal(reps[1].read_pool(0, n_slots), ref) and not np.array_equal(reps[0].read_pool(0, n_slots), ref)
     for g in reps + [single]:

@@ -303,12 +303,13 @@ def test_device_replica_refresh_follows_the_world():
     for i, c in enumerate(chunks):
         table[c[0] % rs[0], c[1] % rs[1], c[2] % rs[2]] = 2 + i
     worlds = []
-    for _ in range(2):
+    for _ in range(3):
         g = vg.VoxelComputePipeline(vg.GameSettings(render_size=rs, max_loaded_chunks=2 + n, max_update_rate=n))
         g.write_table(table)
         g.write_pool(2, grid.reshape(n, 4096))
         worlds.append(g)
-    a, b = worlds
+    a, b, c = worlds  # b follows a through pack / unpack, c through the push into a peer replica
+    a.replica_peers_add([c])
     st = torch.cuda.Stream()
     for g in worlds:
         g.set_stream(st.cuda_stream)
@@ -318,6 +319,7 @@ def test_device_replica_refresh_follows_the_world():
     with torch.cuda.stream(st):
         ref = DeviceReplicaRefresh(torch, None, a, b, shard, sp, sp, capacity=n)
         small = DeviceReplicaRefresh(torch, None, a, b, shard, sp, sp, capacity=2)
+        pushed = DeviceReplicaRefresh(torch, None, a, c, shard, sp, sp, capacity=n, push=True)
         moved = 0
         for t in range(24):
             off = scenes.PHASES[t % 8]
@@ -327,12 +329,15 @@ def test_device_replica_refresh_follows_the_world():
                 st.synchronize()
                 assert int(small.counts()[0].item()) > 2
             ref.refresh(off)
+            pushed.refresh(off)
             st.synchronize()
+            assert int(pushed.counts()[0].item()) == int(ref.counts()[0].item())
             flags = torch.from_numpy(a.update_list_flags().astype(np.int32)).cuda()
             want, _ = changed_chunk_mask(torch, flags, rs[0], rs[1], rs[2], off, False)
             assert torch.equal(ref.mask.bool(), want), "mask differs at tick %d" % t
             moved += int(ref.counts()[0].item())
             assert np.array_equal(b.read_pool(0, 2 + n), a.read_pool(0, 2 + n)), "replica differs after tick %d" % t
+            assert np.array_equal(c.read_pool(0, 2 + n), a.read_pool(0, 2 + n)), "pushed replica differs after tick %d" % t
         assert 0 < moved < 24 * n
     for g in worlds:
         g.close()

@@ -398,9 +398,12 @@ __global__ void __launch_bounds__(PROJ_BLOCK, 6) k_projectiles(World w, vxb_proj
             // sharded batches: the same add on the other replicas of the world, over NVLink, each through its own table
             // (integer adds commute: every replica ends with the sum of all ranks' damage)
             for (uint32_t p = 0; p < peers.n; p++) {
-                World pw = w;
+                World pw = w;  // same start_pos; the peer's own render_size, table and pool
                 pw.table = peers.table[p];
                 pw.pool = peers.pool[p];
+                pw.rs[0] = peers.rs[p][0]; pw.rs[1] = peers.rs[p][1]; pw.rs[2] = peers.rs[p][2];
+                world_derive(pw);
+                if (!in_window(pw, (uint32_t)vx, (uint32_t)vy, (uint32_t)vz)) continue;
                 const uint64_t at = voxel_index(pw, (uint32_t)vx, (uint32_t)vy, (uint32_t)vz);
                 if (at >= 2ull * CHUNK_VOLUME) atomicAdd_system(&pw.pool[at], (uint32_t)f2i(damage));  // never into a sentinel slot
             }

@@ -68,6 +68,34 @@ __global__ void __launch_bounds__(256) k_pack_copy(World w, const uint4* __restr
     for (int k = 0; k < 4; k++) dst[threadIdx.x + 256 * k] = src[threadIdx.x + 256 * k];
 }
 
+// Push: one CTA per selected list entry reads the chunk once and writes it into every peer replica (peer memory),
+// each through the peer's own table; peers that hold no slot for the chunk are skipped.
+__global__ void __launch_bounds__(256) k_push_copy(World w, const uint4* __restrict__ list, const uint4* __restrict__ coords, uint32_t capacity,
+                                                   PeerReplicas peers, uint32_t psx, uint32_t psy, uint32_t psz) {
+    const uint32_t at = blockIdx.x;
+    const uint32_t count = min(reinterpret_cast<const uint32_t*>(&coords[capacity])[0], capacity);
+    if (at >= count) return;
+    const uint4 e = list[coords[at].w];
+    const uint32_t slot = resolve_chunk_slot(w, e.x, e.y, e.z);
+    const uint4* src = reinterpret_cast<const uint4*>(w.pool + ((size_t)slot << 12));
+    uint4 v[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) v[k] = src[threadIdx.x + 256 * k];
+    for (uint32_t p = 0; p < peers.n; p++) {
+        World pw;
+        pw.table = peers.table[p];
+        pw.pool = peers.pool[p];
+        pw.rs[0] = peers.rs[p][0]; pw.rs[1] = peers.rs[p][1]; pw.rs[2] = peers.rs[p][2];
+        pw.sp[0] = psx; pw.sp[1] = psy; pw.sp[2] = psz;
+        world_derive(pw);
+        const uint32_t ps = resolve_chunk_slot(pw, e.x, e.y, e.z);
+        if (ps < 2) continue;
+        uint4* dst = reinterpret_cast<uint4*>(pw.pool + ((size_t)ps << 12));
+#pragma unroll
+        for (int k = 0; k < 4; k++) dst[threadIdx.x + 256 * k] = v[k];
+    }
+}
+
 // One CTA per received record: the first min(count, capacity) records are written into the chunks they name
 // (records naming chunks that hold no slot here — unloaded, all-air, outside the window — are skipped).
 __global__ void __launch_bounds__(256) k_unpack_chunks(World w, const uint4* __restrict__ coords, const uint4* __restrict__ payload, uint32_t capacity) {
@@ -98,6 +126,17 @@ cudaError_t launch_pack_chunks(const World& w, const uint32_t* list, const uint8
     k_pack_select<<<(n + 255) / 256, 256, 0, st>>>(mask, n, reinterpret_cast<uint4*>(coords), capacity);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     k_pack_copy<<<capacity, 256, 0, st>>>(w, reinterpret_cast<const uint4*>(list), reinterpret_cast<uint4*>(coords), reinterpret_cast<uint4*>(payload), capacity);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_push_chunks(const World& w, const uint32_t* list, const uint8_t* mask, uint32_t n, const PeerReplicas& peers,
+                               const uint32_t peer_start_pos[3], uint32_t* coords, uint32_t capacity, cudaStream_t st) {
+    cudaError_t e = cudaMemsetAsync(coords + (size_t)capacity * 4, 0, 16, st);
+    if (e != cudaSuccess || n == 0) return e;
+    k_pack_select<<<(n + 255) / 256, 256, 0, st>>>(mask, n, reinterpret_cast<uint4*>(coords), capacity);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    k_push_copy<<<capacity, 256, 0, st>>>(w, reinterpret_cast<const uint4*>(list), reinterpret_cast<const uint4*>(coords), capacity, peers,
+                                         peer_start_pos[0], peer_start_pos[1], peer_start_pos[2]);
     return cudaGetLastError();
 }
 

@@ -753,62 +753,89 @@ int vxb_chunks_unpack(vxb_ctx* c, const uint32_t start_pos[3], const uint32_t* c
 
 // ---- sharded collision batches: log of voxel damage adds, replayed on the other replicas ----
 // ---- peer replicas: voxel damage added straight into the other replicas of the world ----
-int vxb_replica_export(vxb_ctx* c, unsigned char handles[128]) {
-    if (!c || !handles) return VXB_ERR_INVALID;
+int vxb_replica_export(vxb_ctx* c, vxb_replica_handle* out) {
+    if (!c || !out) return VXB_ERR_INVALID;
     VXB_REQUIRE(c, !c->slab, "vxb_replica_export: a slab ctx's pool is VMM memory (no IPC handle); replicas are plain contexts");
-    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "two 64-byte handles");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64 && sizeof(vxb_replica_handle) == 144, "two 64-byte handles + render_size");
     VXB_CUDA(c, cudaSetDevice(c->device));
     cudaIpcMemHandle_t h[2];
     VXB_CUDA(c, cudaIpcGetMemHandle(&h[0], c->table.p));
     VXB_CUDA(c, cudaIpcGetMemHandle(&h[1], c->pool.p));
-    memcpy(handles, h, 128);
+    memcpy(out->ipc, h, 128);
+    for (int a = 0; a < 3; a++) out->render_size[a] = c->s.render_size[a];
+    out->reserved = 0;
     return VXB_OK;
 }
 
-int vxb_replica_peers_open(vxb_ctx* c, const unsigned char (*handles)[128], uint32_t n_peers) {
+int vxb_replica_peers_clear(vxb_ctx* c) {
     if (!c) return VXB_ERR_INVALID;
-    VXB_REQUIRE(c, n_peers <= MAX_PEER_REPLICAS && (n_peers == 0 || handles), "vxb_replica_peers_open: at most 15 peers");
     VXB_CUDA(c, cudaSetDevice(c->device));
     VXB_CUDA(c, cudaStreamSynchronize(c->stream));
     peers_close(c);
-    for (uint32_t p = 0; p < n_peers; p++) {
+    return VXB_OK;
+}
+
+int vxb_replica_peers_add_ipc(vxb_ctx* c, const vxb_replica_handle* handles, uint32_t n_peers) {
+    if (!c) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, n_peers == 0 || handles, "vxb_replica_peers_add_ipc: handles is NULL");
+    VXB_REQUIRE(c, c->peers.n + n_peers <= MAX_PEER_REPLICAS, "vxb_replica_peers_add_ipc: at most 15 peers");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    for (uint32_t k = 0; k < n_peers; k++) {
         cudaIpcMemHandle_t h[2];
-        memcpy(h, handles[p], 128);
+        memcpy(h, handles[k].ipc, 128);
         void *table = nullptr, *pool = nullptr;
         VXB_CUDA(c, cudaIpcOpenMemHandle(&table, h[0], cudaIpcMemLazyEnablePeerAccess));
         c->peer_ipc.push_back(table);
         VXB_CUDA(c, cudaIpcOpenMemHandle(&pool, h[1], cudaIpcMemLazyEnablePeerAccess));
         c->peer_ipc.push_back(pool);
+        const uint32_t p = c->peers.n;
         c->peers.table[p] = static_cast<const uint32_t*>(table);
         c->peers.pool[p] = static_cast<uint32_t*>(pool);
+        for (int a = 0; a < 3; a++) c->peers.rs[p][a] = handles[k].render_size[a];
         c->peers.n = p + 1;
     }
     return VXB_OK;
 }
 
-int vxb_replica_peers_set(vxb_ctx* c, vxb_ctx* const* peers, uint32_t n_peers) {
+int vxb_replica_peers_add(vxb_ctx* c, vxb_ctx* const* peers, uint32_t n_peers) {
     if (!c) return VXB_ERR_INVALID;
-    VXB_REQUIRE(c, n_peers <= MAX_PEER_REPLICAS && (n_peers == 0 || peers), "vxb_replica_peers_set: at most 15 peers");
+    VXB_REQUIRE(c, n_peers == 0 || peers, "vxb_replica_peers_add: peers is NULL");
+    VXB_REQUIRE(c, c->peers.n + n_peers <= MAX_PEER_REPLICAS, "vxb_replica_peers_add: at most 15 peers");
     VXB_CUDA(c, cudaSetDevice(c->device));
     VXB_CUDA(c, cudaStreamSynchronize(c->stream));
-    peers_close(c);
-    for (uint32_t p = 0; p < n_peers; p++) {
-        vxb_ctx* o = peers[p];
-        VXB_REQUIRE(c, o && o != c, "vxb_replica_peers_set: a peer is NULL or the ctx itself");
-        for (int a = 0; a < 3; a++)
-            VXB_REQUIRE(c, o->s.render_size[a] == c->s.render_size[a], "vxb_replica_peers_set: a peer has another render_size");
+    for (uint32_t k = 0; k < n_peers; k++) {
+        vxb_ctx* o = peers[k];
+        VXB_REQUIRE(c, o && o != c, "vxb_replica_peers_add: a peer is NULL or the ctx itself");
         if (o->device != c->device) {
             int can = 0;
             VXB_CUDA(c, cudaDeviceCanAccessPeer(&can, c->device, o->device));
-            VXB_REQUIRE(c, can, "vxb_replica_peers_set: no peer access to a peer's device");
+            VXB_REQUIRE(c, can, "vxb_replica_peers_add: no peer access to a peer's device");
             cudaError_t e = cudaDeviceEnablePeerAccess(o->device, 0);
             if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
             else if (e != cudaSuccess) return fail(c, VXB_ERR_CUDA, "cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e));
         }
+        const uint32_t p = c->peers.n;
         c->peers.table[p] = o->table.p;
         c->peers.pool[p] = o->pool.p;
+        for (int a = 0; a < 3; a++) c->peers.rs[p][a] = o->s.render_size[a];
         c->peers.n = p + 1;
     }
+    return VXB_OK;
+}
+
+int vxb_update_list_push(vxb_ctx* c, const uint32_t start_pos[3], const uint8_t* mask_dev, const uint32_t peer_start_pos[3],
+                         uint32_t* coords_dev, uint32_t capacity) {
+    if (!c || !start_pos || !peer_start_pos) return VXB_ERR_INVALID;
+    VXB_WINDOW(c, start_pos);
+    VXB_REQUIRE(c, mask_dev && coords_dev && capacity > 0, "vxb_update_list_push: NULL buffer or zero capacity");
+    VXB_REQUIRE(c, c->res_n > 0, "vxb_update_list_push: no resident list uploaded");
+    VXB_REQUIRE(c, c->peers.n > 0, "vxb_update_list_push: the ctx has no peer replicas");
+    for (uint32_t p = 0; p < c->peers.n; p++)
+        for (int a = 0; a < 3; a++)
+            VXB_REQUIRE(c, (uint64_t)peer_start_pos[a] + c->peers.rs[p][a] <= (1ull << 28) - 1, "vxb_update_list_push: peer window exceeds 2^28 chunks");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, launch_push_chunks(c->world(start_pos), c->res_list.p, mask_dev, c->res_n, c->peers, peer_start_pos, coords_dev, capacity, c->stream));
     return VXB_OK;
 }
 

@@ -78,6 +78,7 @@ struct PeerReplicas {
     uint32_t n;
     const uint32_t* table[MAX_PEER_REPLICAS];
     uint32_t* pool[MAX_PEER_REPLICAS];
+    uint32_t rs[MAX_PEER_REPLICAS][3];  // each peer's render_size (the push may target a larger window than the slab's)
 };
 cudaError_t launch_projectiles(const World& w, vxb_projectile* projectiles, uint32_t n_projectiles, const vxb_player* players,
                                uint32_t n_players, vxb_collision* collisions, uint32_t collision_capacity, uint32_t* collision_count,
@@ -91,6 +92,8 @@ cudaError_t launch_changed_chunk_mask(const uint32_t* flags, uint32_t cols, uint
                                       uint8_t* ghost, cudaStream_t st);
 cudaError_t launch_pack_chunks(const World& w, const uint32_t* list, const uint8_t* mask, uint32_t n, uint32_t* coords, uint32_t* payload,
                                uint32_t capacity, cudaStream_t st);
+cudaError_t launch_push_chunks(const World& w, const uint32_t* list, const uint8_t* mask, uint32_t n, const PeerReplicas& peers,
+                               const uint32_t peer_start_pos[3], uint32_t* coords, uint32_t capacity, cudaStream_t st);
 cudaError_t launch_unpack_chunks(const World& w, const uint32_t* coords, const uint32_t* payload, uint32_t capacity, cudaStream_t st);
 
 // RasterizerSystem::draw (rasterizer.rs:196-323) + frag.glsl:716-728 as kernels (k_raster.cu)

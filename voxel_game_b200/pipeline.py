@@ -332,18 +332,27 @@ class VoxelComputePipeline:
 
     # -- peer replicas: voxel damage added straight into the other replicas of the world ------------
     def replica_export(self):
-        """-> 128 bytes (two CUDA IPC handles) another process passes to replica_peers_open."""
-        out = np.zeros(128, np.uint8)
+        """-> 144 bytes (vxb_replica_handle: two CUDA IPC handles + render_size) for replica_peers_add_ipc in another process."""
+        out = np.zeros(144, np.uint8)
         self._check(self._lib.vxb_replica_export(self._h, ptr(out)))
         return out
 
-    def replica_peers_open(self, handles):
-        h = np.ascontiguousarray(np.asarray(handles, np.uint8).reshape(-1, 128))
-        self._check(self._lib.vxb_replica_peers_open(self._h, ptr(h) if h.size else None, h.shape[0]))
+    def replica_peers_add_ipc(self, handles):
+        h = np.ascontiguousarray(np.asarray(handles, np.uint8).reshape(-1, 144))
+        if h.shape[0]:
+            self._check(self._lib.vxb_replica_peers_add_ipc(self._h, ptr(h), h.shape[0]))
 
-    def replica_peers_set(self, peers):
-        arr = (ctypes.c_void_p * max(1, len(peers)))(*[p._h for p in peers])
-        self._check(self._lib.vxb_replica_peers_set(self._h, arr, len(peers)))
+    def replica_peers_add(self, peers):
+        if len(peers):
+            arr = (ctypes.c_void_p * len(peers))(*[p._h for p in peers])
+            self._check(self._lib.vxb_replica_peers_add(self._h, arr, len(peers)))
+
+    def replica_peers_clear(self):
+        self._check(self._lib.vxb_replica_peers_clear(self._h))
+
+    def update_list_push(self, start_pos, mask_ptr, peer_start_pos, coords_ptr, capacity):
+        self._check(self._lib.vxb_update_list_push(self._h, ptr(_u32(start_pos, 3)), ctypes.c_void_p(int(mask_ptr)), ptr(_u32(peer_start_pos, 3)),
+                                                   ctypes.c_void_p(int(coords_ptr)), int(capacity)))
 
     def set_update_kernel(self, variant):
         self._check(self._lib.vxb_set_update_kernel(self._h, int(variant)))

@@ -162,7 +162,11 @@ class DeviceReplicaRefresh:
     slab / replica: VoxelComputePipeline objects on the same CUDA stream; the slab's resident list must be the
     full (x, y, z) grid of its own columns (shard.cols x ry x rz)."""
 
-    def __init__(self, torch, dist, slab, replica, shard, slab_start_pos, replica_start_pos, capacity):
+    def __init__(self, torch, dist, slab, replica, shard, slab_start_pos, replica_start_pos, capacity, push=False):
+        """push = True: the slab ctx knows every replica as a peer (vxb_replica_peers_add / _add_ipc, the local one included)
+        and copies the changed chunks straight into all of them (vxb_update_list_push); what is left of the exchange is
+        one barrier. Otherwise: pack, all-gather, unpack."""
+        self.push = bool(push)
         self.torch, self.dist, self.slab, self.replica, self.shard = torch, dist, slab, replica, shard
         self.lsp, self.rsp, self.cap = tuple(slab_start_pos), tuple(replica_start_pos), int(capacity)
         self.rank, self.ws = shard.rank, shard.world_size
@@ -172,6 +176,9 @@ class DeviceReplicaRefresh:
         self.ghost = torch.zeros(shard.plane_chunks, dtype=torch.uint8, device=dev) if shard.ghost else None
         self.recv = torch.zeros(shard.plane_chunks, dtype=torch.uint8, device=dev) if shard.rank > 0 else None
         self.coords = torch.zeros((self.cap + 1, 4), dtype=torch.int32, device=dev)
+        if self.push:
+            self.one = torch.ones(1, dtype=torch.int32, device=dev)
+            return
         self.payload = torch.empty((self.cap, 4096), dtype=torch.int32, device=dev)
         if self.ws > 1:
             self.g_coords = torch.zeros((self.ws * (self.cap + 1), 4), dtype=torch.int32, device=dev)
@@ -195,6 +202,11 @@ class DeviceReplicaRefresh:
                     req.wait()
             if self.recv is not None:
                 self.mask[:sh.plane_chunks] |= self.recv
+        if self.push:
+            self.slab.update_list_push(self.lsp, self.mask.data_ptr(), self.rsp, self.coords.data_ptr(), self.cap)
+            if self.ws > 1:
+                dist.all_reduce(self.one, op=dist.ReduceOp.MAX)  # on the stream: every rank's chunks have landed in every replica
+            return
         self.slab.update_list_pack(self.lsp, self.mask.data_ptr(), self.coords.data_ptr(), self.payload.data_ptr(), self.cap)
         if self.ws == 1:
             self.replica.chunks_unpack(self.rsp, self.coords.data_ptr(), self.payload.data_ptr(), self.cap)
@@ -209,6 +221,6 @@ class DeviceReplicaRefresh:
     def counts(self):
         """Record counts of the last refresh, one per source rank (device tensor; > capacity means that rank's
         buffer overflowed and its replica rows are incomplete)."""
-        if self.ws == 1:
-            return self.coords[self.cap, :1]
+        if self.ws == 1 or self.push:
+            return self.coords[self.cap, :1]  # push: this rank's own count (every rank checks its own)
         return self.g_coords.view(self.ws, self.cap + 1, 4)[:, self.cap, 0]
