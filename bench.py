@@ -800,6 +800,8 @@ def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp,
     moved = 0
     n_ticks = max(4, min(args.steps, 16))
 
+    sync_one = torch.ones(1, dtype=torch.int32, device="cuda")
+
     def one_tick(i, timed):
         nonlocal moved
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
@@ -808,6 +810,8 @@ def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp,
         gpu.dispatch_worldgen(lsp, regen_loads, complete=True, want_results=False)
         ev[1].record()
         do_update(off)
+        if world_size > 1:
+            dist.all_reduce(sync_one, op=dist.ReduceOp.MAX)  # the slowest slab's update ends the phase: the refresh timer starts level
         ev[2].record()
         refresher.refresh(off, also=regen_t)
         ev[3].record()
