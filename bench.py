@@ -156,6 +156,18 @@ def worldgen_result(torch, wg_vox, wg_s):
     return out
 
 
+def rays_issue_roofline(torch, rays_per_s):
+    """The world of config 2 sits in L2 (measured DRAM traffic is the output), so what bounds the primary DDA is instruction
+    issue: rated like worldgen, with the kernel's measured warp-instruction count per ray (ncu, profiles/traffic.json)."""
+    ipr = traffic_from_profiles("k_raymarch_primary_warp_instructions_per_ray")
+    if not ipr:
+        return None
+    prop = torch.cuda.get_device_properties(torch.cuda.current_device())
+    peak = prop.multi_processor_count * 4 * 1.965e9
+    return {"bound": "issue", "achieved": ipr * rays_per_s, "peak": peak, "unit": "warp-instructions/s", "frac": ipr * rays_per_s / peak,
+            "warp_instructions_per_ray": ipr}
+
+
 def pinned_u32(torch, shape):
     t = torch.empty(shape, dtype=torch.int32, pin_memory=True)
     return t, t.numpy().view(np.uint32)
@@ -1050,7 +1062,8 @@ def bench_rays(args, torch, vg, peak, rank=0, world_size=1, dist=None):
                        "primary_ray_dist": 100},
             "mean_iterations_per_ray": mean_iters / (W * H), "mean_layers_per_ray": mean_layers / (W * H),
             "roofline": {"bound": "hbm", "model": "gather: 8 B per DDA iteration + 16 B + 24 B x layers per ray", "achieved": achieved,
-                         "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic_from_profiles("k_raymarch_primary_bytes_per_launch")},
+                         "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic_from_profiles("k_raymarch_primary_bytes_per_launch"),
+                         "issue": rays_issue_roofline(torch, W * H * args.steps / (ms / 1e3))},
             "cpu_baseline": cpu_rays,
             "e2e": {"value": W * H * args.steps / e2e_s, "unit": "rays/s", "h2d_bytes_per_step": 128, "d2h_bytes_per_step": W * H * 16,
                     "api": "vxb_raymarch (host camera in) + vxb_ray_results / vxb_ray_download: layer_count, depth, layer-0 voxel and layer-0 "
@@ -1112,7 +1125,7 @@ def bench_collisions(args, torch, vg, gpu, SP, RS, centre, peak):
                                "sample": "first %d projectiles of the same batch against the same world, OpenMP over projectiles" % n_s}
         out["roofline"] = {"bound": "hbm", "model": "gather: 224 B per projectile + 8 B per terrain sample + 8 B per LOS iteration + 16 B per collision "
                            "(sample / LOS counts from the oracle on the CPU sample, scaled)", "achieved": alg / (ms / 1e3) / 1e9, "peak": peak,
-                           "unit": "GB/s", "frac": alg / (ms / 1e3) / 1e9 / peak, "traffic": None,
+                           "unit": "GB/s", "frac": alg / (ms / 1e3) / 1e9 / peak, "traffic": traffic_from_profiles("k_projectiles_dram_bytes_per_launch", n_proj / 1048576.0),
                            "terrain_samples_per_projectile": float(counters[1]) / n_s, "los_iterations_per_projectile": float(counters[2]) / n_s}
     return out
 
