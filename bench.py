@@ -772,16 +772,16 @@ def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp,
     try:
         mine_h = torch.from_numpy(rep.replica_export()).cuda()
     except Exception as e:
-        ok, push_note, mine_h = 0, "replica export failed (%s)" % (str(e)[:160],), torch.zeros(144, dtype=torch.uint8, device="cuda")
+        ok, push_note, mine_h = 0, "replica export failed (%s)" % (str(e)[:160],), torch.zeros(vg.VoxelComputePipeline.REPLICA_HANDLE_BYTES, dtype=torch.uint8, device="cuda")
     if world_size > 1:
-        all_h = torch.empty(world_size * 144, dtype=torch.uint8, device="cuda")
+        all_h = torch.empty(world_size * vg.VoxelComputePipeline.REPLICA_HANDLE_BYTES, dtype=torch.uint8, device="cuda")
         dist.all_gather_into_tensor(all_h, mine_h)
     if ok:
         try:
             gpu.replica_peers_clear()
             gpu.replica_peers_add([rep])
             if world_size > 1:
-                gpu.replica_peers_add_ipc(all_h.view(world_size, 144)[[r for r in range(world_size) if r != rank]].cpu().numpy())
+                gpu.replica_peers_add_ipc(all_h.view(world_size, vg.VoxelComputePipeline.REPLICA_HANDLE_BYTES)[[r for r in range(world_size) if r != rank]].cpu().numpy())
         except Exception as e:
             ok, push_note = 0, "opening the peer replicas failed (%s)" % (str(e)[:160],)
     if world_size > 1:
@@ -1145,20 +1145,25 @@ def bench_collisions_sharded(args, torch, vg, dist, gpu, SP, RS, centre, rank, w
     pl = scenes.players_grid(n_side, (cx, col_y, cz), 48.0, col_y + 4.0, seed=64)
     per = n_proj // world_size
     mine = pr[rank * per:(rank + 1) * per]
-    # How the voxel damage reaches the other replicas. "peer" (default): every rank opens the other replicas' table and
-    # pool (CUDA IPC) and k_projectiles adds its damage to all of them itself (system-scope atomics over NVLink); the
-    # only thing left after the kernel is a barrier. "log": round 1's damage logs, all-gathered and replayed.
+    # How the voxel damage reaches the other replicas. "peer" (default): every rank opens the other replicas (CUDA IPC)
+    # and k_projectiles stores its damage records into its region of every peer's inbox itself (contiguous remote stores
+    # over NVLink); after the kernel: one barrier and one replay launch. "log": round 1's damage logs, all-gathered and
+    # replayed.
     mode, mode_note = "peer", None
-    ok = 1
+    ok = 1 if getattr(args, "damage", "peer") == "peer" else 0
+    if not ok:
+        mode_note = "--damage log"
+    HB = vg.VoxelComputePipeline.REPLICA_HANDLE_BYTES
     try:
+        gpu.replica_inbox_enable(world_size, per)  # every projectile of a rank could log one record
         mine_h = torch.from_numpy(gpu.replica_export()).cuda()
     except Exception as e:
-        ok, mode_note, mine_h = 0, "replica export failed (%s)" % (str(e)[:160],), torch.zeros(144, dtype=torch.uint8, device="cuda")
-    all_h = torch.empty(world_size * 144, dtype=torch.uint8, device="cuda")
+        ok, mode_note, mine_h = 0, mode_note or "replica export failed (%s)" % (str(e)[:160],), torch.zeros(HB, dtype=torch.uint8, device="cuda")
+    all_h = torch.empty(world_size * HB, dtype=torch.uint8, device="cuda")
     dist.all_gather_into_tensor(all_h, mine_h)
     if ok:
         try:
-            gpu.replica_peers_add_ipc(all_h.view(world_size, 144)[[r for r in range(world_size) if r != rank]].cpu().numpy())
+            gpu.replica_peers_add_ipc(all_h.view(world_size, HB)[[r for r in range(world_size) if r != rank]].cpu().numpy(), source_index=rank)
         except Exception as e:
             ok, mode_note = 0, "opening the peer replicas failed (%s)" % (str(e)[:160],)
     t_ok = torch.tensor([ok], dtype=torch.int32, device="cuda")
@@ -1194,7 +1199,8 @@ def bench_collisions_sharded(args, torch, vg, dist, gpu, SP, RS, centre, rank, w
         e0.record()
         gpu.entities_resident_run(SP, per, n_side * n_side)
         if mode == "peer":
-            dist.all_reduce(one, op=dist.ReduceOp.MAX)  # on the stream: every rank's adds have landed before anything later runs
+            dist.all_reduce(one, op=dist.ReduceOp.MAX)  # on the stream: every rank's records have landed in every inbox
+            gpu.replica_inbox_apply(SP)
         else:
             exchange_damage_fixed(dist, torch, rec_t, cnt_t, rank, world_size, apply_fn, gathered, counts)
         e1.record()
@@ -1213,7 +1219,7 @@ def bench_collisions_sharded(args, torch, vg, dist, gpu, SP, RS, centre, rank, w
             "replicas_identical": bool((cks == cks[0]).all().item()), "damage_sharing": mode, "damage_sharing_note": mode_note,
             "foreign_damage_records_per_tick": (foreign / steps) if mode == "log" else None,
             "config": {"workload": "BASELINE configs[3]: %d projectiles (index ranges per rank) + %d player hulls vs replicas of the config-2 world; " % (n_proj, n_side * n_side)
-                                   + ("voxel damage added to every replica by the projectile kernel itself (peer memory), one barrier inside the timed region" if mode == "peer" else
+                                   + ("voxel damage stored by the projectile kernel into every replica's inbox (peer memory), one barrier + one replay launch inside the timed region" if mode == "peer" else
                                       "voxel damage logs all-gathered (fixed capacity, counts on the device) and replayed inside the timed region")}}
 
 
@@ -1294,6 +1300,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-rays", action="store_true")
     ap.add_argument("--no-collisions", action="store_true")
+    ap.add_argument("--damage", default="peer", choices=["peer", "log"], help="N > 1 collision batch: damage added into peer replicas by the kernel (default) or logged, all-gathered and replayed")
     ap.add_argument("--tick", action="store_true", help="also run BASELINE configs[4], the full tick (default on at 8 GPUs)")
     ap.add_argument("--no-tick", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the natural-world, control-map and config-1 measurements")

@@ -281,27 +281,39 @@ int vxb_damage_apply_counted(vxb_ctx* ctx, const uint32_t start_pos[3], const ui
                              uint32_t capacity);
 
 /* Peer replicas — the same sharing without any exchange step (no counterpart in the reference, one GPU). A ctx that
- * knows other copies of the world as its peers writes to them itself, over NVLink / peer memory, each through the
- * peer's own chunk table:
- *   - its projectile dispatches add their voxel damage to every peer's pool (system-scope atomics) in the kernel that
- *     adds it to its own; the peers must then share this ctx's render_size and be dispatched with the same start_pos;
+ * knows other copies of the world as its peers writes to them itself, over NVLink / peer memory:
+ *   - its projectile dispatches store their voxel damage as (x, y, z, amount) records into the ctx's own region of every
+ *     peer's INBOX (contiguous 16-byte remote stores; a peer replays its inbox with vxb_replica_inbox_apply). Peers without
+ *     an inbox get system-scope adds straight into their pools instead, each through its own chunk table — scattered
+ *     4-byte remote writes, measured 6x the cost of the whole kernel from 3 peers on: for small set-ups only;
  *   - vxb_update_list_push copies the chunks an update changed straight into every peer (below).
- * When every rank's kernels have finished, every replica is complete — the caller orders that (a barrier on the
- * streams, e.g. a one-word all-reduce).
- *   vxb_replica_export         this ctx's chunk table and voxel pool as CUDA IPC handles + its render_size, for other
+ * The caller orders the two sides with a barrier on the streams (e.g. a one-word all-reduce): all dispatches, barrier,
+ * every replica applies its inbox. Inboxes are double-buffered by dispatch parity, so that one barrier per tick is enough;
+ * every replica must therefore issue the same number of projectile dispatches (one with no projectiles counts).
+ *   vxb_replica_inbox_enable   gives this ctx an inbox of n_sources regions of `capacity` records (a rank's source index is
+ *                              its region; call before vxb_replica_export)
+ *   vxb_replica_export         this ctx's chunk table, voxel pool and inbox as CUDA IPC handles + its render_size, for other
  *                              PROCESSES (plain contexts only: a slab ctx's pool is VMM memory)
- *   vxb_replica_peers_add_ipc  opens exported replicas and appends them to this ctx's peers
+ *   vxb_replica_peers_add_ipc  opens exported replicas and appends them to this ctx's peers; source_index = this ctx's
+ *                              region in their inboxes
  *   vxb_replica_peers_add      appends ctxs of THIS process, on this or on a peer-accessible device
- *   vxb_replica_peers_clear    forgets all peers (and closes what add_ipc opened); at most 15 peers */
+ *   vxb_replica_peers_clear    forgets all peers (and closes what add_ipc opened); at most 15 peers
+ *   vxb_replica_inbox_apply    replays what the peers' last dispatch stored here (min(count, capacity) records per source)
+ *   vxb_replica_inbox_counts   synchronises; the record counts of that dispatch per source (> capacity: overflow, the surplus
+ *                              was dropped) */
 typedef struct vxb_replica_handle {
-    unsigned char ipc[128]; /* two cudaIpcMemHandle_t: chunk table, voxel pool */
+    unsigned char ipc[192]; /* three cudaIpcMemHandle_t: chunk table, voxel pool, inbox (zero without one) */
     uint32_t render_size[3];
-    uint32_t reserved;
+    uint32_t inbox_sources, inbox_capacity;
+    uint32_t reserved[3];
 } vxb_replica_handle;
+int vxb_replica_inbox_enable(vxb_ctx* ctx, uint32_t n_sources, uint32_t capacity);
 int vxb_replica_export(vxb_ctx* ctx, vxb_replica_handle* out);
-int vxb_replica_peers_add_ipc(vxb_ctx* ctx, const vxb_replica_handle* handles, uint32_t n_peers);
-int vxb_replica_peers_add(vxb_ctx* ctx, vxb_ctx* const* peers, uint32_t n_peers);
+int vxb_replica_peers_add_ipc(vxb_ctx* ctx, const vxb_replica_handle* handles, uint32_t n_peers, uint32_t source_index);
+int vxb_replica_peers_add(vxb_ctx* ctx, vxb_ctx* const* peers, uint32_t n_peers, uint32_t source_index);
 int vxb_replica_peers_clear(vxb_ctx* ctx);
+int vxb_replica_inbox_apply(vxb_ctx* ctx, const uint32_t start_pos[3]);
+int vxb_replica_inbox_counts(vxb_ctx* ctx, uint32_t* counts_out);
 /* Replica refresh by push (config 5): the entries of the resident list whose mask byte is set (vxb_changed_chunk_mask)
  * are selected on the device and their 16 KiB payloads are written into the chunk of the same coordinates of every
  * peer, whose window starts at peer_start_pos (peers without a slot for a chunk are skipped). Replaces

@@ -493,11 +493,12 @@ def test_sharded_collision_batch_damage_log():
         g.close()
 
 
-@pytest.mark.parametrize("devices", [(0, 0, 0), (0, 1, 0)])
-def test_sharded_collision_batch_peer_replicas(devices):
+@pytest.mark.parametrize("devices,inbox", [((0, 0, 0), True), ((0, 0, 0), False), ((0, 1, 0), True)])
+def test_sharded_collision_batch_peer_replicas(devices, inbox):
     """Three replicas of one world (on one GPU, or spread over two when the box has them) each run a third of a
-    projectile batch knowing the other two as peers: k_projectiles adds its voxel damage to all three pools itself.
-    No log, no exchange — and every pool equals a single context's run of the whole batch and the oracle's."""
+    projectile batch knowing the other two as peers. With inboxes k_projectiles stores its damage records into its region
+    of each peer's inbox and every replica replays what it received; without, it adds straight into the peers' pools.
+    No log, no all-gather — and every pool equals a single context's run of the whole batch and the oracle's."""
     import torch
 
     import voxel_game_b200 as vg
@@ -514,33 +515,42 @@ def test_sharded_collision_batch_peer_replicas(devices):
         g = vg.VoxelComputePipeline(vg.GameSettings(render_size=rs, max_loaded_chunks=n_slots, max_projectiles=4096, max_collisions=4096), device=d)
         g.write_table(cpu.table)
         g.write_pool(0, cpu.pool)
+        if inbox:
+            g.replica_inbox_enable(3, 2048)
         reps.append(g)
-    for g in reps:
-        g.replica_peers_add([o for o in reps if o is not g])
+    for k, g in enumerate(reps):
+        g.replica_peers_add([o for o in reps if o is not g], source_index=k)
     sy = _surface_y(cpu, center[0], center[2], 16 * (sp[1] + rs[1]) - 1)
     players = scenes.players_grid(2, center, 9.0, sy + 5.0, seed=2)
     lo = (16 * sp[0] + 8, sy - 8, 16 * sp[2] + 8)
     hi = (16 * (sp[0] + rs[0]) - 8, sy + 6, 16 * (sp[2] + rs[2]) - 8)
-    pr = scenes.random_projectiles(3999, lo, hi, seed=21, bounce_frac=0.05)
-    pr["damage"] = np.array([0, 1, 5, 7], np.float32)[np.arange(len(pr)) % 4]
-    third = len(pr) // 3
-    outs = [g.dispatch_entities(sp, projectiles=pr[k * third:(k + 1) * third], players=players, run_players=False) for k, g in enumerate(reps)]
-    for g in reps:
-        g.synchronize()
-    ps, _, cs, ns = single.dispatch_entities(sp, projectiles=pr, players=players, run_players=False)
-    c_pr, c_co, _ = cpu.projectiles(pr, players, capacity=4096)
-    assert (c_pr["chunk_update_pos"][:, 3] == 1).sum() > 100  # damage really landed
-    ref = single.read_pool(0, n_slots)
-    assert np.array_equal(ref, cpu.pool)
-    for g in reps:
-        assert np.array_equal(g.read_pool(0, n_slots), ref)
-    both = np.concatenate([o[0] for o in outs])
-    assert np.array_equal(both.view(np.uint8), ps.view(np.uint8))
-    assert sum(o[3] for o in outs) == ns == len(c_co)
+    ref_pool, ticks = None, (2 if inbox else 1)  # two ticks: the inbox parity flips
+    for tick in range(ticks):
+        pr = scenes.random_projectiles(3999, lo, hi, seed=21 + tick, bounce_frac=0.05)
+        pr["damage"] = np.array([0, 1, 5, 7], np.float32)[np.arange(len(pr)) % 4]
+        third = len(pr) // 3
+        outs = [g.dispatch_entities(sp, projectiles=pr[k * third:(k + 1) * third], players=players, run_players=False) for k, g in enumerate(reps)]
+        for g in reps:
+            g.synchronize()  # the barrier: every replica's dispatch has finished
+        if inbox:
+            for k, g in enumerate(reps):
+                counts = g.replica_inbox_counts()
+                assert counts[k] == 0 and (np.delete(counts, k) > 20).all() and counts.max() <= 2048
+                g.replica_inbox_apply(sp)
+        ps, _, cs, ns = single.dispatch_entities(sp, projectiles=pr, players=players, run_players=False)
+        c_pr, c_co, _ = cpu.projectiles(pr, players, capacity=4096)
+        assert (c_pr["chunk_update_pos"][:, 3] == 1).sum() > 100  # damage really landed
+        ref_pool = single.read_pool(0, n_slots)
+        assert np.array_equal(ref_pool, cpu.pool)
+        for g in reps:
+            assert np.array_equal(g.read_pool(0, n_slots), ref_pool), "tick %d" % tick
+        both = np.concatenate([o[0] for o in outs])
+        assert np.array_equal(both.view(np.uint8), ps.view(np.uint8))
+        assert sum(o[3] for o in outs) == ns == len(c_co)
     # peers can be dropped again: a dispatch then only touches its own world
     reps[0].replica_peers_clear()
     reps[0].dispatch_entities(sp, projectiles=pr[:third], players=players, run_players=False)
-    assert np.array_equal(reps[1].read_pool(0, n_slots), ref) and not np.array_equal(reps[0].read_pool(0, n_slots), ref)
+    assert np.array_equal(reps[1].read_pool(0, n_slots), ref_pool) and not np.array_equal(reps[0].read_pool(0, n_slots), ref_pool)
     for g in reps + [single]:
         g.close()
 

@@ -174,8 +174,11 @@ SIGNATURES = {
     "vxb_damage_apply": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_uint32, ctypes.c_int]),
     "vxb_damage_apply_counted": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, ctypes.c_uint32]),
     "vxb_replica_export": (ctypes.c_int, [c_vp, c_vp]),
-    "vxb_replica_peers_add_ipc": (ctypes.c_int, [c_vp, c_vp, ctypes.c_uint32]),
-    "vxb_replica_peers_add": (ctypes.c_int, [c_vp, c_vp, ctypes.c_uint32]),
+    "vxb_replica_peers_add_ipc": (ctypes.c_int, [c_vp, c_vp, ctypes.c_uint32, ctypes.c_uint32]),
+    "vxb_replica_peers_add": (ctypes.c_int, [c_vp, c_vp, ctypes.c_uint32, ctypes.c_uint32]),
+    "vxb_replica_inbox_enable": (ctypes.c_int, [c_vp, ctypes.c_uint32, ctypes.c_uint32]),
+    "vxb_replica_inbox_apply": (ctypes.c_int, [c_vp, c_vp]),
+    "vxb_replica_inbox_counts": (ctypes.c_int, [c_vp, c_vp]),
     "vxb_replica_peers_clear": (ctypes.c_int, [c_vp]),
     "vxb_update_list_push": (ctypes.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, ctypes.c_uint32]),
     "vxb_raymarch": (ctypes.c_int, [c_vp, c_vp, c_vp, c_u32, c_u32, c_u32, ctypes.POINTER(RayCaps), c_vp]),

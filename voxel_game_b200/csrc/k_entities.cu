@@ -395,17 +395,34 @@ __global__ void __launch_bounds__(PROJ_BLOCK, 6) k_projectiles(World w, vxb_proj
         if (damage > 0) {
             // imageAtomicAdd(voxels, get_index(voxel_pos), int(projectile.damage)) (:230-233)
             atomicAdd(&w.pool[voxel_index(w, (uint32_t)vx, (uint32_t)vy, (uint32_t)vz)], (uint32_t)f2i(damage));
-            // sharded batches: the same add on the other replicas of the world, over NVLink, each through its own table
-            // (integer adds commute: every replica ends with the sum of all ranks' damage)
-            for (uint32_t p = 0; p < peers.n; p++) {
-                World pw = w;  // same start_pos; the peer's own render_size, table and pool
-                pw.table = peers.table[p];
-                pw.pool = peers.pool[p];
-                pw.rs[0] = peers.rs[p][0]; pw.rs[1] = peers.rs[p][1]; pw.rs[2] = peers.rs[p][2];
-                world_derive(pw);
-                if (!in_window(pw, (uint32_t)vx, (uint32_t)vy, (uint32_t)vz)) continue;
-                const uint64_t at = voxel_index(pw, (uint32_t)vx, (uint32_t)vy, (uint32_t)vz);
-                if (at >= 2ull * CHUNK_VOLUME) atomicAdd_system(&pw.pool[at], (uint32_t)f2i(damage));  // never into a sentinel slot
+            // sharded batches: the other replicas of the world get the same add (integer adds commute: every replica ends
+            // with the sum of all ranks' damage)
+            if (peers.inbox_cap) {
+                // as a record in this rank's region of every peer's inbox: one local atomic for the position, then plain
+                // 16-byte remote stores into contiguous memory; the peers replay the records after the barrier
+                const uint32_t k = atomicAdd(peers.seq, 1u);
+                if (k < peers.inbox_cap) {
+                    const uint4 rec = make_uint4((uint32_t)vx, (uint32_t)vy, (uint32_t)vz, (uint32_t)f2i(damage));
+                    for (uint32_t p = 0; p < peers.n; p++) peers.inbox[p][k] = rec;
+                }
+            } else if (peers.n) {
+                // straight into the peers' pools, each through its own table: all look-ups first (two remote round trips
+                // per thread, not two per peer), then reductions that nothing waits for
+                uint64_t at[MAX_PEER_REPLICAS];
+#pragma unroll
+                for (uint32_t p = 0; p < MAX_PEER_REPLICAS; p++) {
+                    at[p] = 0;
+                    if (p < peers.n) {
+                        World pw = w;  // same start_pos; the peer's own render_size, table and pool
+                        pw.table = peers.table[p];
+                        pw.rs[0] = peers.rs[p][0]; pw.rs[1] = peers.rs[p][1]; pw.rs[2] = peers.rs[p][2];
+                        world_derive(pw);
+                        if (in_window(pw, (uint32_t)vx, (uint32_t)vy, (uint32_t)vz)) at[p] = voxel_index(pw, (uint32_t)vx, (uint32_t)vy, (uint32_t)vz);
+                    }
+                }
+#pragma unroll
+                for (uint32_t p = 0; p < MAX_PEER_REPLICAS; p++)
+                    if (p < peers.n && at[p] >= 2ull * CHUNK_VOLUME) atomicAdd_system(&peers.pool[p][at[p]], (uint32_t)f2i(damage));  // never into a sentinel slot
             }
             if (dlog.records) {  // ... or logged, for replicas this GPU cannot reach: they replay the records
                 const uint32_t at = atomicAdd(dlog.count, 1u);
@@ -621,6 +638,34 @@ cudaError_t launch_projectiles(const World& w, vxb_projectile* projectiles, uint
                                                                collision_capacity, collision_count, dt, dlog, peers);
     return cudaGetLastError();
 }
+// tells every peer how many records this dispatch stored into its inbox region (the count may exceed the capacity: overflow)
+__global__ void k_peer_publish(PeerReplicas peers) {
+    const uint32_t p = threadIdx.x;
+    if (p < peers.n) *peers.inbox_count[p] = *peers.seq;
+}
+cudaError_t launch_peer_publish(const PeerReplicas& peers, cudaStream_t st) {
+    if (peers.n == 0 || peers.inbox_cap == 0) return cudaSuccess;
+    k_peer_publish<<<1, 32, 0, st>>>(peers);
+    return cudaGetLastError();
+}
+// replays an inbox: n_sources regions of `capacity` records each with their counts (one launch for all sources)
+__global__ void k_apply_inbox(World w, const uint4* __restrict__ records, const uint32_t* __restrict__ counts, uint32_t n_sources, uint32_t capacity) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t s = (uint32_t)(i / capacity), k = (uint32_t)(i % capacity);
+    if (s >= n_sources || k >= min(counts[s], capacity)) return;
+    const uint4 r = records[(uint64_t)s * capacity + k];
+    if (!in_window(w, r.x, r.y, r.z)) return;
+    const uint64_t idx = voxel_index(w, r.x, r.y, r.z);
+    if (idx >= 2ull * CHUNK_VOLUME) atomicAdd(&w.pool[idx], r.w);
+}
+cudaError_t launch_apply_inbox(const World& w, const uint32_t* records, const uint32_t* counts, uint32_t n_sources, uint32_t capacity,
+                               cudaStream_t st) {
+    if (n_sources == 0 || capacity == 0) return cudaSuccess;
+    const uint64_t n = (uint64_t)n_sources * capacity;
+    k_apply_inbox<<<(uint32_t)((n + 255) / 256), 256, 0, st>>>(w, reinterpret_cast<const uint4*>(records), counts, n_sources, capacity);
+    return cudaGetLastError();
+}
+
 // replays logged voxel damage (x, y, z, amount) on this replica: the same add k_projectiles made on its own
 __global__ void k_apply_damage(World w, const uint4* __restrict__ records, uint32_t n) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;

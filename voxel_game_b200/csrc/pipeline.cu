@@ -28,6 +28,24 @@ static void peers_close(vxb_ctx* c) {
     for (void* p : c->peer_ipc) cudaIpcCloseMemHandle(p);
     c->peer_ipc.clear();
     c->peers = PeerReplicas{};
+    for (uint32_t p = 0; p < MAX_PEER_REPLICAS; p++) c->peer_inbox[p] = nullptr;
+}
+// compute_projectile.glsl dispatch + what sharing its voxel damage with peer replicas needs around it. With inboxes the
+// record counter is cleared before and the count published to every peer after the kernel, and the dispatch counts as a
+// tick (the inbox parity) even without projectiles, so that replicas stay in lockstep.
+static cudaError_t dispatch_projectiles(vxb_ctx* c, const World& w, uint32_t n_projectiles, uint32_t n_players, cudaStream_t st) {
+    const PeerReplicas peers = c->peers_for_dispatch();
+    cudaError_t e;
+    if (peers.inbox_cap && (e = cudaMemsetAsync(c->peer_seq.p, 0, sizeof(uint32_t), st)) != cudaSuccess) return e;
+    if (n_projectiles > 0 &&
+        (e = launch_projectiles(w, c->projectiles.p, n_projectiles, c->players.p, n_players, c->collisions.p, c->s.max_collisions,
+                                c->collision_count.p, c->s.delta_time, c->dlog(), peers, st)) != cudaSuccess)
+        return e;
+    if (peers.inbox_cap) {
+        if ((e = launch_peer_publish(peers, st)) != cudaSuccess) return e;
+        c->peer_tick++;
+    }
+    return cudaSuccess;
 }
 static void free_ctx(vxb_ctx* c) {
     if (!c) return;
@@ -39,7 +57,7 @@ static void free_ctx(vxb_ctx* c) {
     c->update_flags.release(); c->voxel_writes.release(); c->scalars.release(); c->res_list.release(); c->res_flags.release();
     c->ray_pos.release(); c->ray_normal.release(); c->ray_ldist.release(); c->ray_dist.release(); c->ray_in_pos.release();
     c->ray_in_dir.release(); c->raster_depth.release(); c->ray_voxel.release(); c->ray_leaving.release(); c->ray_count.release();
-    c->cams.release(); c->color.release(); c->wave_scratch.release(); c->dmg_log.release(); c->dmg_count.release();
+    c->cams.release(); c->color.release(); c->wave_scratch.release(); c->inbox.release(); c->peer_seq.release(); c->dmg_log.release(); c->dmg_count.release();
     c->mesh_pos.release(); c->mesh_normal.release(); c->raster_instances.release(); c->raster_key.release();
     c->gb_depth.release(); c->gb_normal.release(); c->gb_diffuse.release(); c->gb_max_depth.release();
     c->h_projectiles.release(); c->h_players.release(); c->h_collisions.release(); c->h_collision_count.release();
@@ -396,9 +414,7 @@ int vxb_compute(vxb_ctx* c, const uint32_t start_pos[3], const vxb_projectile* p
     c->chunk_update_queue.queue_set_idx(offset);  // :911
 
     // dispatch order of :944-1000
-    if (c->upload_projectile_count > 0)
-        VXB_CUDA(c, launch_projectiles(w, c->projectiles.p, c->upload_projectile_count, c->players.p, c->upload_player_count,
-                                       c->collisions.p, c->s.max_collisions, c->collision_count.p, c->s.delta_time, c->dlog(), c->peers, st));
+    if (c->upload_projectile_count > 0 || c->peers.n) VXB_CUDA(c, dispatch_projectiles(c, w, c->upload_projectile_count, c->upload_player_count, st));
     if (c->upload_player_count > 0) VXB_CUDA(c, launch_players(w, c->players.p, c->upload_player_count, c->s.delta_time, st));
     if (c->slice_to_unload >= 0) {
         const int comp = c->slice_to_unload / 2;
@@ -631,9 +647,7 @@ int vxb_dispatch_entities(vxb_ctx* c, const uint32_t start_pos[3], vxb_projectil
     VXB_CUDA(c, cudaMemsetAsync(c->collision_count.p, 0, sizeof(uint32_t), st));
     if (c->dmg_cap) VXB_CUDA(c, cudaMemsetAsync(c->dmg_count.p, 0, sizeof(uint32_t), st));
     const World w = c->world(start_pos);
-    if (run_projectiles && n_projectiles)
-        VXB_CUDA(c, launch_projectiles(w, c->projectiles.p, n_projectiles, c->players.p, n_players, c->collisions.p, c->s.max_collisions,
-                                       c->collision_count.p, c->s.delta_time, c->dlog(), c->peers, st));
+    if (run_projectiles && (n_projectiles || c->peers.n)) VXB_CUDA(c, dispatch_projectiles(c, w, n_projectiles, n_players, st));
     if (run_players && n_players) VXB_CUDA(c, launch_players(w, c->players.p, n_players, c->s.delta_time, st));
     if (n_projectiles) VXB_CUDA(c, cudaMemcpyAsync(projectiles, c->projectiles.p, (size_t)n_projectiles * sizeof(vxb_projectile), cudaMemcpyDeviceToHost, st));
     if (n_players) VXB_CUDA(c, cudaMemcpyAsync(players, c->players.p, (size_t)n_players * sizeof(vxb_player), cudaMemcpyDeviceToHost, st));
@@ -661,9 +675,7 @@ int vxb_entities_resident_run(vxb_ctx* c, const uint32_t start_pos[3], uint32_t 
     VXB_CUDA(c, cudaMemsetAsync(c->collision_count.p, 0, sizeof(uint32_t), st));
     if (c->dmg_cap) VXB_CUDA(c, cudaMemsetAsync(c->dmg_count.p, 0, sizeof(uint32_t), st));
     const World w = c->world(start_pos);
-    if (run_projectiles && n_projectiles)
-        VXB_CUDA(c, launch_projectiles(w, c->projectiles.p, n_projectiles, c->players.p, n_players, c->collisions.p, c->s.max_collisions,
-                                       c->collision_count.p, c->s.delta_time, c->dlog(), c->peers, st));
+    if (run_projectiles && (n_projectiles || c->peers.n)) VXB_CUDA(c, dispatch_projectiles(c, w, n_projectiles, n_players, st));
     if (run_players && n_players) VXB_CUDA(c, launch_players(w, c->players.p, n_players, c->s.delta_time, st));
     if (n_collisions_out) {
         VXB_CUDA(c, cudaMemcpyAsync(n_collisions_out, c->collision_count.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
@@ -753,17 +765,39 @@ int vxb_chunks_unpack(vxb_ctx* c, const uint32_t start_pos[3], const uint32_t* c
 
 // ---- sharded collision batches: log of voxel damage adds, replayed on the other replicas ----
 // ---- peer replicas: voxel damage added straight into the other replicas of the world ----
+int vxb_replica_inbox_enable(vxb_ctx* c, uint32_t n_sources, uint32_t capacity) {
+    if (!c) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, n_sources > 0 && n_sources <= MAX_PEER_REPLICAS + 1 && capacity > 0, "vxb_replica_inbox_enable: 1..16 sources, capacity > 0");
+    VXB_REQUIRE(c, (uint64_t)n_sources * capacity < (1ull << 28), "vxb_replica_inbox_enable: inbox too large");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    const size_t words = (size_t)2 * n_sources * capacity * 4 + 2 * n_sources;
+    VXB_CUDA(c, c->inbox.ensure(words));
+    VXB_CUDA(c, cudaMemsetAsync(c->inbox.p, 0, words * sizeof(uint32_t), c->stream));
+    VXB_CUDA(c, c->peer_seq.ensure(1));
+    VXB_CUDA(c, cudaMemsetAsync(c->peer_seq.p, 0, sizeof(uint32_t), c->stream));
+    VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->inbox_sources = n_sources;
+    c->inbox_cap = capacity;
+    c->peer_tick = 0;
+    return VXB_OK;
+}
+
 int vxb_replica_export(vxb_ctx* c, vxb_replica_handle* out) {
     if (!c || !out) return VXB_ERR_INVALID;
     VXB_REQUIRE(c, !c->slab, "vxb_replica_export: a slab ctx's pool is VMM memory (no IPC handle); replicas are plain contexts");
-    static_assert(sizeof(cudaIpcMemHandle_t) == 64 && sizeof(vxb_replica_handle) == 144, "two 64-byte handles + render_size");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64 && sizeof(vxb_replica_handle) == 224, "three 64-byte handles + 8 words");
     VXB_CUDA(c, cudaSetDevice(c->device));
-    cudaIpcMemHandle_t h[2];
+    memset(out, 0, sizeof(*out));
+    cudaIpcMemHandle_t h[3];
+    memset(h, 0, sizeof(h));
     VXB_CUDA(c, cudaIpcGetMemHandle(&h[0], c->table.p));
     VXB_CUDA(c, cudaIpcGetMemHandle(&h[1], c->pool.p));
-    memcpy(out->ipc, h, 128);
+    if (c->inbox_cap) VXB_CUDA(c, cudaIpcGetMemHandle(&h[2], c->inbox.p));
+    memcpy(out->ipc, h, 192);
     for (int a = 0; a < 3; a++) out->render_size[a] = c->s.render_size[a];
-    out->reserved = 0;
+    out->inbox_sources = c->inbox_sources;
+    out->inbox_capacity = c->inbox_cap;
     return VXB_OK;
 }
 
@@ -775,35 +809,58 @@ int vxb_replica_peers_clear(vxb_ctx* c) {
     return VXB_OK;
 }
 
-int vxb_replica_peers_add_ipc(vxb_ctx* c, const vxb_replica_handle* handles, uint32_t n_peers) {
+// shared tail of the two add functions: the peer's inbox (or none) and this ctx's region in it
+static int peer_attach_inbox(vxb_ctx* c, uint32_t p, uint32_t* inbox, uint32_t sources, uint32_t cap, uint32_t source_index) {
+    c->peer_inbox[p] = nullptr;
+    c->peer_inbox_sources[p] = c->peer_inbox_cap[p] = 0;
+    if (!inbox || cap == 0) return VXB_OK;
+    VXB_REQUIRE(c, source_index < sources, "vxb_replica_peers_add*: source_index beyond the peer's inbox sources");
+    c->peer_inbox[p] = inbox;
+    c->peer_inbox_sources[p] = sources;
+    c->peer_inbox_cap[p] = cap;
+    return VXB_OK;
+}
+
+int vxb_replica_peers_add_ipc(vxb_ctx* c, const vxb_replica_handle* handles, uint32_t n_peers, uint32_t source_index) {
     if (!c) return VXB_ERR_INVALID;
     VXB_REQUIRE(c, n_peers == 0 || handles, "vxb_replica_peers_add_ipc: handles is NULL");
     VXB_REQUIRE(c, c->peers.n + n_peers <= MAX_PEER_REPLICAS, "vxb_replica_peers_add_ipc: at most 15 peers");
+    VXB_REQUIRE(c, c->peers.n == 0 || source_index == c->source_index, "vxb_replica_peers_add*: one source_index per ctx");
     VXB_CUDA(c, cudaSetDevice(c->device));
     VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    VXB_CUDA(c, c->peer_seq.ensure(1));
     for (uint32_t k = 0; k < n_peers; k++) {
-        cudaIpcMemHandle_t h[2];
-        memcpy(h, handles[k].ipc, 128);
-        void *table = nullptr, *pool = nullptr;
+        cudaIpcMemHandle_t h[3];
+        memcpy(h, handles[k].ipc, 192);
+        void *table = nullptr, *pool = nullptr, *inbox = nullptr;
         VXB_CUDA(c, cudaIpcOpenMemHandle(&table, h[0], cudaIpcMemLazyEnablePeerAccess));
         c->peer_ipc.push_back(table);
         VXB_CUDA(c, cudaIpcOpenMemHandle(&pool, h[1], cudaIpcMemLazyEnablePeerAccess));
         c->peer_ipc.push_back(pool);
+        if (handles[k].inbox_capacity) {
+            VXB_CUDA(c, cudaIpcOpenMemHandle(&inbox, h[2], cudaIpcMemLazyEnablePeerAccess));
+            c->peer_ipc.push_back(inbox);
+        }
         const uint32_t p = c->peers.n;
         c->peers.table[p] = static_cast<const uint32_t*>(table);
         c->peers.pool[p] = static_cast<uint32_t*>(pool);
         for (int a = 0; a < 3; a++) c->peers.rs[p][a] = handles[k].render_size[a];
+        int rc = peer_attach_inbox(c, p, static_cast<uint32_t*>(inbox), handles[k].inbox_sources, handles[k].inbox_capacity, source_index);
+        if (rc) return rc;
         c->peers.n = p + 1;
     }
+    c->source_index = source_index;
     return VXB_OK;
 }
 
-int vxb_replica_peers_add(vxb_ctx* c, vxb_ctx* const* peers, uint32_t n_peers) {
+int vxb_replica_peers_add(vxb_ctx* c, vxb_ctx* const* peers, uint32_t n_peers, uint32_t source_index) {
     if (!c) return VXB_ERR_INVALID;
     VXB_REQUIRE(c, n_peers == 0 || peers, "vxb_replica_peers_add: peers is NULL");
     VXB_REQUIRE(c, c->peers.n + n_peers <= MAX_PEER_REPLICAS, "vxb_replica_peers_add: at most 15 peers");
+    VXB_REQUIRE(c, c->peers.n == 0 || source_index == c->source_index, "vxb_replica_peers_add*: one source_index per ctx");
     VXB_CUDA(c, cudaSetDevice(c->device));
     VXB_CUDA(c, cudaStreamSynchronize(c->stream));
+    VXB_CUDA(c, c->peer_seq.ensure(1));
     for (uint32_t k = 0; k < n_peers; k++) {
         vxb_ctx* o = peers[k];
         VXB_REQUIRE(c, o && o != c, "vxb_replica_peers_add: a peer is NULL or the ctx itself");
@@ -819,8 +876,35 @@ int vxb_replica_peers_add(vxb_ctx* c, vxb_ctx* const* peers, uint32_t n_peers) {
         c->peers.table[p] = o->table.p;
         c->peers.pool[p] = o->pool.p;
         for (int a = 0; a < 3; a++) c->peers.rs[p][a] = o->s.render_size[a];
+        int rc = peer_attach_inbox(c, p, o->inbox_cap ? o->inbox.p : nullptr, o->inbox_sources, o->inbox_cap, source_index);
+        if (rc) return rc;
         c->peers.n = p + 1;
     }
+    c->source_index = source_index;
+    return VXB_OK;
+}
+
+int vxb_replica_inbox_apply(vxb_ctx* c, const uint32_t start_pos[3]) {
+    if (!c || !start_pos) return VXB_ERR_INVALID;
+    VXB_WINDOW(c, start_pos);
+    VXB_REQUIRE(c, c->inbox_cap > 0, "vxb_replica_inbox_apply: no inbox (vxb_replica_inbox_enable)");
+    VXB_REQUIRE(c, c->peer_tick > 0, "vxb_replica_inbox_apply: no projectile dispatch yet");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    const uint32_t parity = (c->peer_tick - 1) & 1u;  // the dispatch that just ran
+    const size_t src = c->inbox_sources, cap = c->inbox_cap;
+    VXB_CUDA(c, launch_apply_inbox(c->world(start_pos), c->inbox.p + (size_t)parity * src * cap * 4, c->inbox.p + 2 * src * cap * 4 + parity * src,
+                                   c->inbox_sources, c->inbox_cap, c->stream));
+    return VXB_OK;
+}
+
+int vxb_replica_inbox_counts(vxb_ctx* c, uint32_t* counts_out) {
+    if (!c || !counts_out) return VXB_ERR_INVALID;
+    VXB_REQUIRE(c, c->inbox_cap > 0 && c->peer_tick > 0, "vxb_replica_inbox_counts: no inbox or no dispatch yet");
+    VXB_CUDA(c, cudaSetDevice(c->device));
+    const uint32_t parity = (c->peer_tick - 1) & 1u;
+    const size_t src = c->inbox_sources, cap = c->inbox_cap;
+    VXB_CUDA(c, cudaMemcpyAsync(counts_out, c->inbox.p + 2 * src * cap * 4 + parity * src, src * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    VXB_CUDA(c, cudaStreamSynchronize(c->stream));
     return VXB_OK;
 }
 

@@ -84,8 +84,33 @@ struct vxb_ctx {
     DevBuf<uint32_t> collision_count;
     DevBuf<uint32_t> dmg_log, dmg_count;  // voxel damage adds of the last projectile dispatch (vxb_damage_log_enable)
     uint32_t dmg_cap = 0;
-    vxb::PeerReplicas peers{};               // other replicas the projectile pass adds its voxel damage to (vxb_replica_peers_*)
+    vxb::PeerReplicas peers{};               // other replicas the projectile pass shares its voxel damage with (vxb_replica_peers_*)
     std::vector<void*> peer_ipc;             // what cudaIpcOpenMemHandle returned, closed on clear / destroy
+    // inboxes: this ctx's own ([2 parities][sources][capacity] records, then [2][sources] counts) and where the peers' are
+    DevBuf<uint32_t> inbox, peer_seq;
+    uint32_t inbox_sources = 0, inbox_cap = 0;
+    uint32_t* peer_inbox[vxb::MAX_PEER_REPLICAS] = {};
+    uint32_t peer_inbox_sources[vxb::MAX_PEER_REPLICAS] = {}, peer_inbox_cap[vxb::MAX_PEER_REPLICAS] = {};
+    uint32_t source_index = 0;               // this ctx's region in its peers' inboxes
+    uint32_t peer_tick = 0;                  // projectile dispatches so far: picks the inbox parity (all replicas in lockstep)
+    // the peers as a launch sees them: inbox pointers of the current parity filled in
+    vxb::PeerReplicas peers_for_dispatch() const {
+        vxb::PeerReplicas p = peers;
+        p.inbox_cap = 0;
+        p.seq = peer_seq.p;
+        if (p.n == 0) return p;
+        uint32_t cap = 0xFFFFFFFFu;
+        for (uint32_t k = 0; k < p.n; k++) cap = std::min(cap, peer_inbox[k] ? peer_inbox_cap[k] : 0u);
+        if (cap == 0 || cap == 0xFFFFFFFFu) return p;
+        const uint32_t parity = peer_tick & 1u;
+        for (uint32_t k = 0; k < p.n; k++) {
+            const size_t src = peer_inbox_sources[k], pc = peer_inbox_cap[k];
+            p.inbox[k] = reinterpret_cast<uint4*>(peer_inbox[k]) + ((size_t)parity * src + source_index) * pc;
+            p.inbox_count[k] = peer_inbox[k] + 2 * src * pc * 4 + (size_t)parity * src + source_index;
+        }
+        p.inbox_cap = cap;
+        return p;
+    }
     DevBuf<int32_t> worldgen_updates;   // ivec4 per 8^3 workgroup
     DevBuf<uint32_t> worldgen_results;  // one per chunk
     DevBuf<uint32_t> chunk_updates;     // uvec4 per chunk

@@ -71,15 +71,25 @@ struct DamageLog {
     uint32_t capacity;
     uint32_t* count;
 };
-// Other replicas of the same world (same window, their own table and pool; peer-mapped or IPC-opened memory of other GPUs,
-// or plain pointers on this one): k_projectiles adds its voxel damage to them as it adds it to its own world.
+// Other replicas of the same world (their own table and pool; peer-mapped or IPC-opened memory of other GPUs, or plain
+// pointers on this one). k_projectiles shares its voxel damage with them: as (x, y, z, amount) records stored into this
+// ctx's region of each peer's INBOX (inbox_cap > 0; contiguous remote stores, the peers replay them), or, without inboxes,
+// as system-scope adds straight into the peers' pools (scattered 4-byte remote writes into GB-sized mappings: measured
+// 6x slower than the whole kernel from 3 peers on, kept for small set-ups only). k_push_copy writes whole chunks.
 constexpr uint32_t MAX_PEER_REPLICAS = 15;
 struct PeerReplicas {
     uint32_t n;
     const uint32_t* table[MAX_PEER_REPLICAS];
     uint32_t* pool[MAX_PEER_REPLICAS];
     uint32_t rs[MAX_PEER_REPLICAS][3];  // each peer's render_size (the push may target a larger window than the slab's)
+    uint4* inbox[MAX_PEER_REPLICAS];    // this ctx's record region in peer p's inbox, for this dispatch's parity
+    uint32_t* inbox_count[MAX_PEER_REPLICAS];
+    uint32_t inbox_cap;                 // records per region; 0 = no inboxes
+    uint32_t* seq;                      // device counter of the records this dispatch has sent
 };
+cudaError_t launch_peer_publish(const PeerReplicas& peers, cudaStream_t st);
+cudaError_t launch_apply_inbox(const World& w, const uint32_t* records, const uint32_t* counts, uint32_t n_sources, uint32_t capacity,
+                               cudaStream_t st);
 cudaError_t launch_projectiles(const World& w, vxb_projectile* projectiles, uint32_t n_projectiles, const vxb_player* players,
                                uint32_t n_players, vxb_collision* collisions, uint32_t collision_capacity, uint32_t* collision_count,
                                float dt, DamageLog dlog, const PeerReplicas& peers, cudaStream_t st);

@@ -331,21 +331,36 @@ class VoxelComputePipeline:
                                                        ctypes.c_void_p(int(count_ptr)), int(capacity)))
 
     # -- peer replicas: voxel damage added straight into the other replicas of the world ------------
+    REPLICA_HANDLE_BYTES = 224
+
+    def replica_inbox_enable(self, n_sources, capacity):
+        self._inbox_sources = int(n_sources)
+        self._check(self._lib.vxb_replica_inbox_enable(self._h, int(n_sources), int(capacity)))
+
     def replica_export(self):
-        """-> 144 bytes (vxb_replica_handle: two CUDA IPC handles + render_size) for replica_peers_add_ipc in another process."""
-        out = np.zeros(144, np.uint8)
+        """-> 224 bytes (vxb_replica_handle: CUDA IPC handles of table, pool and inbox + render_size) for replica_peers_add_ipc
+        in another process."""
+        out = np.zeros(self.REPLICA_HANDLE_BYTES, np.uint8)
         self._check(self._lib.vxb_replica_export(self._h, ptr(out)))
         return out
 
-    def replica_peers_add_ipc(self, handles):
-        h = np.ascontiguousarray(np.asarray(handles, np.uint8).reshape(-1, 144))
+    def replica_peers_add_ipc(self, handles, source_index=0):
+        h = np.ascontiguousarray(np.asarray(handles, np.uint8).reshape(-1, self.REPLICA_HANDLE_BYTES))
         if h.shape[0]:
-            self._check(self._lib.vxb_replica_peers_add_ipc(self._h, ptr(h), h.shape[0]))
+            self._check(self._lib.vxb_replica_peers_add_ipc(self._h, ptr(h), h.shape[0], int(source_index)))
 
-    def replica_peers_add(self, peers):
+    def replica_peers_add(self, peers, source_index=0):
         if len(peers):
             arr = (ctypes.c_void_p * len(peers))(*[p._h for p in peers])
-            self._check(self._lib.vxb_replica_peers_add(self._h, arr, len(peers)))
+            self._check(self._lib.vxb_replica_peers_add(self._h, arr, len(peers), int(source_index)))
+
+    def replica_inbox_apply(self, start_pos):
+        self._check(self._lib.vxb_replica_inbox_apply(self._h, ptr(_u32(start_pos, 3))))
+
+    def replica_inbox_counts(self):
+        out = np.zeros(self._inbox_sources, np.uint32)
+        self._check(self._lib.vxb_replica_inbox_counts(self._h, ptr(out)))
+        return out
 
     def replica_peers_clear(self):
         self._check(self._lib.vxb_replica_peers_clear(self._h))
