@@ -444,9 +444,9 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
         return (a.x == b.x && a.y == b.y && a.z + 1 == b.z) ? 1u : 0u;
     };
     // issue this thread's copies of work item t into its ring stage (always commits one group)
-    auto issue = [&](uint32_t t) {
+    auto issue = [&](uint32_t t, uint32_t stage) {  // stage == t % UPD_STAGES, kept as a rolling counter by the caller
         {   // past the CTA's last item the slot table holds zeros: the copies read the sentinel chunk (L2 hits), unused
-            UpdStage& st = sm.stage[t % UPD_STAGES];
+            UpdStage& st = sm.stage[stage];
             const ThreadSlots ts = thread_slots(sm.slot[t % UPD_NSLOT]);
 #pragma unroll
             for (int i = 0; i < 2; i++) {
@@ -473,9 +473,10 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
     __syncthreads();
     uint32_t link_prev = 0;  // CTA-uniform: the previous item handed its z == 16 voxels over
 #pragma unroll
-    for (int t = 0; t < UPD_STAGES - 1; t++) issue(t);
+    for (int t = 0; t < UPD_STAGES - 1; t++) issue(t, t);
 
-    for (uint32_t t = 0;; t++) {
+    uint32_t stage_cur = 0;  // t % UPD_STAGES without the division
+    for (uint32_t t = 0;; t++, stage_cur = (stage_cur == UPD_STAGES - 1) ? 0u : stage_cur + 1u) {
         const uint32_t cur = item(t);
         if (cur == NONE) break;  // CTA-uniform: the ring is only written ahead of a barrier
         if (tid == 64) publish(t + AHEAD);  // read from the next iteration on
@@ -485,10 +486,10 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
         if (tid < 8) pend = resolve(t + UPD_STAGES, tid);
         else if (OZ == 1 && LINK && tid == 32) pend = resolve_link(t + UPD_STAGES);
         const uint32_t link_out = (OZ == 1 && LINK) ? sm.link[t % UPD_NSLOT] : 0u;
-        issue(t + UPD_STAGES - 1);
+        issue(t + UPD_STAGES - 1, stage_cur == 0 ? (uint32_t)(UPD_STAGES - 1) : stage_cur - 1u);
         cp_async_wait<UPD_STAGES - 1>();  // this thread's copies of item t have landed
 
-        const UpdStage& st = sm.stage[t % UPD_STAGES];
+        const UpdStage& st = sm.stage[stage_cur];
         const ThreadSlots ts = thread_slots(sm.slot[t % UPD_NSLOT]);
         uint32_t v[2][2][4];  // the thread's 16 voxels, updated in place
 #pragma unroll
@@ -520,9 +521,13 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
                 for (int z = 0; z < 4; z++) diff |= v[q >> 1][q & 1][z] ^ W;
             bool inert = false;
             if (diff == 0) {
-                const uint32_t m0 = W >> 24, d0 = W & 0xFFFFFFu;
-                inert = W == 0x00FFFFFFu || W == (MAT_STONE << 24) ||
-                        (mat_in(MASK_DATA_DISTANCE, m0) ? (d0 == 0xFFFFFFu) : !(mat_in(MASK_DATA_DAMAGE, m0) && d0 >= (m0 == MAT_STONE ? 10u : 5u)));
+                // the two words nearly every uniform block holds first, under a real branch; then the general test
+                if (W == 0x00FFFFFFu || W == (MAT_STONE << 24)) {
+                    inert = true;
+                } else {
+                    const uint32_t m0 = W >> 24, d0 = W & 0xFFFFFFu;
+                    inert = mat_in(MASK_DATA_DISTANCE, m0) ? (d0 == 0xFFFFFFu) : !(mat_in(MASK_DATA_DAMAGE, m0) && d0 >= (m0 == MAT_STONE ? 10u : 5u));
+                }
             }
             if (!inert) {
 #pragma unroll
@@ -614,8 +619,10 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
             link_prev = link_out;
         }
 
-        flags = __reduce_or_sync(0xFFFFFFFFu, flags);
-        if ((tid & 31) == 0 && flags) atomicOr(&sm.flags[t & 1], flags);
+        if (__any_sync(0xFFFFFFFFu, chg2 != 0)) {  // flags != 0 exactly where chg2 != 0: a quiet warp has nothing to report
+            flags = __reduce_or_sync(0xFFFFFFFFu, flags);
+            if ((tid & 31) == 0) atomicOr(&sm.flags[t & 1], flags);
+        }
         if (tid < 8) sm.slot[(t + UPD_STAGES) % UPD_NSLOT][tid] = pend;
         else if (OZ == 1 && LINK && tid == 32) sm.link[(t + UPD_STAGES) % UPD_NSLOT] = pend;
         __syncthreads();
