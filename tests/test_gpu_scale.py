@@ -237,6 +237,35 @@ def test_config2_full_size_primary_rays_equal_explicit_rays():
 
 
 @pytest.mark.timeout(900)
+def test_config2_full_size_wavefront_render_equals_fused_render():
+    """BASELINE configs[1]'s world at 1920x1080 through the whole fragment shader: the default wavefront of small kernels
+    (per-layer rounds over compacted pixel lists) and the fused per-pixel kernel must write the same colour bits and walk the
+    same number of DDA iterations, for a camera over land and one that looks across water and leaves (multi-layer pixels)."""
+    import torch
+
+    import voxel_game_b200 as vg
+
+    g, rs, sp, (cx, sy, cz) = _config2_world(torch)
+    w, h = 1920, 1080
+    caps = vg.RayCaps(100, 40, 20, 15, 0)
+    for yaw, pitch, t in ((0.7, -0.2, 0.0), (3.9, -0.05, 2.5)):
+        cam = scenes.camera((cx + 0.5, sy + 4.5, cz + 0.5), yaw, pitch)
+        out = []
+        for variant in (0, 1):
+            g.set_render_kernel(variant)
+            g.render(sp, cam, w, h, caps, time=t)
+            out.append((g.color_download()[0].copy(), g.ray_download()["total_iterations"]))
+        (a, ia), (b, ib) = out
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32)) and ia == ib > 30 * w * h
+        assert np.isfinite(a).all() and (a[..., 3] == 1.0).all() and a[..., :3].std() > 0.02
+    g.set_render_kernel(0)
+    # the wavefront leaves the primary layers of the frame in the ray buffers
+    lc = g.ray_download()["layer_count"]
+    assert lc.shape == (w * h,) and (lc > 1).mean() > 0.01
+    g.close()
+
+
+@pytest.mark.timeout(900)
 def test_config4_full_size_sharded_batch_equals_single_batch():
     """BASELINE configs[3] at full size (1 048 576 projectiles + 64 hulls against the config-2 world): the batch split
     over two replicas with the voxel damage exchanged (the multi-GPU protocol, here two contexts on one GPU) gives the

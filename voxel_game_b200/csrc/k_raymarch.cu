@@ -865,8 +865,8 @@ cudaError_t launch_render_wave(const World& w, const vxb_player* cams_dev, uint3
     k_raymarch_primary<<<pgrid, 128, 0, st>>>(w, cams_dev, width, height, caps.primary_ray_dist, projectiles, caps.projectile_count, raster, layers);
     float4* color = reinterpret_cast<float4*>(color_out);
     const uint32_t full = cap / WAVE_BLOCK;
-    int sms = 148;
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
+    int sms = 148, dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     for (uint32_t round = 0; round < 5; round++) {
         // round 0 walks every slot; later rounds walk a list whose length only the device knows (grid-stride over it)
         const uint32_t g = round == 0 ? full : (full < (uint32_t)sms * 8u ? full : (uint32_t)sms * 8u);
