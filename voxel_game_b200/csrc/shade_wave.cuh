@@ -154,7 +154,9 @@ __device__ __forceinline__ void wave_count_iters(unsigned long long* total, uint
 //   0  :270-273  simple_raycast_w_projectiles towards the light
 //   1  :275-288  single_raycast along the reflection, then simple_raycast from its hit towards the light
 //   2, 3  :291-301  the two ambient rays
-__global__ void __launch_bounds__(WAVE_BLOCK) k_trace(World w, ShadeParams sp, WaveScratch ws, uint32_t n_slots, uint32_t round,
+// 12 CTAs per SM (40 registers, a few spilled words): the secondary rays wait on scattered loads more than the primary ones,
+// and more resident warps pay here (shaded frame 1.645 -> 1.59 ms; 8 / 10 / 16 CTAs: 1.69 / 1.61 / 1.64 ms)
+__global__ void __launch_bounds__(WAVE_BLOCK, 12) k_trace(World w, ShadeParams sp, WaveScratch ws, uint32_t n_slots, uint32_t round,
                                                       unsigned long long* total_iters) {
     const uint32_t cap = ws.cap, kind = blockIdx.y;
     uint32_t iters = 0;
@@ -187,7 +189,8 @@ __global__ void __launch_bounds__(WAVE_BLOCK) k_trace(World w, ShadeParams sp, W
 }
 
 // :273, :282-312: the light terms in the shader's order, then the multiplier; survivors go to the next round's list
-__global__ void __launch_bounds__(WAVE_BLOCK) k_shade_combine(const vxb_player* __restrict__ cams, uint32_t width, uint32_t height, RayOut layers,
+// 10 CTAs per SM (48 registers): the kernel waits on its ~30 strided loads per slot (shaded frame 1.61 -> 1.57 ms)
+__global__ void __launch_bounds__(WAVE_BLOCK, 10) k_shade_combine(const vxb_player* __restrict__ cams, uint32_t width, uint32_t height, RayOut layers,
                                                               WaveScratch ws, uint32_t n_slots, uint32_t round, float4* __restrict__ color) {
     const uint32_t cap = ws.cap;
     const uint32_t n = round == 0 ? n_slots : ws.count[round];
