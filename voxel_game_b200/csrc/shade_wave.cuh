@@ -16,7 +16,9 @@
 //   res   8 words   shadow hit-the-sky flag, its light | reflected material + (reflection-light flag << 8), its light |
 //                   ambient ray 0 flag, light | ambient ray 1 flag, light
 //   state 1 word    1 = this slot has rays in flight this round
-//   pixel 1 word    the slot's pixel (rounds >= 1; round 0 derives it from the tile order)
+//   list  2 words   two pixel lists (ping-pong): slot t of round r >= 1 is pixel list[r & 1][t]; round 0 derives the pixel
+//                   from the tile order
+//   count 8 words   count[r] = length of round r's list
 // The colour buffer carries the running multiplier in .w between rounds; a finished pixel gets .w = 1 (f_color.a).
 #pragma once
 
@@ -27,7 +29,7 @@ struct WaveScratch {
     uint32_t* res;
     uint32_t* state;
     uint32_t* list[2];   // pixel lists of rounds 1.. (ping-pong)
-    uint32_t* count;     // [6]: entries of the list of round r at count[r]
+    uint32_t* count;     // [8]: entries of the list of round r at count[r]
     uint32_t cap;
 };
 
@@ -58,13 +60,12 @@ __device__ __forceinline__ bool tile_slot_pixel(uint32_t t, uint32_t width, uint
 // which slot / pixel a thread works on. Round 0: slot = thread, pixel from the tile order. Later rounds: a
 // grid-stride walk over the list; slot = list position.
 struct WaveItem {
-    uint32_t slot, px, py, view;
+    uint32_t px, py, view;
     uint64_t pixel;
     bool ok;
 };
 __device__ __forceinline__ WaveItem wave_item(uint32_t t, uint32_t round, const WaveScratch& ws, uint32_t n_slots, uint32_t width, uint32_t height) {
     WaveItem it;
-    it.slot = t;
     if (round == 0) {
         it.ok = t < n_slots && tile_slot_pixel(t, width, height, it.px, it.py, it.view);
         it.pixel = it.ok ? ((uint64_t)it.view * height + it.py) * width + it.px : 0;
