@@ -416,6 +416,9 @@ def run_ours(args):
             "gpu_launches": launches[0],
             "phase_mean_ms": [round(v, 4) for v in phase_ms],
             "ms_per_step_phase_balanced": float(np.nanmean(phase_ms)),
+            "value_phase_balanced": n_total_vox / (float(np.nanmean(phase_ms)) / 1e3) if world_size == 1 else None,
+            "phase_note": "`value` / `ms_per_step` cover exactly the K timed steps (the contract); K = 20 after 5 warm-ups holds phases 5,6,7,0 three times "
+                          "and 1-4 twice, so they sit ~1.5 % below the mean over the 8 Margolus phases, which `*_phase_balanced` report",
             "rank_phase_ms": rank_phase_ms,
             "clocks": clocks,
             "e2e": e2e,
