@@ -807,9 +807,36 @@ def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp,
     cam_y = _surface_from_gpu(rep, rep.read_table(), RS, SP, cx, cz) + 4.0  # surface + 4 at the world centre, as config 4 places its players
     grid = scenes.players_grid(8, (cx, cam_y, cz), 48.0, cam_y, seed=64)
     cams = np.concatenate([scenes.camera(tuple(grid["pos"][k, :3]), k * 2 * np.pi / 64, -0.2) for k in range(64)])
-    mine = cams[rank::world_size]  # interleaved: neighbouring yaw angles see similar scenes, so contiguous ranges would load the ranks unevenly
     W, H = 1920, 1080
     caps = vg.RayCaps(100, 40, 20, 15, 0)
+    # Which rank renders which views. A view's cost depends on what it sees (sky ends a ray in a few steps), and the ranks meet
+    # at a barrier every tick, so the slowest rank's share sets the tick. Every rank holds a full replica, so any view can go
+    # anywhere: each rank times its interleaved share once (device time per view), the costs are all-gathered, and the views
+    # are dealt longest-first to the least loaded rank (the host-side scheduling a game would redo now and then).
+    deal_note = "views interleaved over the ranks"
+    owner = np.arange(64) % world_size
+    if world_size > 1:
+        cost = torch.zeros(64, dtype=torch.float64, device="cuda")
+        for k in range(rank, 64, world_size):
+            rep.raymarch(SP, cams[k:k + 1], W, H, caps)  # warm
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            rep.raymarch(SP, cams[k:k + 1], W, H, caps)
+            e1.record()
+            torch.cuda.synchronize()
+            cost[k] = e0.elapsed_time(e1)
+        dist.all_reduce(cost)
+        cost = cost.cpu().numpy()
+        load = np.zeros(world_size)
+        count = np.zeros(world_size, np.int64)
+        for k in np.argsort(-cost, kind="stable"):  # longest processing time first; ties and counts keep the deal identical on every rank
+            free = np.nonzero(count < 64 // world_size)[0]
+            r = free[np.argmin(load[free])]
+            owner[k], load[r], count[r] = r, load[r] + cost[k], count[r] + 1
+        deal_note = "views dealt by measured cost, longest first (per-view %.3f-%.3f ms; per-rank sums %.3f-%.3f ms, interleaved would be %.3f-%.3f)" % (
+            cost.min(), cost.max(), load.min(), load.max(), min(cost[r::world_size].sum() for r in range(world_size)),
+            max(cost[r::world_size].sum() for r in range(world_size)))
+    mine = cams[np.nonzero(owner == rank)[0]]
     names = ("worldgen", "update", "replica_refresh", "rays")
     acc = {k: 0.0 for k in names}
     moved = 0
@@ -868,6 +895,7 @@ def bench_tick(args, torch, vg, dist, rank, world_size, gpu, shard, pool_t, lsp,
                                 else "pack + all-gather of fixed-capacity buffers + unpack"), "replica_refresh_note": push_note,
             "config": {"workload": "BASELINE configs[4]: %d chunks regenerated IN PLACE with forced = true (not a new slab face streamed with forced = false) "
                                                "+ update over all %d chunks + 64 views x 1920x1080 primary rays per tick" % (per_rank * world_size, n_total),
+                       "views": deal_note,
                        "note": "regeneration is forced (slots keep their place) instead of forced = false; per-phase times are the max over ranks, "
                                "their sum is the max over ranks of the per-rank sum"}}
 
