@@ -555,6 +555,42 @@ def test_sharded_collision_batch_peer_replicas(devices, inbox):
         g.close()
 
 
+def test_replica_api_rejects_misuse():
+    """Error behaviour of the peer-replica entry points: clear messages, nothing half-registered."""
+    import voxel_game_b200 as vg
+
+    gs = vg.GameSettings(render_size=(2, 2, 2), max_loaded_chunks=10)
+    a, b = vg.VoxelComputePipeline(gs), vg.VoxelComputePipeline(gs)
+    with pytest.raises(vg.VxbError, match="no inbox"):
+        a.replica_inbox_apply((0, 0, 0))
+    with pytest.raises(vg.VxbError, match="1..16 sources"):
+        a.replica_inbox_enable(0, 16)
+    with pytest.raises(vg.VxbError, match="1..16 sources"):
+        a.replica_inbox_enable(17, 16)
+    b.replica_inbox_enable(2, 16)
+    with pytest.raises(vg.VxbError, match="source_index beyond"):
+        a.replica_peers_add([b], source_index=2)
+    with pytest.raises(vg.VxbError, match="NULL or the ctx itself"):
+        a.replica_peers_add([a], source_index=0)
+    a.replica_peers_add([b], source_index=1)
+    with pytest.raises(vg.VxbError, match="one source_index per ctx"):
+        a.replica_peers_add([b], source_index=0)
+    with pytest.raises(vg.VxbError, match="no projectile dispatch yet"):
+        b.replica_inbox_apply((0, 0, 0))
+    with pytest.raises(vg.VxbError, match="no peer replicas"):
+        b.update_list_upload(np.zeros((1, 4), np.uint32))
+        b.update_list_push((0, 0, 0), 1, (0, 0, 0), 1, 4)
+    h = a.replica_export()
+    assert h.shape == (224,) and list(h[192:204].view(np.uint32)) == [2, 2, 2] and not h[128:192].any()  # no inbox: third handle zero
+    assert list(b.replica_export()[204:212].view(np.uint32)) == [2, 16]
+    a.replica_peers_clear()
+    a.replica_peers_add([b] * 15, source_index=0)
+    with pytest.raises(vg.VxbError, match="at most 15 peers"):
+        a.replica_peers_add([b], source_index=0)
+    a.close()
+    b.close()
+
+
 @pytest.mark.parametrize("world_gen,seed,yaw,pitch,t", [(0, 0, 0.3, -0.2, 0.0), (0, 0, 2.5, 0.15, 3.25), (1, 3646, 1.2, -0.35, 1.5)])
 def test_render_full_fragment_shader(world_gen, seed, yaw, pitch, t):
     """frag.glsl main = primary DDA + get_color. One transcendental (depth_transparency ^ dist) and long
