@@ -1110,7 +1110,7 @@ def bench_collisions(args, torch, vg, gpu, SP, RS, centre, peak):
     n_proj, n_side = args.projectiles, 8
     lo = (16 * SP[0] + 8, 16 * SP[1] + 8, 16 * SP[2] + 8)
     hi = (16 * (SP[0] + RS[0]) - 8, 16 * (SP[1] + RS[1]) - 8, 16 * (SP[2] + RS[2]) - 8)
-    pr = scenes.random_projectiles(n_proj, lo, hi, seed=0x5EED0001 & 0x7FFFFFFF)
+    pr = scenes.c4_projectiles(n_proj, lo, hi)
     pl = scenes.players_grid(n_side, (cx, col_y, cz), 48.0, col_y + 4.0, seed=64)
     gpu.dispatch_entities(SP, projectiles=pr, players=pl, run_projectiles=False, run_players=False)  # upload only
     ptrs = gpu.device_ptrs()
@@ -1134,8 +1134,8 @@ def bench_collisions(args, torch, vg, gpu, SP, RS, centre, peak):
     n_coll = gpu.entities_resident_run(SP, n_proj, n_side * n_side, want_count=True)
     ms = total_ms / steps
     out = {"metric": "projectiles/s", "value": n_proj / (ms / 1e3), "unit": "projectiles/s", "ms_per_tick": ms, "collisions_found": n_coll,
-           "config": {"workload": "BASELINE configs[3]: %d projectiles + %d player hulls vs the config-2 world, one tick (dt 0.02); batch drawn from "
-                                   "numpy RandomState(0x5EED0001) with the distributions of SURVEY 8(d) C4 (not its xorshift64* stream)" % (n_proj, n_side * n_side),
+           "config": {"workload": "BASELINE configs[3]: %d projectiles + %d player hulls vs the config-2 world, one tick (dt 0.02); batch from one "
+                                   "xorshift64* stream, seed 0x5EED0001, as SURVEY 8(d) C4 specifies (tests/scenes.py c4_projectiles)" % (n_proj, n_side * n_side),
                       "note": "device time of k_projectiles + k_players; entity arrays restored by a device copy between steps (untimed)"}}
     if not args.no_cpu:
         # oracle on a bounded sample of the same batch, same world (downloaded); counters from a sequential pass
@@ -1172,7 +1172,7 @@ def bench_collisions_sharded(args, torch, vg, dist, gpu, SP, RS, centre, rank, w
     n_proj, n_side = args.projectiles, 8
     lo = (16 * SP[0] + 8, 16 * SP[1] + 8, 16 * SP[2] + 8)
     hi = (16 * (SP[0] + RS[0]) - 8, 16 * (SP[1] + RS[1]) - 8, 16 * (SP[2] + RS[2]) - 8)
-    pr = scenes.random_projectiles(n_proj, lo, hi, seed=0x5EED0001 & 0x7FFFFFFF)
+    pr = scenes.c4_projectiles(n_proj, lo, hi)
     pl = scenes.players_grid(n_side, (cx, col_y, cz), 48.0, col_y + 4.0, seed=64)
     per = n_proj // world_size
     mine = pr[rank * per:(rank + 1) * per]

@@ -49,7 +49,7 @@ if what in ("proj", "all"):
     n_proj, n_side = 1 << 20, 8
     lo = (16 * SP[0] + 8, 16 * SP[1] + 8, 16 * SP[2] + 8)
     hi = (16 * (SP[0] + RS[0]) - 8, 16 * (SP[1] + RS[1]) - 8, 16 * (SP[2] + RS[2]) - 8)
-    pr = scenes.random_projectiles(n_proj, lo, hi, seed=0x5EED0001 & 0x7FFFFFFF)
+    pr = scenes.c4_projectiles(n_proj, lo, hi)
     pl = scenes.players_grid(n_side, (cx, sy, cz), 48.0, sy + 4.0, seed=64)
     g.dispatch_entities(SP, projectiles=pr, players=pl, run_projectiles=False, run_players=False)
     ptrs = g.device_ptrs()

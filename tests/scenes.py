@@ -131,6 +131,85 @@ def random_projectiles(n, lo, hi, seed, bounce_frac=0.1, n_owners=64):
     return pr
 
 
+def xorshift64star(seed, n, block=8192):
+    """n outputs of the xorshift64* generator (x ^= x >> 12; x ^= x << 25; x ^= x >> 27; output x * 0x2545F4914F6CDD1D mod 2^64),
+    the stream SURVEY 8(d) C4 names, as uint64. The stream is sequential; it is produced `block` states at a time by applying
+    the `block`-th power of the (GF(2)-linear) state transition to the previous block, which numpy can do on whole arrays."""
+    M64 = (1 << 64) - 1
+
+    def step(x):
+        x ^= x >> 12
+        x ^= (x << 25) & M64
+        x ^= x >> 27
+        return x
+
+    def apply(cols, x):  # matrix (images of the 64 unit vectors) times vector
+        out, j = 0, 0
+        while x:
+            if x & 1:
+                out ^= cols[j]
+            x >>= 1
+            j += 1
+        return out
+
+    first = min(block, n)
+    states = np.empty(first, np.uint64)
+    x = seed & M64
+    assert x != 0
+    for k in range(first):
+        x = step(x)
+        states[k] = x
+    out = np.empty(n, np.uint64)
+    out[:first] = states
+    if n > first:
+        cols = [step(1 << j) for j in range(64)]
+        power, e = [1 << j for j in range(64)], block  # identity
+        sq = cols
+        while e:  # square and multiply: power = T^block
+            if e & 1:
+                power = [apply(sq, c) for c in power]
+            sq = [apply(sq, c) for c in sq]
+            e >>= 1
+        pc = [np.uint64(c) for c in power]
+        done = first
+        while done < n:
+            nxt = np.zeros(block, np.uint64)
+            for j in range(64):
+                bit = (states >> np.uint64(j)) & np.uint64(1)
+                nxt ^= bit * pc[j]
+            states = nxt
+            take = min(block, n - done)
+            out[done:done + take] = states[:take]
+            done += take
+    with np.errstate(over="ignore"):
+        return out * np.uint64(0x2545F4914F6CDD1D)
+
+
+def c4_projectiles(n, lo, hi, seed=0x5EED0001, n_owners=64):
+    """The projectile batch of SURVEY 8(d) C4 from ONE xorshift64* stream, 12 draws per projectile in this order: position x, y, z
+    (uniform in [lo, hi), top 24 bits of a draw / 2^24), three uniforms for a uniform random unit quaternion (Shoemake), the size
+    exponents s in {-2..2} per axis (draw mod 5; size = 1.25^s), vel in {24, 40, 56, 80} (draw mod 4), damage in {0, 1, 5} (draw mod 3),
+    wall_bounce for 10 % (uniform < 0.1). health 1, should_collide_with_terrain 1, owner = index mod 64."""
+    r = xorshift64star(seed, 12 * n).reshape(n, 12)
+    u = ((r >> np.uint64(40)).astype(np.float64) / float(1 << 24))
+    pr = np.zeros(n, PROJECTILE_DTYPE)
+    lo, hi = np.asarray(lo, np.float32), np.asarray(hi, np.float32)
+    pr["pos"][:, :3] = (lo + u[:, 0:3].astype(np.float32) * (hi - lo)).astype(np.float32)
+    u1, u2, u3 = u[:, 3], u[:, 4], u[:, 5]
+    q = np.stack([np.sqrt(1 - u1) * np.sin(2 * np.pi * u2), np.sqrt(1 - u1) * np.cos(2 * np.pi * u2),
+                  np.sqrt(u1) * np.sin(2 * np.pi * u3), np.sqrt(u1) * np.cos(2 * np.pi * u3)], 1).astype(np.float32)
+    q /= np.linalg.norm(q, axis=1, keepdims=True).astype(np.float32)
+    pr["dir"] = q.astype(np.float32)
+    pr["size"][:, :3] = (1.25 ** ((r[:, 6:9] % np.uint64(5)).astype(np.int64) - 2)).astype(np.float32)
+    pr["vel"] = np.array([24, 40, 56, 80], np.float32)[(r[:, 9] % np.uint64(4)).astype(np.int64)]
+    pr["health"] = 1.0
+    pr["owner"] = np.arange(n) % n_owners
+    pr["damage"] = np.array([0, 1, 5], np.float32)[(r[:, 10] % np.uint64(3)).astype(np.int64)]
+    pr["wall_bounce"] = (u[:, 11] < 0.1).astype(np.uint32)
+    pr["should_collide_with_terrain"] = 1
+    return pr
+
+
 def players_grid(n_side, center, spacing, y, seed, size=1.0):
     rng = np.random.RandomState(seed)
     n = n_side * n_side

@@ -94,7 +94,7 @@ def test_config4_projectile_slice_against_the_oracle():
     cpu.pool[:] = g.read_pool(0, 2 + n)
     lo = (16 * sp[0] + 8, 16 * sp[1] + 8, 16 * sp[2] + 8)
     hi = (16 * (sp[0] + rs[0]) - 8, 16 * (sp[1] + rs[1]) - 8, 16 * (sp[2] + rs[2]) - 8)
-    pr = scenes.random_projectiles(1 << 20, lo, hi, seed=0x5EED0001 & 0x7FFFFFFF)[:65536].copy()  # bench.py's batch, first 64 k
+    pr = scenes.c4_projectiles(65536, lo, hi)  # bench.py's batch, first 64 k
     pl = scenes.players_grid(8, (cx, sy, cz), 48.0, sy + 4.0, seed=64)
     pr["pos"][:2000, :3] = pl["pos"][np.arange(2000) % 64, :3] + np.random.RandomState(3).randn(2000, 3).astype(np.float32) * 1.5 + (0, -1.5, 0)
     g_pr, g_pl, g_co, g_n = g.dispatch_entities(sp, projectiles=pr, players=pl)

@@ -279,7 +279,7 @@ def test_config4_full_size_sharded_batch_equals_single_batch():
     n = 1 << 20
     lo = (16 * sp[0] + 8, 16 * sp[1] + 8, 16 * sp[2] + 8)
     hi = (16 * (sp[0] + rs[0]) - 8, 16 * (sp[1] + rs[1]) - 8, 16 * (sp[2] + rs[2]) - 8)
-    pr = scenes.random_projectiles(n, lo, hi, seed=0x5EED0001 & 0x7FFFFFFF)
+    pr = scenes.c4_projectiles(n, lo, hi)
     pl = scenes.players_grid(8, (cx, sy, cz), 48.0, sy + 4.0, seed=64)
     pr["pos"][:4000, :3] = pl["pos"][np.arange(4000) % 64, :3] + np.random.RandomState(3).randn(4000, 3).astype(np.float32) * 1.5 + (0, -1.5, 0)
     half = n // 2

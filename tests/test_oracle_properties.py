@@ -147,3 +147,23 @@ def test_division_by_1414_through_the_reciprocal_is_the_ieee_quotient():
     lib.orc_div1414_mismatches.restype = ctypes.c_uint64
     lib.orc_div1414_mismatches.argtypes = []
     assert lib.orc_div1414_mismatches() == 0
+
+
+def test_xorshift64star_blocks_equal_the_sequential_stream():
+    """tests/scenes.py produces the xorshift64* stream of SURVEY 8(d) C4 a block at a time (a power of the GF(2) state transition
+    applied to whole arrays); it must be the sequential stream, across block boundaries and for block sizes that do not divide n."""
+    M = (1 << 64) - 1
+    x, ref = 0x5EED0001, []
+    for _ in range(1000):
+        x ^= x >> 12
+        x ^= (x << 25) & M
+        x ^= x >> 27
+        ref.append((x * 0x2545F4914F6CDD1D) & M)
+    ref = np.array(ref, np.uint64)
+    for block in (1, 7, 64, 333, 4096):
+        assert np.array_equal(scenes.xorshift64star(0x5EED0001, 1000, block=block), ref), block
+    pr = scenes.c4_projectiles(5000, (10, 10, 10), (1000, 200, 1000))
+    assert (pr["pos"][:, :3] >= 10).all() and (pr["pos"][:, 0] < 1000).all() and (pr["pos"][:, 1] < 200).all()
+    assert set(np.unique(pr["vel"])) == {24.0, 40.0, 56.0, 80.0} and set(np.unique(pr["damage"])) == {0.0, 1.0, 5.0}
+    assert 0.07 < pr["wall_bounce"].mean() < 0.13 and np.abs(np.linalg.norm(pr["dir"], axis=1) - 1).max() < 1e-6
+    assert set(np.round(np.log(np.unique(pr["size"][:, :3])) / np.log(1.25)).astype(int)) == {-2, -1, 0, 1, 2}
