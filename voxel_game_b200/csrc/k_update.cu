@@ -41,6 +41,18 @@ constexpr uint32_t BIT_AIR = 1u << MAT_AIR, BIT_OOB = 1u << MAT_OOB, BIT_WATER =
 
 __device__ __forceinline__ uint32_t umin3(uint32_t a, uint32_t b, uint32_t c) { return __vimin3_u32(a, b, c); }
 
+// (a ^ w) | (b ^ w) and acc | (x ^ w) as single LOP3s: "do these words differ from w"
+__device__ __forceinline__ uint32_t differ2(uint32_t a, uint32_t b, uint32_t w) {
+    uint32_t r;
+    asm("lop3.b32 %0, %1, %2, %3, 0x7E;" : "=r"(r) : "r"(a), "r"(b), "r"(w));
+    return r;
+}
+__device__ __forceinline__ uint32_t differ_acc(uint32_t acc, uint32_t x, uint32_t w) {
+    uint32_t r;
+    asm("lop3.b32 %0, %1, %2, %3, 0xF6;" : "=r"(r) : "r"(acc), "r"(x), "r"(w));
+    return r;
+}
+
 // :114-163 the five water moves of one block, on bit masks: bit cidx(i,j,k) of `air` / `water`
 // says that the cell holds MAT_AIR / MAT_WATER. A move swaps an air cell b below / beside a water
 // cell t (both lose their data); on the masks that flips bits b and t in both. Returns the new air
@@ -109,9 +121,7 @@ template <int PY>
 __device__ __forceinline__ uint32_t margolus_block(uint32_t (&v)[8]) {
     {
         const uint32_t W = v[0];
-        uint32_t diff = 0;
-#pragma unroll
-        for (int c = 1; c < 8; c++) diff |= v[c] ^ W;
+        const uint32_t diff = differ2(v[1], v[2], W) | differ2(v[3], v[4], W) | differ_acc(differ2(v[5], v[6], W), v[7], W);
         if (diff == 0) {
             // the two words nearly every uniform block holds, then the general test
             if (W == 0x00FFFFFFu || W == (MAT_STONE << 24)) return 0;
@@ -490,7 +500,6 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
         cp_async_wait<UPD_STAGES - 1>();  // this thread's copies of item t have landed
 
         const UpdStage& st = sm.stage[stage_cur];
-        const ThreadSlots ts = thread_slots(sm.slot[t % UPD_NSLOT]);
         uint32_t v[2][2][4];  // the thread's 16 voxels, updated in place
 #pragma unroll
         for (int i = 0; i < 2; i++) {
@@ -512,14 +521,16 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
         // for both blocks at once; deep stone and open sky are most of any world).
         uint32_t (&r)[2][2][4] = v;
         uint32_t chg2 = 0;  // bits 0-7: change mask of block 0 (bit = i*4 + j*2 + k), bits 8-15: block 1
+        bool inert = false;
         {
+            // 15 words against the first, two per LOP3 (written as a chain of ORs of XORs the compiler turns it into 15
+            // dependent ISETP.NE.OR on one predicate)
             const uint32_t W = v[0][0][0];
-            uint32_t diff = 0;
-#pragma unroll
-            for (int q = 0; q < 4; q++)
-#pragma unroll
-                for (int z = 0; z < 4; z++) diff |= v[q >> 1][q & 1][z] ^ W;
-            bool inert = false;
+            const uint32_t d0 = differ2(v[0][0][1], v[0][0][2], W), d1 = differ2(v[0][0][3], v[0][1][0], W),
+                           d2 = differ2(v[0][1][1], v[0][1][2], W), d3 = differ2(v[0][1][3], v[1][0][0], W),
+                           d4 = differ2(v[1][0][1], v[1][0][2], W), d5 = differ2(v[1][0][3], v[1][1][0], W),
+                           d6 = differ2(v[1][1][1], v[1][1][2], W), d7 = differ_acc(d6, v[1][1][3], W);
+            const uint32_t diff = (d0 | d1 | d2) | (d3 | d4 | d5) | d7;
             if (diff == 0) {
                 // the two words nearly every uniform block holds first, under a real branch; then the general test
                 if (W == 0x00FFFFFFu || W == (MAT_STONE << 24)) {
@@ -529,16 +540,21 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
                     inert = mat_in(MASK_DATA_DISTANCE, m0) ? (d0 == 0xFFFFFFu) : !(mat_in(MASK_DATA_DAMAGE, m0) && d0 >= (m0 == MAT_STONE ? 10u : 5u));
                 }
             }
-            if (!inert) {
+        }
+        // A warp whose 32 threads all hold inert vectors computes, stores and reports nothing: with stores elided it goes
+        // straight to the end of the iteration (most warps of a settled world). With a hand-over (LINK) a lane may still
+        // have to store the z == 0 voxel it was handed, and without ELIDE everything is stored: those take the long way.
+        constexpr bool QUIET_WARPS = ELIDE && !(OZ == 1 && LINK);
+        if (!(QUIET_WARPS && __all_sync(0xFFFFFFFFu, inert))) {
+        if (!inert) {
 #pragma unroll
-                for (int b = 0; b < 2; b++) {
-                    uint32_t blk[8];
+            for (int b = 0; b < 2; b++) {
+                uint32_t blk[8];
 #pragma unroll
-                    for (int c = 0; c < 8; c++) blk[c] = v[c >> 2][(c >> 1) & 1][2 * b + (c & 1)];
-                    chg2 |= margolus_block<OY>(blk) << (8 * b);
+                for (int c = 0; c < 8; c++) blk[c] = v[c >> 2][(c >> 1) & 1][2 * b + (c & 1)];
+                chg2 |= margolus_block<OY>(blk) << (8 * b);
 #pragma unroll
-                    for (int c = 0; c < 8; c++) v[c >> 2][(c >> 1) & 1][2 * b + (c & 1)] = blk[c];
-                }
+                for (int c = 0; c < 8; c++) v[c >> 2][(c >> 1) & 1][2 * b + (c & 1)] = blk[c];
             }
         }
         uint32_t flags = 0;
@@ -567,6 +583,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
         uint32_t cin_chg = 0;  // ELIDE: change bits of the handed-over z == 0 voxels (lanes tzq == 0)
         if (OZ == 1 && LINK && ELIDE && link_prev && tzq == 0) cin_chg = sm.cc[tid >> 2];
         if (!ELIDE || __any_sync(0xFFFFFFFFu, (chg16 | cin_chg) != 0)) {
+        const ThreadSlots ts = thread_slots(sm.slot[t % UPD_NSLOT]);  // only the stores look at the slots again
 #pragma unroll
         for (int i = 0; i < 2; i++) {
 #pragma unroll
@@ -623,6 +640,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, 
             flags = __reduce_or_sync(0xFFFFFFFFu, flags);
             if ((tid & 31) == 0) atomicOr(&sm.flags[t & 1], flags);
         }
+        }  // !quiet warp
         if (tid < 8) sm.slot[(t + UPD_STAGES) % UPD_NSLOT][tid] = pend;
         else if (OZ == 1 && LINK && tid == 32) sm.link[(t + UPD_STAGES) % UPD_NSLOT] = pend;
         __syncthreads();
