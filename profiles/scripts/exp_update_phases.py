@@ -67,16 +67,19 @@ def phases(variant):
     return ms
 
 
-for gran in (0, 32, 128):
+QUICK = os.environ.get("VXB_EXP_QUICK", "1") != "0"  # default: the library's own settings only
+for gran in ((0,) if QUICK else (0, 32, 128)):
     if gran:
         rc = cudart.cudaDeviceSetLimit(LIMIT_L2_FETCH, ctypes.c_size_t(gran))
     val = ctypes.c_size_t(0)
     cudart.cudaDeviceGetLimit(ctypes.byref(val), LIMIT_L2_FETCH)
-    for order in ("xyz", "z-tiles") if gran == 0 else ("xyz",):
+    for order in ("xyz", "z-tiles") if (gran == 0 and not QUICK) else ("xyz",):
         upload(order)
-        for variant in (2, 0):
-            ms = phases(variant)
-            print(json.dumps({"lib": os.path.basename(_vlib.LIB_PATH), "chunks": n, "l2_fetch_granularity": int(val.value), "order": order, "variant": variant,
+        # VXB_EXP_RUNS="1,4": also force runs of 2^(code-1) list entries per claim (0 = the launcher's choice)
+        codes = [0] + [int(c) for c in os.environ.get("VXB_EXP_RUNS", "").split(",") if c]
+        for variant, code in [(v, c) for c in codes for v in (2, 0)]:
+            ms = phases(variant | (code << 8))
+            print(json.dumps({"lib": os.path.basename(_vlib.LIB_PATH), "chunks": n, "l2_fetch_granularity": int(val.value), "order": order, "variant": variant, "run_code": code,
                               "phase_ms": [round(float(v), 4) for v in ms], "mean_ms": round(float(ms.mean()), 4),
                               "G_voxel_updates_per_s": round(n * 4096 / (ms.mean() * 1e-3) / 1e9, 1)}), flush=True)
 gpu.close()

@@ -4,16 +4,16 @@
 // chunk_updates[] entry.
 //
 // Design (B200, HBM-bound, integer only; see DESIGN.md §"k_voxel_update"):
-//  * persistent CTAs (grid = SMs x resident CTAs) of 256 threads walk the work list with stride
-//    gridDim; a chunk is 16 KiB, a thread owns 2x2 (x,y) columns x 4 consecutive z = two Margolus
+//  * persistent CTAs (grid = SMs x resident CTAs) of 256 threads claim runs of the work list from a
+//    global counter; a chunk is 16 KiB, a thread owns 2x2 (x,y) columns x 4 consecutive z = two Margolus
 //    blocks = 16 voxels. A Margolus block has no neighbours outside itself, so the only "halo" is
 //    the phase shift: up to 8 source chunks per work item.
-//  * memory-level parallelism comes from a 4-stage cp.async (LDGSTS) ring in shared memory, not
-//    from registers or occupancy: every thread copies exactly the 4 aligned 16-byte vectors (+ one
-//    straddled word) it will consume, into a thread-private slot, up to 3 chunks ahead. No CTA
+//  * memory-level parallelism comes from a cp.async (LDGSTS) ring in shared memory (UPD_STAGES deep)
+//    and 4 resident CTAs per SM: every thread copies exactly the 4 aligned 16-byte vectors (+ one
+//    straddled word) it will consume, into a thread-private slot, one chunk ahead. No CTA
 //    barrier guards the data (thread-private); one barrier per chunk publishes the chunk-slot
 //    table and the change flags. The dependent chain list entry -> chunk table -> voxels is taken
-//    off the critical path: 8 lanes resolve the 2x2x2 slot neighbourhood 4 chunks ahead.
+//    off the critical path: 8 lanes resolve the 2x2x2 slot neighbourhood UPD_STAGES chunks ahead.
 //  * in-chunk layout is x*256 + y*16 + z: 4 consecutive z are one aligned 16-byte vector and a warp
 //    covers 8 full 64-byte rows per copy instruction (every 32-byte sector fully used). A warp is a
 //    16 x 2 x 16-voxel horizontal slab so that mostly-horizontal surfaces touch few warps.
@@ -323,8 +323,24 @@ __device__ __forceinline__ void cp_async_wait() {
 }
 
 constexpr int UPD_THREADS = 256;
-constexpr int UPD_STAGES = 3;            // chunks in flight per CTA = UPD_STAGES - 1
-constexpr int UPD_NSLOT = UPD_STAGES + 1;  // slot-table ring: chunks t .. t+STAGES-1 live, t+STAGES being written
+// Ring depth and resident CTAs per SM (compile-time, -D to experiment: profiles/scripts/build_variant.sh).
+// Measured on a settled 262 144-chunk slab, G voxel-updates/s (stores elided | all stores), CTAs per SM x stages:
+//   4 x 3: 1086 | 613     4 x 2: 1157 | 699     5 x 2 (48 registers): 1154 | 649     6 x 2: 1023 | 535     3 x 2: 1036 | 696
+//   3 x 3 (85 registers): 1042 | 693            3 x 4: 979 | 614
+// Two stages win through the L1, not through the ring: 4 CTAs x 3 stages take 214 KB of the SM's 256 KB as shared memory
+// and leave ~30 KB of L1 for the 4-byte copies of the z == 16 words (cp.async.ca, one 32-byte sector each, up to 1024 in
+// flight per CTA); with 2 stages (146 KB) the L1 is ~90 KB and the phases with offset.z == 1 gain 13-22 %. The same
+// 2-stage build with the carve-out forced to all-shared-memory falls back to the 3-stage numbers exactly. Fetching the
+// z == 16 word as a 16-byte cp.async.cg (past the L1) instead: the same with stores elided, 6 % slower with all stores.
+#ifndef VXB_UPD_STAGES
+#define VXB_UPD_STAGES 2
+#endif
+#ifndef VXB_UPD_MIN_BLOCKS
+#define VXB_UPD_MIN_BLOCKS 4
+#endif
+constexpr int UPD_STAGES = VXB_UPD_STAGES;                 // chunks in flight per CTA = UPD_STAGES - 1
+constexpr int UPD_NSLOT = VXB_UPD_STAGES < 4 ? 4 : 8;      // slot-table ring (>= UPD_STAGES + 1; a power of two: the index is a mask)
+static_assert(UPD_STAGES >= 2 && UPD_STAGES < 8, "ring depth");
 
 struct UpdStage {
     uint4 a[4][UPD_THREADS];          // [(i,j)][thread]: the thread's aligned 16-byte vector of column (i,j)
@@ -356,7 +372,7 @@ struct ThreadSlots {
 // LINK: the z hand-over between consecutive items of a CTA (offset.z == 1 only). Runs of one list entry have next to
 // nothing to hand over, and the bookkeeping costs ~290 warp instructions per chunk: the launcher turns it off for them.
 template <int PHASE, bool ELIDE, bool LINK>
-__global__ void __launch_bounds__(UPD_THREADS, 4) k_voxel_update_tiled(World w, const uint4* __restrict__ chunk_updates, uint32_t n_items,
+__global__ void __launch_bounds__(UPD_THREADS, VXB_UPD_MIN_BLOCKS) k_voxel_update_tiled(World w, const uint4* __restrict__ chunk_updates, uint32_t n_items,
                                                                        uint32_t* __restrict__ flags_out, uint32_t run_log2,
                                                                        uint32_t* __restrict__ sched) {
     constexpr int OX = PHASE & 1, OY = (PHASE >> 1) & 1, OZ = (PHASE >> 2) & 1;
@@ -800,22 +816,35 @@ static cudaError_t launch_one(const World& w, const uint4* list, uint32_t n, uin
     return cudaGetLastError();
 }
 
-// Run length. With all stores (the reference's behaviour) runs of 8 list neighbours pay once the list is long: the z-run
-// hand-over turns the 4-byte row-end stores of offset.z == 1 into full vectors. With unchanged-store elision few vectors
-// are stored at all and single-entry runs win: the finer the claims, the shorter the tail.
-// (config 3 settled, elided, ms per step by run length, claimed runs: R=1 4.30, 2 4.30, 4 4.36, 8 4.41, 16 4.45;
-//  a 1/8 slab: 0.565, 0.567, 0.578, 0.594, 0.620. Round 1, statically dealt runs: R=1 5.00, R=8 4.85 / 0.633, 0.673.)
-// (run_code != 0 forces 2^(run_code-1): tests use it to drive the hand-over path with small worlds)
+// Run length (list entries per claim) and whether consecutive items of a run hand their z == 16 voxels over (LINK).
+// Measured per phase on a settled 262 144-chunk slab with the 2-stage ring (profiles/scripts/exp_update_phases.py, ms):
+//   stores elided, offset.z = 0:  R=1 0.828  R=2 0.806  R=4 0.808  R=8 0.817     (no hand-over exists)
+//   stores elided, offset.z = 1:  R=1 0.958  R=2 0.955 without LINK, 1.023 with  (next to nothing to hand over)
+//   all stores,    offset.z = 0:  R=1 1.284  R=2 1.293  R=8 1.332
+//   all stores,    offset.z = 1:  R=1 2.417  R=2 2.021  R=4 1.720  R=8 1.641 with LINK; 1.96-2.37 without
+// (the hand-over turns the 4-byte row-end stores into full vectors). Short lists take single entries: the finer the
+// claims, the shorter the tail. run_code != 0 forces R = 2^(run_code-1) with LINK (tests drive the hand-over path
+// with small worlds that way).
 template <bool ELIDE>
-static uint32_t pick_run_log2(uint32_t n, int run_code) {
-    if (run_code) return (uint32_t)(run_code - 1);
-    return (!ELIDE && n >= 8u * 8u * 592u) ? 3u : 0u;  // 592 = 148 SMs x 4 resident CTAs
+static uint32_t pick_run_log2(uint32_t n, int run_code, bool oz, bool* link) {
+    uint32_t r;
+    if (run_code) {
+        r = (uint32_t)(run_code - 1);
+        *link = r > 0;
+    } else if (ELIDE) {
+        r = n >= 65536u ? 1u : 0u;
+        *link = false;
+    } else {
+        r = (oz && n >= 8u * 8u * 592u) ? 3u : 0u;  // 592 = 148 SMs x 4 resident CTAs
+        *link = r > 0;
+    }
+    return r;
 }
 
 template <bool ELIDE>
 static cudaError_t launch_tiled(int phase, const World& w, const uint4* list, uint32_t n, uint32_t* flags, int run_code, cudaStream_t st) {
-    const uint32_t r = pick_run_log2<ELIDE>(n, run_code);
-    const bool link = r > 0;  // only phases with offset.z == 1 have a hand-over at all
+    bool link = false;  // only phases with offset.z == 1 have a hand-over at all
+    const uint32_t r = pick_run_log2<ELIDE>(n, run_code, (phase & 4) != 0, &link);
     switch (phase) {
         case 0: return launch_one<0, ELIDE, false>(w, list, n, flags, r, st);
         case 1: return launch_one<1, ELIDE, false>(w, list, n, flags, r, st);
