@@ -173,6 +173,43 @@ def test_config3_full_size_three_kernels_agree():
         g.close()
 
 
+@pytest.mark.timeout(600)
+def test_pipelined_dispatch_equals_resident_list_run():
+    """vxb_dispatch_voxel_update cuts a long host list into segments (upload, kernel and flag download overlap) while
+    vxb_update_list_run sweeps the resident list in one launch: same flags, same world, tick by tick, on a list that does
+    not divide evenly into segments and with both store policies."""
+    import torch
+
+    import bench
+    import voxel_game_b200 as vg
+
+    rs, sp = (72, 16, 256), bench.C3_SP  # 294 912 chunks: three segments
+    n = rs[0] * rs[1] * rs[2]
+    chunks = bench.chunk_grid(0, rs[0], rs, sp)
+    lst = np.concatenate([chunks, np.zeros((n, 1), np.int64)], 1).astype(np.uint32)[: n - 777]
+    worlds = []
+    for _ in range(2):
+        g = vg.VoxelComputePipeline(vg.GameSettings(render_size=rs, max_loaded_chunks=2 + n, max_worldgen_rate=8 * 32768, max_update_rate=1024))
+        bench.generate_world(g, sp, chunks, 2, True, torch)
+        worlds.append(g)
+    a, b = worlds
+    b.update_list_upload(lst)
+    changed = 0
+    for t in range(12):
+        variant = 2 if t < 8 else 0
+        a.set_update_kernel(variant)
+        b.set_update_kernel(variant)
+        off = scenes.PHASES[t % 8]
+        fa = a.dispatch_voxel_update(sp, lst, off)
+        b.update_list_run(sp, off)
+        fb = b.update_list_flags()
+        assert np.array_equal(fa, fb), "flags differ at tick %d" % t
+        assert a.world_checksum(sp) == b.world_checksum(sp), "world differs at tick %d" % t
+        changed += int((fa & 1).sum())
+    assert changed > n
+    a.close(); b.close()
+
+
 def _config2_world(torch):
     """BASELINE configs[1] world as the benchmark builds it: 64x16x64 chunks, non-forced worldgen, 64 ticks."""
     import bench

@@ -63,6 +63,13 @@ static void free_ctx(vxb_ctx* c) {
     c->h_projectiles.release(); c->h_players.release(); c->h_collisions.release(); c->h_collision_count.release();
     c->h_worldgen_updates.release(); c->h_worldgen_results.release(); c->h_chunk_updates.release(); c->h_update_flags.release();
     c->h_voxel_writes.release();
+    if (c->up_stream) cudaStreamDestroy(c->up_stream);
+    if (c->down_stream) cudaStreamDestroy(c->down_stream);
+    for (int i = 0; i < vxb_ctx::PIPE_EVENTS; i++) {
+        if (c->pipe_up[i]) cudaEventDestroy(c->pipe_up[i]);
+        if (c->pipe_done[i]) cudaEventDestroy(c->pipe_done[i]);
+    }
+    if (c->pipe_fork) cudaEventDestroy(c->pipe_fork);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
@@ -599,8 +606,47 @@ int vxb_dispatch_voxel_update(vxb_ctx* c, const uint32_t start_pos[3], const uin
     cudaStream_t st = c->stream;
     VXB_CUDA(c, c->chunk_updates.ensure((size_t)n * 4));
     VXB_CUDA(c, c->update_flags.ensure(n));
-    VXB_CUDA(c, cudaMemcpyAsync(c->chunk_updates.p, chunk_updates, (size_t)n * 16, cudaMemcpyHostToDevice, st));
     const World w = c->world(start_pos);
+    // A long list with flags wanted back is cut into segments: segment k+1 goes up and the flags of segment k-1 come down
+    // while the kernel works on segment k (work items are independent of each other: every 2x2x2 block belongs to exactly
+    // one item, so running them in several launches changes nothing). 16 B up + 4 B down per entry would otherwise add
+    // ~0.4 ms of idle GPU to a 3.6 ms step at 1 M entries.
+    constexpr uint32_t SEG = 131072;
+    if (flags_out && n >= 2 * SEG) {
+        if (!c->up_stream) {
+            VXB_CUDA(c, cudaStreamCreateWithFlags(&c->up_stream, cudaStreamNonBlocking));
+            VXB_CUDA(c, cudaStreamCreateWithFlags(&c->down_stream, cudaStreamNonBlocking));
+            VXB_CUDA(c, cudaEventCreateWithFlags(&c->pipe_fork, cudaEventDisableTiming));
+            for (int i = 0; i < vxb_ctx::PIPE_EVENTS; i++) {
+                VXB_CUDA(c, cudaEventCreateWithFlags(&c->pipe_up[i], cudaEventDisableTiming));
+                VXB_CUDA(c, cudaEventCreateWithFlags(&c->pipe_done[i], cudaEventDisableTiming));
+            }
+        }
+        // segment count capped by the event pool: longer lists get longer segments
+        const uint32_t n_seg = std::min<uint32_t>((n + SEG - 1) / SEG, vxb_ctx::PIPE_EVENTS);
+        const uint32_t seg = (n + n_seg - 1) / n_seg;
+        // the side streams start after whatever the ctx stream was given before this call (the buffers may still be in use)
+        VXB_CUDA(c, cudaEventRecord(c->pipe_fork, st));
+        VXB_CUDA(c, cudaStreamWaitEvent(c->up_stream, c->pipe_fork, 0));
+        for (uint32_t k = 0; k < n_seg; k++) {
+            const uint32_t first = k * seg, count = std::min(seg, n - first);
+            VXB_CUDA(c, cudaMemcpyAsync(c->chunk_updates.p + (size_t)first * 4, chunk_updates[first], (size_t)count * 16, cudaMemcpyHostToDevice,
+                                        c->up_stream));
+            VXB_CUDA(c, cudaEventRecord(c->pipe_up[k], c->up_stream));
+        }
+        for (uint32_t k = 0; k < n_seg; k++) {
+            const uint32_t first = k * seg, count = std::min(seg, n - first);
+            VXB_CUDA(c, cudaStreamWaitEvent(st, c->pipe_up[k], 0));
+            VXB_CUDA(c, launch_voxel_update(w, c->chunk_updates.p + (size_t)first * 4, count, offset, c->update_flags.p + first, c->update_variant, st));
+            VXB_CUDA(c, cudaEventRecord(c->pipe_done[k], st));
+            VXB_CUDA(c, cudaStreamWaitEvent(c->down_stream, c->pipe_done[k], 0));
+            VXB_CUDA(c, cudaMemcpyAsync(flags_out + first, c->update_flags.p + first, (size_t)count * 4, cudaMemcpyDeviceToHost, c->down_stream));
+        }
+        VXB_CUDA(c, cudaStreamSynchronize(c->down_stream));  // the last flags are down, so every kernel has finished
+        VXB_CUDA(c, cudaStreamSynchronize(st));
+        return VXB_OK;
+    }
+    VXB_CUDA(c, cudaMemcpyAsync(c->chunk_updates.p, chunk_updates, (size_t)n * 16, cudaMemcpyHostToDevice, st));
     VXB_CUDA(c, launch_voxel_update(w, c->chunk_updates.p, n, offset, c->update_flags.p, c->update_variant, st));
     if (flags_out) {
         VXB_CUDA(c, cudaMemcpyAsync(flags_out, c->update_flags.p, (size_t)n * 4, cudaMemcpyDeviceToHost, st));

@@ -74,6 +74,11 @@ struct vxb_ctx {
     int device = 0;
     cudaStream_t own_stream = nullptr;
     cudaStream_t stream = nullptr;
+    // vxb_dispatch_voxel_update on long lists: list segments go up and flags come down on these while the kernel runs
+    cudaStream_t up_stream = nullptr, down_stream = nullptr;
+    static constexpr int PIPE_EVENTS = 64;
+    cudaEvent_t pipe_up[PIPE_EVENTS] = {}, pipe_done[PIPE_EVENTS] = {};
+    cudaEvent_t pipe_fork = nullptr;
     std::string error;
 
     // device state (D1, D2 of SURVEY §8a)
