@@ -5,6 +5,9 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspa
 import numpy as np, torch
 import bench
 import voxel_game_b200 as vg
+import voxel_game_b200._lib as _vlib
+if os.environ.get("VXB_EXP_LIB"):  # A/B against another build of the library
+    _vlib.LIB_PATH = os.path.abspath(os.environ["VXB_EXP_LIB"])
 from tests import scenes
 from tests.test_gpu_scale import _config2_world
 

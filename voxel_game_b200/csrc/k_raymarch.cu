@@ -680,15 +680,20 @@ __device__ __forceinline__ void count_iters(const RayOut& o, uint32_t iters) {
 }
 
 // One thread per pixel; block = 8x8 pixels = two 8x4 warp tiles; blockIdx.z = view.
+#ifndef VXB_PRIMARY_TW
+#define VXB_PRIMARY_TW 8
+#endif
+constexpr uint32_t PRIMARY_TW = VXB_PRIMARY_TW, PRIMARY_TH = 32 / VXB_PRIMARY_TW;
 #ifndef VXB_PRIMARY_MIN_BLOCKS
 #define VXB_PRIMARY_MIN_BLOCKS 8
 #endif
 __global__ void __launch_bounds__(128, VXB_PRIMARY_MIN_BLOCKS) k_raymarch_primary(World w, const vxb_player* __restrict__ cams, uint32_t width, uint32_t height,
                                                          uint32_t max_iterations, const vxb_projectile* __restrict__ projectiles,
                                                          uint32_t projectile_count, RasterIn raster, RayOut out) {
-    // block = 16 x 8 pixels, four warps of 8 wide x 4 high
+    // block = 2 x 2 warps, a warp = PRIMARY_TW wide x 32 / PRIMARY_TW high pixels (default 8 x 4: block = 16 x 8 pixels)
     const uint32_t tl = threadIdx.x;
-    const uint32_t px = blockIdx.x * 16 + ((tl >> 5) & 1u) * 8 + (tl & 7), py = blockIdx.y * 8 + (tl >> 6) * 4 + ((tl >> 3) & 3u);
+    const uint32_t px = blockIdx.x * (2 * PRIMARY_TW) + ((tl >> 5) & 1u) * PRIMARY_TW + (tl & 31u) % PRIMARY_TW,
+                   py = blockIdx.y * (2 * PRIMARY_TH) + (tl >> 6) * PRIMARY_TH + (tl & 31u) / PRIMARY_TW;
     const uint32_t view = blockIdx.z;
     uint32_t iters = 0;
     if (px < width && py < height) {
@@ -805,7 +810,7 @@ cudaError_t launch_raymarch_views(const World& w, const vxb_player* cams_dev, ui
                                   uint32_t max_iterations, const vxb_projectile* projectiles, uint32_t projectile_count,
                                   RasterIn raster, RayOut out, cudaStream_t st) {
     if (n_views == 0 || width == 0 || height == 0) return cudaSuccess;
-    dim3 grid((width + 15) / 16, (height + 7) / 8, n_views);
+    dim3 grid((width + 2 * PRIMARY_TW - 1) / (2 * PRIMARY_TW), (height + 2 * PRIMARY_TH - 1) / (2 * PRIMARY_TH), n_views);
     k_raymarch_primary<<<grid, 128, 0, st>>>(w, cams_dev, width, height, max_iterations, projectiles, projectile_count, raster, out);
     return cudaGetLastError();
 }
@@ -861,7 +866,7 @@ cudaError_t launch_render_wave(const World& w, const vxb_player* cams_dev, uint3
     ws.count = scratch + (size_t)29 * cap;
     cudaError_t e = cudaMemsetAsync(ws.count, 0, 8 * sizeof(uint32_t), st);
     if (e != cudaSuccess) return e;
-    dim3 pgrid((width + 15) / 16, (height + 7) / 8, n_views);
+    dim3 pgrid((width + 2 * PRIMARY_TW - 1) / (2 * PRIMARY_TW), (height + 2 * PRIMARY_TH - 1) / (2 * PRIMARY_TH), n_views);
     k_raymarch_primary<<<pgrid, 128, 0, st>>>(w, cams_dev, width, height, caps.primary_ray_dist, projectiles, caps.projectile_count, raster, layers);
     float4* color = reinterpret_cast<float4*>(color_out);
     const uint32_t full = cap / WAVE_BLOCK;
