@@ -84,6 +84,9 @@ __device__ void quaternion_from_arc(f3 src, f3 dst, float out[4]) {
 
 constexpr int PLAYER_TILE = 64;  // 64 x 128 B = 8 KiB of shared memory
 constexpr int PROJ_BLOCK = 128;
+#ifndef VXB_PROJ_MIN_BLOCKS
+#define VXB_PROJ_MIN_BLOCKS 7
+#endif
 constexpr uint64_t LATTICE_COOP_MAX = 1u << 20;  // sample indices stay exact in a float quotient
 
 // per-projectile lattice of the terrain test, parked in shared memory for the warp-cooperative search
@@ -106,7 +109,7 @@ __device__ __forceinline__ int lattice_map(int g, int i) {
 
 // 7 CTAs per SM (72 registers, ~60 spilled bytes): measured 0.650 ms per 1 M-projectile tick against 0.683 at 6 (80 registers),
 // 0.74 at 4-5 and 0.71 at 8 (64 registers, 200+ spilled bytes)
-__global__ void __launch_bounds__(PROJ_BLOCK, 7) k_projectiles(World w, vxb_projectile* __restrict__ projectiles, uint32_t n_projectiles,
+__global__ void __launch_bounds__(PROJ_BLOCK, VXB_PROJ_MIN_BLOCKS) k_projectiles(World w, vxb_projectile* __restrict__ projectiles, uint32_t n_projectiles,
                                                      const vxb_player* __restrict__ players, uint32_t n_players,
                                                      vxb_collision* __restrict__ collisions, uint32_t collision_capacity,
                                                      uint32_t* __restrict__ collision_count, float dt, DamageLog dlog,
