@@ -219,7 +219,11 @@ int vxb_device_ptrs(vxb_ctx* ctx, vxb_ptrs* out);
 int vxb_dispatch_worldgen(vxb_ctx* ctx, const uint32_t start_pos[3], const int32_t (*chunk_loads)[4], uint32_t n_workgroups,
                           int complete, uint32_t* load_results_out);
 /* compute_voxel.glsl main. chunk_updates: n x uvec4 (chunk.xyz, 0); offset = voxel_update_offset in
- * {0,1}^3; flags_out (nullable): n u32 = chunk_updates[i].w after the dispatch. */
+ * {0,1}^3; flags_out (nullable): n u32 = chunk_updates[i].w after the dispatch.
+ * With flags_out and 262 144 entries or more the list is processed in segments on two side streams of the ctx, so that list
+ * upload, kernel and flag download overlap (work items are independent; results are those of one dispatch). The overlap needs
+ * page-locked host buffers (cudaHostAlloc / cudaHostRegister); pageable ones work and serialise. Returns after flags_out is
+ * complete. A list must not name a chunk twice (the reference's queue never does). */
 int vxb_dispatch_voxel_update(vxb_ctx* ctx, const uint32_t start_pos[3], const uint32_t (*chunk_updates)[4], uint32_t n,
                               const uint32_t offset[3], uint32_t* flags_out);
 /* write_voxels.glsl main. writes: n x (x, y, z, voxel word). */

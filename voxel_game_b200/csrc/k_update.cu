@@ -387,6 +387,9 @@ __global__ void __launch_bounds__(UPD_THREADS, VXB_UPD_MIN_BLOCKS) k_voxel_updat
     // CTA dealt round-robin took 11 % longer per chunk than the 1 M-chunk list (profiles/r02_scaling.md). With claims
     // the CTAs still sweep the list as one front (DRAM page locality) and finish within one run of each other.
     // The launcher picks R = 1 for short lists. sched[1] counts finished CTAs; the last one re-arms both counters.
+    // (Measured and not kept: all housekeeping — claim, slot resolution, link — in warp 0 with the claim's result first
+    // touched at the end of the iteration, so that the other warps pay one branch: -4 %, warp 0 becomes the one the barrier
+    // waits for. The claim after issue() instead of before it, so that its round trip overlaps the copies: -2 %.)
     const uint32_t R = 1u << run_log2;
     const uint32_t n_runs = (n_items + R - 1) >> run_log2;
     constexpr uint32_t NONE = 0xFFFFFFFFu;
