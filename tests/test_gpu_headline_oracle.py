@@ -1,6 +1,7 @@
 """GPU: the oracle on BASELINE's own configurations (not on small stand-ins).
  - configs[2]: a 4-column slab of the 256x16x256-chunk world, generated as bench.py generates it (forced worldgen at C3_SP), walked
    through the benchmark's 96 settle ticks and 8 more on the GPU and on the oracle: change flags every tick, the world at three points;
+   and a 16-column slab (65 536 chunks, the list length from which the launcher claims runs) while it is still changing everywhere;
  - configs[1]: one whole 1920x1080 primary-ray frame of the 1024x256x1024-voxel world against the oracle's raycast on the
    downloaded world: layers, hit voxels, iteration total exact, distances to 1e-4;
  - configs[3]: the first 65 536 projectiles of the benchmark's batch + the 64 hulls against the oracle on the same world."""
@@ -45,6 +46,44 @@ def test_config3_slab_walks_with_the_oracle(first_col):
         if t in (7, 95, 103):
             assert np.array_equal(gpu.read_pool(0, 2 + n), cpu.pool), "world differs after tick %d" % t
     assert changed > n  # the slab really evolved
+    gpu.close()
+
+
+@pytest.mark.timeout(900)
+def test_config3_sixteen_columns_with_the_launchers_run_lengths():
+    """65 536 chunks of the config-3 world: long enough for the launcher to pick what it picks at full size (claims of two entries
+    with stores elided; runs of eight with the z hand-over for unconditional stores on z-shifted phases), walked 16 ticks on the GPU
+    alone (distance fields still building: most chunks change), then 8 ticks of each store policy against the oracle: flags every
+    tick, the world after each policy."""
+    import torch
+
+    import bench
+    import voxel_game_b200 as vg
+
+    rs = (16, bench.C3_RS[1], bench.C3_RS[2])
+    sp = (bench.C3_SP[0] + 64, bench.C3_SP[1], bench.C3_SP[2])
+    n = rs[0] * rs[1] * rs[2]
+    gpu = vg.VoxelComputePipeline(vg.GameSettings(render_size=rs, max_loaded_chunks=2 + n, max_worldgen_rate=8 * 32768, max_update_rate=1024))
+    chunks = bench.chunk_grid(0, rs[0], rs, sp)
+    bench.generate_world(gpu, sp, chunks, 2, True, torch)
+    lst = np.concatenate([chunks, np.zeros((n, 1), np.int64)], 1).astype(np.uint32)
+    gpu.update_list_upload(lst)
+    for t in range(16):
+        gpu.update_list_run(sp, scenes.PHASES[t % 8])
+    cpu = CpuWorld(rs, sp, 2 + n)
+    cpu.table[:] = gpu.read_table()
+    cpu.pool[:] = gpu.read_pool(0, 2 + n)
+    changed = 0
+    for variant in (2, 0):
+        gpu.set_update_kernel(variant)
+        for t in range(8):
+            off = scenes.PHASES[t]
+            gpu.update_list_run(sp, off)
+            c_flags = cpu.voxel_update(lst, off)
+            assert np.array_equal(gpu.update_list_flags(), c_flags), "flags differ, variant %d phase %d" % (variant, t)
+            changed += int((c_flags & 1).sum())
+        assert np.array_equal(gpu.read_pool(0, 2 + n), cpu.pool), "world differs after variant %d" % variant
+    assert changed > n  # the world is still building its distance fields: the stores and the hand-over carry real changes
     gpu.close()
 
 
