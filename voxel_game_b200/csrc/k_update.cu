@@ -344,7 +344,10 @@ static_assert(UPD_STAGES >= 2 && UPD_STAGES < 8, "ring depth");
 
 struct UpdStage {
     uint4 a[4][UPD_THREADS];          // [(i,j)][thread]: the thread's aligned 16-byte vector of column (i,j)
-    uint32_t zx[4][UPD_THREADS / 4];  // [(i,j)][thread/4]: straddled voxel z == 16 (threads with tzq == 3, offset.z == 1)
+    // offset.z == 1: the straddled voxels z == 16 of the four columns of a thread quad (same tx, ty), word q = column
+    // (i,j) = (q >> 1, q & 1). Lane tzq == q copies word q (one 4-byte cp.async per warp instead of four with a quarter of
+    // the lanes), lane tzq == 3 reads all four with one LDS.128 after a __syncwarp.
+    __align__(16) uint32_t zx[UPD_THREADS / 4][4];
 };
 struct UpdSmem {
     UpdStage stage[UPD_STAGES];
@@ -360,6 +363,7 @@ struct UpdSmem {
 // the chunk holding column (i,j), z[i*2+j] the slot of its +z neighbour (only used when offset.z == 1).
 struct ThreadSlots {
     uint32_t s[4], z[4];
+    uint32_t zq;  // z[tid & 3]: the +z slot of the column whose z == 16 voxel this lane copies
 };
 
 // PHASE bit0 = offset.x, bit1 = offset.y, bit2 = offset.z. ELIDE: skip stores of unchanged vectors.
@@ -427,6 +431,9 @@ __global__ void __launch_bounds__(UPD_THREADS, VXB_UPD_MIN_BLOCKS) k_voxel_updat
     // (i,j) column of this thread: in-chunk word offset of its vector, and which neighbour chunk holds it.
     // Only the last thread column / row straddles (x or y == 16), and only for i / j == 1.
     const bool bx = OX == 1 && tx == 7, by = OY == 1 && ty == 7;
+    // the column q = tzq whose z == 16 voxel this lane copies (offset.z == 1): does it straddle, and its row offset
+    const bool bxq = bx && (tzq >> 1), byq = by && (tzq & 1);
+    const uint32_t rowq = (uint32_t)((((2 * tx + OX + (tzq >> 1)) & 15) << 8) | (((2 * ty + OY + (tzq & 1)) & 15) << 4));
     // read the item's 8 slots with two 16-byte shared loads BEFORE any cp.async (their asm memory clobber
     // would otherwise force a reload per use; 32 LDS per item made the z-shifted phases MIO-bound)
     auto thread_slots = [&](const uint32_t* sl) {
@@ -437,6 +444,7 @@ __global__ void __launch_bounds__(UPD_THREADS, VXB_UPD_MIN_BLOCKS) k_voxel_updat
         r.s[1] = by ? lo.z : lo.x;                  r.z[1] = by ? lo.w : lo.y;
         r.s[2] = bx ? hi.x : lo.x;                  r.z[2] = bx ? hi.y : lo.y;
         r.s[3] = bx ? (by ? hi.z : hi.x) : r.s[1];  r.z[3] = bx ? (by ? hi.w : hi.y) : r.z[1];
+        r.zq = bxq ? (byq ? hi.w : hi.y) : (byq ? lo.w : lo.y);
         return r;
     };
     auto rowoff = [&](int i, int j) { return (uint32_t)((((2 * tx + OX + i) & 15) << 8) | (((2 * ty + OY + j) & 15) << 4)); };
@@ -483,10 +491,10 @@ __global__ void __launch_bounds__(UPD_THREADS, VXB_UPD_MIN_BLOCKS) k_voxel_updat
                 for (int j = 0; j < 2; j++) {
                     const uint32_t row = rowoff(i, j);
                     cp_async16(&st.a[i * 2 + j][tid], slot_ptr(ts.s[i * 2 + j], row + 4 * tzq));
-                    if (OZ == 1 && tzq == 3)  // z == 16: first voxel of the row in the +z neighbour chunk
-                        cp_async4(&st.zx[i * 2 + j][tid >> 2], slot_ptr(ts.z[i * 2 + j], row));
                 }
             }
+            if (OZ == 1)  // z == 16 of column tzq: first voxel of the row in the +z neighbour chunk
+                cp_async4(&st.zx[tid >> 2][tzq], slot_ptr(ts.zq, rowq));
         }
         cp_async_commit();
     };
@@ -520,6 +528,12 @@ __global__ void __launch_bounds__(UPD_THREADS, VXB_UPD_MIN_BLOCKS) k_voxel_updat
 
         const UpdStage& st = sm.stage[stage_cur];
         uint32_t v[2][2][4];  // the thread's 16 voxels, updated in place
+        uint4 Z16 = make_uint4(0, 0, 0, 0);
+        if (OZ == 1) {
+            __syncwarp();  // the other lanes of the quad have waited for their copies too
+            if (tzq == 3) Z16 = *reinterpret_cast<const uint4*>(st.zx[tid >> 2]);
+        }
+        const uint32_t z16[4] = {Z16.x, Z16.y, Z16.z, Z16.w};
 #pragma unroll
         for (int i = 0; i < 2; i++) {
 #pragma unroll
@@ -529,7 +543,7 @@ __global__ void __launch_bounds__(UPD_THREADS, VXB_UPD_MIN_BLOCKS) k_voxel_updat
                     v[i][j][0] = A.x; v[i][j][1] = A.y; v[i][j][2] = A.z; v[i][j][3] = A.w;
                 } else {
                     uint32_t next = __shfl_down_sync(0xFFFFFFFFu, A.x, 1);
-                    if (tzq == 3) next = st.zx[i * 2 + j][tid >> 2];
+                    if (tzq == 3) next = z16[i * 2 + j];
                     v[i][j][0] = A.y; v[i][j][1] = A.z; v[i][j][2] = A.w; v[i][j][3] = next;
                 }
             }
