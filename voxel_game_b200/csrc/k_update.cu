@@ -354,7 +354,7 @@ struct UpdSmem {
     __align__(16) uint32_t slot[UPD_NSLOT][8];
     uint32_t link[UPD_NSLOT];               // offset.z == 1: the CTA's next item is this item's +z neighbour
     uint32_t flags[2];
-    uint32_t cz[4][UPD_THREADS / 4];        // z-run carry: updated voxel z == 16 of column (i,j), kept for the next item
+    uint4 cz[UPD_THREADS / 4];              // z-run carry: updated voxels z == 16 of a thread quad's columns (x = (0,0), y = (0,1), z = (1,0), w = (1,1)), kept for the next item
     uint32_t cc[UPD_THREADS / 4];           // ... and whether it changed (bit i*2+j), for ELIDE
     uint32_t item_ring[16];                 // list index of the CTA's t-th item at [t % 16], NONE past its last one
 };
@@ -617,6 +617,9 @@ __global__ void __launch_bounds__(UPD_THREADS, VXB_UPD_MIN_BLOCKS) k_voxel_updat
         if (OZ == 1 && LINK && ELIDE && link_prev && tzq == 0) cin_chg = sm.cc[tid >> 2];
         if (!ELIDE || __any_sync(0xFFFFFFFFu, (chg16 | cin_chg) != 0)) {
         const ThreadSlots ts = thread_slots(sm.slot[t % UPD_NSLOT]);  // only the stores look at the slots again
+        uint4 CZ = make_uint4(0, 0, 0, 0);  // what the previous item handed over (lanes tzq == 0)
+        if (OZ == 1 && LINK && link_prev && tzq == 0) CZ = sm.cz[tid >> 2];
+        const uint32_t cz4[4] = {CZ.x, CZ.y, CZ.z, CZ.w};
 #pragma unroll
         for (int i = 0; i < 2; i++) {
 #pragma unroll
@@ -632,14 +635,14 @@ __global__ void __launch_bounds__(UPD_THREADS, VXB_UPD_MIN_BLOCKS) k_voxel_updat
                     const uint32_t prev = __shfl_up_sync(0xFFFFFFFFu, r[i][j][3], 1);
                     uint32_t prev_chg = 1;
                     if (ELIDE) prev_chg = __shfl_up_sync(0xFFFFFFFFu, c4 & 8u, 1);
-                    if (tzq > 0) {
-                        if (slot >= 2 && !(ELIDE && (c4 & 7u) == 0 && prev_chg == 0))
-                            *reinterpret_cast<uint4*>(slot_ptr(slot, row + 4 * tzq)) = make_uint4(prev, r[i][j][0], r[i][j][1], r[i][j][2]);
-                    } else if (link_prev) {
-                        // z == 0 of this row was computed by the previous item of this CTA (the -z neighbour)
-                        // and handed over: the row start is one full vector like the others
-                        if (slot >= 2 && !(ELIDE && (c4 & 7u) == 0 && (cin_chg & (1u << (i * 2 + j))) == 0))
-                            *reinterpret_cast<uint4*>(slot_ptr(slot, row)) = make_uint4(sm.cz[i * 2 + j][tid >> 2], r[i][j][0], r[i][j][1], r[i][j][2]);
+                    // lanes tzq > 0 store (previous lane's last voxel, own first three); after a hand-over lane tzq == 0 does
+                    // the same with the voxel z == 0 the previous item of this CTA (the -z neighbour) computed: one full
+                    // vector per lane and one store instruction per column
+                    const uint32_t first = tzq == 0 ? cz4[i * 2 + j] : prev;
+                    const uint32_t first_chg = tzq == 0 ? (cin_chg & (1u << (i * 2 + j))) : prev_chg;
+                    if (tzq > 0 || link_prev) {
+                        if (slot >= 2 && !(ELIDE && (c4 & 7u) == 0 && first_chg == 0))
+                            *reinterpret_cast<uint4*>(slot_ptr(slot, row + 4 * tzq)) = make_uint4(first, r[i][j][0], r[i][j][1], r[i][j][2]);
                     } else if (slot >= 2 && !(ELIDE && (c4 & 6u) == 0)) {
                         // z == 0 of this row belongs to the -z neighbour's work item in this phase
                         *reinterpret_cast<uint2*>(slot_ptr(slot, row + 2)) = make_uint2(r[i][j][1], r[i][j][2]);
@@ -662,8 +665,7 @@ __global__ void __launch_bounds__(UPD_THREADS, VXB_UPD_MIN_BLOCKS) k_voxel_updat
         if (OZ == 1 && LINK) {
             __syncwarp();  // the hand-over words of the previous item have been read by lanes tzq == 0
             if (link_out && tzq == 3) {
-#pragma unroll
-                for (int q = 0; q < 4; q++) sm.cz[q][tid >> 2] = r[q >> 1][q & 1][3];
+                sm.cz[tid >> 2] = make_uint4(r[0][0][3], r[0][1][3], r[1][0][3], r[1][1][3]);
                 if (ELIDE) sm.cc[tid >> 2] = ((chg16 >> 3) & 1u) | ((chg16 >> 6) & 2u) | ((chg16 >> 9) & 4u) | ((chg16 >> 12) & 8u);
             }
             link_prev = link_out;
