@@ -433,7 +433,8 @@ __global__ void __launch_bounds__(UPD_THREADS, VXB_UPD_MIN_BLOCKS) k_voxel_updat
     const bool bx = OX == 1 && tx == 7, by = OY == 1 && ty == 7;
     // the column q = tzq whose z == 16 voxel this lane copies (offset.z == 1): does it straddle, and its row offset
     const bool bxq = bx && (tzq >> 1), byq = by && (tzq & 1);
-    const uint32_t rowq = (uint32_t)((((2 * tx + OX + (tzq >> 1)) & 15) << 8) | (((2 * ty + OY + (tzq & 1)) & 15) << 4));
+    uint32_t rowq = (uint32_t)((((2 * tx + OX + (tzq >> 1)) & 15) << 8) | (((2 * ty + OY + (tzq & 1)) & 15) << 4));
+    asm volatile("" : "+r"(rowq));  // opaque: kept in a register instead of being re-derived from tid every iteration (-1 % on z-shifted phases)
     // read the item's 8 slots with two 16-byte shared loads BEFORE any cp.async (their asm memory clobber
     // would otherwise force a reload per use; 32 LDS per item made the z-shifted phases MIO-bound)
     auto thread_slots = [&](const uint32_t* sl) {
