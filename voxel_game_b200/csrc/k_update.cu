@@ -328,8 +328,8 @@ constexpr int UPD_THREADS = 256;
 //   4 x 3: 1086 | 613     4 x 2: 1157 | 699     5 x 2 (48 registers): 1154 | 649     6 x 2: 1023 | 535     3 x 2: 1036 | 696
 //   3 x 3 (85 registers): 1042 | 693            3 x 4: 979 | 614
 // Two stages win through the L1, not through the ring: 4 CTAs x 3 stages take 214 KB of the SM's 256 KB as shared memory
-// and leave ~30 KB of L1 for the 4-byte copies of the z == 16 words (cp.async.ca, one 32-byte sector each, up to 1024 in
-// flight per CTA); with 2 stages (146 KB) the L1 is ~90 KB and the phases with offset.z == 1 gain 13-22 %. The same
+// and leave ~30 KB of L1 for the 4-byte copies of the z == 16 words (cp.async.ca, one 32-byte sector each, 256 per
+// chunk); with 2 stages (146 KB) the L1 is ~90 KB and the phases with offset.z == 1 gain 13-22 %. The same
 // 2-stage build with the carve-out forced to all-shared-memory falls back to the 3-stage numbers exactly. Fetching the
 // z == 16 word as a 16-byte cp.async.cg (past the L1) instead: the same with stores elided, 6 % slower with all stores.
 #ifndef VXB_UPD_STAGES
