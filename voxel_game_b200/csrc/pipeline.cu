@@ -622,20 +622,27 @@ int vxb_dispatch_voxel_update(vxb_ctx* c, const uint32_t start_pos[3], const uin
                 VXB_CUDA(c, cudaEventCreateWithFlags(&c->pipe_done[i], cudaEventDisableTiming));
             }
         }
-        // segment count capped by the event pool: longer lists get longer segments
-        const uint32_t n_seg = std::min<uint32_t>((n + SEG - 1) / SEG, vxb_ctx::PIPE_EVENTS);
-        const uint32_t seg = (n + n_seg - 1) / n_seg;
+        // Segment boundaries: a short first segment so that the kernel starts early (32 768 entries = 0.5 MB up), then
+        // growing ones (fewer launches, each with its own tail); the event pool caps their number, the last takes the rest.
+        uint32_t bound[vxb_ctx::PIPE_EVENTS + 1];
+        uint32_t n_seg = 0;
+        bound[0] = 0;
+        for (uint32_t pos = 0, step = SEG / 4; pos < n; step = std::min<uint32_t>(step * 3, 2 * SEG)) {
+            const uint32_t len = (n_seg + 1 == (uint32_t)vxb_ctx::PIPE_EVENTS) ? n - pos : std::min(step, n - pos);
+            pos += len;
+            bound[++n_seg] = pos;
+        }
         // the side streams start after whatever the ctx stream was given before this call (the buffers may still be in use)
         VXB_CUDA(c, cudaEventRecord(c->pipe_fork, st));
         VXB_CUDA(c, cudaStreamWaitEvent(c->up_stream, c->pipe_fork, 0));
         for (uint32_t k = 0; k < n_seg; k++) {
-            const uint32_t first = k * seg, count = std::min(seg, n - first);
+            const uint32_t first = bound[k], count = bound[k + 1] - first;
             VXB_CUDA(c, cudaMemcpyAsync(c->chunk_updates.p + (size_t)first * 4, chunk_updates[first], (size_t)count * 16, cudaMemcpyHostToDevice,
                                         c->up_stream));
             VXB_CUDA(c, cudaEventRecord(c->pipe_up[k], c->up_stream));
         }
         for (uint32_t k = 0; k < n_seg; k++) {
-            const uint32_t first = k * seg, count = std::min(seg, n - first);
+            const uint32_t first = bound[k], count = bound[k + 1] - first;
             VXB_CUDA(c, cudaStreamWaitEvent(st, c->pipe_up[k], 0));
             VXB_CUDA(c, launch_voxel_update(w, c->chunk_updates.p + (size_t)first * 4, count, offset, c->update_flags.p + first, c->update_variant, st));
             VXB_CUDA(c, cudaEventRecord(c->pipe_done[k], st));
