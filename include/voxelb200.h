@@ -328,7 +328,11 @@ int vxb_update_list_push(vxb_ctx* ctx, const uint32_t start_pos[3], const uint8_
                          uint32_t* coords_dev, uint32_t capacity);
 
 /* Resident work list for repeated full sweeps (benchmark configs 3 and 5): upload once, then run
- * the update dispatch on it any number of times without host traffic. */
+ * the update dispatch on it any number of times without host traffic. Asynchronous: chunk_updates must stay unchanged
+ * until the first call that synchronises (vxb_update_list_flags, vxb_synchronize). A list of 65 536 entries or more goes
+ * up in segments on a side stream, and the first sweep over it (vxb_update_list_run, vxb_slab_update) starts on each
+ * segment as it arrives, so a host that uploads a fresh list every tick overlaps the upload with the kernel (page-locked
+ * buffers; pageable ones serialise). */
 int vxb_update_list_upload(vxb_ctx* ctx, const uint32_t (*chunk_updates)[4], uint32_t n);
 int vxb_update_list_run(vxb_ctx* ctx, const uint32_t start_pos[3], const uint32_t offset[3]);
 /* The same dispatch over entries [first, first + count) of the resident list only (their flags land at

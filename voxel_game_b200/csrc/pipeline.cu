@@ -595,6 +595,59 @@ int vxb_dispatch_worldgen(vxb_ctx* c, const uint32_t start_pos[3], const int32_t
     return VXB_OK;
 }
 
+}  // extern "C"
+#pragma GCC visibility pop
+namespace vxb {
+constexpr uint32_t LIST_SEG = 131072;
+// Segment boundaries of a long work list: a short first segment so that the kernel starts early (32 768 entries = 0.5 MB up),
+// then growing ones (fewer launches, each with its own tail); the event pool caps their number, the last takes the rest.
+static uint32_t list_segments(uint32_t n, uint32_t* bound) {
+    uint32_t n_seg = 0;
+    bound[0] = 0;
+    for (uint32_t pos = 0, step = LIST_SEG / 4; pos < n; step = std::min<uint32_t>(step * 3, 2 * LIST_SEG)) {
+        const uint32_t len = (n_seg + 1 == (uint32_t)vxb_ctx::PIPE_EVENTS) ? n - pos : std::min(step, n - pos);
+        pos += len;
+        bound[++n_seg] = pos;
+    }
+    return n_seg;
+}
+int pipe_ensure(vxb_ctx* c) {
+    if (c->up_stream) return VXB_OK;
+    VXB_CUDA(c, cudaStreamCreateWithFlags(&c->up_stream, cudaStreamNonBlocking));
+    VXB_CUDA(c, cudaStreamCreateWithFlags(&c->down_stream, cudaStreamNonBlocking));
+    VXB_CUDA(c, cudaEventCreateWithFlags(&c->pipe_fork, cudaEventDisableTiming));
+    for (int i = 0; i < vxb_ctx::PIPE_EVENTS; i++) {
+        VXB_CUDA(c, cudaEventCreateWithFlags(&c->pipe_up[i], cudaEventDisableTiming));
+        VXB_CUDA(c, cudaEventCreateWithFlags(&c->pipe_done[i], cudaEventDisableTiming));
+    }
+    return VXB_OK;
+}
+int resident_list_join(vxb_ctx* c, cudaStream_t st) {
+    if (c->res_seg_n) {
+        VXB_CUDA(c, cudaStreamWaitEvent(st, c->pipe_up[c->res_seg_n - 1], 0));  // up_stream is in order: the last segment is the whole list
+        c->res_seg_n = 0;
+    }
+    return VXB_OK;
+}
+int resident_list_update(vxb_ctx* c, const World& w, const uint32_t offset[3], cudaStream_t st) {
+    if (c->res_seg_n == 0) {
+        VXB_CUDA(c, launch_voxel_update(w, c->res_list.p, c->res_n, offset, c->res_flags.p, c->update_variant, st));
+        return VXB_OK;
+    }
+    // the first sweep after a segmented upload: one launch per segment, each as soon as its entries have arrived (work items
+    // are independent of each other, so the result is that of one launch)
+    for (uint32_t k = 0; k < c->res_seg_n; k++) {
+        const uint32_t first = c->res_seg_bound[k], count = c->res_seg_bound[k + 1] - first;
+        VXB_CUDA(c, cudaStreamWaitEvent(st, c->pipe_up[k], 0));
+        VXB_CUDA(c, launch_voxel_update(w, c->res_list.p + (size_t)first * 4, count, offset, c->res_flags.p + first, c->update_variant, st));
+    }
+    c->res_seg_n = 0;
+    return VXB_OK;
+}
+}  // namespace vxb
+#pragma GCC visibility push(default)
+extern "C" {
+
 int vxb_dispatch_voxel_update(vxb_ctx* c, const uint32_t start_pos[3], const uint32_t (*chunk_updates)[4], uint32_t n,
                               const uint32_t offset[3], uint32_t* flags_out) {
     if (!c || !start_pos || !offset) return VXB_ERR_INVALID;
@@ -611,27 +664,10 @@ int vxb_dispatch_voxel_update(vxb_ctx* c, const uint32_t start_pos[3], const uin
     // while the kernel works on segment k (work items are independent of each other: every 2x2x2 block belongs to exactly
     // one item, so running them in several launches changes nothing). 16 B up + 4 B down per entry would otherwise add
     // ~0.4 ms of idle GPU to a 3.6 ms step at 1 M entries.
-    constexpr uint32_t SEG = 131072;
-    if (flags_out && n >= 2 * SEG) {
-        if (!c->up_stream) {
-            VXB_CUDA(c, cudaStreamCreateWithFlags(&c->up_stream, cudaStreamNonBlocking));
-            VXB_CUDA(c, cudaStreamCreateWithFlags(&c->down_stream, cudaStreamNonBlocking));
-            VXB_CUDA(c, cudaEventCreateWithFlags(&c->pipe_fork, cudaEventDisableTiming));
-            for (int i = 0; i < vxb_ctx::PIPE_EVENTS; i++) {
-                VXB_CUDA(c, cudaEventCreateWithFlags(&c->pipe_up[i], cudaEventDisableTiming));
-                VXB_CUDA(c, cudaEventCreateWithFlags(&c->pipe_done[i], cudaEventDisableTiming));
-            }
-        }
-        // Segment boundaries: a short first segment so that the kernel starts early (32 768 entries = 0.5 MB up), then
-        // growing ones (fewer launches, each with its own tail); the event pool caps their number, the last takes the rest.
+    if (flags_out && n >= 2 * LIST_SEG) {
+        if (int rcp = pipe_ensure(c)) return rcp;
         uint32_t bound[vxb_ctx::PIPE_EVENTS + 1];
-        uint32_t n_seg = 0;
-        bound[0] = 0;
-        for (uint32_t pos = 0, step = SEG / 4; pos < n; step = std::min<uint32_t>(step * 3, 2 * SEG)) {
-            const uint32_t len = (n_seg + 1 == (uint32_t)vxb_ctx::PIPE_EVENTS) ? n - pos : std::min(step, n - pos);
-            pos += len;
-            bound[++n_seg] = pos;
-        }
+        const uint32_t n_seg = list_segments(n, bound);
         // the side streams start after whatever the ctx stream was given before this call (the buffers may still be in use)
         VXB_CUDA(c, cudaEventRecord(c->pipe_fork, st));
         VXB_CUDA(c, cudaStreamWaitEvent(c->up_stream, c->pipe_fork, 0));
@@ -743,8 +779,25 @@ int vxb_update_list_upload(vxb_ctx* c, const uint32_t (*chunk_updates)[4], uint3
     VXB_CUDA(c, cudaSetDevice(c->device));
     VXB_CUDA(c, c->res_list.ensure((size_t)n * 4));
     VXB_CUDA(c, c->res_flags.ensure(n));
-    if (n) VXB_CUDA(c, cudaMemcpyAsync(c->res_list.p, chunk_updates, (size_t)n * 16, cudaMemcpyHostToDevice, c->stream));
+    c->res_seg_n = 0;
     c->res_n = n;
+    if (n >= LIST_SEG / 2) {
+        // a long list goes up in segments on the side stream, and the first sweep over it (vxb_update_list_run, vxb_slab_update)
+        // starts on each segment as it arrives; every other reader of the list waits for all of it (resident_list_join)
+        if (int rcp = pipe_ensure(c)) return rcp;
+        const uint32_t n_seg = list_segments(n, c->res_seg_bound);
+        VXB_CUDA(c, cudaEventRecord(c->pipe_fork, c->stream));  // the buffer may still be read by work already on the stream
+        VXB_CUDA(c, cudaStreamWaitEvent(c->up_stream, c->pipe_fork, 0));
+        for (uint32_t k = 0; k < n_seg; k++) {
+            const uint32_t first = c->res_seg_bound[k], count = c->res_seg_bound[k + 1] - first;
+            VXB_CUDA(c, cudaMemcpyAsync(c->res_list.p + (size_t)first * 4, chunk_updates[first], (size_t)count * 16, cudaMemcpyHostToDevice,
+                                        c->up_stream));
+            VXB_CUDA(c, cudaEventRecord(c->pipe_up[k], c->up_stream));
+        }
+        c->res_seg_n = n_seg;
+    } else if (n) {
+        VXB_CUDA(c, cudaMemcpyAsync(c->res_list.p, chunk_updates, (size_t)n * 16, cudaMemcpyHostToDevice, c->stream));
+    }
     return VXB_OK;
 }
 
@@ -753,8 +806,7 @@ int vxb_update_list_run(vxb_ctx* c, const uint32_t start_pos[3], const uint32_t 
     VXB_WINDOW(c, start_pos);
     VXB_REQUIRE(c, offset[0] < 2 && offset[1] < 2 && offset[2] < 2, "vxb_update_list_run: offset must be in {0,1}^3");
     VXB_CUDA(c, cudaSetDevice(c->device));
-    VXB_CUDA(c, launch_voxel_update(c->world(start_pos), c->res_list.p, c->res_n, offset, c->res_flags.p, c->update_variant, c->stream));
-    return VXB_OK;
+    return resident_list_update(c, c->world(start_pos), offset, c->stream);
 }
 
 int vxb_update_list_run_range(vxb_ctx* c, const uint32_t start_pos[3], const uint32_t offset[3], uint32_t first, uint32_t count,
@@ -764,6 +816,7 @@ int vxb_update_list_run_range(vxb_ctx* c, const uint32_t start_pos[3], const uin
     VXB_REQUIRE(c, offset[0] < 2 && offset[1] < 2 && offset[2] < 2, "vxb_update_list_run_range: offset must be in {0,1}^3");
     VXB_REQUIRE(c, (uint64_t)first + count <= c->res_n, "vxb_update_list_run_range: range exceeds the resident list");
     VXB_CUDA(c, cudaSetDevice(c->device));
+    if (int rcj = resident_list_join(c, cuda_stream ? (cudaStream_t)*cuda_stream : c->stream)) return rcj;
     VXB_CUDA(c, launch_voxel_update(c->world(start_pos), c->res_list.p + (size_t)first * 4, count, offset, c->res_flags.p + first, c->update_variant,
                                     cuda_stream ? (cudaStream_t)*cuda_stream : c->stream));
     return VXB_OK;
@@ -803,6 +856,7 @@ int vxb_update_list_pack(vxb_ctx* c, const uint32_t start_pos[3], const uint8_t*
     VXB_REQUIRE(c, mask_dev && coords_dev && payload_dev && capacity > 0, "vxb_update_list_pack: NULL buffer or zero capacity");
     VXB_REQUIRE(c, c->res_n > 0, "vxb_update_list_pack: no resident list uploaded");
     VXB_CUDA(c, cudaSetDevice(c->device));
+    if (int rcj = resident_list_join(c, c->stream)) return rcj;
     VXB_CUDA(c, launch_pack_chunks(c->world(start_pos), c->res_list.p, mask_dev, c->res_n, coords_dev, payload_dev, capacity, c->stream));
     return VXB_OK;
 }
@@ -972,6 +1026,7 @@ int vxb_update_list_push(vxb_ctx* c, const uint32_t start_pos[3], const uint8_t*
         for (int a = 0; a < 3; a++)
             VXB_REQUIRE(c, (uint64_t)peer_start_pos[a] + c->peers.rs[p][a] <= (1ull << 28) - 1, "vxb_update_list_push: peer window exceeds 2^28 chunks");
     VXB_CUDA(c, cudaSetDevice(c->device));
+    if (int rcj = resident_list_join(c, c->stream)) return rcj;
     VXB_CUDA(c, launch_push_chunks(c->world(start_pos), c->res_list.p, mask_dev, c->res_n, c->peers, peer_start_pos, coords_dev, capacity, c->stream));
     return VXB_OK;
 }

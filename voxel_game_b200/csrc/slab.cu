@@ -504,7 +504,7 @@ static int slab_update(vxb_ctx* c, const uint32_t offset[3]) {
         k_slab_wait<<<1, 1, 0, st>>>(s->mailbox(), need_left, need_right, SLAB_WAIT_CYCLES);
         VXB_CUDA(c, cudaGetLastError());
     }
-    VXB_CUDA(c, launch_voxel_update(c->world(s->local_sp), c->res_list.p, c->res_n, offset, c->res_flags.p, c->update_variant, st));
+    if (int rcu = resident_list_update(c, c->world(s->local_sp), offset, st)) return rcu;
     if (has_left || has_right) {
         k_slab_signal<<<1, 1, 0, st>>>(has_left ? reinterpret_cast<uint32_t*>(s->mbox_left_va) : nullptr,
                                         has_right ? reinterpret_cast<uint32_t*>(s->mbox_right_va) : nullptr, t);

@@ -125,6 +125,10 @@ struct vxb_ctx {
     // resident update list
     DevBuf<uint32_t> res_list, res_flags;
     uint32_t res_n = 0;
+    // a long resident list goes up in segments on up_stream (vxb_update_list_upload); until the first sweep over it (or any
+    // other reader) has run, res_seg_n > 0 and segment k = entries [res_seg_bound[k], res_seg_bound[k+1]) arrives with pipe_up[k]
+    uint32_t res_seg_n = 0;
+    uint32_t res_seg_bound[PIPE_EVENTS + 1] = {};
     // rays
     DevBuf<float> ray_pos, ray_normal, ray_ldist, ray_dist, ray_in_pos, ray_in_dir, raster_depth;
     DevBuf<uint32_t> ray_voxel, ray_leaving, ray_count;
@@ -229,4 +233,9 @@ namespace vxb {
 // ctx->pool.p / ctx->pool.n itself (and sets ctx->slab, which then owns that memory).
 int create_ctx(const vxb_settings* settings, int device, cudaError_t (*pool_alloc)(vxb_ctx*, void*), void* user, vxb_ctx** out);
 void slab_release(vxb_ctx* c);  // slab.cu: unmaps and frees what ctx->slab owns
+// pipeline.cu: the side streams and events of the segmented transfers; one sweep of the update kernel over the resident list
+// (per segment while a segmented upload is still arriving); make `st` wait for the whole resident list
+int pipe_ensure(vxb_ctx* c);
+int resident_list_update(vxb_ctx* c, const World& w, const uint32_t offset[3], cudaStream_t st);
+int resident_list_join(vxb_ctx* c, cudaStream_t st);
 }  // namespace vxb
