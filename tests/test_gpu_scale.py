@@ -210,6 +210,42 @@ def test_pipelined_dispatch_equals_resident_list_run():
     a.close(); b.close()
 
 
+def test_segmented_resident_list_equals_one_launch():
+    """A resident list of 65 536 entries or more is uploaded in segments and its first sweep is launched per segment
+    (vxb_update_list_run); vxb_update_list_run_range waits for the whole list and sweeps it in ONE launch. Same flags, same world,
+    for a fresh upload every tick (what a multi-GPU host does) and both store policies."""
+    import torch
+
+    import bench
+    import voxel_game_b200 as vg
+
+    rs, sp = (17, 16, 256), bench.C3_SP  # 69 632 chunks
+    n = rs[0] * rs[1] * rs[2]
+    chunks = bench.chunk_grid(0, rs[0], rs, sp)
+    lst = np.concatenate([chunks, np.zeros((n, 1), np.int64)], 1).astype(np.uint32)[: n - 5]
+    worlds = []
+    for _ in range(2):
+        g = vg.VoxelComputePipeline(vg.GameSettings(render_size=rs, max_loaded_chunks=2 + n, max_worldgen_rate=8 * 32768, max_update_rate=1024))
+        bench.generate_world(g, sp, chunks, 2, True, torch)
+        worlds.append(g)
+    a, b = worlds
+    changed = 0
+    for t in range(10):
+        variant = 2 if t < 6 else 0
+        off = scenes.PHASES[(t * 3) % 8]
+        for g in (a, b):
+            g.set_update_kernel(variant)
+            g.update_list_upload(lst)
+        a.update_list_run(sp, off)                      # per segment, as the entries arrive
+        b.update_list_run_range(sp, off, 0, len(lst))   # joined, one launch
+        fa, fb = a.update_list_flags(), b.update_list_flags()
+        assert np.array_equal(fa, fb), "flags differ at tick %d" % t
+        assert a.world_checksum(sp) == b.world_checksum(sp), "world differs at tick %d" % t
+        changed += int((fa & 1).sum())
+    assert changed > n
+    a.close(); b.close()
+
+
 def _config2_world(torch):
     """BASELINE configs[1] world as the benchmark builds it: 64x16x64 chunks, non-forced worldgen, 64 ticks."""
     import bench
