@@ -779,7 +779,7 @@ int vxb_update_list_upload(vxb_ctx* c, const uint32_t (*chunk_updates)[4], uint3
     VXB_CUDA(c, cudaSetDevice(c->device));
     VXB_CUDA(c, c->res_list.ensure((size_t)n * 4));
     VXB_CUDA(c, c->res_flags.ensure(n));
-    c->res_seg_n = 0;
+    if (int rcj = resident_list_join(c, c->stream)) return rcj;  // an earlier segmented upload nobody swept: it must not land after this one
     c->res_n = n;
     if (n >= LIST_SEG / 2) {
         // a long list goes up in segments on the side stream, and the first sweep over it (vxb_update_list_run, vxb_slab_update)
